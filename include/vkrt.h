@@ -1,0 +1,268 @@
+/*
+ * vkrt.h — C ABI of libvkrt_b200.so: the B200-native (sm_100a CUDA) replacement for the Vulkan
+ * KHR ray-tracing calls that jparimaa/vkrt's `Raytracer` class makes.
+ *
+ * The reference has no FFI layer; the boundary sits where `Raytracer` crosses into the Vulkan
+ * driver.  Each entry point below names the reference call site it replaces (paths relative to the
+ * reference checkout).  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a VkrtResult error code otherwise; the library never
+ *     aborts (the reference's VK_CHECK -> abort() convention, src/VulkanUtils.hpp:28-37, is kept by
+ *     the host-side VKRT_CHECK macro in vkrt_b200/host/Utils.hpp);
+ *   - host input buffers are copied during the call and may be freed on return;
+ *   - a context is single-threaded, owns one CUDA device and one stream; builds are complete on
+ *     return; vkrt_trace is stream-ordered; vkrt_frame_read synchronises;
+ *   - there is NO CPU fallback: without a CUDA device vkrt_context_create fails.
+ */
+#ifndef VKRT_H
+#define VKRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define VKRT_API __attribute__((visibility("default")))
+#else
+#define VKRT_API
+#endif
+
+typedef struct VkrtContext VkrtContext;
+typedef struct VkrtBlas VkrtBlas;
+typedef struct VkrtTlas VkrtTlas;
+typedef struct VkrtFrame VkrtFrame;
+
+typedef enum VkrtResult
+{
+    VKRT_SUCCESS = 0,
+    VKRT_ERROR_INVALID_ARGUMENT = 1,
+    VKRT_ERROR_NO_DEVICE = 2,
+    VKRT_ERROR_CUDA = 3,
+    VKRT_ERROR_OUT_OF_MEMORY = 4,
+    VKRT_ERROR_NCCL = 5,
+    VKRT_ERROR_NOT_READY = 6
+} VkrtResult;
+
+/* ------------------------------------------------------------------------------------------------
+ * Context — replaces the device half of `Context` (src/Context.cpp:280-366 createDevice,
+ * :368-380 queue/command pool).  One CUDA device, one stream.
+ * ---------------------------------------------------------------------------------------------- */
+VKRT_API int vkrt_context_create(int deviceOrdinal, VkrtContext** out);
+VKRT_API void vkrt_context_destroy(VkrtContext* ctx);
+/* Text of the last error on this context (or of the last failed vkrt_context_create if ctx==NULL). */
+VKRT_API const char* vkrt_last_error(const VkrtContext* ctx);
+/* Library/ABI version, `major*10000 + minor*100 + patch`. */
+VKRT_API int vkrt_version(void);
+/* Blocks until all work queued on the context's stream is done (vkQueueWaitIdle, src/VulkanUtils.cpp:202). */
+VKRT_API int vkrt_context_synchronize(VkrtContext* ctx);
+/* The context's cudaStream_t, for callers that time with CUDA events on the launching stream. */
+VKRT_API void* vkrt_context_stream(VkrtContext* ctx);
+
+/* ------------------------------------------------------------------------------------------------
+ * Bottom-level acceleration structure — replaces Raytracer::createBLAS (src/Raytracer.cpp:1027-1157):
+ * one BLAS with `geometryCount` triangle geometries that share one vertex buffer (positions are the
+ * first 3 floats of each `vertexStride`-byte vertex, VK_FORMAT_R32G32B32_SFLOAT, :1060-1062) and one
+ * u32 index buffer (:1064).  All geometries are opaque, no culling (:1072, :1176).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VkrtGeometryRange
+{
+    uint32_t primitiveCount;  /* VkAccelerationStructureBuildRangeInfoKHR::primitiveCount  (:1078) */
+    uint32_t maxVertex;       /* VkAccelerationStructureGeometryTrianglesDataKHR::maxVertex (:1063) */
+    uint64_t indexByteOffset; /* ...BuildRangeInfoKHR::primitiveOffset, bytes into the index buffer (:1079) */
+} VkrtGeometryRange;
+
+typedef enum VkrtBuildFlags
+{
+    VKRT_BUILD_DEFAULT = 0,
+    VKRT_BUILD_PREFER_FAST_BUILD = 1u << 0, /* LBVH only, skip tree optimisation (per-frame rebuilds) */
+    VKRT_BUILD_INPUT_ON_DEVICE = 1u << 1,   /* `vertices` and `indices` are CUDA device pointers */
+    VKRT_BUILD_KEEP_HOST_INPUT = 1u << 2    /* reserved */
+} VkrtBuildFlags;
+
+typedef struct VkrtBuildSizes
+{
+    uint64_t accelerationStructureSize; /* bytes of compressed nodes + packed triangles */
+    uint64_t buildScratchSize;          /* bytes of builder scratch */
+    uint64_t geometryCopySize;          /* bytes of the device copy of vertex+index data kept for shading */
+} VkrtBuildSizes;
+
+/* Mirror of vkGetAccelerationStructureBuildSizesKHR (src/Raytracer.cpp:1106): upper bounds. */
+VKRT_API int vkrt_blas_sizes(VkrtContext* ctx, const VkrtGeometryRange* ranges, uint32_t geometryCount,
+                             uint64_t vertexBytes, uint64_t indexCount, VkrtBuildSizes* out);
+
+VKRT_API int vkrt_blas_build(VkrtContext* ctx, const void* vertices, size_t vertexBytes, uint32_t vertexStride,
+                             const uint32_t* indices, size_t indexCount, const VkrtGeometryRange* ranges,
+                             uint32_t geometryCount, uint32_t flags, VkrtBlas** out);
+/* Re-runs the build over new vertex data of the same size, reusing all storage (config 5: per-frame rebuild). */
+VKRT_API int vkrt_blas_rebuild(VkrtContext* ctx, VkrtBlas* blas, const void* vertices, size_t vertexBytes,
+                               uint32_t flags);
+VKRT_API void vkrt_blas_destroy(VkrtContext* ctx, VkrtBlas* blas);
+/* Handle to put in VkrtInstance::accelerationStructureReference
+ * (vkGetAccelerationStructureDeviceAddressKHR, src/Raytracer.cpp:1141-1146). */
+VKRT_API uint64_t vkrt_blas_reference(const VkrtBlas* blas);
+
+typedef struct VkrtBlasInfo
+{
+    uint64_t triangleCount;
+    uint64_t nodeCount;      /* compressed 8-wide nodes, 80 B each */
+    uint64_t nodeBytes;
+    uint64_t triangleBytes;  /* 48 B per packed triangle */
+    float boundsMin[3];
+    float boundsMax[3];
+    float sahCost;           /* SAH cost of the wide BVH (node cost 1, triangle cost 1, root-area normalised) */
+    float buildMilliseconds; /* device time of the last build, CUDA events */
+} VkrtBlasInfo;
+VKRT_API int vkrt_blas_info(VkrtContext* ctx, const VkrtBlas* blas, VkrtBlasInfo* out);
+
+/* Debug/readback of the built structure for invariant tests (every primitive referenced once, quantised
+ * child boxes contain the exact boxes).  `nodes` receives nodeCount*80 bytes, `triangles` triangleCount*48. */
+VKRT_API int vkrt_blas_read(VkrtContext* ctx, const VkrtBlas* blas, void* nodes, size_t nodeBytes, void* triangles,
+                            size_t triangleBytes);
+
+/* ------------------------------------------------------------------------------------------------
+ * Top-level acceleration structure — replaces Raytracer::createTLAS (src/Raytracer.cpp:1159-1283).
+ * VkrtInstance is byte-compatible with the 64-byte VkAccelerationStructureInstanceKHR (:1171-1177).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VkrtInstance
+{
+    float transform[12];                     /* row-major 3x4 object->world (VkTransformMatrixKHR) */
+    uint32_t instanceCustomIndex : 24;
+    uint32_t mask : 8;
+    uint32_t instanceShaderBindingTableRecordOffset : 24;
+    uint32_t flags : 8;
+    uint64_t accelerationStructureReference; /* vkrt_blas_reference() */
+} VkrtInstance;
+
+VKRT_API int vkrt_tlas_build(VkrtContext* ctx, const VkrtInstance* instances, uint32_t instanceCount, VkrtTlas** out);
+VKRT_API void vkrt_tlas_destroy(VkrtContext* ctx, VkrtTlas* tlas);
+
+/* ------------------------------------------------------------------------------------------------
+ * Shading resources
+ * ---------------------------------------------------------------------------------------------- */
+/* One row per geometry: the reference's SubmeshInfo / GLSL MaterialInfo
+ * (src/Raytracer.cpp:33-39, :1412-1427; shaders/shader.rchit:43-49). */
+typedef struct VkrtSubmeshInfo
+{
+    int32_t baseColorTextureIndex;
+    int32_t metallicRoughnessTextureIndex;
+    int32_t normalTextureIndex;
+    int32_t indexBufferOffset; /* cumulative TRIANGLE count */
+} VkrtSubmeshInfo;
+/* Replaces createMaterialIndexBuffer + updateMaterialIndexDescriptorSet (src/Raytracer.cpp:1004-1012, :1386-1442). */
+VKRT_API int vkrt_materials_set(VkrtContext* ctx, const VkrtSubmeshInfo* rows, uint32_t count);
+
+typedef struct VkrtImage
+{
+    uint32_t width, height;
+    const uint8_t* rgba8; /* R8G8B8A8_UNORM, tightly packed rows (src/Raytracer.cpp:467) */
+} VkrtImage;
+/* Replaces createTextures + createSampler + updateTexturesDescriptorSets (src/Raytracer.cpp:436-570, :1444-1467):
+ * bindless array of RGBA8 images sampled LINEAR / REPEAT at LOD 0 (shaders/shader.rchit:76,107,157,162). */
+VKRT_API int vkrt_textures_set(VkrtContext* ctx, const VkrtImage* images, uint32_t count);
+
+/* ------------------------------------------------------------------------------------------------
+ * Frames and tracing
+ * ---------------------------------------------------------------------------------------------- */
+/* 256-byte per-frame constants, identical layout to UniformBufferInfo (src/Raytracer.cpp:15-24) and the GLSL
+ * CommonUniformBuffer (shaders/shader.rgen:16-26). */
+typedef struct VkrtUniforms
+{
+    float viewInverse[16]; /* column-major */
+    float projInverse[16]; /* column-major */
+    float position[4];
+    float right[4];
+    float up[4];
+    float forward[4];
+    float lightPositions[4][4];
+} VkrtUniforms;
+
+/* Offscreen colour target + AOVs; replaces createColorImage (src/Raytracer.cpp:326-392).  With a communicator
+ * attached (vkrt_comm_init) the frame is split into 64x64-pixel tiles, tile i owned by rank i % size. */
+VKRT_API int vkrt_frame_create(VkrtContext* ctx, uint32_t width, uint32_t height, VkrtFrame** out);
+VKRT_API void vkrt_frame_destroy(VkrtContext* ctx, VkrtFrame* frame);
+
+typedef enum VkrtTraceFlags
+{
+    VKRT_TRACE_DEFAULT = 0,
+    VKRT_TRACE_NO_AOV = 1u << 0 /* skip the triangle-id / shadow-mask / float RGB outputs (timed runs) */
+} VkrtTraceFlags;
+
+/* Replaces the per-frame UBO memcpy (src/Raytracer.cpp:218-235) + vkCmdTraceRaysKHR(W,H,1) (:157): runs
+ * shader.rgen/.rchit/.rmiss/shader_shadow.rmiss semantics for every owned pixel, `spp` samples per pixel
+ * (spp==1: pixel centre +0.5 as shaders/shader.rgen:32; spp>1: Halton(2,3) offsets), and resolves to B8G8R8A8.
+ * Asynchronous on the context stream. */
+VKRT_API int vkrt_trace(VkrtContext* ctx, const VkrtTlas* tlas, const VkrtUniforms* uniforms, uint32_t spp,
+                        uint32_t frameIndex, uint32_t flags, VkrtFrame* frame);
+
+typedef enum VkrtAov
+{
+    VKRT_AOV_BGRA8 = 0,           /* 4 B/pixel, B,G,R,A (VK_FORMAT_B8G8R8A8_UNORM, src/VulkanUtils.hpp:24) */
+    VKRT_AOV_RGB32F = 1,          /* 12 B/pixel, finalHitValue averaged over spp */
+    VKRT_AOV_TRIANGLE_ID_U32 = 2, /* (instance<<24) + indexBufferOffset + gl_PrimitiveID of the primary hit, ~0 = miss */
+    VKRT_AOV_SHADOW_MASK_U8 = 3   /* bits 0-3: light i shadowed, bits 4-7: shadow ray i cast (primary hit, sample 0) */
+} VkrtAov;
+/* Copies one output plane to host memory (`pitch` = bytes per row, 0 = tight). Replaces the copy to the
+ * swapchain image (src/Raytracer.cpp:175-185) in the headless mode.  Synchronises the stream.  With a
+ * communicator, valid on the root rank after vkrt_tiles_gather (BGRA8) and on every rank for owned tiles. */
+VKRT_API int vkrt_frame_read(VkrtContext* ctx, VkrtFrame* frame, int aov, void* dst, size_t pitch);
+/* Device pointer of the assembled BGRA8 image (width*height*4), valid until the frame is destroyed. */
+VKRT_API void* vkrt_frame_device_bgra8(VkrtFrame* frame);
+
+/* Ray-level entry (ray-query style; used by the parity tests and per-ray-type benchmarks).  `rays` are
+ * 32-byte records {origin[3], tmin, direction[3], tmax}; `hits` 24-byte records {t, b1, b2, instance, geometry,
+ * primitive}; instance == 0xFFFFFFFF on miss.  anyHit != 0 → gl_RayFlagsTerminateOnFirstHitEXT semantics
+ * (shaders/shader.rchit:114-117): only hit/miss is meaningful.  Host pointers. */
+typedef struct VkrtRay
+{
+    float origin[3];
+    float tmin;
+    float direction[3];
+    float tmax;
+} VkrtRay;
+typedef struct VkrtHit
+{
+    float t, b1, b2;
+    uint32_t instance, geometry, primitive;
+} VkrtHit;
+VKRT_API int vkrt_trace_rays(VkrtContext* ctx, const VkrtTlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit,
+                             VkrtHit* hits);
+
+/* ------------------------------------------------------------------------------------------------
+ * Statistics for the roofline: counted since the last vkrt_stats_reset.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VkrtStats
+{
+    uint64_t raysPrimary, raysShadow, raysReflection;
+    uint64_t nodesVisited, trianglesTested; /* only counted when enabled with vkrt_stats_enable(ctx, 1) */
+    uint64_t kernelLaunches;                /* kernels launched by this library */
+    float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* last vkrt_trace, if timing enabled */
+} VkrtStats;
+VKRT_API int vkrt_stats_enable(VkrtContext* ctx, int countTraversal, int timeStages);
+VKRT_API int vkrt_stats_reset(VkrtContext* ctx);
+VKRT_API int vkrt_stats_get(VkrtContext* ctx, VkrtStats* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * Multi-GPU: one context per GPU/process, NCCL over NVLink.  The scene is replicated; frames are
+ * partitioned into interleaved 64x64 tiles and gathered to `root`.  (No counterpart in the reference.)
+ * ---------------------------------------------------------------------------------------------- */
+#define VKRT_TILE_SIZE 64
+#define VKRT_UNIQUE_ID_BYTES 128
+/* Rank 0 creates the id; the caller ships the 128 bytes to the other ranks (MPI, torch.distributed store, file). */
+VKRT_API int vkrt_comm_unique_id(uint8_t id[VKRT_UNIQUE_ID_BYTES]);
+VKRT_API int vkrt_comm_init(VkrtContext* ctx, const uint8_t id[VKRT_UNIQUE_ID_BYTES], int rank, int size);
+/* Tile partition without NCCL (tests, emulation): subsequent frames own tiles with index % size == rank. */
+VKRT_API int vkrt_comm_emulate(VkrtContext* ctx, int rank, int size);
+VKRT_API int vkrt_comm_destroy(VkrtContext* ctx);
+/* Owner rank of the tile containing pixel (x,y) for a frame of this width. */
+VKRT_API int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size);
+/* Gathers the BGRA8 tiles of all ranks into root's frame (stream-ordered; NCCL send/recv group). */
+VKRT_API int vkrt_tiles_gather(VkrtContext* ctx, VkrtFrame* frame, int root);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VKRT_H */

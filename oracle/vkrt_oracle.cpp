@@ -1,0 +1,1063 @@
+/*
+ * vkrt_oracle.cpp — CPU ORACLE (test infrastructure, see vkrt_oracle.h).  PARITY UNPINNED (see header).
+ *
+ * Restates, in scalar FP32 C++ with no FMA contraction (build with -ffp-contract=off):
+ *   shader.rgen:30-77, shader.rchit:78-172, shader.rmiss:15-18, shader_shadow.rmiss:6-9
+ * and the traceRayEXT semantics the Vulkan driver provides to them.  Every arithmetic expression
+ * below fixes an evaluation order (left-to-right, no fused multiply-add); the CUDA kernels restate
+ * the same order independently so the two can be compared bit-for-bit.
+ *
+ * Conventions fixed here (the GLSL/Vulkan specs leave them open):
+ *   normalize(v) = v / sqrt(dot(v,v));  length(v) = sqrt(dot(v,v));  dot = (x*x' + y*y') + z*z'
+ *   clamp(x,0,1) = fmin(fmax(x,0),1)   (NaN -> 0, CUDA fmaxf/fminf semantics)
+ *   mat*vec      = ((c0*x + c1*y) + c2*z) + c3*w  per row
+ *   ray/triangle = Woop, Benthin, Wald 2013 "Watertight Ray/Triangle Intersection", no culling,
+ *                  hit interval tmin < t < tmax exclusive (Vulkan spec), equal-t ties -> lower id
+ *   non-finite or zero-direction rays miss everything
+ */
+#include "vkrt_oracle.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <thread>
+#include <vector>
+
+namespace
+{
+struct V3
+{
+    float x, y, z;
+};
+inline V3 mk(float x, float y, float z) { return V3{x, y, z}; }
+inline V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+inline V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+inline float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline float length(V3 a) { return std::sqrt(dot(a, a)); }
+inline V3 normalize(V3 a) { return a / length(a); }
+inline V3 cross(V3 a, V3 b) { return mk(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+inline float clamp01(float x) { return std::fmin(std::fmax(x, 0.0f), 1.0f); }
+inline float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+inline bool finite3(V3 v) { return std::isfinite(v.x) && std::isfinite(v.y) && std::isfinite(v.z); }
+
+/* column-major mat4 * vec4, rows 0..2 */
+inline V3 mat4MulVec(const float* m, float x, float y, float z, float w)
+{
+    V3 r;
+    r.x = ((m[0] * x + m[4] * y) + m[8] * z) + m[12] * w;
+    r.y = ((m[1] * x + m[5] * y) + m[9] * z) + m[13] * w;
+    r.z = ((m[2] * x + m[6] * y) + m[10] * z) + m[14] * w;
+    return r;
+}
+
+/* row-major 3x4 affine * (p,1) and * (d,0) */
+inline V3 affinePoint(const float* m, V3 p)
+{
+    V3 r;
+    r.x = ((m[0] * p.x + m[1] * p.y) + m[2] * p.z) + m[3];
+    r.y = ((m[4] * p.x + m[5] * p.y) + m[6] * p.z) + m[7];
+    r.z = ((m[8] * p.x + m[9] * p.y) + m[10] * p.z) + m[11];
+    return r;
+}
+inline V3 affineDir(const float* m, V3 d)
+{
+    V3 r;
+    r.x = (m[0] * d.x + m[1] * d.y) + m[2] * d.z;
+    r.y = (m[4] * d.x + m[5] * d.y) + m[6] * d.z;
+    r.z = (m[8] * d.x + m[9] * d.y) + m[10] * d.z;
+    return r;
+}
+
+void affineInverse(const float m[12], float inv[12])
+{
+    const double a = m[0], b = m[1], c = m[2], tx = m[3];
+    const double d = m[4], e = m[5], f = m[6], ty = m[7];
+    const double g = m[8], h = m[9], i = m[10], tz = m[11];
+    const double c00 = e * i - f * h;
+    const double c01 = f * g - d * i;
+    const double c02 = d * h - e * g;
+    const double det = (a * c00 + b * c01) + c * c02;
+    const double r00 = c00 / det, r01 = (c * h - b * i) / det, r02 = (b * f - c * e) / det;
+    const double r10 = c01 / det, r11 = (a * i - c * g) / det, r12 = (c * d - a * f) / det;
+    const double r20 = c02 / det, r21 = (b * g - a * h) / det, r22 = (a * e - b * d) / det;
+    inv[0] = (float)r00, inv[1] = (float)r01, inv[2] = (float)r02;
+    inv[4] = (float)r10, inv[5] = (float)r11, inv[6] = (float)r12;
+    inv[8] = (float)r20, inv[9] = (float)r21, inv[10] = (float)r22;
+    inv[3] = (float)(-((r00 * tx + r01 * ty) + r02 * tz));
+    inv[7] = (float)(-((r10 * tx + r11 * ty) + r12 * tz));
+    inv[11] = (float)(-((r20 * tx + r21 * ty) + r22 * tz));
+}
+
+struct Tri
+{
+    V3 v0, v1, v2;
+    uint32_t geometry, primitive, globalTri;
+};
+
+struct Box
+{
+    float lo[3], hi[3];
+    void reset()
+    {
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = std::numeric_limits<float>::infinity();
+            hi[k] = -std::numeric_limits<float>::infinity();
+        }
+    }
+    void grow(V3 p)
+    {
+        lo[0] = std::min(lo[0], p.x), lo[1] = std::min(lo[1], p.y), lo[2] = std::min(lo[2], p.z);
+        hi[0] = std::max(hi[0], p.x), hi[1] = std::max(hi[1], p.y), hi[2] = std::max(hi[2], p.z);
+    }
+    void grow(const Box& b)
+    {
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = std::min(lo[k], b.lo[k]);
+            hi[k] = std::max(hi[k], b.hi[k]);
+        }
+    }
+    float halfArea() const
+    {
+        const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return dx * dy + dy * dz + dz * dx;
+    }
+};
+
+struct Node
+{
+    Box box;
+    uint32_t left;  /* inner: index of left child (right = left+1); leaf: first triangle slot */
+    uint32_t count; /* 0 = inner, else number of triangles */
+};
+
+struct Image
+{
+    uint32_t w, h;
+    std::vector<uint8_t> px;
+};
+
+struct Instance
+{
+    float o2w[12];
+    float w2o[12];
+};
+
+/* Watertight per-ray precomputation (Woop et al. 2013, section 3). */
+struct RayPre
+{
+    int kx, ky, kz;
+    float Sx, Sy, Sz;
+};
+
+inline RayPre rayPre(V3 d)
+{
+    RayPre r;
+    const float ax = std::fabs(d.x), ay = std::fabs(d.y), az = std::fabs(d.z);
+    r.kz = 0;
+    float best = ax;
+    if (ay > best)
+    {
+        r.kz = 1;
+        best = ay;
+    }
+    if (az > best)
+    {
+        r.kz = 2;
+    }
+    r.kx = (r.kz + 1) % 3;
+    r.ky = (r.kx + 1) % 3;
+    if (comp(d, r.kz) < 0.0f)
+    {
+        std::swap(r.kx, r.ky);
+    }
+    const float dz = comp(d, r.kz);
+    r.Sx = comp(d, r.kx) / dz;
+    r.Sy = comp(d, r.ky) / dz;
+    r.Sz = 1.0f / dz;
+    return r;
+}
+
+/* Returns true and updates (t,b1,b2) if the triangle is hit with tmin < t < tmax. */
+inline bool intersectTri(const Tri& tri, V3 o, const RayPre& rp, float tmin, float tmax, float& tOut, float& b1,
+                         float& b2)
+{
+    const V3 A = tri.v0 - o, B = tri.v1 - o, C = tri.v2 - o;
+    const float Akz = comp(A, rp.kz), Bkz = comp(B, rp.kz), Ckz = comp(C, rp.kz);
+    const float Ax = comp(A, rp.kx) - rp.Sx * Akz, Ay = comp(A, rp.ky) - rp.Sy * Akz;
+    const float Bx = comp(B, rp.kx) - rp.Sx * Bkz, By = comp(B, rp.ky) - rp.Sy * Bkz;
+    const float Cx = comp(C, rp.kx) - rp.Sx * Ckz, Cy = comp(C, rp.ky) - rp.Sy * Ckz;
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f)
+    {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f))
+    {
+        return false;
+    }
+    const float det = (U + V) + W;
+    if (det == 0.0f)
+    {
+        return false;
+    }
+    const float Az = rp.Sz * Akz, Bz = rp.Sz * Bkz, Cz = rp.Sz * Ckz;
+    const float T = (U * Az + V * Bz) + W * Cz;
+    const float rcp = 1.0f / det;
+    const float t = T * rcp;
+    if (!(t > tmin && t < tmax))
+    {
+        return false;
+    }
+    tOut = t;
+    b1 = V * rcp;
+    b2 = W * rcp;
+    return true;
+}
+
+struct Hit
+{
+    float t, b1, b2;
+    uint32_t instance, geometry, primitive, globalTri;
+    bool valid;
+};
+
+struct Counters
+{
+    uint64_t raysPrimary = 0, raysShadow = 0, raysReflection = 0, nodes = 0, tris = 0;
+    void add(const Counters& o)
+    {
+        raysPrimary += o.raysPrimary, raysShadow += o.raysShadow, raysReflection += o.raysReflection;
+        nodes += o.nodes, tris += o.tris;
+    }
+};
+} // namespace
+
+struct OrcScene
+{
+    std::vector<float> vertices; /* 16 floats per vertex */
+    std::vector<uint32_t> indices;
+    std::vector<OrcGeometryRange> ranges;
+    std::vector<OrcSubmeshInfo> rows;
+    std::vector<Image> images;
+    std::vector<Instance> instances;
+    std::vector<Tri> tris;       /* in (geometry, primitive) order */
+    std::vector<uint32_t> order; /* BVH leaf order -> index into tris */
+    std::vector<Node> nodes;
+    double buildSeconds = 0.0;
+
+    void buildTriangles();
+    void buildBvh();
+    uint32_t buildRange(std::vector<Box>& tb, std::vector<V3>& cent, uint32_t first, uint32_t count);
+    void subdivide(uint32_t nodeIdx, std::vector<Box>& tb, std::vector<V3>& cent);
+
+    bool traceObject(V3 o, V3 d, float tmin, float& tmax, bool anyHit, int mode, uint32_t instance, Hit& hit,
+                     Counters& c) const;
+    Hit trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, Counters& c) const;
+    void sample(uint32_t index, float u, float v, float rgba[4]) const;
+};
+
+void OrcScene::buildTriangles()
+{
+    tris.clear();
+    uint32_t globalTri = 0;
+    for (uint32_t g = 0; g < ranges.size(); ++g)
+    {
+        const uint64_t firstIndex = ranges[g].indexByteOffset / 4;
+        for (uint32_t p = 0; p < ranges[g].primitiveCount; ++p)
+        {
+            Tri t;
+            const uint32_t i0 = indices[firstIndex + 3 * (uint64_t)p + 0];
+            const uint32_t i1 = indices[firstIndex + 3 * (uint64_t)p + 1];
+            const uint32_t i2 = indices[firstIndex + 3 * (uint64_t)p + 2];
+            const float* a = &vertices[(size_t)i0 * 16];
+            const float* b = &vertices[(size_t)i1 * 16];
+            const float* c = &vertices[(size_t)i2 * 16];
+            t.v0 = mk(a[0], a[1], a[2]);
+            t.v1 = mk(b[0], b[1], b[2]);
+            t.v2 = mk(c[0], c[1], c[2]);
+            t.geometry = g;
+            t.primitive = p;
+            /* global id as the closest-hit shader forms it: indexBufferOffset + gl_PrimitiveID (rchit:88-89) */
+            t.globalTri = (uint32_t)rows[g].indexBufferOffset + p;
+            (void)globalTri;
+            tris.push_back(t);
+        }
+    }
+}
+
+void OrcScene::subdivide(uint32_t nodeIdx, std::vector<Box>& tb, std::vector<V3>& cent)
+{
+    /* iterative binned-SAH build; explicit stack to survive deep trees */
+    std::vector<uint32_t> stack{nodeIdx};
+    while (!stack.empty())
+    {
+        const uint32_t ni = stack.back();
+        stack.pop_back();
+        const uint32_t first = nodes[ni].left, count = nodes[ni].count;
+        if (count <= 2)
+        {
+            continue;
+        }
+        Box cb;
+        cb.reset();
+        for (uint32_t i = first; i < first + count; ++i)
+        {
+            cb.grow(cent[order[i]]);
+        }
+        constexpr int BINS = 16;
+        float bestCost = std::numeric_limits<float>::infinity();
+        int bestAxis = -1, bestBin = -1;
+        for (int axis = 0; axis < 3; ++axis)
+        {
+            const float lo = cb.lo[axis], hi = cb.hi[axis];
+            if (!(hi > lo))
+            {
+                continue;
+            }
+            Box bins[BINS];
+            uint32_t cnt[BINS] = {};
+            for (auto& b : bins)
+            {
+                b.reset();
+            }
+            const float scale = (float)BINS / (hi - lo);
+            for (uint32_t i = first; i < first + count; ++i)
+            {
+                const uint32_t ti = order[i];
+                int b = (int)((comp(cent[ti], axis) - lo) * scale);
+                b = std::min(std::max(b, 0), BINS - 1);
+                bins[b].grow(tb[ti]);
+                ++cnt[b];
+            }
+            float rightArea[BINS];
+            uint32_t rightCnt[BINS];
+            Box acc;
+            acc.reset();
+            uint32_t n = 0;
+            for (int b = BINS - 1; b > 0; --b)
+            {
+                acc.grow(bins[b]);
+                n += cnt[b];
+                rightArea[b] = n ? acc.halfArea() : 0.0f;
+                rightCnt[b] = n;
+            }
+            acc.reset();
+            n = 0;
+            for (int b = 0; b < BINS - 1; ++b)
+            {
+                acc.grow(bins[b]);
+                n += cnt[b];
+                if (n == 0 || rightCnt[b + 1] == 0)
+                {
+                    continue;
+                }
+                const float cost = acc.halfArea() * (float)n + rightArea[b + 1] * (float)rightCnt[b + 1];
+                if (cost < bestCost)
+                {
+                    bestCost = cost, bestAxis = axis, bestBin = b;
+                }
+            }
+        }
+        uint32_t mid;
+        if (bestAxis < 0)
+        {
+            if (count <= 4)
+            {
+                continue;
+            }
+            mid = first + count / 2; /* all centroids equal: split by order */
+        }
+        else
+        {
+            const float leafCost = nodes[ni].box.halfArea() * (float)count;
+            if (count <= 4 && bestCost >= leafCost)
+            {
+                continue;
+            }
+            const float lo = cb.lo[bestAxis], hi = cb.hi[bestAxis];
+            const float scale = (float)BINS / (hi - lo);
+            auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t ti) {
+                int b = (int)((comp(cent[ti], bestAxis) - lo) * scale);
+                b = std::min(std::max(b, 0), BINS - 1);
+                return b <= bestBin;
+            });
+            mid = (uint32_t)(it - order.begin());
+            if (mid == first || mid == first + count)
+            {
+                mid = first + count / 2;
+            }
+        }
+        const uint32_t l = (uint32_t)nodes.size();
+        nodes.push_back(Node{});
+        nodes.push_back(Node{});
+        nodes[l].left = first, nodes[l].count = mid - first;
+        nodes[l + 1].left = mid, nodes[l + 1].count = first + count - mid;
+        for (int s = 0; s < 2; ++s)
+        {
+            Node& n = nodes[l + s];
+            n.box.reset();
+            for (uint32_t i = n.left; i < n.left + n.count; ++i)
+            {
+                n.box.grow(tb[order[i]]);
+            }
+        }
+        nodes[ni].left = l;
+        nodes[ni].count = 0;
+        stack.push_back(l);
+        stack.push_back(l + 1);
+    }
+}
+
+void OrcScene::buildBvh()
+{
+    const auto t0 = std::chrono::steady_clock::now();
+    const uint32_t n = (uint32_t)tris.size();
+    std::vector<Box> tb(n);
+    std::vector<V3> cent(n);
+    order.resize(n);
+    nodes.clear();
+    nodes.reserve(2 * (size_t)n + 1);
+    Node root;
+    root.box.reset();
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        tb[i].reset();
+        tb[i].grow(tris[i].v0), tb[i].grow(tris[i].v1), tb[i].grow(tris[i].v2);
+        cent[i] = mk(0.5f * (tb[i].lo[0] + tb[i].hi[0]), 0.5f * (tb[i].lo[1] + tb[i].hi[1]),
+                     0.5f * (tb[i].lo[2] + tb[i].hi[2]));
+        order[i] = i;
+        root.box.grow(tb[i]);
+    }
+    root.left = 0;
+    root.count = n;
+    nodes.push_back(root);
+    if (n > 0)
+    {
+        subdivide(0, tb, cent);
+    }
+    buildSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+/* Conservative slab test in double precision with relative slack, so that BVH culling can never
+ * reject a triangle the brute-force loop would accept. */
+static inline bool slab(const Box& b, const double o[3], const double inv[3], double tmin, double tmax, double& tnear)
+{
+    double tn = tmin, tf = tmax;
+    for (int k = 0; k < 3; ++k)
+    {
+        double t0 = ((double)b.lo[k] - o[k]) * inv[k];
+        double t1 = ((double)b.hi[k] - o[k]) * inv[k];
+        if (t0 != t0 || t1 != t1)
+        {
+            continue; /* 0 * inf: the ray lies in the plane; do not cull on this axis */
+        }
+        if (t0 > t1)
+        {
+            std::swap(t0, t1);
+        }
+        t0 -= std::fabs(t0) * 1e-4;
+        t1 += std::fabs(t1) * 1e-4;
+        tn = std::max(tn, t0);
+        tf = std::min(tf, t1);
+    }
+    tnear = tn;
+    return tn <= tf;
+}
+
+/* Intersect one instance's BLAS with an object-space ray. `tmax` shrinks on closest hits. */
+bool OrcScene::traceObject(V3 o, V3 d, float tmin, float& tmax, bool anyHit, int mode, uint32_t instance, Hit& hit,
+                           Counters& c) const
+{
+    bool found = false;
+    const RayPre rp = rayPre(d);
+    auto test = [&](uint32_t ti) -> bool {
+        const Tri& tri = tris[ti];
+        float t, b1, b2;
+        ++c.tris;
+        /* accept strictly closer hits; on an exact tie in t prefer the lower (instance, triangle) id */
+        if (intersectTri(tri, o, rp, tmin, std::nextafter(tmax, std::numeric_limits<float>::infinity()), t, b1, b2))
+        {
+            if (!(t < tmax))
+            {
+                /* t == tmax (previous best or the ray's tmax): only a tie with a previous hit counts */
+                if (!(hit.valid && t == hit.t))
+                {
+                    return false;
+                }
+                const uint64_t idNew = ((uint64_t)instance << 32) | tri.globalTri;
+                const uint64_t idOld = ((uint64_t)hit.instance << 32) | hit.globalTri;
+                if (idNew >= idOld)
+                {
+                    return false;
+                }
+            }
+            hit.t = t, hit.b1 = b1, hit.b2 = b2;
+            hit.instance = instance, hit.geometry = tri.geometry, hit.primitive = tri.primitive;
+            hit.globalTri = tri.globalTri;
+            hit.valid = true;
+            tmax = t;
+            found = true;
+            return true;
+        }
+        return false;
+    };
+
+    if (mode == ORC_MODE_BRUTE)
+    {
+        for (uint32_t i = 0; i < tris.size(); ++i)
+        {
+            if (test(i) && anyHit)
+            {
+                return true;
+            }
+        }
+        return found;
+    }
+
+    if (nodes.empty() || tris.empty())
+    {
+        return false;
+    }
+    const double od[3] = {o.x, o.y, o.z};
+    const double inv[3] = {1.0 / (double)d.x, 1.0 / (double)d.y, 1.0 / (double)d.z};
+    const double slackLo = (double)tmin * (1.0 - 1e-4);
+    uint32_t stack[128];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0)
+    {
+        const Node& n = nodes[stack[--sp]];
+        double tn;
+        ++c.nodes;
+        if (!slab(n.box, od, inv, slackLo, (double)tmax * (1.0 + 1e-4), tn))
+        {
+            continue;
+        }
+        if (n.count)
+        {
+            for (uint32_t i = n.left; i < n.left + n.count; ++i)
+            {
+                if (test(order[i]) && anyHit)
+                {
+                    return true;
+                }
+            }
+        }
+        else
+        {
+            /* near child last so it is popped first */
+            double t0, t1;
+            const bool h0 = slab(nodes[n.left].box, od, inv, slackLo, (double)tmax * (1.0 + 1e-4), t0);
+            const bool h1 = slab(nodes[n.left + 1].box, od, inv, slackLo, (double)tmax * (1.0 + 1e-4), t1);
+            if (h0 && h1)
+            {
+                if (t0 <= t1)
+                {
+                    stack[sp++] = n.left + 1, stack[sp++] = n.left;
+                }
+                else
+                {
+                    stack[sp++] = n.left, stack[sp++] = n.left + 1;
+                }
+            }
+            else if (h0)
+            {
+                stack[sp++] = n.left;
+            }
+            else if (h1)
+            {
+                stack[sp++] = n.left + 1;
+            }
+        }
+    }
+    return found;
+}
+
+/* traceRayEXT over the TLAS: every instance (mask 0xFF, no culling; Raytracer.cpp:1172-1177). */
+Hit OrcScene::trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, Counters& c) const
+{
+    Hit hit{};
+    hit.valid = false;
+    hit.instance = 0xFFFFFFFFu;
+    if (!finite3(o) || !finite3(d) || (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) || !(tmax > tmin))
+    {
+        return hit;
+    }
+    for (uint32_t i = 0; i < instances.size(); ++i)
+    {
+        /* object-space ray: origin and direction through world->object, t shared (Vulkan spec) */
+        const V3 oo = affinePoint(instances[i].w2o, o);
+        const V3 dd = affineDir(instances[i].w2o, d);
+        if (!finite3(oo) || !finite3(dd) || (dd.x == 0.0f && dd.y == 0.0f && dd.z == 0.0f))
+        {
+            continue;
+        }
+        if (traceObject(oo, dd, tmin, tmax, anyHit, mode, i, hit, c) && anyHit)
+        {
+            return hit;
+        }
+    }
+    return hit;
+}
+
+/* Bilinear, REPEAT, LOD 0, texel = u8/255 (UNORM). Vulkan texel addressing: u*W - 0.5. */
+void OrcScene::sample(uint32_t index, float u, float v, float rgba[4]) const
+{
+    const Image& img = images[index];
+    float x = u * (float)img.w - 0.5f;
+    float y = v * (float)img.h - 0.5f;
+    if (!std::isfinite(x))
+    {
+        x = -0.5f;
+    }
+    if (!std::isfinite(y))
+    {
+        y = -0.5f;
+    }
+    const float fx = std::floor(x), fy = std::floor(y);
+    const float a = x - fx, b = y - fy;
+    auto wrap = [](float f, uint32_t n) -> uint32_t {
+        /* floor value -> [0,n) with REPEAT; f is integral. Large magnitudes go through fmod first. */
+        float m = std::fmod(f, (float)n);
+        if (m < 0.0f)
+        {
+            m += (float)n;
+        }
+        uint32_t i = (uint32_t)m;
+        return i >= n ? 0u : i;
+    };
+    const uint32_t x0 = wrap(fx, img.w), y0 = wrap(fy, img.h);
+    const uint32_t x1 = (x0 + 1 == img.w) ? 0u : x0 + 1, y1 = (y0 + 1 == img.h) ? 0u : y0 + 1;
+    const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+    const uint8_t* p00 = &img.px[((size_t)y0 * img.w + x0) * 4];
+    const uint8_t* p10 = &img.px[((size_t)y0 * img.w + x1) * 4];
+    const uint8_t* p01 = &img.px[((size_t)y1 * img.w + x0) * 4];
+    const uint8_t* p11 = &img.px[((size_t)y1 * img.w + x1) * 4];
+    for (int ch = 0; ch < 4; ++ch)
+    {
+        const float t00 = (float)p00[ch] / 255.0f, t10 = (float)p10[ch] / 255.0f;
+        const float t01 = (float)p01[ch] / 255.0f, t11 = (float)p11[ch] / 255.0f;
+        rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+    }
+}
+
+namespace
+{
+float radicalInverse(uint32_t s, uint32_t base)
+{
+    const float inv = 1.0f / (float)base;
+    float f = inv, r = 0.0f;
+    while (s)
+    {
+        r += (float)(s % base) * f;
+        s /= base;
+        f *= inv;
+    }
+    return r;
+}
+
+struct Payload
+{
+    V3 hitValue;
+    int done;
+    int depth;
+    float attenuation;
+    V3 rayOrigin;
+    V3 rayDir;
+};
+
+/* shader.rchit main(), lines 86-172. Returns the 8-bit shadow mask of this hit. */
+uint8_t closestHit(const OrcScene& s, const OrcUniforms& u, const Hit& hit, V3 worldRayDir, Payload& payload, int mode,
+                   Counters& c)
+{
+    const OrcSubmeshInfo& mat = s.rows[hit.geometry];
+    const uint64_t tri = (uint64_t)(uint32_t)mat.indexBufferOffset + hit.primitive; /* rchit:88-89 */
+    const float* v0 = &s.vertices[(size_t)s.indices[3 * tri + 0] * 16];
+    const float* v1 = &s.vertices[(size_t)s.indices[3 * tri + 1] * 16];
+    const float* v2 = &s.vertices[(size_t)s.indices[3 * tri + 2] * 16];
+    const Instance& inst = s.instances[hit.instance];
+
+    const float bx = 1.0f - hit.b1 - hit.b2, by = hit.b1, bz = hit.b2; /* rchit:94 */
+    auto interp3 = [&](int off) {
+        return (mk(v0[off], v0[off + 1], v0[off + 2]) * bx + mk(v1[off], v1[off + 1], v1[off + 2]) * by) +
+               mk(v2[off], v2[off + 1], v2[off + 2]) * bz;
+    };
+    const float uvx = (v0[8] * bx + v1[8] * by) + v2[8] * bz; /* rchit:95 */
+    const float uvy = (v0[9] * bx + v1[9] * by) + v2[9] * bz;
+    const V3 position = interp3(0);                         /* rchit:97 */
+    const V3 worldPos = affinePoint(inst.o2w, position);    /* rchit:98 */
+    const V3 normal = interp3(4);                           /* rchit:100 */
+    /* normal * gl_WorldToObjectEXT: row vector times the 3x3 part (rchit:101) */
+    const float* w = inst.w2o;
+    const V3 nW = mk((normal.x * w[0] + normal.y * w[4]) + normal.z * w[8],
+                     (normal.x * w[1] + normal.y * w[5]) + normal.z * w[9],
+                     (normal.x * w[2] + normal.y * w[6]) + normal.z * w[10]);
+    const V3 worldNormal = normalize(nW);
+    const V3 tangent = interp3(12); /* rchit:103 */
+
+    /* getTBN (rchit:78-84) with M = identity */
+    const V3 N = worldNormal;
+    const V3 T = normalize(tangent);
+    const V3 B = cross(T, N);
+    float texel[4];
+    s.sample((uint32_t)mat.normalTextureIndex, uvx, uvy, texel); /* rchit:106-107 */
+    const V3 mapN = mk(texel[0] * 2.0f - 1.0f, texel[1] * 2.0f - 1.0f, texel[2] * 2.0f - 1.0f);
+    const V3 mn = normalize(mapN);
+    const V3 perturbed = normalize((T * mn.x + B * mn.y) + N * mn.z); /* rchit:108 */
+
+    float totalLightAmount = 0.0f;
+    const float lightIntensity = 10.0f;
+    uint8_t mask = 0;
+    for (int i = 0; i < 4; ++i) /* rchit:119-152 */
+    {
+        const V3 lightVec = mk(u.lightPositions[i][0], u.lightPositions[i][1], u.lightPositions[i][2]) - worldPos;
+        const float lightDistance = length(lightVec);
+        const V3 lightDir = lightVec / lightDistance;
+        const float ndl = dot(perturbed, lightDir);
+        const float diffuse = clamp01(ndl);
+        const float lightPower = lightIntensity / (lightDistance * lightDistance);
+        float shadowMultiplier = 1.0f;
+        if (ndl > 0.0f)
+        {
+            ++c.raysShadow;
+            mask |= (uint8_t)(0x10u << i);
+            const Hit sh = s.trace(worldPos, lightDir, 0.001f, lightDistance, true, mode, c);
+            if (sh.valid)
+            {
+                shadowMultiplier = 0.3f;
+                mask |= (uint8_t)(1u << i);
+            }
+        }
+        totalLightAmount += (diffuse * lightPower) * shadowMultiplier;
+    }
+
+    const float ambient = 0.1f;
+    s.sample((uint32_t)mat.baseColorTextureIndex, uvx, uvy, texel); /* rchit:156-157 */
+    const V3 baseColor = mk(texel[0], texel[1], texel[2]);
+    payload.hitValue = (baseColor * totalLightAmount) * payload.attenuation + baseColor * ambient; /* rchit:158 */
+
+    s.sample((uint32_t)mat.metallicRoughnessTextureIndex, uvx, uvy, texel); /* rchit:161-162 */
+    const float metallic = texel[2];
+    if (metallic > 0.1f) /* rchit:163-171 */
+    {
+        const float reflectAmount = 0.5f * metallic;
+        payload.attenuation *= reflectAmount;
+        payload.hitValue = payload.hitValue * (1.0f - payload.attenuation);
+        payload.done = 0;
+        payload.rayOrigin = worldPos;
+        /* reflect(I,N) = I - 2*dot(N,I)*N */
+        const float k = 2.0f * dot(perturbed, worldRayDir);
+        payload.rayDir = worldRayDir - perturbed * k;
+    }
+    return mask;
+}
+
+void primaryRay(const OrcUniforms& u, uint32_t width, uint32_t height, uint32_t x, uint32_t y, float jx, float jy,
+                V3& origin, V3& direction)
+{
+    /* shader.rgen:32-38 */
+    const float pcx = (float)x + jx, pcy = (float)y + jy;
+    const float inx = pcx / (float)width, iny = pcy / (float)height;
+    const float ux = inx * 2.0f - 1.0f, uy = iny * 2.0f - 1.0f;
+    const V3 target = mat4MulVec(u.projInverse, ux, uy, 1.0f, 1.0f);
+    const V3 tn = normalize(target);
+    direction = mat4MulVec(u.viewInverse, tn.x, tn.y, tn.z, 0.0f);
+    origin = mat4MulVec(u.viewInverse, 0.0f, 0.0f, 0.0f, 1.0f);
+}
+
+inline uint8_t unorm8(float x)
+{
+    return (uint8_t)(clamp01(x) * 255.0f + 0.5f);
+}
+} // namespace
+
+extern "C" {
+
+OrcScene* orc_scene_create(const float* vertices, uint64_t vertexCount, const uint32_t* indices, uint64_t indexCount,
+                           const OrcGeometryRange* ranges, const OrcSubmeshInfo* rows, uint32_t geometryCount,
+                           const OrcImage* images, uint32_t imageCount, const float* instances, uint32_t instanceCount)
+{
+    OrcScene* s = new OrcScene();
+    s->vertices.assign(vertices, vertices + vertexCount * 16);
+    s->indices.assign(indices, indices + indexCount);
+    s->ranges.assign(ranges, ranges + geometryCount);
+    s->rows.assign(rows, rows + geometryCount);
+    s->images.resize(imageCount);
+    for (uint32_t i = 0; i < imageCount; ++i)
+    {
+        s->images[i].w = images[i].width;
+        s->images[i].h = images[i].height;
+        s->images[i].px.assign(images[i].rgba8, images[i].rgba8 + (size_t)images[i].width * images[i].height * 4);
+    }
+    s->instances.resize(instanceCount);
+    for (uint32_t i = 0; i < instanceCount; ++i)
+    {
+        std::memcpy(s->instances[i].o2w, instances + 12 * (size_t)i, sizeof(float) * 12);
+        affineInverse(s->instances[i].o2w, s->instances[i].w2o);
+    }
+    s->buildTriangles();
+    s->buildBvh();
+    return s;
+}
+
+void orc_scene_destroy(OrcScene* scene)
+{
+    delete scene;
+}
+
+void orc_scene_update_vertices(OrcScene* scene, const float* vertices, uint64_t vertexCount)
+{
+    scene->vertices.assign(vertices, vertices + vertexCount * 16);
+    scene->buildTriangles();
+    scene->buildBvh();
+}
+
+double orc_scene_build_seconds(const OrcScene* scene)
+{
+    return scene->buildSeconds;
+}
+
+void orc_halton23(uint32_t s, float out[2])
+{
+    /* 1-based so the degenerate (0,0) corner is skipped */
+    out[0] = radicalInverse(s + 1, 2);
+    out[1] = radicalInverse(s + 1, 3);
+}
+
+void orc_primary_ray(const OrcUniforms* uniforms, uint32_t width, uint32_t height, uint32_t x, uint32_t y, float jx,
+                     float jy, OrcRay* ray)
+{
+    V3 o, d;
+    primaryRay(*uniforms, width, height, x, y, jx, jy, o, d);
+    ray->origin[0] = o.x, ray->origin[1] = o.y, ray->origin[2] = o.z;
+    ray->direction[0] = d.x, ray->direction[1] = d.y, ray->direction[2] = d.z;
+    ray->tmin = 0.001f;
+    ray->tmax = 1000.0f;
+}
+
+void orc_affine_inverse(const float m[12], float inv[12])
+{
+    affineInverse(m, inv);
+}
+
+void orc_sample_texture(const OrcScene* scene, uint32_t index, float u, float v, float rgba[4])
+{
+    scene->sample(index, u, v, rgba);
+}
+
+void orc_render(OrcScene* scene, const OrcUniforms* uniforms, uint32_t width, uint32_t height, uint32_t spp, int mode,
+                int threads, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t strideX, uint32_t strideY,
+                float* rgb32f, uint8_t* bgra8, uint32_t* triangleId, uint8_t* shadowMask, OrcStats* stats)
+{
+    const auto tStart = std::chrono::steady_clock::now();
+    if (threads <= 0)
+    {
+        threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    }
+    strideX = std::max(strideX, 1u), strideY = std::max(strideY, 1u);
+    spp = std::max(spp, 1u);
+    x1 = std::min(x1, width), y1 = std::min(y1, height);
+    const uint32_t rows = y1 > y0 ? (y1 - y0 + strideY - 1) / strideY : 0;
+    std::atomic<uint32_t> nextRow{0};
+    std::vector<Counters> perThread((size_t)threads);
+    const OrcScene& s = *scene;
+    const OrcUniforms& u = *uniforms;
+
+    auto worker = [&](int tid) {
+        Counters& c = perThread[(size_t)tid];
+        for (;;)
+        {
+            const uint32_t r = nextRow.fetch_add(1);
+            if (r >= rows)
+            {
+                break;
+            }
+            const uint32_t y = y0 + r * strideY;
+            for (uint32_t x = x0; x < x1; x += strideX)
+            {
+                V3 acc = mk(0, 0, 0);
+                uint32_t aovTri = 0xFFFFFFFFu;
+                uint8_t aovMask = 0;
+                for (uint32_t sIdx = 0; sIdx < spp; ++sIdx)
+                {
+                    float jx = 0.5f, jy = 0.5f; /* rgen:32 */
+                    if (spp > 1)
+                    {
+                        float h[2];
+                        orc_halton23(sIdx, h);
+                        jx = h[0], jy = h[1];
+                    }
+                    V3 origin, direction;
+                    primaryRay(u, width, height, x, y, jx, jy, origin, direction);
+                    V3 finalHitValue = mk(0, 0, 0);
+                    Payload p;
+                    p.hitValue = mk(0, 0, 0), p.attenuation = 1.0f, p.depth = 0, p.done = 1; /* rgen:44-47 */
+                    p.rayOrigin = mk(0, 0, 0), p.rayDir = mk(0, 0, 0);
+                    const int maxDepth = 2;
+                    for (;;) /* rgen:49-74 */
+                    {
+                        if (p.depth == 0)
+                        {
+                            ++c.raysPrimary;
+                        }
+                        else
+                        {
+                            ++c.raysReflection;
+                        }
+                        const Hit hit = s.trace(origin, direction, 0.001f, 1000.0f, false, mode, c);
+                        uint8_t mask = 0;
+                        if (hit.valid)
+                        {
+                            mask = closestHit(s, u, hit, direction, p, mode, c);
+                        }
+                        else
+                        {
+                            p.hitValue = mk(0.8f, 0.8f, 1.0f); /* rmiss:17 */
+                        }
+                        if (p.depth == 0 && sIdx == 0)
+                        {
+                            aovTri = hit.valid ? ((hit.instance << 24) + hit.globalTri) : 0xFFFFFFFFu;
+                            aovMask = mask;
+                        }
+                        finalHitValue = finalHitValue + p.hitValue;
+                        ++p.depth;
+                        if (p.done == 1 || p.depth >= maxDepth)
+                        {
+                            break;
+                        }
+                        origin = p.rayOrigin;
+                        direction = p.rayDir;
+                        p.done = 1;
+                    }
+                    acc = acc + finalHitValue;
+                }
+                const V3 out = spp > 1 ? acc / (float)spp : acc;
+                const size_t pix = (size_t)y * width + x;
+                if (rgb32f)
+                {
+                    rgb32f[pix * 3 + 0] = out.x, rgb32f[pix * 3 + 1] = out.y, rgb32f[pix * 3 + 2] = out.z;
+                }
+                if (bgra8)
+                {
+                    bgra8[pix * 4 + 0] = unorm8(out.z), bgra8[pix * 4 + 1] = unorm8(out.y);
+                    bgra8[pix * 4 + 2] = unorm8(out.x), bgra8[pix * 4 + 3] = 255;
+                }
+                if (triangleId)
+                {
+                    triangleId[pix] = aovTri;
+                }
+                if (shadowMask)
+                {
+                    shadowMask[pix] = aovMask;
+                }
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t)
+    {
+        pool.emplace_back(worker, t);
+    }
+    worker(0);
+    for (auto& t : pool)
+    {
+        t.join();
+    }
+    if (stats)
+    {
+        Counters total;
+        for (const Counters& c : perThread)
+        {
+            total.add(c);
+        }
+        stats->raysPrimary = total.raysPrimary, stats->raysShadow = total.raysShadow;
+        stats->raysReflection = total.raysReflection;
+        stats->nodesVisited = total.nodes, stats->trianglesTested = total.tris;
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - tStart).count();
+    }
+}
+
+void orc_trace_rays(OrcScene* scene, const OrcRay* rays, uint64_t count, int anyHit, int mode, int threads,
+                    OrcHit* hits, OrcStats* stats)
+{
+    const auto tStart = std::chrono::steady_clock::now();
+    if (threads <= 0)
+    {
+        threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    }
+    std::atomic<uint64_t> next{0};
+    std::vector<Counters> perThread((size_t)threads);
+    const uint64_t chunk = 256;
+    auto worker = [&](int tid) {
+        Counters& c = perThread[(size_t)tid];
+        for (;;)
+        {
+            const uint64_t b = next.fetch_add(chunk);
+            if (b >= count)
+            {
+                break;
+            }
+            const uint64_t e = std::min(count, b + chunk);
+            for (uint64_t i = b; i < e; ++i)
+            {
+                const OrcRay& r = rays[i];
+                const Hit h = scene->trace(mk(r.origin[0], r.origin[1], r.origin[2]),
+                                           mk(r.direction[0], r.direction[1], r.direction[2]), r.tmin, r.tmax,
+                                           anyHit != 0, mode, c);
+                OrcHit& o = hits[i];
+                o.t = h.t, o.b1 = h.b1, o.b2 = h.b2;
+                o.instance = h.valid ? h.instance : 0xFFFFFFFFu;
+                o.geometry = h.valid ? h.geometry : 0xFFFFFFFFu;
+                o.primitive = h.valid ? h.primitive : 0xFFFFFFFFu;
+                if (!h.valid)
+                {
+                    o.t = 0.0f, o.b1 = 0.0f, o.b2 = 0.0f;
+                }
+                if (anyHit)
+                {
+                    ++c.raysShadow;
+                }
+                else
+                {
+                    ++c.raysPrimary;
+                }
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t)
+    {
+        pool.emplace_back(worker, t);
+    }
+    worker(0);
+    for (auto& t : pool)
+    {
+        t.join();
+    }
+    if (stats)
+    {
+        Counters total;
+        for (const Counters& c : perThread)
+        {
+            total.add(c);
+        }
+        stats->raysPrimary = total.raysPrimary, stats->raysShadow = total.raysShadow;
+        stats->raysReflection = total.raysReflection;
+        stats->nodesVisited = total.nodes, stats->trianglesTested = total.tris;
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - tStart).count();
+    }
+}
+
+} // extern "C"

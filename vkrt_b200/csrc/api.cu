@@ -1,0 +1,782 @@
+// api.cu — the extern "C" entry points declared in include/vkrt.h.
+#include "context.hpp"
+#include "device_math.cuh"
+#include "traverse.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+using namespace vkrt;
+
+namespace
+{
+std::string g_createError;
+
+Context* C(VkrtContext* c) { return static_cast<Context*>(c); }
+const Context* C(const VkrtContext* c) { return static_cast<const Context*>(c); }
+Blas* B(VkrtBlas* b) { return static_cast<Blas*>(b); }
+const Blas* B(const VkrtBlas* b) { return static_cast<const Blas*>(b); }
+Tlas* T(VkrtTlas* t) { return static_cast<Tlas*>(t); }
+const Tlas* T(const VkrtTlas* t) { return static_cast<const Tlas*>(t); }
+Frame* F(VkrtFrame* f) { return static_cast<Frame*>(f); }
+
+int uploadGeometry(Context* ctx, Blas* blas, const void* vertices, size_t vertexBytes, const uint32_t* indices, size_t indexCount,
+                   bool onDevice)
+{
+    const cudaMemcpyKind kind = onDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    VKRT_CUDA_TRY(ctx, blas->vertices.reserve(std::max<size_t>(vertexBytes, 16)));
+    if (vertexBytes)
+    {
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(blas->vertices.ptr, vertices, vertexBytes, kind, ctx->stream));
+    }
+    if (indices)
+    {
+        VKRT_CUDA_TRY(ctx, blas->indices.reserve(std::max<size_t>(indexCount * 4, 16)));
+        if (indexCount)
+        {
+            VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(blas->indices.ptr, indices, indexCount * 4, kind, ctx->stream));
+        }
+    }
+    return VKRT_SUCCESS;
+}
+} // namespace
+
+extern "C" {
+
+int vkrt_version(void)
+{
+    return 100; // 0.1.0
+}
+
+int vkrt_context_create(int deviceOrdinal, VkrtContext** out)
+{
+    if (!out)
+    {
+        g_createError = "vkrt_context_create: out is NULL";
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+    {
+        g_createError = std::string("vkrt_context_create: no CUDA device (") + cudaGetErrorString(e) +
+                        "); libvkrt_b200 has no CPU fallback";
+        return VKRT_ERROR_NO_DEVICE;
+    }
+    if (deviceOrdinal < 0 || deviceOrdinal >= count)
+    {
+        g_createError = "vkrt_context_create: device ordinal out of range";
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    e = cudaSetDevice(deviceOrdinal);
+    if (e != cudaSuccess)
+    {
+        g_createError = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
+        return VKRT_ERROR_CUDA;
+    }
+    Context* ctx = new (std::nothrow) Context();
+    if (!ctx)
+    {
+        return VKRT_ERROR_OUT_OF_MEMORY;
+    }
+    ctx->device = deviceOrdinal;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, deviceOrdinal) == cudaSuccess)
+    {
+        ctx->smCount = prop.multiProcessorCount;
+    }
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess)
+    {
+        e = ctx->statCounters.reserve(64);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemsetAsync(ctx->statCounters.ptr, 0, 64, ctx->stream);
+    }
+    if (e != cudaSuccess)
+    {
+        g_createError = std::string("vkrt_context_create: ") + cudaGetErrorString(e);
+        delete ctx;
+        return VKRT_ERROR_CUDA;
+    }
+    *out = ctx;
+    return VKRT_SUCCESS;
+}
+
+void vkrt_context_destroy(VkrtContext* c)
+{
+    if (!c)
+    {
+        return;
+    }
+    Context* ctx = C(c);
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    commDestroy(ctx);
+    for (void* p : ctx->textureAllocs)
+    {
+        cudaFree(p);
+    }
+    ctx->materials.release();
+    ctx->textureRecords.release();
+    ctx->uniforms.release();
+    ctx->buildScratch.release();
+    ctx->wave.release();
+    ctx->statCounters.release();
+    ctx->gatherStaging.release();
+    if (ctx->eventsCreated)
+    {
+        for (auto& ev : ctx->stageEvents)
+        {
+            cudaEventDestroy(ev);
+        }
+    }
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* vkrt_last_error(const VkrtContext* c)
+{
+    return c ? C(c)->lastError.c_str() : g_createError.c_str();
+}
+
+int vkrt_context_synchronize(VkrtContext* c)
+{
+    Context* ctx = C(c);
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return VKRT_SUCCESS;
+}
+
+void* vkrt_context_stream(VkrtContext* c)
+{
+    return c ? (void*)C(c)->stream : nullptr;
+}
+
+int vkrt_blas_sizes(VkrtContext* c, const VkrtGeometryRange* ranges, uint32_t geometryCount, uint64_t vertexBytes, uint64_t indexCount,
+                    VkrtBuildSizes* out)
+{
+    Context* ctx = C(c);
+    if (!out || (!ranges && geometryCount))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_sizes: NULL argument");
+    }
+    uint64_t n = 0;
+    for (uint32_t g = 0; g < geometryCount; ++g)
+    {
+        n += ranges[g].primitiveCount;
+    }
+    const uint64_t nodeCap = std::max<uint64_t>(1, n / 2 + 8);
+    out->accelerationStructureSize = nodeCap * sizeof(Node8) + std::max<uint64_t>(1, n) * sizeof(PackedTri);
+    // triLo/triHi 32, keys/vals x2 16, children 8, node boxes 32, flags 4, taskRef 2, primSource 4, sort histograms ~0.25
+    out->buildScratchSize = std::max<uint64_t>(1, n) * 100 + 4096;
+    out->geometryCopySize = vertexBytes + indexCount * 4;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_blas_build(VkrtContext* c, const void* vertices, size_t vertexBytes, uint32_t vertexStride, const uint32_t* indices,
+                    size_t indexCount, const VkrtGeometryRange* ranges, uint32_t geometryCount, uint32_t flags, VkrtBlas** out)
+{
+    Context* ctx = C(c);
+    if (!out)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: out is NULL");
+    }
+    *out = nullptr;
+    if (vertexStride < 12 || (vertexStride & 3u))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: vertexStride must be a multiple of 4 and >= 12");
+    }
+    if ((!ranges && geometryCount) || (!vertices && vertexBytes) || (!indices && indexCount))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: NULL input");
+    }
+    std::vector<uint32_t> firstTri(geometryCount + 1, 0);
+    std::vector<uint64_t> indexBase(std::max<uint32_t>(geometryCount, 1), 0);
+    uint64_t n = 0;
+    for (uint32_t g = 0; g < geometryCount; ++g)
+    {
+        if (ranges[g].indexByteOffset & 3u)
+        {
+            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: indexByteOffset must be a multiple of 4");
+        }
+        indexBase[g] = ranges[g].indexByteOffset / 4;
+        if (indexBase[g] + 3ull * ranges[g].primitiveCount > indexCount)
+        {
+            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: geometry " + std::to_string(g) + " reads past the index buffer");
+        }
+        firstTri[g] = (uint32_t)n;
+        n += ranges[g].primitiveCount;
+    }
+    if (n >= 0x7FFFFFFFull)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: at most 2^31-2 triangles per BLAS");
+    }
+    firstTri[geometryCount] = (uint32_t)n;
+    const bool onDevice = (flags & VKRT_BUILD_INPUT_ON_DEVICE) != 0;
+    if (!onDevice && n > 0)
+    {
+        // host-side validation of the index range (the reference relies on maxVertex, Raytracer.cpp:1063)
+        const uint64_t vertexCount = vertexBytes / vertexStride;
+        for (uint32_t g = 0; g < geometryCount; ++g)
+        {
+            const uint32_t* idx = indices + indexBase[g];
+            for (uint64_t k = 0; k < 3ull * ranges[g].primitiveCount; ++k)
+            {
+                if (idx[k] >= vertexCount)
+                {
+                    return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: index out of range in geometry " + std::to_string(g));
+                }
+            }
+        }
+    }
+
+    cudaSetDevice(ctx->device);
+    Blas* blas = new (std::nothrow) Blas();
+    if (!blas)
+    {
+        return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_blas_build: host allocation failed");
+    }
+    blas->vertexStride = vertexStride;
+    blas->vertexBytes = vertexBytes;
+    blas->indexCount = indexCount;
+    blas->geometryCount = geometryCount;
+    blas->triangleCount = (uint32_t)n;
+    blas->flags = flags;
+    auto cleanup = [&](int code) {
+        vkrt_blas_destroy(c, blas);
+        return code;
+    };
+    int r = uploadGeometry(ctx, blas, vertices, vertexBytes, indices, indexCount, onDevice);
+    if (r != VKRT_SUCCESS)
+    {
+        return cleanup(r);
+    }
+    cudaError_t e = blas->geomFirstTri.reserve(firstTri.size() * 4);
+    if (e == cudaSuccess)
+    {
+        e = blas->geomIndexBase.reserve(indexBase.size() * 8);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemcpyAsync(blas->geomFirstTri.ptr, firstTri.data(), firstTri.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemcpyAsync(blas->geomIndexBase.ptr, indexBase.data(), indexBase.size() * 8, cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaStreamSynchronize(ctx->stream); // the host vectors above go out of scope
+    }
+    if (e != cudaSuccess)
+    {
+        return cleanup(ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_blas_build: ") + cudaGetErrorString(e)));
+    }
+    r = buildBlasOnDevice(ctx, blas);
+    if (r != VKRT_SUCCESS)
+    {
+        return cleanup(r);
+    }
+    *out = blas;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_blas_rebuild(VkrtContext* c, VkrtBlas* b, const void* vertices, size_t vertexBytes, uint32_t flags)
+{
+    Context* ctx = C(c);
+    Blas* blas = B(b);
+    if (!blas || (!vertices && vertexBytes))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_rebuild: NULL argument");
+    }
+    if (vertexBytes != blas->vertexBytes)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_rebuild: vertex data size differs from the original build");
+    }
+    cudaSetDevice(ctx->device);
+    int r = uploadGeometry(ctx, blas, vertices, vertexBytes, nullptr, 0, (flags & VKRT_BUILD_INPUT_ON_DEVICE) != 0);
+    if (r != VKRT_SUCCESS)
+    {
+        return r;
+    }
+    return buildBlasOnDevice(ctx, blas);
+}
+
+void vkrt_blas_destroy(VkrtContext* c, VkrtBlas* b)
+{
+    if (!b)
+    {
+        return;
+    }
+    Blas* blas = B(b);
+    if (c)
+    {
+        cudaSetDevice(C(c)->device);
+        cudaStreamSynchronize(C(c)->stream);
+    }
+    blas->vertices.release(), blas->indices.release();
+    blas->geomFirstTri.release(), blas->geomIndexBase.release();
+    blas->nodes.release(), blas->tris.release();
+    delete blas;
+}
+
+uint64_t vkrt_blas_reference(const VkrtBlas* b)
+{
+    return (uint64_t)(uintptr_t)b;
+}
+
+int vkrt_blas_info(VkrtContext* c, const VkrtBlas* b, VkrtBlasInfo* out)
+{
+    Context* ctx = C(c);
+    if (!b || !out)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_info: NULL argument");
+    }
+    const Blas* blas = B(b);
+    out->triangleCount = blas->triangleCount;
+    out->nodeCount = blas->nodeCount;
+    out->nodeBytes = (uint64_t)blas->nodeCount * sizeof(Node8);
+    out->triangleBytes = (uint64_t)blas->triangleCount * sizeof(PackedTri);
+    for (int k = 0; k < 3; ++k)
+    {
+        out->boundsMin[k] = blas->boundsMin[k];
+        out->boundsMax[k] = blas->boundsMax[k];
+    }
+    out->sahCost = blas->sahCost;
+    out->buildMilliseconds = blas->buildMs;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_blas_read(VkrtContext* c, const VkrtBlas* b, void* nodes, size_t nodeBytes, void* triangles, size_t triangleBytes)
+{
+    Context* ctx = C(c);
+    const Blas* blas = B(b);
+    if (!blas)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_read: NULL blas");
+    }
+    cudaSetDevice(ctx->device);
+    if (nodes)
+    {
+        const size_t bytes = std::min<size_t>(nodeBytes, (size_t)blas->nodeCount * sizeof(Node8));
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(nodes, blas->nodes.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (triangles)
+    {
+        const size_t bytes = std::min<size_t>(triangleBytes, (size_t)blas->triangleCount * sizeof(PackedTri));
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(triangles, blas->tris.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return VKRT_SUCCESS;
+}
+
+int vkrt_tlas_build(VkrtContext* c, const VkrtInstance* instances, uint32_t instanceCount, VkrtTlas** out)
+{
+    Context* ctx = C(c);
+    if (!out || (!instances && instanceCount))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: NULL argument");
+    }
+    *out = nullptr;
+    if (instanceCount == 0 || instanceCount > 256)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: instanceCount must be in 1..256");
+    }
+    cudaSetDevice(ctx->device);
+    std::vector<InstanceRecord> recs(instanceCount);
+    std::vector<InstanceBounds> bounds(instanceCount);
+    for (uint32_t i = 0; i < instanceCount; ++i)
+    {
+        const Blas* blas = reinterpret_cast<const Blas*>((uintptr_t)instances[i].accelerationStructureReference);
+        if (!blas)
+        {
+            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: instance " + std::to_string(i) + " has no BLAS reference");
+        }
+        InstanceRecord& r = recs[i];
+        std::memset(&r, 0, sizeof(r));
+        std::memcpy(r.o2w, instances[i].transform, sizeof(float) * 12);
+        affineInverseHost(r.o2w, r.w2o);
+        r.nodes = blas->nodes.as<Node8>();
+        r.tris = blas->tris.as<PackedTri>();
+        r.vertices = blas->vertices.as<uint8_t>();
+        r.indices = blas->indices.as<uint32_t>();
+        r.vertexStride = blas->vertexStride;
+        // world bounds: the 8 corners of the BLAS box through object->world, padded by a few ulps
+        InstanceBounds& wb = bounds[i];
+        for (int k = 0; k < 3; ++k)
+        {
+            wb.lo[k] = INFINITY;
+            wb.hi[k] = -INFINITY;
+        }
+        for (int corner = 0; corner < 8; ++corner)
+        {
+            const F3 p = f3((corner & 1) ? blas->boundsMax[0] : blas->boundsMin[0], (corner & 2) ? blas->boundsMax[1] : blas->boundsMin[1],
+                            (corner & 4) ? blas->boundsMax[2] : blas->boundsMin[2]);
+            const F3 q = affinePoint(r.o2w, p);
+            wb.lo[0] = std::min(wb.lo[0], q.x), wb.lo[1] = std::min(wb.lo[1], q.y), wb.lo[2] = std::min(wb.lo[2], q.z);
+            wb.hi[0] = std::max(wb.hi[0], q.x), wb.hi[1] = std::max(wb.hi[1], q.y), wb.hi[2] = std::max(wb.hi[2], q.z);
+        }
+        for (int k = 0; k < 3; ++k)
+        {
+            const float padAbs = (std::fabs(wb.lo[k]) + std::fabs(wb.hi[k])) * 1e-5f + 1e-30f;
+            wb.lo[k] -= padAbs;
+            wb.hi[k] += padAbs;
+        }
+    }
+    Tlas* tlas = new (std::nothrow) Tlas();
+    if (!tlas)
+    {
+        return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_tlas_build: host allocation failed");
+    }
+    tlas->instanceCount = instanceCount;
+    cudaError_t e = tlas->instances.reserve(recs.size() * sizeof(InstanceRecord));
+    if (e == cudaSuccess)
+    {
+        e = tlas->bounds.reserve(bounds.size() * sizeof(InstanceBounds));
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemcpyAsync(tlas->instances.ptr, recs.data(), recs.size() * sizeof(InstanceRecord), cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemcpyAsync(tlas->bounds.ptr, bounds.data(), bounds.size() * sizeof(InstanceBounds), cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaStreamSynchronize(ctx->stream);
+    }
+    if (e != cudaSuccess)
+    {
+        vkrt_tlas_destroy(c, tlas);
+        return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_tlas_build: ") + cudaGetErrorString(e));
+    }
+    *out = tlas;
+    return VKRT_SUCCESS;
+}
+
+void vkrt_tlas_destroy(VkrtContext* c, VkrtTlas* t)
+{
+    if (!t)
+    {
+        return;
+    }
+    if (c)
+    {
+        cudaSetDevice(C(c)->device);
+        cudaStreamSynchronize(C(c)->stream);
+    }
+    Tlas* tlas = T(t);
+    tlas->instances.release();
+    tlas->bounds.release();
+    delete tlas;
+}
+
+int vkrt_materials_set(VkrtContext* c, const VkrtSubmeshInfo* rows, uint32_t count)
+{
+    Context* ctx = C(c);
+    if (!rows || count == 0)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_materials_set: empty table");
+    }
+    cudaSetDevice(ctx->device);
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    VKRT_CUDA_TRY(ctx, ctx->materials.reserve((size_t)count * sizeof(VkrtSubmeshInfo)));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->materials.ptr, rows, (size_t)count * sizeof(VkrtSubmeshInfo), cudaMemcpyHostToDevice, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->materialCount = count;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
+{
+    Context* ctx = C(c);
+    if (!images || count == 0)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_textures_set: empty array");
+    }
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        if (!images[i].rgba8 || images[i].width == 0 || images[i].height == 0)
+        {
+            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_textures_set: image " + std::to_string(i) + " is empty");
+        }
+    }
+    cudaSetDevice(ctx->device);
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    for (void* p : ctx->textureAllocs)
+    {
+        cudaFree(p);
+    }
+    ctx->textureAllocs.clear();
+    ctx->textureCount = 0;
+    // one allocation for all texels (256-byte aligned sub-ranges)
+    std::vector<size_t> offsets(count);
+    size_t total = 0;
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        offsets[i] = total;
+        total += (((size_t)images[i].width * images[i].height * 4) + 255) & ~(size_t)255;
+    }
+    void* pool = nullptr;
+    VKRT_CUDA_TRY(ctx, cudaMalloc(&pool, total));
+    ctx->textureAllocs.push_back(pool);
+    std::vector<TextureRecord> recs(count);
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        uint8_t* dst = static_cast<uint8_t*>(pool) + offsets[i];
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(dst, images[i].rgba8, (size_t)images[i].width * images[i].height * 4, cudaMemcpyHostToDevice, ctx->stream));
+        recs[i].texels = dst;
+        recs[i].width = images[i].width;
+        recs[i].height = images[i].height;
+    }
+    VKRT_CUDA_TRY(ctx, ctx->textureRecords.reserve(recs.size() * sizeof(TextureRecord)));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->textureRecords.ptr, recs.data(), recs.size() * sizeof(TextureRecord), cudaMemcpyHostToDevice, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->textureCount = count;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_frame_create(VkrtContext* c, uint32_t width, uint32_t height, VkrtFrame** out)
+{
+    Context* ctx = C(c);
+    if (!out || width == 0 || height == 0 || width > 65536 || height > 65536)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_create: bad size");
+    }
+    *out = nullptr;
+    cudaSetDevice(ctx->device);
+    Frame* f = new (std::nothrow) Frame();
+    if (!f)
+    {
+        return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_frame_create: host allocation failed");
+    }
+    f->width = width, f->height = height;
+    f->tilesX = (width + kTile - 1) / kTile;
+    f->tilesY = (height + kTile - 1) / kTile;
+    f->rank = ctx->rank, f->size = ctx->size;
+    const uint32_t tiles = f->tilesX * f->tilesY;
+    f->ownedTiles = tiles > (uint32_t)f->rank ? (tiles - (uint32_t)f->rank + (uint32_t)f->size - 1) / (uint32_t)f->size : 0;
+    f->paths = f->ownedTiles * (uint32_t)kTilePixels;
+    cudaError_t e = f->bgra8.reserve((size_t)width * height * 4);
+    if (e == cudaSuccess)
+    {
+        e = cudaMemsetAsync(f->bgra8.ptr, 0, (size_t)width * height * 4, ctx->stream);
+    }
+    if (e == cudaSuccess && f->size > 1)
+    {
+        e = f->tileBgra8.reserve(std::max<size_t>(1, f->ownedTiles) * kTilePixels * 4);
+    }
+    if (e != cudaSuccess)
+    {
+        vkrt_frame_destroy(c, f);
+        return ctx->fail(e == cudaErrorMemoryAllocation ? VKRT_ERROR_OUT_OF_MEMORY : VKRT_ERROR_CUDA,
+                         std::string("vkrt_frame_create: ") + cudaGetErrorString(e));
+    }
+    *out = f;
+    return VKRT_SUCCESS;
+}
+
+void vkrt_frame_destroy(VkrtContext* c, VkrtFrame* fr)
+{
+    if (!fr)
+    {
+        return;
+    }
+    if (c)
+    {
+        cudaSetDevice(C(c)->device);
+        cudaStreamSynchronize(C(c)->stream);
+    }
+    Frame* f = F(fr);
+    f->bgra8.release(), f->tileBgra8.release(), f->rgb32f.release(), f->triangleId.release(), f->shadowMask.release();
+    delete f;
+}
+
+int vkrt_trace(VkrtContext* c, const VkrtTlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
+               VkrtFrame* frame)
+{
+    Context* ctx = C(c);
+    if (!tlas || !uniforms || !frame)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    return traceFrame(ctx, T(tlas), uniforms, spp, frameIndex, flags, F(frame));
+}
+
+int vkrt_frame_read(VkrtContext* c, VkrtFrame* fr, int aov, void* dst, size_t pitch)
+{
+    Context* ctx = C(c);
+    Frame* f = F(fr);
+    if (!f || !dst)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_read: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    const void* src = nullptr;
+    size_t bpp = 0;
+    switch (aov)
+    {
+    case VKRT_AOV_BGRA8:
+        src = f->bgra8.ptr, bpp = 4;
+        break;
+    case VKRT_AOV_RGB32F:
+        src = f->rgb32f.ptr, bpp = 12;
+        break;
+    case VKRT_AOV_TRIANGLE_ID_U32:
+        src = f->triangleId.ptr, bpp = 4;
+        break;
+    case VKRT_AOV_SHADOW_MASK_U8:
+        src = f->shadowMask.ptr, bpp = 1;
+        break;
+    default:
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_read: unknown AOV");
+    }
+    if (!src)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_frame_read: this output was not rendered (VKRT_TRACE_NO_AOV?)");
+    }
+    const size_t row = (size_t)f->width * bpp;
+    if (pitch == 0)
+    {
+        pitch = row;
+    }
+    if (pitch < row)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_read: pitch smaller than a row");
+    }
+    VKRT_CUDA_TRY(ctx, cudaMemcpy2DAsync(dst, pitch, src, row, row, f->height, cudaMemcpyDeviceToHost, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return VKRT_SUCCESS;
+}
+
+void* vkrt_frame_device_bgra8(VkrtFrame* fr)
+{
+    return fr ? F(fr)->bgra8.ptr : nullptr;
+}
+
+int vkrt_trace_rays(VkrtContext* c, const VkrtTlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits)
+{
+    Context* ctx = C(c);
+    if (!tlas || (count && (!rays || !hits)))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    return traceRaysHost(ctx, T(tlas), rays, count, anyHit, hits);
+}
+
+int vkrt_stats_enable(VkrtContext* c, int countTraversal, int timeStages)
+{
+    Context* ctx = C(c);
+    ctx->countTraversal = countTraversal != 0;
+    ctx->timeStages = timeStages != 0;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_stats_reset(VkrtContext* c)
+{
+    Context* ctx = C(c);
+    cudaSetDevice(ctx->device);
+    ctx->stats = VkrtStats{};
+    ctx->launches = 0;
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(ctx->statCounters.ptr, 0, 64, ctx->stream));
+    return VKRT_SUCCESS;
+}
+
+int vkrt_stats_get(VkrtContext* c, VkrtStats* out)
+{
+    Context* ctx = C(c);
+    if (!out)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_stats_get: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    unsigned long long host[8] = {};
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(host, ctx->statCounters.ptr, sizeof(host), cudaMemcpyDeviceToHost, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->stats.raysShadow = host[1];
+    ctx->stats.raysReflection = host[2];
+    ctx->stats.nodesVisited = host[3];
+    ctx->stats.trianglesTested = host[4];
+    ctx->stats.kernelLaunches = ctx->launches;
+    if (ctx->timeStages && ctx->stageEventCount == 11)
+    {
+        auto ms = [&](int a, int b) {
+            float v = 0.f;
+            cudaEventElapsedTime(&v, ctx->stageEvents[a], ctx->stageEvents[b]);
+            return v;
+        };
+        ctx->stats.msRaygen = ms(0, 1);
+        ctx->stats.msTraceClosest = ms(1, 2) + ms(5, 6);
+        ctx->stats.msShade = ms(2, 3) + ms(4, 5) + ms(6, 7) + ms(8, 9);
+        ctx->stats.msTraceAny = ms(3, 4) + ms(7, 8);
+        ctx->stats.msResolve = ms(9, 10);
+        ctx->stats.msTotal = ms(0, 10);
+    }
+    *out = ctx->stats;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_comm_unique_id(uint8_t id[VKRT_UNIQUE_ID_BYTES])
+{
+    std::string err;
+    const int r = commUniqueId(id, err);
+    if (r != VKRT_SUCCESS)
+    {
+        g_createError = err;
+    }
+    return r;
+}
+
+int vkrt_comm_init(VkrtContext* c, const uint8_t id[VKRT_UNIQUE_ID_BYTES], int rank, int size)
+{
+    Context* ctx = C(c);
+    if (size < 1 || rank < 0 || rank >= size || !id)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_comm_init: bad rank/size");
+    }
+    cudaSetDevice(ctx->device);
+    return commInit(ctx, id, rank, size);
+}
+
+int vkrt_comm_emulate(VkrtContext* c, int rank, int size)
+{
+    Context* ctx = C(c);
+    if (size < 1 || rank < 0 || rank >= size)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_comm_emulate: bad rank/size");
+    }
+    ctx->rank = rank;
+    ctx->size = size;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_comm_destroy(VkrtContext* c)
+{
+    return commDestroy(C(c));
+}
+
+int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size)
+{
+    const uint32_t tilesX = (width + kTile - 1) / kTile;
+    const uint32_t tile = (y / kTile) * tilesX + (x / kTile);
+    return size > 0 ? (int)(tile % (uint32_t)size) : 0;
+}
+
+int vkrt_tiles_gather(VkrtContext* c, VkrtFrame* frame, int root)
+{
+    Context* ctx = C(c);
+    if (!frame || root < 0 || root >= ctx->size)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tiles_gather: bad argument");
+    }
+    cudaSetDevice(ctx->device);
+    return gatherTiles(ctx, F(frame), root);
+}
+
+} // extern "C"

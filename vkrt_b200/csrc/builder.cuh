@@ -1,0 +1,476 @@
+// builder.cuh — per-item logic of the GPU BVH builder that replaces vkCmdBuildAccelerationStructuresKHR
+// (src/Raytracer.cpp:1027-1157 createBLAS).  Pipeline (one kernel per step, see bvh_build.cu):
+//
+//   triangle bounds + scene bounds -> 30-bit Morton codes -> LSD radix sort -> agglomerative LBVH with
+//   fused refit (Apetrei 2014) -> greedy surface-area collapse into 8-wide nodes with octant-ordered child
+//   slots -> conservative 8-bit quantisation (80-byte nodes) -> 48-byte packed triangles.
+//
+// Functions are host+device so the logic can be unit-tested by the no-GPU emulation harness (tests/emu).
+#pragma once
+
+#include "common.cuh"
+#include "device_math.cuh"
+
+namespace vkrt
+{
+
+// (geometry, primitive) lookup for a triangle's build index (= position in geometry-major order).
+struct GeometryTable
+{
+    const uint32_t* firstTri;  // geometryCount+1 prefix sums of primitiveCount
+    const uint64_t* indexBase; // geometryCount: first index of the geometry (indexByteOffset / 4)
+    uint32_t geometryCount;
+};
+
+VKRT_HD uint32_t findGeometry(const GeometryTable& g, uint32_t buildIndex)
+{
+    uint32_t lo = 0, hi = g.geometryCount; // invariant: firstTri[lo] <= buildIndex < firstTri[hi]
+    while (hi - lo > 1)
+    {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (g.firstTri[mid] <= buildIndex)
+        {
+            lo = mid;
+        }
+        else
+        {
+            hi = mid;
+        }
+    }
+    return lo;
+}
+
+VKRT_HD void fetchTriangle(const GeometryTable& g, const uint8_t* vertices, uint32_t stride, const uint32_t* indices,
+                           uint32_t buildIndex, F3& v0, F3& v1, F3& v2, uint32_t& geometry, uint32_t& primitive)
+{
+    geometry = findGeometry(g, buildIndex);
+    primitive = buildIndex - g.firstTri[geometry];
+    const uint64_t base = g.indexBase[geometry] + 3ull * primitive;
+    const uint32_t i0 = indices[base + 0], i1 = indices[base + 1], i2 = indices[base + 2];
+    const float* a = reinterpret_cast<const float*>(vertices + (size_t)i0 * stride);
+    const float* b = reinterpret_cast<const float*>(vertices + (size_t)i1 * stride);
+    const float* c = reinterpret_cast<const float*>(vertices + (size_t)i2 * stride);
+    v0 = f3(a[0], a[1], a[2]);
+    v1 = f3(b[0], b[1], b[2]);
+    v2 = f3(c[0], c[1], c[2]);
+}
+
+VKRT_HD uint32_t expandBits10(uint32_t v) // 10 bits -> every third bit
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+// 30-bit Morton code of p inside [lo, lo+extent]; invExtent = 1/extent (0 for flat axes)
+VKRT_HD uint32_t morton30(F3 p, F3 lo, F3 invExtent)
+{
+    const float fx = fminf(fmaxf((p.x - lo.x) * invExtent.x * 1024.0f, 0.0f), 1023.0f);
+    const float fy = fminf(fmaxf((p.y - lo.y) * invExtent.y * 1024.0f, 0.0f), 1023.0f);
+    const float fz = fminf(fmaxf((p.z - lo.z) * invExtent.z * 1024.0f, 0.0f), 1023.0f);
+    return (expandBits10((uint32_t)fx) << 2) | (expandBits10((uint32_t)fy) << 1) | expandBits10((uint32_t)fz);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Binary LBVH (intermediate): N-1 internal nodes, children >= 0 internal, < 0 => ~sortedLeafIndex.
+// lo.w / hi.w carry the first / last sorted leaf index of the subtree (as raw bits).
+// ------------------------------------------------------------------------------------------------
+struct Bvh2
+{
+    int2* children;
+    float4* lo;
+    float4* hi;
+    int* flags;        // init -1; Apetrei range hand-off
+    const uint32_t* keys;  // sorted Morton codes
+    const uint32_t* vals;  // sorted build indices
+    const float4* triLo;   // per build index
+    const float4* triHi;
+    uint32_t count;    // number of leaves
+    int* root;
+};
+
+VKRT_HD uint64_t lbvhDelta(const Bvh2& b, uint32_t j) // distance between sorted leaves j and j+1
+{
+    const uint32_t x = b.keys[j] ^ b.keys[j + 1];
+    return ((uint64_t)x << 32) | (uint64_t)(j ^ (j + 1)); // index bits break ties between equal codes
+}
+
+#if defined(__CUDA_ARCH__)
+#define VKRT_ATOMIC_EXCH(ptr, v) atomicExch((ptr), (v))
+#define VKRT_ATOMIC_ADD(ptr, v) atomicAdd((ptr), (v))
+#define VKRT_FENCE() __threadfence()
+#define VKRT_LOAD_CG_F4(ptr) __ldcg(ptr)
+#else
+template<typename T>
+inline T hostExch(T* p, T v)
+{
+    T o = *p;
+    *p = v;
+    return o;
+}
+template<typename T>
+inline T hostAdd(T* p, T v)
+{
+    T o = *p;
+    *p = o + v;
+    return o;
+}
+#define VKRT_ATOMIC_EXCH(ptr, v) hostExch((ptr), (v))
+#define VKRT_ATOMIC_ADD(ptr, v) hostAdd((ptr), (v))
+#define VKRT_FENCE() ((void)0)
+#define VKRT_LOAD_CG_F4(ptr) (*(ptr))
+#endif
+
+// One thread per sorted leaf: climbs towards the root, the second thread to reach a node merges the boxes.
+VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
+{
+    const uint32_t n = b.count;
+    uint32_t left = leaf, right = leaf;
+    int current = ~(int)leaf;
+    const uint32_t tri = b.vals[leaf];
+    float4 lo = b.triLo[tri], hi = b.triHi[tri];
+    for (;;)
+    {
+        uint32_t parent;
+        int prev;
+        bool isLeftChild;
+        if (left == 0 || (right != n - 1 && lbvhDelta(b, right) < lbvhDelta(b, left - 1)))
+        {
+            parent = right;
+            isLeftChild = true;
+            b.children[parent].x = current;
+            VKRT_FENCE();
+            prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)left);
+            if (prev != -1)
+            {
+                right = (uint32_t)prev;
+            }
+        }
+        else
+        {
+            parent = left - 1;
+            isLeftChild = false;
+            b.children[parent].y = current;
+            VKRT_FENCE();
+            prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)right);
+            if (prev != -1)
+            {
+                left = (uint32_t)prev;
+            }
+        }
+        if (prev == -1)
+        {
+            return; // first to arrive: the sibling's thread finishes this node
+        }
+        VKRT_FENCE();
+        // fetch the sibling's box (written before its fence)
+        const int sibling = isLeftChild ? ((volatile int2*)b.children)[parent].y : ((volatile int2*)b.children)[parent].x;
+        float4 slo, shi;
+        if (sibling < 0)
+        {
+            const uint32_t st = b.vals[~sibling];
+            slo = b.triLo[st];
+            shi = b.triHi[st];
+        }
+        else
+        {
+            slo = VKRT_LOAD_CG_F4(&b.lo[sibling]);
+            shi = VKRT_LOAD_CG_F4(&b.hi[sibling]);
+        }
+        lo.x = fminf(lo.x, slo.x), lo.y = fminf(lo.y, slo.y), lo.z = fminf(lo.z, slo.z);
+        hi.x = fmaxf(hi.x, shi.x), hi.y = fmaxf(hi.y, shi.y), hi.z = fmaxf(hi.z, shi.z);
+        lo.w = uintAsFloat(left);
+        hi.w = uintAsFloat(right);
+        b.lo[parent] = lo;
+        b.hi[parent] = hi;
+        current = (int)parent;
+        if (left == 0 && right == n - 1)
+        {
+            *b.root = current;
+            return;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Collapse to 8-wide nodes
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kMaxLeafTris = 3; // a child slot references at most 3 triangles (unary count in 3 bits)
+
+struct CollapseArgs
+{
+    Bvh2 bvh2;
+    Node8* nodes;
+    int* taskRef;          // per wide node: the binary subtree it covers (ref encoding as Bvh2 children)
+    uint32_t* primSource;  // per packed-triangle slot: build index of the triangle to pack there
+    uint32_t* nodeCounter; // next free wide node index
+    uint32_t* primCounter; // next free packed-triangle slot
+    float* sahAccum;       // [0] += area(node) (internal cost), [1] += area(leaf)*count
+    uint32_t nodeCapacity;
+    uint32_t* overflow;
+};
+
+struct CollapseChild
+{
+    int ref;
+    F3 lo, hi;
+    uint32_t first, count;
+};
+
+VKRT_HD CollapseChild collapseFetch(const Bvh2& b, int ref)
+{
+    CollapseChild c;
+    c.ref = ref;
+    if (ref < 0)
+    {
+        const uint32_t leaf = (uint32_t)~ref;
+        const uint32_t tri = b.vals[leaf];
+        const float4 lo = b.triLo[tri], hi = b.triHi[tri];
+        c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
+        c.first = leaf, c.count = 1;
+    }
+    else
+    {
+        const float4 lo = b.lo[ref], hi = b.hi[ref];
+        c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
+        c.first = floatAsUint(lo.w);
+        c.count = floatAsUint(hi.w) - c.first + 1;
+    }
+    return c;
+}
+
+VKRT_HD float halfArea(F3 lo, F3 hi)
+{
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// Smallest biased exponent byte e such that lo + 255 * 2^(e-127) >= hi (evaluated in float, as traversal decodes it)
+VKRT_HD uint32_t quantExponent(float lo, float hi)
+{
+    const float extent = hi - lo;
+    if (!(extent > 0.0f))
+    {
+        return 1u;
+    }
+    int ex;
+    frexpf(extent / 255.0f, &ex); // extent/255 = m * 2^ex, m in [0.5,1) -> 2^ex >= extent/255
+    int e = ex + 127;
+    e = e < 1 ? 1 : (e > 254 ? 254 : e);
+    while (e < 254 && !(lo + 255.0f * uintAsFloat((uint32_t)e << 23) >= hi))
+    {
+        ++e;
+    }
+    return (uint32_t)e;
+}
+
+VKRT_HD uint32_t quantLo(float v, float origin, float scale)
+{
+    float q = floorf((v - origin) / scale);
+    q = fminf(fmaxf(q, 0.0f), 255.0f);
+    uint32_t qi = (uint32_t)q;
+    while (qi > 0 && origin + (float)qi * scale > v)
+    {
+        --qi;
+    }
+    return qi;
+}
+VKRT_HD uint32_t quantHi(float v, float origin, float scale)
+{
+    float q = ceilf((v - origin) / scale);
+    q = fminf(fmaxf(q, 0.0f), 255.0f);
+    uint32_t qi = (uint32_t)q;
+    while (qi < 255 && origin + (float)qi * scale < v)
+    {
+        ++qi;
+    }
+    return qi;
+}
+
+// Builds wide node `wideIndex` from the binary subtree taskRef[wideIndex].
+VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex)
+{
+    const Bvh2& b = a.bvh2;
+    const int rootRef = a.taskRef[wideIndex];
+    const CollapseChild self = collapseFetch(b, rootRef);
+
+    CollapseChild c[8];
+    int n = 0;
+    if (rootRef < 0 || self.count <= kMaxLeafTris)
+    {
+        // whole BLAS has <= 3 triangles: the root holds one leaf child
+        c[0] = self;
+        n = 1;
+    }
+    else
+    {
+        c[0] = collapseFetch(b, b.children[rootRef].x);
+        c[1] = collapseFetch(b, b.children[rootRef].y);
+        n = 2;
+        while (n < 8)
+        {
+            int pick = -1;
+            float bestArea = -1.0f;
+            for (int k = 0; k < n; ++k)
+            {
+                if (c[k].count > kMaxLeafTris)
+                {
+                    const float ar = halfArea(c[k].lo, c[k].hi);
+                    if (ar > bestArea)
+                    {
+                        bestArea = ar;
+                        pick = k;
+                    }
+                }
+            }
+            if (pick < 0)
+            {
+                break;
+            }
+            const int2 ch = b.children[c[pick].ref];
+            c[pick] = collapseFetch(b, ch.x);
+            c[n++] = collapseFetch(b, ch.y);
+        }
+    }
+
+    // octant-ordered slot assignment: slot s suits children lying towards corner (s&1 ? +x : -x, ...)
+    const F3 centre = f3(0.5f * (self.lo.x + self.hi.x), 0.5f * (self.lo.y + self.hi.y), 0.5f * (self.lo.z + self.hi.z));
+    int slotOf[8];
+    bool slotUsed[8];
+    bool childDone[8];
+    for (int k = 0; k < 8; ++k)
+    {
+        slotOf[k] = -1;
+        slotUsed[k] = false;
+        childDone[k] = false;
+    }
+    for (int iter = 0; iter < n; ++iter)
+    {
+        float bestCost = -INFINITY;
+        int bc = -1, bs = -1;
+        for (int k = 0; k < n; ++k)
+        {
+            if (childDone[k])
+            {
+                continue;
+            }
+            const float cx = 0.5f * (c[k].lo.x + c[k].hi.x) - centre.x;
+            const float cy = 0.5f * (c[k].lo.y + c[k].hi.y) - centre.y;
+            const float cz = 0.5f * (c[k].lo.z + c[k].hi.z) - centre.z;
+            for (int s = 0; s < 8; ++s)
+            {
+                if (slotUsed[s])
+                {
+                    continue;
+                }
+                const float cost = ((s & 1) ? cx : -cx) + ((s & 2) ? cy : -cy) + ((s & 4) ? cz : -cz);
+                if (cost > bestCost)
+                {
+                    bestCost = cost, bc = k, bs = s;
+                }
+            }
+        }
+        slotOf[bc] = bs;
+        slotUsed[bs] = true;
+        childDone[bc] = true;
+    }
+    int childInSlot[8];
+    for (int s = 0; s < 8; ++s)
+    {
+        childInSlot[s] = -1;
+    }
+    for (int k = 0; k < n; ++k)
+    {
+        childInSlot[slotOf[k]] = k;
+    }
+
+    uint32_t innerCount = 0, primCount = 0;
+    for (int k = 0; k < n; ++k)
+    {
+        if (c[k].count > kMaxLeafTris)
+        {
+            ++innerCount;
+        }
+        else
+        {
+            primCount += c[k].count;
+        }
+    }
+    const uint32_t childBase = innerCount ? VKRT_ATOMIC_ADD(a.nodeCounter, innerCount) : 0u;
+    const uint32_t primBase = primCount ? VKRT_ATOMIC_ADD(a.primCounter, primCount) : 0u;
+    if (childBase + innerCount > a.nodeCapacity)
+    {
+        *a.overflow = 1u;
+        return;
+    }
+
+    Node8 node;
+    node.px = self.lo.x, node.py = self.lo.y, node.pz = self.lo.z;
+    const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
+                   ez = quantExponent(self.lo.z, self.hi.z);
+    node.ex = (uint8_t)ex, node.ey = (uint8_t)ey, node.ez = (uint8_t)ez;
+    const float sx = uintAsFloat(ex << 23), sy = uintAsFloat(ey << 23), sz = uintAsFloat(ez << 23);
+    node.imask = 0;
+    node.childBase = childBase;
+    node.primBase = primBase;
+    uint32_t innerSeen = 0, primOffset = 0;
+    float leafArea = 0.0f;
+    for (int s = 0; s < 8; ++s)
+    {
+        const int k = childInSlot[s];
+        if (k < 0)
+        {
+            node.meta[s] = 0;
+            node.qlox[s] = node.qloy[s] = node.qloz[s] = 0;
+            node.qhix[s] = node.qhiy[s] = node.qhiz[s] = 0;
+            continue;
+        }
+        node.qlox[s] = (uint8_t)quantLo(c[k].lo.x, self.lo.x, sx);
+        node.qloy[s] = (uint8_t)quantLo(c[k].lo.y, self.lo.y, sy);
+        node.qloz[s] = (uint8_t)quantLo(c[k].lo.z, self.lo.z, sz);
+        node.qhix[s] = (uint8_t)quantHi(c[k].hi.x, self.lo.x, sx);
+        node.qhiy[s] = (uint8_t)quantHi(c[k].hi.y, self.lo.y, sy);
+        node.qhiz[s] = (uint8_t)quantHi(c[k].hi.z, self.lo.z, sz);
+        if (c[k].count > kMaxLeafTris)
+        {
+            node.imask |= (uint8_t)(1u << s);
+            node.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
+            a.taskRef[childBase + innerSeen] = c[k].ref;
+            ++innerSeen;
+        }
+        else
+        {
+            const uint32_t unary = (1u << c[k].count) - 1u; // 1 -> 001, 2 -> 011, 3 -> 111
+            node.meta[s] = (uint8_t)((unary << 5) | primOffset);
+            for (uint32_t j = 0; j < c[k].count; ++j)
+            {
+                a.primSource[primBase + primOffset + j] = b.vals[c[k].first + j];
+            }
+            primOffset += c[k].count;
+            leafArea += halfArea(c[k].lo, c[k].hi) * (float)c[k].count;
+        }
+    }
+    a.nodes[wideIndex] = node;
+    if (a.sahAccum)
+    {
+        VKRT_ATOMIC_ADD(&a.sahAccum[0], halfArea(self.lo, self.hi));
+        VKRT_ATOMIC_ADD(&a.sahAccum[1], leafArea);
+    }
+}
+
+VKRT_HD PackedTri packTriangle(const GeometryTable& g, const uint8_t* vertices, uint32_t stride, const uint32_t* indices,
+                               uint32_t buildIndex)
+{
+    F3 v0, v1, v2;
+    PackedTri t;
+    fetchTriangle(g, vertices, stride, indices, buildIndex, v0, v1, v2, t.geometry, t.primitive);
+    t.v0x = v0.x, t.v0y = v0.y, t.v0z = v0.z;
+    t.v1x = v1.x, t.v1y = v1.y, t.v1z = v1.z;
+    t.v2x = v2.x, t.v2y = v2.y, t.v2z = v2.z;
+    t.buildIndex = buildIndex;
+    return t;
+}
+
+} // namespace vkrt

@@ -1,0 +1,556 @@
+// bvh_build.cu — GPU BVH builder kernels and their host driver.
+// Replaces Raytracer::createBLAS / vkCmdBuildAccelerationStructuresKHR (src/Raytracer.cpp:1027-1157).
+//
+// HBM-bound integer/byte work: kernels are sized in multiples of the SM count where they are grid-stride,
+// all per-triangle streams are coalesced 4/16-byte accesses, the sort stages tiles through shared memory.
+#include "builder.cuh"
+#include "context.hpp"
+
+#include <algorithm>
+#include <cfloat>
+
+namespace vkrt
+{
+
+namespace
+{
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ uint32_t orderedFromFloat(float f)
+{
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float floatFromOrdered(uint32_t o)
+{
+    const uint32_t u = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+
+// sceneBounds: 12 ordered uints — [0..2] min of triangle boxes, [3..5] max, [6..8] centroid min, [9..11] centroid max
+__global__ void k_init_build(uint32_t* sceneBounds, uint32_t* counters, float* sahAccum, int* root)
+{
+    const int i = threadIdx.x;
+    if (i < 12)
+    {
+        const bool isMin = (i < 3) || (i >= 6 && i < 9);
+        sceneBounds[i] = isMin ? 0xFFFFFFFFu : 0u;
+    }
+    if (i < 8)
+    {
+        counters[i] = 0u;
+    }
+    if (i < 2)
+    {
+        sahAccum[i] = 0.0f;
+    }
+    if (i == 0)
+    {
+        *root = 0;
+    }
+}
+
+__device__ __forceinline__ float warpMin(float v)
+{
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        v = fminf(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+    }
+    return v;
+}
+__device__ __forceinline__ float warpMax(float v)
+{
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        v = fmaxf(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+    }
+    return v;
+}
+
+// Per-triangle AABB + reduction of the scene and centroid bounds (warp shuffle -> one atomic per warp).
+__global__ void __launch_bounds__(kThreads)
+k_tri_bounds(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t stride, const uint32_t* __restrict__ indices,
+             uint32_t count, float4* __restrict__ triLo, float4* __restrict__ triHi, uint32_t* sceneBounds)
+{
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        F3 v0, v1, v2;
+        uint32_t g, p;
+        fetchTriangle(geo, vertices, stride, indices, i, v0, v1, v2, g, p);
+        const float4 l = make_float4(fminf(fminf(v0.x, v1.x), v2.x), fminf(fminf(v0.y, v1.y), v2.y),
+                                     fminf(fminf(v0.z, v1.z), v2.z), 0.0f);
+        const float4 h = make_float4(fmaxf(fmaxf(v0.x, v1.x), v2.x), fmaxf(fmaxf(v0.y, v1.y), v2.y),
+                                     fmaxf(fmaxf(v0.z, v1.z), v2.z), 0.0f);
+        triLo[i] = l;
+        triHi[i] = h;
+        const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
+        lo[0] = fminf(lo[0], l.x), lo[1] = fminf(lo[1], l.y), lo[2] = fminf(lo[2], l.z);
+        hi[0] = fmaxf(hi[0], h.x), hi[1] = fmaxf(hi[1], h.y), hi[2] = fmaxf(hi[2], h.z);
+        for (int k = 0; k < 3; ++k)
+        {
+            clo[k] = fminf(clo[k], c[k]);
+            chi[k] = fmaxf(chi[k], c[k]);
+        }
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        const float a = warpMin(lo[k]), b = warpMax(hi[k]), c = warpMin(clo[k]), d = warpMax(chi[k]);
+        if ((threadIdx.x & 31) == 0)
+        {
+            atomicMin(&sceneBounds[k], orderedFromFloat(a));
+            atomicMax(&sceneBounds[3 + k], orderedFromFloat(b));
+            atomicMin(&sceneBounds[6 + k], orderedFromFloat(c));
+            atomicMax(&sceneBounds[9 + k], orderedFromFloat(d));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_morton(const float4* __restrict__ triLo, const float4* __restrict__ triHi, const uint32_t* __restrict__ sceneBounds,
+         uint32_t count, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    const F3 lo = f3(floatFromOrdered(sceneBounds[6]), floatFromOrdered(sceneBounds[7]), floatFromOrdered(sceneBounds[8]));
+    const F3 hi = f3(floatFromOrdered(sceneBounds[9]), floatFromOrdered(sceneBounds[10]), floatFromOrdered(sceneBounds[11]));
+    const F3 inv = f3(hi.x > lo.x ? 1.0f / (hi.x - lo.x) : 0.0f, hi.y > lo.y ? 1.0f / (hi.y - lo.y) : 0.0f,
+                      hi.z > lo.z ? 1.0f / (hi.z - lo.z) : 0.0f);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const float4 l = triLo[i], h = triHi[i];
+        const F3 c = f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z));
+        keys[i] = morton30(c, lo, inv);
+        vals[i] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LSD radix sort, 8-bit digits, key-value (u32,u32).  Per pass: tile histograms -> exclusive scan ->
+// stable scatter (warp-level match ranking).  Tiles of 4096 keys, 256 threads, 16 keys per thread.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kThreads * kSortItems; // 4096
+constexpr int kSortWarps = kThreads / 32;
+
+__global__ void __launch_bounds__(kThreads)
+k_sort_hist(const uint32_t* __restrict__ keys, uint32_t count, uint32_t shift, uint32_t numTiles, uint32_t* __restrict__ tileHist)
+{
+    __shared__ uint32_t hist[256];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kSortTile;
+#pragma unroll 4
+    for (int j = 0; j < kSortItems; ++j)
+    {
+        const uint32_t idx = base + j * kThreads + threadIdx.x;
+        if (idx < count)
+        {
+            atomicAdd(&hist[(keys[idx] >> shift) & 0xFFu], 1u);
+        }
+    }
+    __syncthreads();
+    tileHist[threadIdx.x * numTiles + blockIdx.x] = hist[threadIdx.x]; // digit-major: one scan gives global offsets
+}
+
+// Single-block exclusive scan (1024 threads, contiguous chunk per thread).
+__global__ void __launch_bounds__(1024) k_exclusive_scan(uint32_t* data, uint32_t count)
+{
+    __shared__ uint32_t warpSums[32];
+    __shared__ uint32_t carry;
+    const uint32_t chunk = (count + 1023u) / 1024u;
+    const uint32_t begin = min(count, threadIdx.x * chunk), end = min(count, begin + chunk);
+    uint32_t sum = 0;
+    for (uint32_t i = begin; i < end; ++i)
+    {
+        sum += data[i];
+    }
+    // block exclusive scan of `sum`
+    uint32_t incl = sum;
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if ((threadIdx.x & 31) >= o)
+        {
+            incl += v;
+        }
+    }
+    if ((threadIdx.x & 31) == 31)
+    {
+        warpSums[threadIdx.x >> 5] = incl;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32)
+    {
+        uint32_t w = warpSums[threadIdx.x];
+        uint32_t wi = w;
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+            if (threadIdx.x >= o)
+            {
+                wi += v;
+            }
+        }
+        warpSums[threadIdx.x] = wi - w;
+        if (threadIdx.x == 31)
+        {
+            carry = wi;
+        }
+    }
+    __syncthreads();
+    uint32_t run = warpSums[threadIdx.x >> 5] + (incl - sum);
+    for (uint32_t i = begin; i < end; ++i)
+    {
+        const uint32_t v = data[i];
+        data[i] = run;
+        run += v;
+    }
+    (void)carry;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_sort_scatter(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn, uint32_t count, uint32_t shift,
+               uint32_t numTiles, const uint32_t* __restrict__ tileOffsets, uint32_t* __restrict__ keysOut,
+               uint32_t* __restrict__ valsOut)
+{
+    __shared__ uint32_t warpHist[kSortWarps][256];
+    __shared__ uint32_t digitBase[256];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (int w = 0; w < kSortWarps; ++w)
+    {
+        warpHist[w][threadIdx.x] = 0;
+    }
+    digitBase[threadIdx.x] = tileOffsets[threadIdx.x * numTiles + blockIdx.x];
+    __syncthreads();
+
+    // warp-striped: warp w owns 512 consecutive keys; item j, lane l -> key w*512 + j*32 + l (stable order)
+    const uint32_t base = blockIdx.x * kSortTile + warp * (32 * kSortItems);
+    uint32_t key[kSortItems], rank[kSortItems];
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int j = 0; j < kSortItems; ++j)
+    {
+        const uint32_t idx = base + j * 32 + lane;
+        const bool valid = idx < count;
+        key[j] = valid ? keysIn[idx] : 0xFFFFFFFFu;
+        const uint32_t digit = (key[j] >> shift) & 0xFFu;
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, valid ? digit : 0x100u);
+        const uint32_t leader = __ffs(peers) - 1;
+        uint32_t pre = 0;
+        if (valid && lane == leader)
+        {
+            pre = warpHist[warp][digit];
+            warpHist[warp][digit] = pre + __popc(peers);
+        }
+        pre = __shfl_sync(0xFFFFFFFFu, pre, leader);
+        rank[j] = pre + __popc(peers & lt);
+        __syncwarp();
+    }
+    __syncthreads();
+    // per digit: exclusive prefix over the warps of this tile
+    {
+        uint32_t run = 0;
+        for (int w = 0; w < kSortWarps; ++w)
+        {
+            const uint32_t v = warpHist[w][threadIdx.x];
+            warpHist[w][threadIdx.x] = run;
+            run += v;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kSortItems; ++j)
+    {
+        const uint32_t idx = base + j * 32 + lane;
+        if (idx < count)
+        {
+            const uint32_t digit = (key[j] >> shift) & 0xFFu;
+            const uint32_t dst = digitBase[digit] + warpHist[warp][digit] + rank[j];
+            keysOut[dst] = key[j];
+            valsOut[dst] = valsIn[idx];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_fill_i32(int* data, uint32_t count, int value)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        data[i] = value;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < bvh.count)
+    {
+        lbvhClimb(bvh, i);
+    }
+}
+
+__global__ void k_collapse_seed(CollapseArgs a)
+{
+    a.taskRef[0] = a.bvh2.count > 1 ? *a.bvh2.root : ~0;
+    *a.nodeCounter = 1u;
+    *a.primCounter = 0u;
+}
+
+__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a, uint32_t first, uint32_t last)
+{
+    const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < last)
+    {
+        collapseNode(a, i);
+    }
+}
+
+__global__ void k_empty_root(Node8* nodes)
+{
+    Node8 n;
+    memset(&n, 0, sizeof(n));
+    n.ex = n.ey = n.ez = 1;
+    nodes[0] = n;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_pack_tris(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t stride, const uint32_t* __restrict__ indices,
+            const uint32_t* __restrict__ primSource, uint32_t count, PackedTri* __restrict__ out)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const PackedTri t = packTriangle(geo, vertices, stride, indices, primSource[i]);
+        float4* dst = reinterpret_cast<float4*>(out + i);
+        dst[0] = make_float4(t.v0x, t.v0y, t.v0z, t.v1x);
+        dst[1] = make_float4(t.v1y, t.v1z, t.v2x, t.v2y);
+        dst[2] = make_float4(t.v2z, __uint_as_float(t.geometry), __uint_as_float(t.primitive), __uint_as_float(t.buildIndex));
+    }
+}
+
+inline uint32_t gridFor(uint32_t count, int threads, int smCount)
+{
+    const uint32_t blocks = (count + threads - 1) / threads;
+    const uint32_t cap = (uint32_t)smCount * 16u; // grid-stride kernels: a whole number of waves
+    return std::max(1u, std::min(blocks, cap));
+}
+} // namespace
+
+// Sorts (keys, vals) by key; result ends in keysA/valsA (4 passes ping-pong A->B->A->B->A).
+static int radixSort(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* tileHist,
+                     uint32_t count)
+{
+    const uint32_t numTiles = (count + kSortTile - 1) / kSortTile;
+    uint32_t *kin = keysA, *vin = valsA, *kout = keysB, *vout = valsB;
+    for (uint32_t pass = 0; pass < 4; ++pass)
+    {
+        const uint32_t shift = pass * 8;
+        k_sort_hist<<<numTiles, kThreads, 0, ctx->stream>>>(kin, count, shift, numTiles, tileHist);
+        k_exclusive_scan<<<1, 1024, 0, ctx->stream>>>(tileHist, 256u * numTiles);
+        k_sort_scatter<<<numTiles, kThreads, 0, ctx->stream>>>(kin, vin, count, shift, numTiles, tileHist, kout, vout);
+        ctx->launches += 3;
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    VKRT_CUDA_TRY(ctx, cudaGetLastError());
+    return VKRT_SUCCESS;
+}
+
+// Debug entry used by the tests: sorts host arrays on the device with the builder's sort.
+int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count)
+{
+    if (count == 0)
+    {
+        return VKRT_SUCCESS;
+    }
+    DeviceBuffer a, b, c, d, h;
+    const uint32_t numTiles = (count + kSortTile - 1) / kSortTile;
+    VKRT_CUDA_TRY(ctx, a.reserve(count * 4ull));
+    VKRT_CUDA_TRY(ctx, b.reserve(count * 4ull));
+    VKRT_CUDA_TRY(ctx, c.reserve(count * 4ull));
+    VKRT_CUDA_TRY(ctx, d.reserve(count * 4ull));
+    VKRT_CUDA_TRY(ctx, h.reserve(256ull * numTiles * 4ull));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(a.ptr, keys, count * 4ull, cudaMemcpyHostToDevice, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(b.ptr, vals, count * 4ull, cudaMemcpyHostToDevice, ctx->stream));
+    int r = radixSort(ctx, a.as<uint32_t>(), b.as<uint32_t>(), c.as<uint32_t>(), d.as<uint32_t>(), h.as<uint32_t>(), count);
+    if (r == VKRT_SUCCESS)
+    {
+        cudaMemcpyAsync(keys, a.ptr, count * 4ull, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaMemcpyAsync(vals, b.ptr, count * 4ull, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess)
+        {
+            r = ctx->fail(VKRT_ERROR_CUDA, cudaGetErrorString(e));
+        }
+    }
+    a.release(), b.release(), c.release(), d.release(), h.release();
+    return r;
+}
+
+// Runs the whole builder over the BLAS's device geometry copy.
+int buildBlasOnDevice(Context* ctx, Blas* blas)
+{
+    const uint32_t n = blas->triangleCount;
+    cudaStream_t s = ctx->stream;
+    const int sm = ctx->smCount;
+
+    cudaEvent_t ev0, ev1;
+    VKRT_CUDA_TRY(ctx, cudaEventCreate(&ev0));
+    VKRT_CUDA_TRY(ctx, cudaEventCreate(&ev1));
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(ev0, s));
+
+    // node capacity: every wide node with internal children covers > 3 triangles per child
+    const uint32_t nodeCapacity = std::max(1u, n / 2u + 8u);
+    VKRT_CUDA_TRY(ctx, blas->nodes.reserve((size_t)nodeCapacity * sizeof(Node8)));
+    VKRT_CUDA_TRY(ctx, blas->tris.reserve(std::max<size_t>(1, n) * sizeof(PackedTri)));
+
+    // scratch layout
+    BuildScratch& sc = ctx->buildScratch;
+    const size_t n1 = std::max<size_t>(n, 1);
+    const uint32_t numTiles = (uint32_t)((n1 + kSortTile - 1) / kSortTile);
+    VKRT_CUDA_TRY(ctx, sc.triLo.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.triHi.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.keysA.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.keysB.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.valsA.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.valsB.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(256ull * numTiles * 4));
+    VKRT_CUDA_TRY(ctx, sc.children.reserve(n1 * sizeof(int2)));
+    VKRT_CUDA_TRY(ctx, sc.nodeLo.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.nodeHi.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.flags.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.taskRef.reserve((size_t)nodeCapacity * 4));
+    VKRT_CUDA_TRY(ctx, sc.primSource.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.small.reserve(256));
+
+    uint32_t* sceneBounds = sc.small.as<uint32_t>();           // 12 uints
+    uint32_t* counters = sc.small.as<uint32_t>() + 16;         // [0] nodes, [1] prims, [2] overflow
+    float* sahAccum = reinterpret_cast<float*>(sc.small.as<uint32_t>() + 32);
+    int* root = reinterpret_cast<int*>(sc.small.as<uint32_t>() + 40);
+
+    k_init_build<<<1, 32, 0, s>>>(sceneBounds, counters, sahAccum, root);
+    ctx->launches += 1;
+
+    GeometryTable geo;
+    geo.firstTri = blas->geomFirstTri.as<uint32_t>();
+    geo.indexBase = blas->geomIndexBase.as<uint64_t>();
+    geo.geometryCount = blas->geometryCount;
+    const uint8_t* vertices = blas->vertices.as<uint8_t>();
+    const uint32_t* indices = blas->indices.as<uint32_t>();
+
+    if (n == 0)
+    {
+        k_empty_root<<<1, 1, 0, s>>>(blas->nodes.as<Node8>());
+        ctx->launches += 1;
+        blas->nodeCount = 1;
+        for (int k = 0; k < 3; ++k)
+        {
+            blas->boundsMin[k] = 0.0f;
+            blas->boundsMax[k] = 0.0f;
+        }
+        blas->sahCost = 0.0f;
+    }
+    else
+    {
+        k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices, n,
+                                                                      sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds);
+        k_morton<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds, n,
+                                                                  sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>());
+        ctx->launches += 2;
+        int r = radixSort(ctx, sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(), sc.keysB.as<uint32_t>(),
+                          sc.valsB.as<uint32_t>(), sc.tileHist.as<uint32_t>(), n);
+        if (r != VKRT_SUCCESS)
+        {
+            return r;
+        }
+
+        Bvh2 bvh;
+        bvh.children = sc.children.as<int2>();
+        bvh.lo = sc.nodeLo.as<float4>();
+        bvh.hi = sc.nodeHi.as<float4>();
+        bvh.flags = sc.flags.as<int>();
+        bvh.keys = sc.keysA.as<uint32_t>();
+        bvh.vals = sc.valsA.as<uint32_t>();
+        bvh.triLo = sc.triLo.as<float4>();
+        bvh.triHi = sc.triHi.as<float4>();
+        bvh.count = n;
+        bvh.root = root;
+        if (n > 1)
+        {
+            k_fill_i32<<<gridFor(n - 1, kThreads, sm), kThreads, 0, s>>>(bvh.flags, n - 1, -1);
+            k_lbvh<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+            ctx->launches += 2;
+        }
+
+        CollapseArgs ca;
+        ca.bvh2 = bvh;
+        ca.nodes = blas->nodes.as<Node8>();
+        ca.taskRef = sc.taskRef.as<int>();
+        ca.primSource = sc.primSource.as<uint32_t>();
+        ca.nodeCounter = counters + 0;
+        ca.primCounter = counters + 1;
+        ca.overflow = counters + 2;
+        ca.sahAccum = sahAccum;
+        ca.nodeCapacity = nodeCapacity;
+        k_collapse_seed<<<1, 1, 0, s>>>(ca);
+        ctx->launches += 1;
+        // level-synchronous collapse: wide nodes [first,last) were allocated by the previous level
+        uint32_t first = 0, last = 1;
+        while (first < last)
+        {
+            const uint32_t cnt = last - first;
+            k_collapse_level<<<(cnt + 127) / 128, 128, 0, s>>>(ca, first, last);
+            ctx->launches += 1;
+            uint32_t hostCounters[3];
+            VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
+            VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+            if (hostCounters[2])
+            {
+                return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "BVH collapse: wide node capacity exceeded");
+            }
+            first = last;
+            last = hostCounters[0];
+            if (first == last && hostCounters[1] != n)
+            {
+                return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: packed " + std::to_string(hostCounters[1]) + " of " +
+                                                      std::to_string(n) + " triangles");
+            }
+        }
+        blas->nodeCount = last;
+        k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices,
+                                                                     sc.primSource.as<uint32_t>(), n, blas->tris.as<PackedTri>());
+        ctx->launches += 1;
+
+        uint32_t hb[12];
+        float hs[2];
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hb, sceneBounds, sizeof(hb), cudaMemcpyDeviceToHost, s));
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hs, sahAccum, sizeof(hs), cudaMemcpyDeviceToHost, s));
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+        for (int k = 0; k < 3; ++k)
+        {
+            blas->boundsMin[k] = floatFromOrdered(hb[k]);
+            blas->boundsMax[k] = floatFromOrdered(hb[3 + k]);
+        }
+        const float dx = blas->boundsMax[0] - blas->boundsMin[0], dy = blas->boundsMax[1] - blas->boundsMin[1],
+                    dz = blas->boundsMax[2] - blas->boundsMin[2];
+        const float rootArea = dx * dy + dy * dz + dz * dx;
+        blas->sahCost = rootArea > 0.0f ? (hs[0] + hs[1]) / rootArea : 0.0f;
+    }
+
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(ev1, s));
+    VKRT_CUDA_TRY(ctx, cudaEventSynchronize(ev1));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    blas->buildMs = ms;
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    VKRT_CUDA_TRY(ctx, cudaGetLastError());
+    return VKRT_SUCCESS;
+}
+
+} // namespace vkrt

@@ -1,0 +1,144 @@
+// common.cuh — shared types of libvkrt_b200 (device layouts, error plumbing, small math).
+//
+// Everything on the parity path is FP32 with a FIXED evaluation order and NO implicit FMA
+// contraction (the library is compiled with -fmad=false); explicit __fmaf_rn is used only where
+// results need to be conservative rather than bit-equal to the CPU oracle (box tests).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/vkrt.h"
+
+namespace vkrt
+{
+
+// ---------------------------------------------------------------------------------------------
+// Device data layouts
+// ---------------------------------------------------------------------------------------------
+
+// Compressed 8-wide BVH node, 80 bytes (Ylitie, Karras, Laine 2017, "Efficient Incoherent Ray Traversal on
+// GPUs Through Compressed Wide BVHs").  Loaded as five 16-byte vectors.
+struct alignas(16) Node8
+{
+    float px, py, pz;     // quantisation origin (node box minimum)
+    uint8_t ex, ey, ez;   // per-axis scale exponents (biased IEEE exponent bytes: scale = 2^(e-127))
+    uint8_t imask;        // bit s set: slot s holds an internal child
+    uint32_t childBase;   // index of the first internal child node
+    uint32_t primBase;    // index of the first primitive (packed triangle or instance) of this node
+    uint8_t meta[8];      // per slot: 0 empty | internal: 0b001xxxxx (low5 = 24+slot) | leaf: unary count<<5 | offset
+    uint8_t qlox[8], qloy[8], qloz[8];
+    uint8_t qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
+
+// Packed triangle, 48 bytes: raw vertex positions (the watertight test needs all three) + Vulkan ids.
+struct alignas(16) PackedTri
+{
+    float v0x, v0y, v0z;
+    float v1x, v1y, v1z;
+    float v2x, v2y, v2z;
+    uint32_t geometry;   // gl_GeometryIndexEXT
+    uint32_t primitive;  // gl_PrimitiveID
+    uint32_t buildIndex; // position in (geometry, primitive) order; tie-break key for equal-t hits
+};
+static_assert(sizeof(PackedTri) == 48, "PackedTri must be 48 bytes");
+
+// Per-instance record used by traversal (w2o) and shading (o2w, geometry pointers).
+struct alignas(16) InstanceRecord
+{
+    float w2o[12];
+    float o2w[12];
+    const Node8* nodes;
+    const PackedTri* tris;
+    const uint8_t* vertices; // device copy of the vertex buffer (stride bytes per vertex)
+    const uint32_t* indices; // device copy of the (global) index buffer
+    uint32_t vertexStride;
+    uint32_t pad[3];
+};
+
+struct TextureRecord
+{
+    const uint8_t* texels; // RGBA8 rows
+    uint32_t width, height;
+};
+
+// Hit record written by the closest-hit traversal.
+struct HitRecord
+{
+    float t, b1, b2;
+    uint32_t tri;      // index into the instance's packed triangle array, 0xFFFFFFFF = miss
+    uint32_t instance; // index into the TLAS instance array
+};
+
+constexpr uint32_t kInvalid = 0xFFFFFFFFu;
+constexpr float kRayTMin = 0.001f;    // shaders/shader.rgen:58, shader.rchit:139
+constexpr float kRayTMax = 1000.0f;   // shaders/shader.rgen:60
+constexpr int kTile = VKRT_TILE_SIZE; // multi-GPU image tile edge in pixels
+constexpr int kTilePixels = kTile * kTile;
+
+// ---------------------------------------------------------------------------------------------
+// Error plumbing
+// ---------------------------------------------------------------------------------------------
+struct Error
+{
+    int code;
+    std::string text;
+};
+
+#define VKRT_CUDA_TRY(ctx, expr)                                                                            \
+    do                                                                                                      \
+    {                                                                                                       \
+        cudaError_t err__ = (expr);                                                                         \
+        if (err__ != cudaSuccess)                                                                           \
+        {                                                                                                   \
+            return (ctx)->fail(err__ == cudaErrorMemoryAllocation ? VKRT_ERROR_OUT_OF_MEMORY : VKRT_ERROR_CUDA, \
+                               std::string(#expr) + ": " + cudaGetErrorString(err__));                      \
+        }                                                                                                   \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Device buffer with grow-only capacity (library-owned scratch, reused across frames/rebuilds)
+// ---------------------------------------------------------------------------------------------
+struct DeviceBuffer
+{
+    void* ptr = nullptr;
+    size_t capacity = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= capacity)
+        {
+            return cudaSuccess;
+        }
+        if (ptr)
+        {
+            cudaFree(ptr);
+            ptr = nullptr;
+            capacity = 0;
+        }
+        cudaError_t e = cudaMalloc(&ptr, bytes);
+        if (e == cudaSuccess)
+        {
+            capacity = bytes;
+        }
+        return e;
+    }
+    void release()
+    {
+        if (ptr)
+        {
+            cudaFree(ptr);
+        }
+        ptr = nullptr;
+        capacity = 0;
+    }
+    template<typename T>
+    T* as() const
+    {
+        return reinterpret_cast<T*>(ptr);
+    }
+};
+
+} // namespace vkrt

@@ -1,0 +1,154 @@
+// context.hpp — host-side objects behind the opaque handles of include/vkrt.h.
+#pragma once
+
+#include "common.cuh"
+
+#include <memory>
+
+struct VkrtContext
+{
+};
+struct VkrtBlas
+{
+};
+struct VkrtTlas
+{
+};
+struct VkrtFrame
+{
+};
+
+namespace vkrt
+{
+
+struct BuildScratch
+{
+    DeviceBuffer triLo, triHi, keysA, keysB, valsA, valsB, tileHist, children, nodeLo, nodeHi, flags, taskRef, primSource, small;
+    void release()
+    {
+        DeviceBuffer* all[] = {&triLo, &triHi, &keysA, &keysB, &valsA, &valsB, &tileHist, &children, &nodeLo, &nodeHi, &flags,
+                               &taskRef, &primSource, &small};
+        for (DeviceBuffer* b : all)
+        {
+            b->release();
+        }
+    }
+};
+
+// Wavefront queues of one frame; grow-only, sized by the number of owned pixel paths.
+struct WaveBuffers
+{
+    DeviceBuffer rayO, rayD;         // float4[P] current closest-hit rays (primary), then reflection queue rays
+    DeviceBuffer reflO, reflD;       // float4[P] reflection rays (compacted)
+    DeviceBuffer reflPath;           // u32[P] path index of each reflection queue entry
+    DeviceBuffer hitA;               // float4[P] (t, b1, b2, tri bits)
+    DeviceBuffer hitInst;            // u32[P]
+    DeviceBuffer surfA, surfB;       // float4[P] (worldPos, u) / (normal, v)
+    DeviceBuffer surfGeom;           // u32[P]
+    DeviceBuffer shadowBits;         // u32[P] per queue entry
+    DeviceBuffer shadowO, shadowD;   // float4[4*P] per-light shadow ray queues
+    DeviceBuffer pathAccum;          // float4[P] finalHitValue of the current sample (xyz) + attenuation (w)
+    DeviceBuffer sampleSum;          // float4[P] sum over samples
+    DeviceBuffer counters;           // u32[16]: [0..3] shadow queue sizes, [4] reflection queue size, [8..] stats
+    void release()
+    {
+        DeviceBuffer* all[] = {&rayO, &rayD, &reflO, &reflD, &reflPath, &hitA, &hitInst, &surfA, &surfB, &surfGeom, &shadowBits,
+                               &shadowO, &shadowD, &pathAccum, &sampleSum, &counters};
+        for (DeviceBuffer* b : all)
+        {
+            b->release();
+        }
+    }
+};
+
+struct NcclApi; // dlopen'ed NCCL entry points (comm.cpp)
+
+struct Context : VkrtContext
+{
+    int device = 0;
+    int smCount = 148;
+    cudaStream_t stream = nullptr;
+    std::string lastError;
+    uint64_t launches = 0;
+
+    // shading resources
+    DeviceBuffer materials; // VkrtSubmeshInfo[]
+    uint32_t materialCount = 0;
+    DeviceBuffer textureRecords; // TextureRecord[]
+    std::vector<void*> textureAllocs;
+    uint32_t textureCount = 0;
+    DeviceBuffer uniforms; // VkrtUniforms
+
+    BuildScratch buildScratch;
+    WaveBuffers wave;
+
+    // stats
+    bool countTraversal = false;
+    bool timeStages = false;
+    VkrtStats stats{};
+    DeviceBuffer statCounters; // u64[8] device-side: rays p/s/r, nodes, tris
+    cudaEvent_t stageEvents[16] = {};
+    bool eventsCreated = false;
+    int stageEventCount = 0;
+
+    // multi-GPU
+    int rank = 0, size = 1;
+    void* ncclComm = nullptr;
+    DeviceBuffer gatherStaging;
+
+    int fail(int code, const std::string& text)
+    {
+        lastError = text;
+        return code;
+    }
+};
+
+struct Blas : VkrtBlas
+{
+    DeviceBuffer vertices, indices;       // device copies of the geometry (kept for shading)
+    DeviceBuffer geomFirstTri, geomIndexBase;
+    uint32_t vertexStride = 0;
+    uint64_t vertexBytes = 0, indexCount = 0;
+    uint32_t geometryCount = 0;
+    uint32_t triangleCount = 0;
+    DeviceBuffer nodes, tris;
+    uint32_t nodeCount = 0;
+    float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
+    float sahCost = 0.0f;
+    float buildMs = 0.0f;
+    uint32_t flags = 0;
+};
+
+struct Tlas : VkrtTlas
+{
+    DeviceBuffer instances; // InstanceRecord[]
+    DeviceBuffer bounds;    // InstanceBounds[]
+    uint32_t instanceCount = 0;
+};
+
+struct Frame : VkrtFrame
+{
+    uint32_t width = 0, height = 0;
+    uint32_t tilesX = 0, tilesY = 0;
+    int rank = 0, size = 1;
+    uint32_t ownedTiles = 0;
+    uint32_t paths = 0;       // ownedTiles * 4096
+    DeviceBuffer bgra8;       // width*height*4 linear image (root / single GPU)
+    DeviceBuffer tileBgra8;   // ownedTiles*4096*4 tile-major (multi-GPU send buffer)
+    DeviceBuffer rgb32f;      // width*height*3 floats (AOV)
+    DeviceBuffer triangleId;  // width*height u32 (AOV)
+    DeviceBuffer shadowMask;  // width*height u8 (AOV)
+    bool gathered = false;
+};
+
+int buildBlasOnDevice(Context* ctx, Blas* blas);
+int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count);
+int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
+               Frame* frame);
+int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits);
+int gatherTiles(Context* ctx, Frame* frame, int root);
+int commInit(Context* ctx, const uint8_t* id, int rank, int size);
+int commDestroy(Context* ctx);
+int commUniqueId(uint8_t* id, std::string& err);
+
+} // namespace vkrt

@@ -1,0 +1,428 @@
+// traverse.cuh — per-ray traversal of the compressed 8-wide BVH and the watertight ray/triangle test.
+//
+// Replaces what the Vulkan driver does behind traceRayEXT (shaders/shader.rgen:51-62 closest hit,
+// shaders/shader.rchit:132-143 any hit) over the BLAS/TLAS of src/Raytracer.cpp:1027-1283.
+//
+// Node format and octant-ordered traversal follow Ylitie, Karras, Laine 2017 (compressed wide BVH);
+// the triangle test is Woop, Benthin, Wald 2013 (watertight), no culling, exclusive (tmin, tmax).
+#pragma once
+
+#include "common.cuh"
+#include "device_math.cuh"
+
+namespace vkrt
+{
+
+constexpr int kStackSize = 48; // node-group entries; deeper trees set TraceCounters::overflow
+
+struct TraceCounters
+{
+    uint32_t nodes = 0, tris = 0, overflow = 0;
+};
+
+struct RayPre // watertight per-ray constants
+{
+    int kx, ky, kz;
+    float Sx, Sy, Sz;
+};
+
+VKRT_HD RayPre makeRayPre(F3 d)
+{
+    RayPre r;
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    r.kz = 0;
+    float best = ax;
+    if (ay > best)
+    {
+        r.kz = 1;
+        best = ay;
+    }
+    if (az > best)
+    {
+        r.kz = 2;
+    }
+    r.kx = r.kz + 1 == 3 ? 0 : r.kz + 1;
+    r.ky = r.kx + 1 == 3 ? 0 : r.kx + 1;
+    if (comp3(d, r.kz) < 0.0f)
+    {
+        const int t = r.kx;
+        r.kx = r.ky;
+        r.ky = t;
+    }
+    const float dz = comp3(d, r.kz);
+    r.Sx = comp3(d, r.kx) / dz;
+    r.Sy = comp3(d, r.ky) / dz;
+    r.Sz = 1.0f / dz;
+    return r;
+}
+
+// Watertight test. Accepts tmin < t < tmax, or t == tmax when `tieOk` (an earlier hit at exactly tmax with a
+// higher id).  Outputs t and the barycentric weights of vertices 1 and 2.
+VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, float tmin, float tmax, bool tieOk, float& tOut,
+                               float& b1, float& b2)
+{
+    const F3 A = v0 - o, B = v1 - o, C = v2 - o;
+    const float Akz = comp3(A, rp.kz), Bkz = comp3(B, rp.kz), Ckz = comp3(C, rp.kz);
+    const float Ax = comp3(A, rp.kx) - rp.Sx * Akz, Ay = comp3(A, rp.ky) - rp.Sy * Akz;
+    const float Bx = comp3(B, rp.kx) - rp.Sx * Bkz, By = comp3(B, rp.ky) - rp.Sy * Bkz;
+    const float Cx = comp3(C, rp.kx) - rp.Sx * Ckz, Cy = comp3(C, rp.ky) - rp.Sy * Ckz;
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f)
+    {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f))
+    {
+        return false;
+    }
+    const float det = (U + V) + W;
+    if (det == 0.0f)
+    {
+        return false;
+    }
+    const float Az = rp.Sz * Akz, Bz = rp.Sz * Bkz, Cz = rp.Sz * Ckz;
+    const float T = (U * Az + V * Bz) + W * Cz;
+    const float rcp = 1.0f / det;
+    const float t = T * rcp;
+    if (!(t > tmin))
+    {
+        return false;
+    }
+    if (!(t < tmax) && !(tieOk && t == tmax))
+    {
+        return false;
+    }
+    tOut = t;
+    b1 = V * rcp;
+    b2 = W * rcp;
+    return true;
+}
+
+VKRT_HD uint32_t highestBit(uint32_t v) // index of the most significant set bit, v != 0
+{
+#if defined(__CUDA_ARCH__)
+    return 31u - (uint32_t)__clz((int)v);
+#else
+    return 31u - (uint32_t)__builtin_clz(v);
+#endif
+}
+VKRT_HD uint32_t popCount(uint32_t v)
+{
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)__popc(v);
+#else
+    return (uint32_t)__builtin_popcount(v);
+#endif
+}
+
+// Box-test direction reciprocal: tiny components are clamped so no inf/NaN enters the slab arithmetic.
+VKRT_HD float safeRcp(float d)
+{
+    const float lim = 1e-20f;
+    const float dd = fabsf(d) < lim ? (d < 0.0f ? -lim : lim) : d;
+    return 1.0f / dd;
+}
+
+struct NodeWords // one Node8 fetched as five 16-byte vectors
+{
+    float4 n0;
+    uint4 n1, n2, n3, n4;
+};
+
+VKRT_HD NodeWords loadNode(const Node8* nodes, uint32_t index)
+{
+    NodeWords w;
+    const float4* p = reinterpret_cast<const float4*>(nodes + index);
+#if defined(__CUDA_ARCH__)
+    w.n0 = __ldg(p);
+    w.n1 = __ldg(reinterpret_cast<const uint4*>(p + 1));
+    w.n2 = __ldg(reinterpret_cast<const uint4*>(p + 2));
+    w.n3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+    w.n4 = __ldg(reinterpret_cast<const uint4*>(p + 4));
+#else
+    w.n0 = p[0];
+    memcpy(&w.n1, p + 1, 16);
+    memcpy(&w.n2, p + 2, 16);
+    memcpy(&w.n3, p + 3, 16);
+    memcpy(&w.n4, p + 4, 16);
+#endif
+    return w;
+}
+
+VKRT_HD uint32_t byteOf(uint32_t word, int i) { return (word >> (8 * i)) & 0xFFu; }
+
+// Intersects the ray with the 8 quantised child boxes of a node.  Returns the hit mask: bits 24..31 = internal
+// children in traversal priority order (nearest octant-order child in the highest bit), bits 0..23 = primitives.
+//   idir = safeRcp(d), octant bit k set when d_k < 0
+VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tmin, float tmax)
+{
+    const uint32_t e = floatAsUint(w.n0.w);
+    const float sx = uintAsFloat((e & 0xFFu) << 23), sy = uintAsFloat(((e >> 8) & 0xFFu) << 23),
+                sz = uintAsFloat(((e >> 16) & 0xFFu) << 23);
+    const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
+    const float bx = (w.n0.x - o.x) * idir.x, by = (w.n0.y - o.y) * idir.y, bz = (w.n0.z - o.z) * idir.z;
+    const uint32_t octinv = 7u - octant;
+    const float pad = 3.8146973e-06f; // 2^-18 relative padding: box culling must never reject a watertight hit
+    uint32_t hitmask = 0;
+    // n1 = {childBase, primBase, meta[0..3], meta[4..7]}; n2 = {qlox[0..3], qlox[4..7], qloy[0..3], qloy[4..7]}
+    // n3 = {qloz lo, qloz hi, qhix lo, qhix hi};          n4 = {qhiy lo, qhiy hi, qhiz lo, qhiz hi}
+#pragma unroll
+    for (int half = 0; half < 2; ++half)
+    {
+        const uint32_t meta4 = half ? w.n1.w : w.n1.z;
+        const uint32_t qlox = half ? w.n2.y : w.n2.x, qloy = half ? w.n2.w : w.n2.z, qloz = half ? w.n3.y : w.n3.x;
+        const uint32_t qhix = half ? w.n3.w : w.n3.z, qhiy = half ? w.n4.y : w.n4.x, qhiz = half ? w.n4.w : w.n4.z;
+        // near/far plane selection by ray direction sign
+        const uint32_t nx = (octant & 1u) ? qhix : qlox, fx = (octant & 1u) ? qlox : qhix;
+        const uint32_t ny = (octant & 2u) ? qhiy : qloy, fy = (octant & 2u) ? qloy : qhiy;
+        const uint32_t nz = (octant & 4u) ? qhiz : qloz, fz = (octant & 4u) ? qloz : qhiz;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            const uint32_t meta = byteOf(meta4, i);
+            if (meta == 0)
+            {
+                continue;
+            }
+            const float tnx = fmaExplicit((float)byteOf(nx, i), ax, bx), tfx = fmaExplicit((float)byteOf(fx, i), ax, bx);
+            const float tny = fmaExplicit((float)byteOf(ny, i), ay, by), tfy = fmaExplicit((float)byteOf(fy, i), ay, by);
+            const float tnz = fmaExplicit((float)byteOf(nz, i), az, bz), tfz = fmaExplicit((float)byteOf(fz, i), az, bz);
+            float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+            float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
+            tn = fmaExplicit(-fabsf(tn), pad, tn);
+            tf = fmaExplicit(fabsf(tf), pad, tf);
+            if (tn <= tf)
+            {
+                const bool inner = (meta & 0xE0u) == 0x20u && (meta & 0x1Fu) >= 24u;
+                const uint32_t bits = meta >> 5;
+                const uint32_t index = inner ? (24u + (((meta & 0x1Fu) - 24u) ^ octinv)) : (meta & 0x1Fu);
+                hitmask |= bits << index;
+            }
+        }
+    }
+    return hitmask;
+}
+
+VKRT_HD void loadTriangle(const PackedTri* tris, uint32_t index, F3& v0, F3& v1, F3& v2, uint32_t& geometry,
+                          uint32_t& primitive, uint32_t& buildIndex)
+{
+    const float4* p = reinterpret_cast<const float4*>(tris + index);
+#if defined(__CUDA_ARCH__)
+    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+#else
+    const float4 a = p[0], b = p[1], c = p[2];
+#endif
+    v0 = f3(a.x, a.y, a.z);
+    v1 = f3(a.w, b.x, b.y);
+    v2 = f3(b.z, b.w, c.x);
+    geometry = floatAsUint(c.y);
+    primitive = floatAsUint(c.z);
+    buildIndex = floatAsUint(c.w);
+}
+
+// State of the best hit so far for one ray (world-parametrised t, shared across instances).
+struct BestHit
+{
+    float t;             // current tmax (shrinks on closest hits)
+    float b1, b2;
+    uint32_t tri;        // packed-triangle slot in the instance's BLAS, kInvalid = none
+    uint32_t instance;
+    uint32_t buildIndex; // tie-break key of the current hit
+};
+
+// Traverses one BLAS with an object-space ray.  ANY: return true at the first accepted triangle.
+template<bool ANY>
+VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d, float tmin, uint32_t instance,
+                          BestHit& best, TraceCounters* counters)
+{
+    const RayPre rp = makeRayPre(d);
+    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    const uint32_t octinv = 7u - octant;
+
+    uint2 stack[kStackSize];
+    int sp = 0;
+    // node group: x = base index of the internal children, y = hit bits 24..31 | imask in bits 0..7
+    uint2 ngroup = make_uint2(0u, 0x80000000u);
+    uint2 tgroup = make_uint2(0u, 0u);
+    bool found = false;
+
+    for (;;)
+    {
+        if (ngroup.y > 0x00FFFFFFu)
+        {
+            const uint32_t bit = highestBit(ngroup.y);
+            const uint32_t base = ngroup.x;
+            ngroup.y &= ~(1u << bit);
+            if (ngroup.y > 0x00FFFFFFu)
+            {
+                if (sp < kStackSize)
+                {
+                    stack[sp++] = ngroup;
+                }
+                else if (counters)
+                {
+                    counters->overflow = 1;
+                }
+            }
+            const uint32_t slot = (bit - 24u) ^ octinv;
+            const uint32_t rel = popCount(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
+            const NodeWords w = loadNode(nodes, base + rel);
+            if (counters)
+            {
+                ++counters->nodes;
+            }
+            const uint32_t hits = intersectNode(w, o, idir, octant, tmin, best.t);
+            const uint32_t imask = floatAsUint(w.n0.w) >> 24;
+            ngroup = make_uint2(w.n1.x, (hits & 0xFF000000u) | imask);
+            tgroup = make_uint2(w.n1.y, hits & 0x00FFFFFFu);
+        }
+        else
+        {
+            tgroup = make_uint2(0u, 0u);
+        }
+
+        while (tgroup.y != 0u)
+        {
+            const uint32_t bit = highestBit(tgroup.y);
+            tgroup.y &= ~(1u << bit);
+            const uint32_t slotIndex = tgroup.x + bit;
+            F3 v0, v1, v2;
+            uint32_t geometry, primitive, buildIndex;
+            loadTriangle(tris, slotIndex, v0, v1, v2, geometry, primitive, buildIndex);
+            if (counters)
+            {
+                ++counters->tris;
+            }
+            (void)geometry;
+            (void)primitive;
+            bool tieOk = false;
+            if (!ANY)
+            {
+                tieOk = best.tri != kInvalid &&
+                        (instance < best.instance || (instance == best.instance && buildIndex < best.buildIndex));
+            }
+            float t, b1, b2;
+            if (intersectTriangle(v0, v1, v2, o, rp, tmin, best.t, tieOk, t, b1, b2))
+            {
+                best.t = t, best.b1 = b1, best.b2 = b2;
+                best.tri = slotIndex, best.instance = instance, best.buildIndex = buildIndex;
+                found = true;
+                if (ANY)
+                {
+                    return true;
+                }
+            }
+        }
+
+        if (ngroup.y <= 0x00FFFFFFu)
+        {
+            if (sp == 0)
+            {
+                break;
+            }
+            ngroup = stack[--sp];
+        }
+    }
+    return found;
+}
+
+// World AABB of one instance for the top-level pass.
+struct InstanceBounds
+{
+    float lo[3], hi[3];
+};
+
+// Conservative ray/AABB entry distance; returns false when the padded slab interval is empty.
+VKRT_HD bool intersectBounds(const InstanceBounds& b, F3 o, F3 idir, float tmin, float tmax, float& tnear)
+{
+    const float pad = 3.8146973e-06f;
+    float t0x = (b.lo[0] - o.x) * idir.x, t1x = (b.hi[0] - o.x) * idir.x;
+    float t0y = (b.lo[1] - o.y) * idir.y, t1y = (b.hi[1] - o.y) * idir.y;
+    float t0z = (b.lo[2] - o.z) * idir.z, t1z = (b.hi[2] - o.z) * idir.z;
+    float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
+    float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
+    tn = tn - fabsf(tn) * pad;
+    tf = tf + fabsf(tf) * pad;
+    tnear = tn;
+    return tn <= tf;
+}
+
+// traceRayEXT over the whole scene: all instances (mask 0xFF, cull disabled — src/Raytracer.cpp:1172-1177),
+// visited front to back by the entry distance of their world bounds.  Returns true on any accepted hit.
+// `best.t` must be initialised to the ray's tmax and best.tri to kInvalid.
+template<bool ANY>
+VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 d,
+                        float tmin, BestHit& best, TraceCounters* counters)
+{
+    if (!finite3(o) || !finite3(d) || (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) || !(best.t > tmin))
+    {
+        return false;
+    }
+    bool found = false;
+    if (instanceCount == 1)
+    {
+        const InstanceRecord& inst = instances[0];
+        const F3 oo = affinePoint(inst.w2o, o);
+        const F3 dd = affineDir(inst.w2o, d);
+        if (!finite3(oo) || !finite3(dd) || (dd.x == 0.0f && dd.y == 0.0f && dd.z == 0.0f))
+        {
+            return false;
+        }
+        return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters);
+    }
+    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    // visit instances in order of increasing entry distance: repeatedly select the nearest not yet visited one
+    float lastT = -INFINITY;
+    uint32_t lastIdx = 0;
+    bool first = true;
+    for (;;)
+    {
+        float bestT = INFINITY;
+        uint32_t bestIdx = kInvalid;
+        for (uint32_t i = 0; i < instanceCount; ++i)
+        {
+            float tn;
+            if (!intersectBounds(bounds[i], o, idir, tmin, best.t, tn))
+            {
+                continue;
+            }
+            // strict (t, index) ordering after the last visited instance
+            const bool after = first || tn > lastT || (tn == lastT && i > lastIdx);
+            if (after && (tn < bestT || (tn == bestT && i < bestIdx)))
+            {
+                bestT = tn;
+                bestIdx = i;
+            }
+        }
+        if (bestIdx == kInvalid)
+        {
+            break;
+        }
+        first = false;
+        lastT = bestT;
+        lastIdx = bestIdx;
+        const InstanceRecord& inst = instances[bestIdx];
+        const F3 oo = affinePoint(inst.w2o, o);
+        const F3 dd = affineDir(inst.w2o, d);
+        if (!finite3(oo) || !finite3(dd) || (dd.x == 0.0f && dd.y == 0.0f && dd.z == 0.0f))
+        {
+            continue;
+        }
+        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, bestIdx, best, counters))
+        {
+            found = true;
+            if (ANY)
+            {
+                return true;
+            }
+        }
+    }
+    return found;
+}
+
+} // namespace vkrt

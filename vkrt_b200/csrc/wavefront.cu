@@ -1,0 +1,738 @@
+// wavefront.cu — the wavefront ray engine that replaces vkCmdTraceRaysKHR(W,H,1) (src/Raytracer.cpp:157) and the
+// shader pipeline it dispatches (shader.rgen -> traceRayEXT -> shader.rchit / shader.rmiss / shader_shadow.rmiss).
+//
+// Stages per sample (each a persistent grid-stride kernel; queue sizes stay on the device, no host sync):
+//   k_raygen -> k_trace_closest -> k_shade_surface (emits per-light shadow-ray queues, warp-aggregated compaction)
+//            -> k_trace_any -> k_shade_resolve (emits the compacted reflection queue)
+//            -> k_trace_closest -> k_shade_surface -> k_trace_any -> k_shade_resolve   (the single bounce, rgen:40)
+//            -> k_resolve_sample (sample average, B8G8R8A8 store, tile-major copy for the NCCL gather)
+#include "context.hpp"
+#include "shading.cuh"
+#include "traverse.cuh"
+
+#include <algorithm>
+
+namespace vkrt
+{
+
+namespace
+{
+constexpr int kTraceThreads = 128;
+constexpr int kShadeThreads = 128;
+
+struct SceneDev
+{
+    const InstanceRecord* instances;
+    const InstanceBounds* bounds;
+    uint32_t instanceCount;
+    const VkrtSubmeshInfo* rows;
+    const TextureRecord* textures;
+};
+
+struct WaveDev
+{
+    float4 *rayO, *rayD, *reflO, *reflD;
+    uint32_t* reflPath;
+    float4* hitA;
+    uint32_t* hitInst;
+    float4 *surfA, *surfB;
+    uint32_t *surfGeom, *shadowBits;
+    float4 *shadowO, *shadowD;
+    float4 *pathAccum, *sampleSum;
+    uint32_t* counters; // [0..3] shadow queue sizes, [4] reflection queue size
+    uint32_t capacity;  // P
+};
+
+struct FrameDev
+{
+    TileMap map;
+    uint32_t* bgra8;      // linear image or nullptr
+    uint32_t* tileBgra8;  // tile-major or nullptr
+    float* rgb32f;        // AOVs or nullptr
+    uint32_t* triangleId;
+    uint8_t* shadowMask;
+};
+
+__device__ __forceinline__ uint32_t warpAppend(uint32_t* counter, bool want)
+{
+    // warp-aggregated queue append: one atomic per warp, slots handed out in lane order
+    const uint32_t mask = __ballot_sync(__activemask(), want);
+    if (!want)
+    {
+        return 0;
+    }
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader)
+    {
+        base = atomicAdd(counter, __popc(mask));
+    }
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+__global__ void k_reset_counters(uint32_t* counters)
+{
+    if (threadIdx.x < 8)
+    {
+        counters[threadIdx.x] = 0u;
+    }
+}
+
+// shader.rgen:32-47 — one primary ray per owned pixel path
+__global__ void __launch_bounds__(kShadeThreads)
+k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, uint32_t sample, uint32_t spp, float4* __restrict__ rayO,
+         float4* __restrict__ rayD, float4* __restrict__ pathAccum)
+{
+    float jx, jy;
+    sampleOffset(sample, spp, jx, jy);
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < paths; p += gridDim.x * blockDim.x)
+    {
+        uint32_t x, y, tl, pit;
+        if (pathToPixel(map, p, x, y, tl, pit))
+        {
+            F3 o, d;
+            primaryRay(u, map.width, map.height, x, y, jx, jy, o, d);
+            rayO[p] = make_float4(o.x, o.y, o.z, kRayTMin);
+            rayD[p] = make_float4(d.x, d.y, d.z, kRayTMax);
+        }
+        else
+        {
+            rayO[p] = make_float4(0.f, 0.f, 0.f, kRayTMin);
+            rayD[p] = make_float4(0.f, 0.f, 0.f, -1.0f); // inactive path
+        }
+        pathAccum[p] = make_float4(0.f, 0.f, 0.f, 1.0f); // finalHitValue = 0, attenuation = 1 (rgen:42-45)
+    }
+}
+
+template<bool STATS>
+__global__ void __launch_bounds__(kTraceThreads)
+k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
+                uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
+                int statSlot)
+{
+    const uint32_t count = countPtr ? *countPtr : countImm;
+    TraceCounters tc;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const float4 o4 = rayO[i], d4 = rayD[i];
+        BestHit best;
+        best.t = d4.w;
+        best.b1 = best.b2 = 0.0f;
+        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+        traceScene<false>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z), f3(d4.x, d4.y, d4.z), o4.w, best,
+                          STATS ? &tc : nullptr);
+        hitA[i] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.tri));
+        hitInst[i] = best.instance;
+    }
+    if (STATS)
+    {
+        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+        if (tc.overflow)
+        {
+            atomicAdd(&statCounters[5], 1ull);
+        }
+    }
+    if (statSlot >= 0 && blockIdx.x == 0 && threadIdx.x == 0 && countPtr)
+    {
+        atomicAdd(&statCounters[statSlot], (unsigned long long)count);
+    }
+}
+
+// shader.rchit:88-129 for every hit; shader.rmiss:17 for every miss.  Emits shadow rays.
+__global__ void __launch_bounds__(kShadeThreads)
+k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, int writeAov)
+{
+    const uint32_t count = countPtr ? *countPtr : countImm;
+    const uint32_t rounded = (count + 31u) & ~31u; // whole warps stay in the loop for the ballots
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < rounded; q += gridDim.x * blockDim.x)
+    {
+        bool active = q < count;
+        uint32_t p = 0;
+        float4 h = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (active)
+        {
+            p = pathOf ? pathOf[q] : q;
+            active = rayD[q].w >= 0.0f; // padded pixels of partial tiles
+        }
+        bool hit = false;
+        SurfacePoint sp;
+        LightTerm lt[4];
+        uint32_t castMask = 0;
+        uint32_t instance = 0, primitive = 0;
+        if (active)
+        {
+            h = w.hitA[q];
+            const uint32_t tri = __float_as_uint(h.w);
+            hit = tri != kInvalid;
+            if (!hit)
+            {
+                float4 acc = w.pathAccum[p];
+                acc.x += 0.8f, acc.y += 0.8f, acc.z += 1.0f; // rmiss:17, rgen:63
+                w.pathAccum[p] = acc;
+                w.surfGeom[q] = kInvalid;
+                if (writeAov && depth == 0)
+                {
+                    uint32_t x, y, tl, pit;
+                    pathToPixel(f.map, p, x, y, tl, pit);
+                    f.triangleId[(size_t)y * f.map.width + x] = kInvalid;
+                    f.shadowMask[(size_t)y * f.map.width + x] = 0;
+                }
+            }
+            else
+            {
+                instance = w.hitInst[q];
+                const InstanceRecord& inst = scene.instances[instance];
+                const float4 tag = __ldg(reinterpret_cast<const float4*>(inst.tris + tri) + 2);
+                const uint32_t geometry = __float_as_uint(tag.y);
+                primitive = __float_as_uint(tag.z);
+                sp = shadeSurface(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z);
+                for (int i = 0; i < 4; ++i)
+                {
+                    lt[i] = lightTerm(u, i, sp.worldPos, sp.normal);
+                    if (lt[i].castShadow)
+                    {
+                        castMask |= 1u << i;
+                    }
+                }
+                w.surfA[q] = make_float4(sp.worldPos.x, sp.worldPos.y, sp.worldPos.z, sp.u);
+                w.surfB[q] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.v);
+                w.surfGeom[q] = geometry;
+                w.shadowBits[q] = castMask << 4;
+                if (writeAov && depth == 0)
+                {
+                    uint32_t x, y, tl, pit;
+                    pathToPixel(f.map, p, x, y, tl, pit);
+                    f.triangleId[(size_t)y * f.map.width + x] =
+                        (instance << 24) + (uint32_t)scene.rows[geometry].indexBufferOffset + primitive;
+                }
+            }
+        }
+        // compaction into the 4 per-light shadow queues (light-major keeps rays towards one light together)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            const bool want = hit && ((castMask >> i) & 1u);
+            const uint32_t slot = warpAppend(&w.counters[i], want);
+            if (want)
+            {
+                const size_t dst = (size_t)i * w.capacity + slot;
+                w.shadowO[dst] = make_float4(sp.worldPos.x, sp.worldPos.y, sp.worldPos.z, lt[i].distance);
+                w.shadowD[dst] = make_float4(lt[i].dir.x, lt[i].dir.y, lt[i].dir.z, __uint_as_float(q));
+            }
+        }
+    }
+}
+
+// shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
+template<bool STATS>
+__global__ void __launch_bounds__(kTraceThreads)
+k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters)
+{
+    const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
+    const uint32_t total = c0 + c1 + c2 + c3;
+    TraceCounters tc;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+    {
+        uint32_t light, slot;
+        if (i < c0)
+        {
+            light = 0, slot = i;
+        }
+        else if (i < c0 + c1)
+        {
+            light = 1, slot = i - c0;
+        }
+        else if (i < c0 + c1 + c2)
+        {
+            light = 2, slot = i - c0 - c1;
+        }
+        else
+        {
+            light = 3, slot = i - c0 - c1 - c2;
+        }
+        const size_t src = (size_t)light * w.capacity + slot;
+        const float4 o4 = w.shadowO[src], d4 = w.shadowD[src];
+        BestHit best;
+        best.t = o4.w;
+        best.b1 = best.b2 = 0.0f;
+        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+        const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
+                                               f3(d4.x, d4.y, d4.z), kRayTMin, best, STATS ? &tc : nullptr);
+        if (occluded)
+        {
+            atomicOr(&w.shadowBits[__float_as_uint(d4.w)], 1u << light);
+        }
+    }
+    if (STATS)
+    {
+        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+        if (tc.overflow)
+        {
+            atomicAdd(&statCounters[5], 1ull);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        atomicAdd(&statCounters[1], (unsigned long long)total);
+    }
+}
+
+// shader.rchit:144-171 and the bounce bookkeeping of shader.rgen:63-73
+__global__ void __launch_bounds__(kShadeThreads)
+k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, int writeAov)
+{
+    const uint32_t count = countPtr ? *countPtr : countImm;
+    const uint32_t rounded = (count + 31u) & ~31u;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < rounded; q += gridDim.x * blockDim.x)
+    {
+        bool active = q < count;
+        uint32_t geometry = kInvalid;
+        if (active)
+        {
+            geometry = w.surfGeom[q];
+            active = geometry != kInvalid && rayD[q].w >= 0.0f;
+        }
+        bool reflect = false;
+        uint32_t p = 0;
+        F3 origin = f3(0.f, 0.f, 0.f), dir = f3(0.f, 0.f, 0.f);
+        if (active)
+        {
+            p = pathOf ? pathOf[q] : q;
+            const float4 a = w.surfA[q], b = w.surfB[q];
+            SurfacePoint sp;
+            sp.worldPos = f3(a.x, a.y, a.z), sp.normal = f3(b.x, b.y, b.z);
+            sp.u = a.w, sp.v = b.w, sp.geometry = geometry;
+            const uint32_t bits = w.shadowBits[q];
+            float4 acc = w.pathAccum[p];
+            const float4 d4 = rayD[q];
+            const ResolveOut r = shadeResolve(u, scene.rows, scene.textures, sp, bits & 0xFu, acc.w, f3(d4.x, d4.y, d4.z));
+            acc.x += r.hitValue.x, acc.y += r.hitValue.y, acc.z += r.hitValue.z; // rgen:63
+            acc.w = r.attenuation;
+            w.pathAccum[p] = acc;
+            reflect = r.reflect && depth == 0; // rgen:65-69: maxDepth 2
+            origin = sp.worldPos, dir = r.rayDir;
+            if (writeAov && depth == 0)
+            {
+                uint32_t x, y, tl, pit;
+                pathToPixel(f.map, p, x, y, tl, pit);
+                f.shadowMask[(size_t)y * f.map.width + x] = (uint8_t)bits;
+            }
+        }
+        const uint32_t slot = warpAppend(&w.counters[4], reflect);
+        if (reflect)
+        {
+            w.reflO[slot] = make_float4(origin.x, origin.y, origin.z, kRayTMin);
+            w.reflD[slot] = make_float4(dir.x, dir.y, dir.z, kRayTMax);
+            w.reflPath[slot] = p;
+        }
+    }
+}
+
+// shader.rgen:76 imageStore + sample averaging; writes the linear image and/or the tile-major send buffer
+__global__ void __launch_bounds__(kShadeThreads)
+k_resolve_sample(WaveDev w, FrameDev f, uint32_t paths, uint32_t sample, uint32_t spp)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < paths; p += gridDim.x * blockDim.x)
+    {
+        uint32_t x, y, tl, pit;
+        const bool valid = pathToPixel(f.map, p, x, y, tl, pit);
+        const float4 acc = w.pathAccum[p];
+        F3 sum = f3(acc.x, acc.y, acc.z);
+        if (spp > 1)
+        {
+            if (sample > 0)
+            {
+                const float4 s = w.sampleSum[p];
+                sum = f3(s.x, s.y, s.z) + sum;
+            }
+            if (sample + 1 < spp)
+            {
+                w.sampleSum[p] = make_float4(sum.x, sum.y, sum.z, 0.f);
+                continue;
+            }
+            sum = sum / (float)spp;
+        }
+        const uint32_t px = packBgra8(sum);
+        if (f.tileBgra8)
+        {
+            f.tileBgra8[(size_t)tl * kTilePixels + pit] = valid ? px : 0u;
+        }
+        if (valid)
+        {
+            if (f.bgra8)
+            {
+                f.bgra8[(size_t)y * f.map.width + x] = px;
+            }
+            if (f.rgb32f)
+            {
+                float* dst = f.rgb32f + ((size_t)y * f.map.width + x) * 3;
+                dst[0] = sum.x, dst[1] = sum.y, dst[2] = sum.z;
+            }
+        }
+    }
+}
+
+__global__ void k_hits_export(SceneDev scene, const float4* __restrict__ hitA, const uint32_t* __restrict__ hitInst, uint32_t count,
+                              VkrtHit* __restrict__ out)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const float4 h = hitA[i];
+        const uint32_t tri = __float_as_uint(h.w);
+        VkrtHit o;
+        if (tri == kInvalid)
+        {
+            o.t = 0.f, o.b1 = 0.f, o.b2 = 0.f;
+            o.instance = o.geometry = o.primitive = kInvalid;
+        }
+        else
+        {
+            const uint32_t inst = hitInst[i];
+            const float4 tag = reinterpret_cast<const float4*>(scene.instances[inst].tris + tri)[2];
+            o.t = h.x, o.b1 = h.y, o.b2 = h.z;
+            o.instance = inst;
+            o.geometry = __float_as_uint(tag.y);
+            o.primitive = __float_as_uint(tag.z);
+        }
+        out[i] = o;
+    }
+}
+
+// any-hit over a plain ray list (ray-level API): writes instance = 0 / kInvalid
+template<bool STATS>
+__global__ void __launch_bounds__(kTraceThreads)
+k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, uint32_t count, VkrtHit* __restrict__ out,
+                 unsigned long long* statCounters)
+{
+    TraceCounters tc;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const float4 o4 = rayO[i], d4 = rayD[i];
+        BestHit best;
+        best.t = d4.w;
+        best.b1 = best.b2 = 0.0f;
+        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+        const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
+                                               f3(d4.x, d4.y, d4.z), o4.w, best, STATS ? &tc : nullptr);
+        VkrtHit o;
+        o.t = occluded ? best.t : 0.f, o.b1 = 0.f, o.b2 = 0.f;
+        o.instance = occluded ? best.instance : kInvalid;
+        o.geometry = o.primitive = occluded ? 0u : kInvalid;
+        out[i] = o;
+    }
+    if (STATS)
+    {
+        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+    }
+}
+
+int reserveWave(Context* ctx, uint32_t paths)
+{
+    WaveBuffers& w = ctx->wave;
+    const size_t p = std::max<size_t>(paths, 32);
+    VKRT_CUDA_TRY(ctx, w.rayO.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.rayD.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.reflO.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.reflD.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.reflPath.reserve(p * 4));
+    VKRT_CUDA_TRY(ctx, w.hitA.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.hitInst.reserve(p * 4));
+    VKRT_CUDA_TRY(ctx, w.surfA.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.surfB.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.surfGeom.reserve(p * 4));
+    VKRT_CUDA_TRY(ctx, w.shadowBits.reserve(p * 4));
+    VKRT_CUDA_TRY(ctx, w.shadowO.reserve(p * 16 * 4));
+    VKRT_CUDA_TRY(ctx, w.shadowD.reserve(p * 16 * 4));
+    VKRT_CUDA_TRY(ctx, w.pathAccum.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.sampleSum.reserve(p * 16));
+    VKRT_CUDA_TRY(ctx, w.counters.reserve(64));
+    VKRT_CUDA_TRY(ctx, ctx->statCounters.reserve(64));
+    return VKRT_SUCCESS;
+}
+
+WaveDev waveDev(Context* ctx, uint32_t paths)
+{
+    WaveBuffers& b = ctx->wave;
+    WaveDev w;
+    w.rayO = b.rayO.as<float4>(), w.rayD = b.rayD.as<float4>();
+    w.reflO = b.reflO.as<float4>(), w.reflD = b.reflD.as<float4>();
+    w.reflPath = b.reflPath.as<uint32_t>();
+    w.hitA = b.hitA.as<float4>(), w.hitInst = b.hitInst.as<uint32_t>();
+    w.surfA = b.surfA.as<float4>(), w.surfB = b.surfB.as<float4>();
+    w.surfGeom = b.surfGeom.as<uint32_t>(), w.shadowBits = b.shadowBits.as<uint32_t>();
+    w.shadowO = b.shadowO.as<float4>(), w.shadowD = b.shadowD.as<float4>();
+    w.pathAccum = b.pathAccum.as<float4>(), w.sampleSum = b.sampleSum.as<float4>();
+    w.counters = b.counters.as<uint32_t>();
+    w.capacity = std::max<uint32_t>(paths, 32);
+    return w;
+}
+
+uint32_t persistentGrid(const Context* ctx, int blocksPerSm)
+{
+    return (uint32_t)(ctx->smCount * blocksPerSm);
+}
+} // namespace
+
+int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
+               Frame* frame)
+{
+    (void)frameIndex;
+    if (spp == 0)
+    {
+        spp = 1;
+    }
+    if (ctx->materialCount == 0 || ctx->textureCount == 0)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_trace: materials and textures must be set first");
+    }
+    const uint32_t paths = frame->paths;
+    int r = reserveWave(ctx, paths);
+    if (r != VKRT_SUCCESS)
+    {
+        return r;
+    }
+    cudaStream_t s = ctx->stream;
+    const bool aov = !(flags & VKRT_TRACE_NO_AOV);
+    if (aov)
+    {
+        const size_t px = (size_t)frame->width * frame->height;
+        VKRT_CUDA_TRY(ctx, frame->rgb32f.reserve(px * 12));
+        VKRT_CUDA_TRY(ctx, frame->triangleId.reserve(px * 4));
+        VKRT_CUDA_TRY(ctx, frame->shadowMask.reserve(px));
+    }
+
+    SceneDev scene;
+    scene.instances = tlas->instances.as<InstanceRecord>();
+    scene.bounds = tlas->bounds.as<InstanceBounds>();
+    scene.instanceCount = tlas->instanceCount;
+    scene.rows = ctx->materials.as<VkrtSubmeshInfo>();
+    scene.textures = ctx->textureRecords.as<TextureRecord>();
+
+    WaveDev w = waveDev(ctx, paths);
+    FrameDev f;
+    f.map.width = frame->width, f.map.height = frame->height;
+    f.map.tilesX = frame->tilesX, f.map.tilesY = frame->tilesY;
+    f.map.rank = (uint32_t)frame->rank, f.map.size = (uint32_t)frame->size;
+    f.map.ownedTiles = frame->ownedTiles;
+    f.bgra8 = frame->bgra8.as<uint32_t>();
+    f.tileBgra8 = frame->size > 1 ? frame->tileBgra8.as<uint32_t>() : nullptr;
+    f.rgb32f = aov ? frame->rgb32f.as<float>() : nullptr;
+    f.triangleId = aov ? frame->triangleId.as<uint32_t>() : nullptr;
+    f.shadowMask = aov ? frame->shadowMask.as<uint8_t>() : nullptr;
+
+    const VkrtUniforms u = *uniforms;
+    unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
+    const uint32_t gridTrace = persistentGrid(ctx, 8);
+    const uint32_t gridShade = persistentGrid(ctx, 8);
+    const bool st = ctx->countTraversal;
+
+    // valid (non-padded) primary rays owned by this rank
+    uint64_t validPixels = 0;
+    for (uint32_t t = 0; t < frame->ownedTiles; ++t)
+    {
+        const uint32_t tile = (uint32_t)frame->rank + t * (uint32_t)frame->size;
+        const uint32_t tx = tile % frame->tilesX, ty = tile / frame->tilesX;
+        const uint32_t wpx = std::min<uint32_t>(kTile, frame->width - tx * kTile), hpx = std::min<uint32_t>(kTile, frame->height - ty * kTile);
+        validPixels += (uint64_t)wpx * hpx;
+    }
+
+    int ev = 0;
+    auto mark = [&]() {
+        if (ctx->timeStages && ev < 16)
+        {
+            cudaEventRecord(ctx->stageEvents[ev++], s);
+        }
+    };
+    if (ctx->timeStages && !ctx->eventsCreated)
+    {
+        for (auto& e : ctx->stageEvents)
+        {
+            cudaEventCreate(&e);
+        }
+        ctx->eventsCreated = true;
+    }
+    ctx->stats.msRaygen = ctx->stats.msTraceClosest = ctx->stats.msShade = ctx->stats.msTraceAny = ctx->stats.msResolve = 0.f;
+    ctx->stats.msTotal = 0.f;
+
+    for (uint32_t sample = 0; sample < spp; ++sample)
+    {
+        const int writeAov = (aov && sample == 0) ? 1 : 0;
+        const bool timed = ctx->timeStages && sample == 0;
+        if (timed)
+        {
+            mark(); // 0
+        }
+        k_reset_counters<<<1, 32, 0, s>>>(w.counters);
+        k_raygen<<<gridShade, kShadeThreads, 0, s>>>(u, f.map, paths, sample, spp, w.rayO, w.rayD, w.pathAccum);
+        if (timed)
+        {
+            mark(); // 1
+        }
+        // depth 0: primary rays
+        if (st)
+        {
+            k_trace_closest<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, stat, -1);
+        }
+        else
+        {
+            k_trace_closest<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, stat, -1);
+        }
+        if (timed)
+        {
+            mark(); // 2
+        }
+        k_shade_surface<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, paths, 0, writeAov);
+        if (timed)
+        {
+            mark(); // 3
+        }
+        if (st)
+        {
+            k_trace_any<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
+        }
+        else
+        {
+            k_trace_any<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
+        }
+        if (timed)
+        {
+            mark(); // 4
+        }
+        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, paths, 0, writeAov);
+        if (timed)
+        {
+            mark(); // 5
+        }
+        // depth 1: the compacted reflection queue
+        k_reset_counters<<<1, 4, 0, s>>>(w.counters); // only the 4 shadow queues; [4] holds the reflection count
+        if (st)
+        {
+            k_trace_closest<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.reflO, w.reflD, w.counters + 4, 0, w.hitA, w.hitInst, stat, 2);
+        }
+        else
+        {
+            k_trace_closest<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.reflO, w.reflD, w.counters + 4, 0, w.hitA, w.hitInst, stat, 2);
+        }
+        if (timed)
+        {
+            mark(); // 6
+        }
+        k_shade_surface<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        if (timed)
+        {
+            mark(); // 7
+        }
+        if (st)
+        {
+            k_trace_any<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
+        }
+        else
+        {
+            k_trace_any<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
+        }
+        if (timed)
+        {
+            mark(); // 8
+        }
+        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        if (timed)
+        {
+            mark(); // 9
+        }
+        k_resolve_sample<<<gridShade, kShadeThreads, 0, s>>>(w, f, paths, sample, spp);
+        if (timed)
+        {
+            mark(); // 10
+        }
+        ctx->launches += 12;
+    }
+    ctx->stageEventCount = ev;
+    ctx->stats.raysPrimary += validPixels * spp;
+    frame->gathered = false;
+    VKRT_CUDA_TRY(ctx, cudaGetLastError());
+    return VKRT_SUCCESS;
+}
+
+int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits)
+{
+    if (count == 0)
+    {
+        return VKRT_SUCCESS;
+    }
+    if (count > 0x7FFFFFFFull)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays: at most 2^31-1 rays per call");
+    }
+    const uint32_t n = (uint32_t)count;
+    int r = reserveWave(ctx, n);
+    if (r != VKRT_SUCCESS)
+    {
+        return r;
+    }
+    cudaStream_t s = ctx->stream;
+    // split the 32-byte host records into the engine's two float4 streams on the host side
+    std::vector<float4> o(n), d(n);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        o[i] = make_float4(rays[i].origin[0], rays[i].origin[1], rays[i].origin[2], rays[i].tmin);
+        d[i] = make_float4(rays[i].direction[0], rays[i].direction[1], rays[i].direction[2], rays[i].tmax);
+    }
+    WaveDev w = waveDev(ctx, n);
+    DeviceBuffer out;
+    VKRT_CUDA_TRY(ctx, out.reserve((size_t)n * sizeof(VkrtHit)));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(w.rayO, o.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(w.rayD, d.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
+    SceneDev scene;
+    scene.instances = tlas->instances.as<InstanceRecord>();
+    scene.bounds = tlas->bounds.as<InstanceBounds>();
+    scene.instanceCount = tlas->instanceCount;
+    scene.rows = nullptr;
+    scene.textures = nullptr;
+    unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
+    const uint32_t grid = persistentGrid(ctx, 8);
+    if (anyHit)
+    {
+        if (ctx->countTraversal)
+        {
+            k_trace_any_list<true><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, n, out.as<VkrtHit>(), stat);
+        }
+        else
+        {
+            k_trace_any_list<false><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, n, out.as<VkrtHit>(), stat);
+        }
+        ctx->launches += 1;
+    }
+    else
+    {
+        if (ctx->countTraversal)
+        {
+            k_trace_closest<true><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, n, w.hitA, w.hitInst, stat, -1);
+        }
+        else
+        {
+            k_trace_closest<false><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, n, w.hitA, w.hitInst, stat, -1);
+        }
+        k_hits_export<<<grid, 128, 0, s>>>(scene, w.hitA, w.hitInst, n, out.as<VkrtHit>());
+        ctx->launches += 2;
+    }
+    cudaError_t e = cudaMemcpyAsync(hits, out.ptr, (size_t)n * sizeof(VkrtHit), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess)
+    {
+        e = cudaStreamSynchronize(s);
+    }
+    out.release();
+    if (e != cudaSuccess)
+    {
+        return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_trace_rays: ") + cudaGetErrorString(e));
+    }
+    return VKRT_SUCCESS;
+}
+
+} // namespace vkrt
