@@ -237,7 +237,8 @@ VKRT_API int vkrt_trace_rays(VkrtContext* ctx, const VkrtTlas* tlas, const VkrtR
 typedef struct VkrtStats
 {
     uint64_t raysPrimary, raysShadow, raysReflection;
-    uint64_t nodesVisited, trianglesTested; /* only counted when enabled with vkrt_stats_enable(ctx, 1) */
+    uint64_t nodesVisited, trianglesTested; /* closest-hit + any-hit; only counted when enabled with vkrt_stats_enable */
+    uint64_t nodesVisitedAny, trianglesTestedAny; /* the any-hit (shadow ray) share of the two totals above */
     uint64_t kernelLaunches;                /* kernels launched by this library */
     float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* last vkrt_trace, if timing enabled */
 } VkrtStats;

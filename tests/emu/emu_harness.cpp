@@ -1,0 +1,389 @@
+/*
+ * emu_harness.cpp — NO-GPU UNIT-TEST AID.  Not part of the product; nothing in libvkrt_b200.so links or calls it.
+ *
+ * The kernel LOGIC of libvkrt_b200 lives in `__host__ __device__` headers (vkrt_b200/csrc/*.cuh).  This file compiles
+ * those headers with g++ and drives them sequentially — one loop iteration per CUDA thread — so that the builder,
+ * the traversal and the shading restatement can be checked against the CPU oracle in the `-m "not gpu"` test tier,
+ * before any GPU time is spent.  Warp-level code (radix sort, queue compaction) is not emulated: the sort is replaced
+ * by std::stable_sort and the wavefront queues by a per-pixel loop; both are covered by the `-m gpu` tests.
+ */
+#include "../../vkrt_b200/csrc/builder.cuh"
+#include "../../vkrt_b200/csrc/shading.cuh"
+#include "../../vkrt_b200/csrc/traverse.cuh"
+
+#include <algorithm>
+#include <cfloat>
+#include <cstdio>
+#include <numeric>
+#include <vector>
+
+using namespace vkrt;
+
+struct EmuBlas
+{
+    std::vector<uint8_t> vertices;
+    std::vector<uint32_t> indices;
+    std::vector<uint32_t> firstTri;
+    std::vector<uint64_t> indexBase;
+    uint32_t stride = 0;
+    uint32_t triangleCount = 0;
+    std::vector<Node8> nodes;
+    std::vector<PackedTri> tris;
+    float boundsMin[3], boundsMax[3];
+    float sahCost = 0.f;
+};
+
+struct EmuScene
+{
+    EmuBlas* blas = nullptr;
+    std::vector<InstanceRecord> instances;
+    std::vector<InstanceBounds> bounds;
+    std::vector<VkrtSubmeshInfo> rows;
+    std::vector<std::vector<uint8_t>> texels;
+    std::vector<TextureRecord> textures;
+};
+
+extern "C" {
+
+EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t stride, const uint32_t* indices, size_t indexCount,
+                        const VkrtGeometryRange* ranges, uint32_t geometryCount)
+{
+    EmuBlas* b = new EmuBlas();
+    b->vertices.assign((const uint8_t*)vertices, (const uint8_t*)vertices + vertexBytes);
+    b->indices.assign(indices, indices + indexCount);
+    b->stride = stride;
+    b->firstTri.resize(geometryCount + 1);
+    b->indexBase.resize(std::max(geometryCount, 1u));
+    uint32_t n = 0;
+    for (uint32_t g = 0; g < geometryCount; ++g)
+    {
+        b->firstTri[g] = n;
+        b->indexBase[g] = ranges[g].indexByteOffset / 4;
+        n += ranges[g].primitiveCount;
+    }
+    b->firstTri[geometryCount] = n;
+    b->triangleCount = n;
+
+    GeometryTable geo;
+    geo.firstTri = b->firstTri.data();
+    geo.indexBase = b->indexBase.data();
+    geo.geometryCount = geometryCount;
+
+    const uint32_t nodeCapacity = std::max(1u, n / 2u + 8u);
+    b->nodes.assign(nodeCapacity, Node8{});
+    b->tris.assign(std::max(1u, n), PackedTri{});
+    if (n == 0)
+    {
+        Node8 root;
+        memset(&root, 0, sizeof(root));
+        root.ex = root.ey = root.ez = 1;
+        b->nodes[0] = root;
+        b->nodes.resize(1);
+        for (int k = 0; k < 3; ++k)
+        {
+            b->boundsMin[k] = b->boundsMax[k] = 0.f;
+        }
+        return b;
+    }
+
+    // k_tri_bounds
+    std::vector<float4> triLo(n), triHi(n);
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        F3 v0, v1, v2;
+        uint32_t g, p;
+        fetchTriangle(geo, b->vertices.data(), stride, b->indices.data(), i, v0, v1, v2, g, p);
+        const float4 l = make_float4(fminf(fminf(v0.x, v1.x), v2.x), fminf(fminf(v0.y, v1.y), v2.y), fminf(fminf(v0.z, v1.z), v2.z), 0.f);
+        const float4 h = make_float4(fmaxf(fmaxf(v0.x, v1.x), v2.x), fmaxf(fmaxf(v0.y, v1.y), v2.y), fmaxf(fmaxf(v0.z, v1.z), v2.z), 0.f);
+        triLo[i] = l, triHi[i] = h;
+        const float lv[3] = {l.x, l.y, l.z}, hv[3] = {h.x, h.y, h.z};
+        for (int k = 0; k < 3; ++k)
+        {
+            const float c = 0.5f * (lv[k] + hv[k]);
+            lo[k] = fminf(lo[k], lv[k]), hi[k] = fmaxf(hi[k], hv[k]);
+            clo[k] = fminf(clo[k], c), chi[k] = fmaxf(chi[k], c);
+        }
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        b->boundsMin[k] = lo[k], b->boundsMax[k] = hi[k];
+    }
+    // k_morton
+    std::vector<uint32_t> keys(n), vals(n);
+    const F3 clo3 = f3(clo[0], clo[1], clo[2]);
+    const F3 inv = f3(chi[0] > clo[0] ? 1.0f / (chi[0] - clo[0]) : 0.f, chi[1] > clo[1] ? 1.0f / (chi[1] - clo[1]) : 0.f,
+                      chi[2] > clo[2] ? 1.0f / (chi[2] - clo[2]) : 0.f);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        const float4 l = triLo[i], h = triHi[i];
+        keys[i] = morton30(f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)), clo3, inv);
+        vals[i] = i;
+    }
+    // radix sort stand-in (stable, like the GPU LSD sort)
+    std::vector<uint32_t> perm(n);
+    std::iota(perm.begin(), perm.end(), 0u);
+    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t c) { return keys[a] < keys[c]; });
+    std::vector<uint32_t> sk(n), sv(n);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        sk[i] = keys[perm[i]], sv[i] = vals[perm[i]];
+    }
+    // k_lbvh
+    std::vector<int2> children(std::max(1u, n));
+    std::vector<float4> nlo(std::max(1u, n)), nhi(std::max(1u, n));
+    std::vector<int> flags(std::max(1u, n), -1);
+    int root = 0;
+    Bvh2 bvh;
+    bvh.children = children.data(), bvh.lo = nlo.data(), bvh.hi = nhi.data(), bvh.flags = flags.data();
+    bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triLo = triLo.data(), bvh.triHi = triHi.data();
+    bvh.count = n, bvh.root = &root;
+    if (n > 1)
+    {
+        for (uint32_t i = 0; i < n; ++i)
+        {
+            lbvhClimb(bvh, i);
+        }
+    }
+    // collapse
+    std::vector<int> taskRef(nodeCapacity);
+    std::vector<uint32_t> primSource(n);
+    uint32_t nodeCounter = 1, primCounter = 0, overflow = 0;
+    float sah[2] = {0.f, 0.f};
+    CollapseArgs ca;
+    ca.bvh2 = bvh, ca.nodes = b->nodes.data(), ca.taskRef = taskRef.data(), ca.primSource = primSource.data();
+    ca.nodeCounter = &nodeCounter, ca.primCounter = &primCounter, ca.sahAccum = sah, ca.nodeCapacity = nodeCapacity;
+    ca.overflow = &overflow;
+    taskRef[0] = n > 1 ? root : ~0;
+    uint32_t first = 0, last = 1;
+    while (first < last)
+    {
+        for (uint32_t i = first; i < last; ++i)
+        {
+            collapseNode(ca, i);
+        }
+        first = last;
+        last = nodeCounter;
+    }
+    if (overflow || primCounter != n)
+    {
+        fprintf(stderr, "emu_blas_build: collapse failed (overflow=%u packed=%u of %u)\n", overflow, primCounter, n);
+        delete b;
+        return nullptr;
+    }
+    b->nodes.resize(last);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        b->tris[i] = packTriangle(geo, b->vertices.data(), stride, b->indices.data(), primSource[i]);
+    }
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    const float ra = dx * dy + dy * dz + dz * dx;
+    b->sahCost = ra > 0.f ? (sah[0] + sah[1]) / ra : 0.f;
+    return b;
+}
+
+void emu_blas_destroy(EmuBlas* b) { delete b; }
+uint32_t emu_blas_node_count(const EmuBlas* b) { return (uint32_t)b->nodes.size(); }
+uint32_t emu_blas_triangle_count(const EmuBlas* b) { return b->triangleCount; }
+const void* emu_blas_nodes(const EmuBlas* b) { return b->nodes.data(); }
+const void* emu_blas_triangles(const EmuBlas* b) { return b->tris.data(); }
+float emu_blas_sah(const EmuBlas* b) { return b->sahCost; }
+
+EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t instanceCount, const VkrtSubmeshInfo* rows, uint32_t rowCount,
+                           const VkrtImage* images, uint32_t imageCount)
+{
+    EmuScene* s = new EmuScene();
+    s->blas = blas;
+    s->instances.resize(instanceCount);
+    s->bounds.resize(instanceCount);
+    for (uint32_t i = 0; i < instanceCount; ++i)
+    {
+        InstanceRecord& r = s->instances[i];
+        memset(&r, 0, sizeof(r));
+        memcpy(r.o2w, instances + 12 * (size_t)i, 48);
+        affineInverseHost(r.o2w, r.w2o);
+        r.nodes = blas->nodes.data(), r.tris = blas->tris.data();
+        r.vertices = blas->vertices.data(), r.indices = blas->indices.data();
+        r.vertexStride = blas->stride;
+        InstanceBounds& wb = s->bounds[i];
+        for (int k = 0; k < 3; ++k)
+        {
+            wb.lo[k] = INFINITY, wb.hi[k] = -INFINITY;
+        }
+        for (int corner = 0; corner < 8; ++corner)
+        {
+            const F3 p = f3((corner & 1) ? blas->boundsMax[0] : blas->boundsMin[0], (corner & 2) ? blas->boundsMax[1] : blas->boundsMin[1],
+                            (corner & 4) ? blas->boundsMax[2] : blas->boundsMin[2]);
+            const F3 q = affinePoint(r.o2w, p);
+            wb.lo[0] = std::min(wb.lo[0], q.x), wb.lo[1] = std::min(wb.lo[1], q.y), wb.lo[2] = std::min(wb.lo[2], q.z);
+            wb.hi[0] = std::max(wb.hi[0], q.x), wb.hi[1] = std::max(wb.hi[1], q.y), wb.hi[2] = std::max(wb.hi[2], q.z);
+        }
+        for (int k = 0; k < 3; ++k)
+        {
+            const float padAbs = (std::fabs(wb.lo[k]) + std::fabs(wb.hi[k])) * 1e-5f + 1e-30f;
+            wb.lo[k] -= padAbs, wb.hi[k] += padAbs;
+        }
+    }
+    if (rows)
+    {
+        s->rows.assign(rows, rows + rowCount);
+    }
+    s->texels.resize(imageCount);
+    s->textures.resize(imageCount);
+    for (uint32_t i = 0; i < imageCount; ++i)
+    {
+        s->texels[i].assign(images[i].rgba8, images[i].rgba8 + (size_t)images[i].width * images[i].height * 4);
+        s->textures[i].texels = s->texels[i].data();
+        s->textures[i].width = images[i].width, s->textures[i].height = images[i].height;
+    }
+    return s;
+}
+
+void emu_scene_destroy(EmuScene* s) { delete s; }
+
+void emu_trace_rays(const EmuScene* s, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits, uint64_t* nodesVisited,
+                    uint64_t* trisTested)
+{
+    TraceCounters tc;
+    uint64_t nodes = 0, tris = 0;
+    for (uint64_t i = 0; i < count; ++i)
+    {
+        BestHit best;
+        best.t = rays[i].tmax, best.b1 = best.b2 = 0.f;
+        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+        const F3 o = f3(rays[i].origin[0], rays[i].origin[1], rays[i].origin[2]);
+        const F3 d = f3(rays[i].direction[0], rays[i].direction[1], rays[i].direction[2]);
+        tc.nodes = tc.tris = 0;
+        bool found;
+        if (anyHit)
+        {
+            found = traceScene<true>(s->instances.data(), s->bounds.data(), (uint32_t)s->instances.size(), o, d, rays[i].tmin, best, &tc);
+        }
+        else
+        {
+            found = traceScene<false>(s->instances.data(), s->bounds.data(), (uint32_t)s->instances.size(), o, d, rays[i].tmin, best, &tc);
+        }
+        nodes += tc.nodes, tris += tc.tris;
+        VkrtHit& h = hits[i];
+        if (!found)
+        {
+            h.t = h.b1 = h.b2 = 0.f;
+            h.instance = h.geometry = h.primitive = kInvalid;
+        }
+        else
+        {
+            const PackedTri& t = s->instances[best.instance].tris[best.tri];
+            h.t = best.t, h.b1 = anyHit ? 0.f : best.b1, h.b2 = anyHit ? 0.f : best.b2;
+            h.instance = best.instance;
+            h.geometry = anyHit ? 0u : t.geometry, h.primitive = anyHit ? 0u : t.primitive;
+        }
+        if (tc.overflow)
+        {
+            fprintf(stderr, "emu_trace_rays: traversal stack overflow\n");
+        }
+    }
+    if (nodesVisited)
+    {
+        *nodesVisited = nodes;
+    }
+    if (trisTested)
+    {
+        *trisTested = tris;
+    }
+}
+
+// Per-pixel emulation of vkrt_trace (the wavefront stages run back to back for one path).
+void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32_t height, uint32_t spp, uint32_t x0, uint32_t y0,
+                uint32_t x1, uint32_t y1, uint32_t strideX, uint32_t strideY, float* rgb32f, uint8_t* bgra8, uint32_t* triangleId,
+                uint8_t* shadowMask)
+{
+    const InstanceRecord* inst = s->instances.data();
+    const InstanceBounds* bnd = s->bounds.data();
+    const uint32_t ic = (uint32_t)s->instances.size();
+    spp = std::max(spp, 1u);
+    for (uint32_t y = y0; y < std::min(y1, height); y += std::max(strideY, 1u))
+    {
+        for (uint32_t x = x0; x < std::min(x1, width); x += std::max(strideX, 1u))
+        {
+            F3 sampleSum = f3(0, 0, 0);
+            uint32_t aovTri = kInvalid;
+            uint8_t aovMask = 0;
+            for (uint32_t sample = 0; sample < spp; ++sample)
+            {
+                float jx, jy;
+                sampleOffset(sample, spp, jx, jy);
+                F3 o, d;
+                primaryRay(*u, width, height, x, y, jx, jy, o, d);
+                F3 acc = f3(0, 0, 0);
+                float attenuation = 1.0f;
+                for (int depth = 0; depth < 2; ++depth)
+                {
+                    BestHit best;
+                    best.t = kRayTMax, best.b1 = best.b2 = 0.f;
+                    best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+                    traceScene<false>(inst, bnd, ic, o, d, kRayTMin, best, nullptr);
+                    if (best.tri == kInvalid)
+                    {
+                        acc.x += 0.8f, acc.y += 0.8f, acc.z += 1.0f;
+                        break;
+                    }
+                    const PackedTri& t = inst[best.instance].tris[best.tri];
+                    const SurfacePoint sp = shadeSurface(inst[best.instance], s->rows.data(), s->textures.data(), t.geometry, t.primitive,
+                                                         best.b1, best.b2);
+                    uint32_t bits = 0, cast = 0;
+                    for (int i = 0; i < 4; ++i)
+                    {
+                        const LightTerm lt = lightTerm(*u, i, sp.worldPos, sp.normal);
+                        if (lt.castShadow)
+                        {
+                            cast |= 1u << i;
+                            BestHit sh;
+                            sh.t = lt.distance, sh.b1 = sh.b2 = 0.f;
+                            sh.tri = kInvalid, sh.instance = kInvalid, sh.buildIndex = kInvalid;
+                            if (traceScene<true>(inst, bnd, ic, sp.worldPos, lt.dir, kRayTMin, sh, nullptr))
+                            {
+                                bits |= 1u << i;
+                            }
+                        }
+                    }
+                    if (depth == 0 && sample == 0)
+                    {
+                        aovTri = (best.instance << 24) + (uint32_t)s->rows[t.geometry].indexBufferOffset + t.primitive;
+                        aovMask = (uint8_t)(bits | (cast << 4));
+                    }
+                    const ResolveOut r = shadeResolve(*u, s->rows.data(), s->textures.data(), sp, bits, attenuation, d);
+                    acc.x += r.hitValue.x, acc.y += r.hitValue.y, acc.z += r.hitValue.z;
+                    attenuation = r.attenuation;
+                    if (!r.reflect)
+                    {
+                        break;
+                    }
+                    o = sp.worldPos, d = r.rayDir;
+                }
+                sampleSum = sample == 0 ? acc : sampleSum + acc;
+            }
+            const F3 out = spp > 1 ? sampleSum / (float)spp : sampleSum;
+            const size_t pix = (size_t)y * width + x;
+            if (rgb32f)
+            {
+                rgb32f[pix * 3] = out.x, rgb32f[pix * 3 + 1] = out.y, rgb32f[pix * 3 + 2] = out.z;
+            }
+            if (bgra8)
+            {
+                const uint32_t px = packBgra8(out);
+                memcpy(bgra8 + pix * 4, &px, 4);
+            }
+            if (triangleId)
+            {
+                triangleId[pix] = aovTri;
+            }
+            if (shadowMask)
+            {
+                shadowMask[pix] = aovMask;
+            }
+        }
+    }
+}
+
+} // extern "C"

@@ -1,0 +1,142 @@
+"""CPU tier: the kernel LOGIC of libvkrt_b200 (the `__host__ __device__` headers compiled by g++ into the emulation
+harness, tests/emu) against the oracle — builder invariants, ray-level parity, frame-level parity.  The same
+comparisons run against the real CUDA library in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import helpers as H
+from bvh_check import check_bvh8
+from vkrt_b200 import camera, scenes
+from vkrt_b200.raytracer import flatten_model
+
+
+def test_builder_invariants_small_counts():
+    for n in (0, 1, 2, 3, 4, 5, 9, 33):
+        flat = flatten_model(scenes.random_soup(max(n, 1), seed=n + 1, geometries=1))
+        if n == 0:
+            flat["ranges"][0, 0] = 0
+            flat["indices"] = flat["indices"][:0]
+        e = H.EmuScene(flat, scenes.identity_instance(1.0))
+        nodes, tris = e.read_blas()
+        check_bvh8(nodes, tris, n)
+
+
+def test_builder_invariants_soup_and_duplicates():
+    flat = flatten_model(scenes.random_soup(5000, seed=7, geometries=4))
+    e = H.EmuScene(flat, scenes.identity_instance(1.0))
+    nodes, tris = e.read_blas()
+    depth, slots, inner = check_bvh8(nodes, tris, 5000)
+    assert depth < 40 and inner < 5000 // 2 + 8
+    # all centroids identical: Morton codes tie, the index tie-break must still give a valid tree
+    m = scenes.random_soup(300, seed=9, geometries=1)
+    m["submeshes"][0]["vertices"][:, :3] = np.tile(m["submeshes"][0]["vertices"][:3, :3], (300, 1))
+    e = H.EmuScene(flatten_model(m), scenes.identity_instance(1.0))
+    nodes, tris = e.read_blas()
+    check_bvh8(nodes, tris, 300)
+
+
+def test_builder_invariants_sponza(sponza_flat):
+    e = H.EmuScene(sponza_flat, scenes.REFERENCE_INSTANCE)
+    nodes, tris = e.read_blas()
+    depth, slots, inner = check_bvh8(nodes, tris, 262267)
+    assert slots == 262267 and depth < 48
+    # geometry / primitive tags follow the reference's (geometryIndex, primitiveID) numbering
+    first = np.concatenate([[0], np.cumsum(sponza_flat["ranges"][:, 0].astype(np.int64))])
+    assert np.array_equal(first[tris["geometry"]] + tris["primitive"], tris["buildIndex"])
+
+
+@pytest.mark.parametrize("seed", [3, 4])
+def test_ray_parity_soup(seed):
+    flat = flatten_model(scenes.random_soup(6000, seed=seed))
+    inst = scenes.identity_instance(1.0)
+    o, e = H.OracleScene(flat, inst), H.EmuScene(flat, inst)
+    rays = H.random_rays(30000, seed, (-12, -8, -10), (12, 8, 10))
+    rays["tmax"][::7] = 3.0  # short rays exercise the exclusive tmax
+    ho, _ = o.trace_rays(rays)
+    he, nodes, tris = e.trace_rays(rays)
+    assert np.array_equal(ho, he)
+    ao, _ = o.trace_rays(rays, any_hit=True)
+    ae, _, _ = e.trace_rays(rays, any_hit=True)
+    assert np.array_equal(ao["instance"] != 0xFFFFFFFF, ae["instance"] != 0xFFFFFFFF)
+
+
+def test_ray_parity_degenerate_rays():
+    flat = flatten_model(scenes.analytic_scene())
+    inst = scenes.identity_instance(1.0)
+    o, e = H.OracleScene(flat, inst), H.EmuScene(flat, inst)
+    rays = np.zeros(8, dtype=H.B.RAY_DTYPE)
+    rays["origin"] = (0, 3, 0)
+    rays["tmin"], rays["tmax"] = 0.001, 1000
+    rays["direction"] = [(0, -1, 0), (0, 0, 0), (np.nan, -1, 0), (np.inf, -1, 0), (0, -1, 0), (1, 0, 0), (0, -1e-30, 0), (0, 1, 0)]
+    rays["tmax"][4] = 0.0005  # tmax < tmin
+    rays["origin"][5] = (-20, 0, 0)  # ray lying exactly in the floor plane
+    ho, _ = o.trace_rays(rays, mode=H.MODE_BRUTE)
+    he, _, _ = e.trace_rays(rays)
+    assert np.array_equal(ho, he)
+    assert ho["instance"][0] == 0 and (ho["instance"][1:5] == 0xFFFFFFFF).all()
+
+
+def test_ray_parity_shared_edges_and_duplicates():
+    """Rays aimed exactly at shared edges/vertices of a regular grid and at exactly duplicated triangles: watertight
+    test + equal-t tie-break must give the same winner as the oracle."""
+    n = 12
+    xs = np.linspace(-3, 3, n + 1, dtype=np.float32)
+    gx, gz = np.meshgrid(xs, xs)
+    pos = np.stack([gx.ravel(), np.zeros_like(gx).ravel(), gz.ravel()], axis=1)
+    quads = [(r * (n + 1) + c, r * (n + 1) + c + 1, (r + 1) * (n + 1) + c + 1, (r + 1) * (n + 1) + c) for r in range(n) for c in range(n)]
+    idx = np.array([[a, b, c, a, c, d] for a, b, c, d in quads], dtype=np.uint32).ravel()
+    idx = np.concatenate([idx, np.roll(idx.reshape(-1, 3), 1, axis=1).ravel()])  # every triangle twice
+    v = scenes.make_vertex_array(pos, np.tile([0, 1, 0], (len(pos), 1)), pos[:, [0, 2]], np.tile([1, 0, 0, 1], (len(pos), 1)))
+    model = {"submeshes": [{"vertices": v, "indices": idx, "material": 0}], "materials": [(1, 2, 0)],
+             "images": scenes.analytic_scene()["images"]}
+    flat = flatten_model(model)
+    inst = scenes.identity_instance(1.0)
+    o, e = H.OracleScene(flat, inst), H.EmuScene(flat, inst)
+    rays = np.zeros(len(pos) * 2, dtype=H.B.RAY_DTYPE)
+    rays["origin"][: len(pos)] = pos + np.array([0, 5, 0], dtype=np.float32)
+    rays["direction"][: len(pos)] = (0, -1, 0)
+    rays["origin"][len(pos):] = (0.1, 4, 0.2)
+    rays["direction"][len(pos):] = pos - np.array([0.1, 4, 0.2], dtype=np.float32)
+    rays["tmin"], rays["tmax"] = 0.001, 1000
+    ho, _ = o.trace_rays(rays, mode=H.MODE_BRUTE)
+    hb, _ = o.trace_rays(rays, mode=H.MODE_BVH)
+    he, _, _ = e.trace_rays(rays)
+    assert np.array_equal(ho, hb) and np.array_equal(ho, he)
+    interior = ho["instance"][: len(pos)] != 0xFFFFFFFF
+    assert interior.mean() > 0.8  # watertight: grid vertices and edges are hit, not leaked through
+    assert (ho["primitive"][ho["instance"] != 0xFFFFFFFF] < 2 * n * n).all()  # ties go to the first copy
+
+
+def test_frame_parity_analytic_and_instances():
+    flat = flatten_model(scenes.analytic_scene(metallic_floor=True))
+    inst = np.stack([scenes.identity_instance(1.0), scenes.identity_instance(0.5, (10, 0, -4)), scenes.identity_instance(1.0, (-18, 1, 2))])
+    o, e = H.OracleScene(flat, inst), H.EmuScene(flat, inst)
+    W, Hh = 128, 72
+    u = camera.make_uniforms(W, Hh, position=(0, 5, 16), rotation=(-0.25, 0.1, 0))
+    a, b = o.render(u, W, Hh), e.render(u, W, Hh)
+    c = H.compare_frames(a, b)
+    assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"] and c["bgra_max_diff"] == 0
+    assert len(np.unique(a["tri"] >> 24)) >= 3  # several instances (and the sky) are visible
+
+
+def test_frame_parity_sponza_config1_subset(sponza_flat):
+    o, e = H.OracleScene(sponza_flat, scenes.REFERENCE_INSTANCE), H.EmuScene(sponza_flat, scenes.REFERENCE_INSTANCE)
+    W, Hh = 1280, 720
+    u = camera.make_uniforms(W, Hh)
+    a, b = o.render(u, W, Hh, stride=(5, 5)), e.render(u, W, Hh, stride=(5, 5))
+    sel = np.zeros((Hh, W), dtype=bool)
+    sel[::5, ::5] = True
+    c = H.compare_frames(a, b, sel)
+    assert c["tri_agree"] >= 0.999 and c["mask_agree"] >= 0.999 and c["bgra_max_diff"] <= 1
+    assert c["tri_agree"] == 1.0 and c["rgb_bit_equal"]  # the design goal is bit equality, the bar above is the contract
+
+
+def test_frame_parity_spp8_jitter(sponza_flat):
+    o, e = H.OracleScene(sponza_flat, scenes.REFERENCE_INSTANCE), H.EmuScene(sponza_flat, scenes.REFERENCE_INSTANCE)
+    W, Hh = 384, 216
+    u = camera.make_uniforms(W, Hh)
+    a, b = o.render(u, W, Hh, spp=8, stride=(3, 3)), e.render(u, W, Hh, spp=8, stride=(3, 3))
+    sel = np.zeros((Hh, W), dtype=bool)
+    sel[::3, ::3] = True
+    c = H.compare_frames(a, b, sel)
+    assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"]

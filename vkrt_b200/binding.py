@@ -1,0 +1,420 @@
+"""ctypes binding of include/vkrt.h.  No fallbacks: a missing library or a missing CUDA device raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libvkrt_b200.so")
+
+AOV_BGRA8, AOV_RGB32F, AOV_TRIANGLE_ID, AOV_SHADOW_MASK = 0, 1, 2, 3
+BUILD_DEFAULT, BUILD_PREFER_FAST_BUILD, BUILD_INPUT_ON_DEVICE = 0, 1, 2
+TRACE_DEFAULT, TRACE_NO_AOV = 0, 1
+TILE = 64
+UNIQUE_ID_BYTES = 128
+
+
+class VkrtError(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__(f"vkrt error {code}: {text}")
+        self.code = code
+
+
+class GeometryRange(C.Structure):
+    _fields_ = [("primitiveCount", C.c_uint32), ("maxVertex", C.c_uint32), ("indexByteOffset", C.c_uint64)]
+
+
+class BuildSizes(C.Structure):
+    _fields_ = [("accelerationStructureSize", C.c_uint64), ("buildScratchSize", C.c_uint64), ("geometryCopySize", C.c_uint64)]
+
+
+class BlasInfo(C.Structure):
+    _fields_ = [
+        ("triangleCount", C.c_uint64),
+        ("nodeCount", C.c_uint64),
+        ("nodeBytes", C.c_uint64),
+        ("triangleBytes", C.c_uint64),
+        ("boundsMin", C.c_float * 3),
+        ("boundsMax", C.c_float * 3),
+        ("sahCost", C.c_float),
+        ("buildMilliseconds", C.c_float),
+    ]
+
+
+class Instance(C.Structure):
+    _fields_ = [
+        ("transform", C.c_float * 12),
+        ("instanceCustomIndex", C.c_uint32, 24),
+        ("mask", C.c_uint32, 8),
+        ("sbtOffset", C.c_uint32, 24),
+        ("flags", C.c_uint32, 8),
+        ("accelerationStructureReference", C.c_uint64),
+    ]
+
+
+class SubmeshInfo(C.Structure):
+    _fields_ = [
+        ("baseColorTextureIndex", C.c_int32),
+        ("metallicRoughnessTextureIndex", C.c_int32),
+        ("normalTextureIndex", C.c_int32),
+        ("indexBufferOffset", C.c_int32),
+    ]
+
+
+class Image(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("rgba8", C.c_void_p)]
+
+
+class Uniforms(C.Structure):
+    _fields_ = [
+        ("viewInverse", C.c_float * 16),
+        ("projInverse", C.c_float * 16),
+        ("position", C.c_float * 4),
+        ("right", C.c_float * 4),
+        ("up", C.c_float * 4),
+        ("forward", C.c_float * 4),
+        ("lightPositions", (C.c_float * 4) * 4),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("raysPrimary", C.c_uint64),
+        ("raysShadow", C.c_uint64),
+        ("raysReflection", C.c_uint64),
+        ("nodesVisited", C.c_uint64),
+        ("trianglesTested", C.c_uint64),
+        ("nodesVisitedAny", C.c_uint64),
+        ("trianglesTestedAny", C.c_uint64),
+        ("kernelLaunches", C.c_uint64),
+        ("msRaygen", C.c_float),
+        ("msTraceClosest", C.c_float),
+        ("msShade", C.c_float),
+        ("msTraceAny", C.c_float),
+        ("msResolve", C.c_float),
+        ("msTotal", C.c_float),
+    ]
+
+
+RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("tmin", "<f4"), ("direction", "<f4", 3), ("tmax", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("geometry", "<u4"), ("primitive", "<u4")])
+NODE_DTYPE = np.dtype(
+    [
+        ("p", "<f4", 3),
+        ("e", "u1", 3),
+        ("imask", "u1"),
+        ("childBase", "<u4"),
+        ("primBase", "<u4"),
+        ("meta", "u1", 8),
+        ("qlox", "u1", 8),
+        ("qloy", "u1", 8),
+        ("qloz", "u1", 8),
+        ("qhix", "u1", 8),
+        ("qhiy", "u1", 8),
+        ("qhiz", "u1", 8),
+    ]
+)
+TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("v1", "<f4", 3), ("v2", "<f4", 3), ("geometry", "<u4"), ("primitive", "<u4"), ("buildIndex", "<u4")])
+assert NODE_DTYPE.itemsize == 80 and TRI_DTYPE.itemsize == 48 and RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 24
+
+# every symbol include/vkrt.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "vkrt_version",
+    "vkrt_context_create",
+    "vkrt_context_destroy",
+    "vkrt_last_error",
+    "vkrt_context_synchronize",
+    "vkrt_context_stream",
+    "vkrt_blas_sizes",
+    "vkrt_blas_build",
+    "vkrt_blas_rebuild",
+    "vkrt_blas_destroy",
+    "vkrt_blas_reference",
+    "vkrt_blas_info",
+    "vkrt_blas_read",
+    "vkrt_tlas_build",
+    "vkrt_tlas_destroy",
+    "vkrt_materials_set",
+    "vkrt_textures_set",
+    "vkrt_frame_create",
+    "vkrt_frame_destroy",
+    "vkrt_trace",
+    "vkrt_frame_read",
+    "vkrt_frame_device_bgra8",
+    "vkrt_trace_rays",
+    "vkrt_stats_enable",
+    "vkrt_stats_reset",
+    "vkrt_stats_get",
+    "vkrt_comm_unique_id",
+    "vkrt_comm_init",
+    "vkrt_comm_emulate",
+    "vkrt_comm_destroy",
+    "vkrt_tile_owner",
+    "vkrt_tiles_gather",
+]
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """Loads libvkrt_b200.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise FileNotFoundError(f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(there is no CPU fallback)")
+    lib = C.CDLL(p)
+    vp, u32, u64, i32, sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
+    sig = {
+        "vkrt_version": (i32, []),
+        "vkrt_context_create": (i32, [i32, C.POINTER(vp)]),
+        "vkrt_context_destroy": (None, [vp]),
+        "vkrt_last_error": (C.c_char_p, [vp]),
+        "vkrt_context_synchronize": (i32, [vp]),
+        "vkrt_context_stream": (vp, [vp]),
+        "vkrt_blas_sizes": (i32, [vp, C.POINTER(GeometryRange), u32, u64, u64, C.POINTER(BuildSizes)]),
+        "vkrt_blas_build": (i32, [vp, vp, sz, u32, vp, sz, C.POINTER(GeometryRange), u32, u32, C.POINTER(vp)]),
+        "vkrt_blas_rebuild": (i32, [vp, vp, vp, sz, u32]),
+        "vkrt_blas_destroy": (None, [vp, vp]),
+        "vkrt_blas_reference": (u64, [vp]),
+        "vkrt_blas_info": (i32, [vp, vp, C.POINTER(BlasInfo)]),
+        "vkrt_blas_read": (i32, [vp, vp, vp, sz, vp, sz]),
+        "vkrt_tlas_build": (i32, [vp, C.POINTER(Instance), u32, C.POINTER(vp)]),
+        "vkrt_tlas_destroy": (None, [vp, vp]),
+        "vkrt_materials_set": (i32, [vp, C.POINTER(SubmeshInfo), u32]),
+        "vkrt_textures_set": (i32, [vp, C.POINTER(Image), u32]),
+        "vkrt_frame_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
+        "vkrt_frame_destroy": (None, [vp, vp]),
+        "vkrt_trace": (i32, [vp, vp, C.POINTER(Uniforms), u32, u32, u32, vp]),
+        "vkrt_frame_read": (i32, [vp, vp, i32, vp, sz]),
+        "vkrt_frame_device_bgra8": (vp, [vp]),
+        "vkrt_trace_rays": (i32, [vp, vp, vp, u64, i32, vp]),
+        "vkrt_stats_enable": (i32, [vp, i32, i32]),
+        "vkrt_stats_reset": (i32, [vp]),
+        "vkrt_stats_get": (i32, [vp, C.POINTER(Stats)]),
+        "vkrt_comm_unique_id": (i32, [vp]),
+        "vkrt_comm_init": (i32, [vp, vp, i32, i32]),
+        "vkrt_comm_emulate": (i32, [vp, i32, i32]),
+        "vkrt_comm_destroy": (i32, [vp]),
+        "vkrt_tile_owner": (i32, [u32, u32, u32, i32]),
+        "vkrt_tiles_gather": (i32, [vp, vp, i32]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One CUDA device + stream (headless stand-in for the device half of the reference's Context)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        r = self.lib.vkrt_context_create(device, C.byref(h))
+        if r != 0:
+            raise VkrtError(r, (self.lib.vkrt_last_error(None) or b"").decode())
+        self.handle = h
+        self._keep = []
+
+    def check(self, r: int):
+        if r != 0:
+            raise VkrtError(r, (self.lib.vkrt_last_error(self.handle) or b"").decode())
+
+    def close(self):
+        if self.handle:
+            self.lib.vkrt_context_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self.check(self.lib.vkrt_context_synchronize(self.handle))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.vkrt_context_stream(self.handle) or 0)
+
+    def set_materials(self, rows: np.ndarray):
+        rows = np.ascontiguousarray(rows, dtype=np.int32).reshape(-1, 4)
+        self.check(self.lib.vkrt_materials_set(self.handle, rows.ctypes.data_as(C.POINTER(SubmeshInfo)), rows.shape[0]))
+
+    def set_textures(self, images: Sequence[np.ndarray]):
+        arr = (Image * len(images))()
+        keep = []
+        for i, im in enumerate(images):
+            im = np.ascontiguousarray(im, dtype=np.uint8)
+            assert im.ndim == 3 and im.shape[2] == 4
+            keep.append(im)
+            arr[i].width, arr[i].height, arr[i].rgba8 = im.shape[1], im.shape[0], im.ctypes.data
+        self.check(self.lib.vkrt_textures_set(self.handle, arr, len(images)))
+
+    def stats_enable(self, count_traversal: bool, time_stages: bool = False):
+        self.check(self.lib.vkrt_stats_enable(self.handle, int(count_traversal), int(time_stages)))
+
+    def stats_reset(self):
+        self.check(self.lib.vkrt_stats_reset(self.handle))
+
+    def stats(self) -> Stats:
+        s = Stats()
+        self.check(self.lib.vkrt_stats_get(self.handle, C.byref(s)))
+        return s
+
+    def comm_emulate(self, rank: int, size: int):
+        self.check(self.lib.vkrt_comm_emulate(self.handle, rank, size))
+
+    def comm_init(self, unique_id: bytes, rank: int, size: int):
+        buf = (C.c_uint8 * UNIQUE_ID_BYTES).from_buffer_copy(unique_id)
+        self.check(self.lib.vkrt_comm_init(self.handle, buf, rank, size))
+
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        lib = load_library()
+        buf = (C.c_uint8 * UNIQUE_ID_BYTES)()
+        r = lib.vkrt_comm_unique_id(buf)
+        if r != 0:
+            raise VkrtError(r, (lib.vkrt_last_error(None) or b"").decode())
+        return bytes(buf)
+
+
+class Blas:
+    def __init__(self, ctx: Context, vertices: np.ndarray, indices: np.ndarray, ranges: np.ndarray, flags: int = 0, stride: int = 64):
+        """vertices: (V,16) float32 (Model::Vertex) or raw bytes with `stride`; indices: global u32; ranges: rows of
+        (primitiveCount, maxVertex, indexByteOffset)."""
+        self.ctx = ctx
+        v = np.ascontiguousarray(vertices)
+        idx = np.ascontiguousarray(indices, dtype=np.uint32)
+        rng = (GeometryRange * len(ranges))()
+        for i, r in enumerate(ranges):
+            rng[i].primitiveCount, rng[i].maxVertex, rng[i].indexByteOffset = int(r[0]), int(r[1]), int(r[2])
+        h = C.c_void_p()
+        ctx.check(ctx.lib.vkrt_blas_build(ctx.handle, _ptr(v), v.nbytes, stride, _ptr(idx), idx.size, rng, len(ranges), flags, C.byref(h)))
+        self.handle = h
+        self._ranges = rng
+
+    def rebuild(self, vertices: np.ndarray, flags: int = 0):
+        v = np.ascontiguousarray(vertices)
+        self.ctx.check(self.ctx.lib.vkrt_blas_rebuild(self.ctx.handle, self.handle, _ptr(v), v.nbytes, flags))
+
+    @property
+    def reference(self) -> int:
+        return int(self.ctx.lib.vkrt_blas_reference(self.handle))
+
+    def info(self) -> BlasInfo:
+        out = BlasInfo()
+        self.ctx.check(self.ctx.lib.vkrt_blas_info(self.ctx.handle, self.handle, C.byref(out)))
+        return out
+
+    def read(self):
+        info = self.info()
+        nodes = np.zeros(int(info.nodeCount), dtype=NODE_DTYPE)
+        tris = np.zeros(int(info.triangleCount), dtype=TRI_DTYPE)
+        self.ctx.check(self.ctx.lib.vkrt_blas_read(self.ctx.handle, self.handle, _ptr(nodes), nodes.nbytes,
+                                                   _ptr(tris) if tris.size else None, tris.nbytes))
+        return nodes, tris
+
+    def close(self):
+        if self.handle and self.ctx.handle:
+            self.ctx.lib.vkrt_blas_destroy(self.ctx.handle, self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Tlas:
+    def __init__(self, ctx: Context, blases: Sequence[Blas], transforms: np.ndarray):
+        """transforms: (N,12) row-major 3x4; blases: one Blas per instance (or a single one, shared)."""
+        self.ctx = ctx
+        t = np.ascontiguousarray(transforms, dtype=np.float32).reshape(-1, 12)
+        n = t.shape[0]
+        inst = (Instance * n)()
+        for i in range(n):
+            b = blases[i] if len(blases) > 1 else blases[0]
+            for k in range(12):
+                inst[i].transform[k] = float(t[i, k])
+            inst[i].instanceCustomIndex = 0
+            inst[i].mask = 0xFF
+            inst[i].sbtOffset = 0
+            inst[i].flags = 0x1  # VK_GEOMETRY_INSTANCE_TRIANGLE_FACING_CULL_DISABLE_BIT_KHR
+            inst[i].accelerationStructureReference = b.reference
+        h = C.c_void_p()
+        ctx.check(ctx.lib.vkrt_tlas_build(ctx.handle, inst, n, C.byref(h)))
+        self.handle = h
+        self._blases = list(blases)
+
+    def trace_rays(self, rays: np.ndarray, any_hit: bool = False) -> np.ndarray:
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        self.ctx.check(self.ctx.lib.vkrt_trace_rays(self.ctx.handle, self.handle, _ptr(rays), rays.shape[0], int(any_hit), _ptr(hits)))
+        return hits
+
+    def close(self):
+        if self.handle and self.ctx.handle:
+            self.ctx.lib.vkrt_tlas_destroy(self.ctx.handle, self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Frame:
+    def __init__(self, ctx: Context, width: int, height: int):
+        self.ctx, self.width, self.height = ctx, width, height
+        h = C.c_void_p()
+        ctx.check(ctx.lib.vkrt_frame_create(ctx.handle, width, height, C.byref(h)))
+        self.handle = h
+
+    def trace(self, tlas: Tlas, uniforms: Uniforms, spp: int = 1, frame_index: int = 0, flags: int = 0):
+        self.ctx.check(self.ctx.lib.vkrt_trace(self.ctx.handle, tlas.handle, C.byref(uniforms), spp, frame_index, flags, self.handle))
+
+    def gather(self, root: int = 0):
+        self.ctx.check(self.ctx.lib.vkrt_tiles_gather(self.ctx.handle, self.handle, root))
+
+    def read(self, aov: int, out: Optional[np.ndarray] = None) -> np.ndarray:
+        shape, dt = {
+            AOV_BGRA8: ((self.height, self.width, 4), np.uint8),
+            AOV_RGB32F: ((self.height, self.width, 3), np.float32),
+            AOV_TRIANGLE_ID: ((self.height, self.width), np.uint32),
+            AOV_SHADOW_MASK: ((self.height, self.width), np.uint8),
+        }[aov]
+        if out is None:
+            out = np.empty(shape, dtype=dt)
+        self.ctx.check(self.ctx.lib.vkrt_frame_read(self.ctx.handle, self.handle, aov, _ptr(out), 0))
+        return out
+
+    @property
+    def device_bgra8(self) -> int:
+        return int(self.ctx.lib.vkrt_frame_device_bgra8(self.handle) or 0)
+
+    def close(self):
+        if self.handle and self.ctx.handle:
+            self.ctx.lib.vkrt_frame_destroy(self.ctx.handle, self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

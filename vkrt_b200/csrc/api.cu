@@ -701,8 +701,10 @@ int vkrt_stats_get(VkrtContext* c, VkrtStats* out)
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->stats.raysShadow = host[1];
     ctx->stats.raysReflection = host[2];
-    ctx->stats.nodesVisited = host[3];
-    ctx->stats.trianglesTested = host[4];
+    ctx->stats.nodesVisited = host[3] + host[6];
+    ctx->stats.trianglesTested = host[4] + host[7];
+    ctx->stats.nodesVisitedAny = host[6];
+    ctx->stats.trianglesTestedAny = host[7];
     ctx->stats.kernelLaunches = ctx->launches;
     if (ctx->timeStages && ctx->stageEventCount == 11)
     {
@@ -720,6 +722,14 @@ int vkrt_stats_get(VkrtContext* c, VkrtStats* out)
     }
     *out = ctx->stats;
     return VKRT_SUCCESS;
+}
+
+// Test hook (not part of include/vkrt.h): runs the builder's radix sort on host arrays.
+VKRT_API int vkrt_debug_sort_pairs(VkrtContext* c, uint32_t* keys, uint32_t* vals, uint32_t count)
+{
+    Context* ctx = C(c);
+    cudaSetDevice(ctx->device);
+    return sortPairsForTest(ctx, keys, vals, count);
 }
 
 int vkrt_comm_unique_id(uint8_t id[VKRT_UNIQUE_ID_BYTES])

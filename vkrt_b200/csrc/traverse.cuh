@@ -119,12 +119,13 @@ VKRT_HD uint32_t popCount(uint32_t v)
 #endif
 }
 
-// Box-test direction reciprocal: tiny components are clamped so no inf/NaN enters the slab arithmetic.
+// Box-test direction reciprocal.  Zero components give +-inf on purpose: with IEEE arithmetic every slab product is
+// then +-inf or NaN, and since fmaxf/fminf drop NaN operands an axis the ray runs parallel to either culls the box
+// correctly (ray outside the slab on the node-origin side) or is ignored (conservative).  Clamping to a large
+// finite value instead would wrongly cull rays that lie exactly in a box face.
 VKRT_HD float safeRcp(float d)
 {
-    const float lim = 1e-20f;
-    const float dd = fabsf(d) < lim ? (d < 0.0f ? -lim : lim) : d;
-    return 1.0f / dd;
+    return 1.0f / d;
 }
 
 struct NodeWords // one Node8 fetched as five 16-byte vectors

@@ -269,8 +269,8 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters)
     }
     if (STATS)
     {
-        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
-        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+        atomicAdd(&statCounters[6], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[7], (unsigned long long)tc.tris);
         if (tc.overflow)
         {
             atomicAdd(&statCounters[5], 1ull);
@@ -428,8 +428,8 @@ k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* 
     }
     if (STATS)
     {
-        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
-        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+        atomicAdd(&statCounters[6], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[7], (unsigned long long)tc.tris);
     }
 }
 

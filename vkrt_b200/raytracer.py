@@ -1,0 +1,86 @@
+"""Raytracer: Python mirror of the reference's `Raytracer` host logic (src/Raytracer.cpp) over the C ABI.
+
+`flatten_model` restates createVertexAndIndexBuffer (src/Raytracer.cpp:642-742) and the SubmeshInfo table of
+updateMaterialIndexDescriptorSet (:1412-1427); `Raytracer` owns context, BLAS, TLAS, materials, textures and a
+frame, and `render()` is one vkrt_trace (+ tile gather) like one iteration of Raytracer::render (:132-203).
+The C++ equivalent used by the headless executable lives in vkrt_b200/host/Raytracer.cpp.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import numpy as np
+
+from . import binding as B
+from .camera import Camera, LIGHT_POSITIONS
+from .scenes import REFERENCE_INSTANCE
+
+
+def flatten_model(model: Dict) -> Dict:
+    """Concatenate submesh vertices; rebase indices by the running vertex count; per submesh record
+    {primitiveCount, maxVertex (local), indexByteOffset}; material rows with cumulative triangle offsets and the
+    reference's clamp of missing normal / metallic-roughness indices to image 0 (base colour is not clamped)."""
+    subs = model["submeshes"]
+    vertices = np.concatenate([s["vertices"] for s in subs], axis=0).astype(np.float32)
+    indices = np.empty(sum(s["indices"].size for s in subs), dtype=np.uint32)
+    ranges = np.zeros((len(subs), 3), dtype=np.uint64)
+    rows = np.zeros((len(subs), 4), dtype=np.int32)
+    index_counter_offset = 0
+    index_counter = 0
+    index_byte_offset = 0
+    index_buffer_offset = 0  # triangles
+    for i, s in enumerate(subs):
+        idx = s["indices"].astype(np.uint32)
+        indices[index_counter:index_counter + idx.size] = idx + np.uint32(index_counter_offset)
+        ranges[i] = (idx.size // 3, int(idx.max()) if idx.size else 0, index_byte_offset)
+        base, mr, nrm = model["materials"][s["material"]]
+        rows[i] = (base, max(mr, 0), max(nrm, 0), index_buffer_offset)
+        index_counter += idx.size
+        index_counter_offset += s["vertices"].shape[0]
+        index_byte_offset += 4 * idx.size
+        index_buffer_offset += idx.size // 3
+    return {"vertices": vertices, "indices": indices, "ranges": ranges, "rows": rows, "images": model["images"]}
+
+
+class Raytracer:
+    """Headless renderer: scene upload + acceleration-structure build in the constructor, `render()` per frame."""
+
+    def __init__(self, model: Dict, width: int, height: int, device: int = 0, instances: Optional[np.ndarray] = None,
+                 build_flags: int = 0, rank: int = 0, world_size: int = 1, unique_id: Optional[bytes] = None,
+                 emulate_ranks: bool = False):
+        self.width, self.height = width, height
+        self.flat = flatten_model(model)
+        self.instances = np.asarray(instances if instances is not None else REFERENCE_INSTANCE, dtype=np.float32).reshape(-1, 12)
+        self.ctx = B.Context(device)
+        if world_size > 1:
+            if emulate_ranks:
+                self.ctx.comm_emulate(rank, world_size)
+            else:
+                self.ctx.comm_init(unique_id, rank, world_size)
+        self.rank, self.world_size = rank, world_size
+        self.blas = B.Blas(self.ctx, self.flat["vertices"], self.flat["indices"], self.flat["ranges"], flags=build_flags)
+        self.tlas = B.Tlas(self.ctx, [self.blas], self.instances)
+        self.ctx.set_materials(self.flat["rows"])
+        self.ctx.set_textures(self.flat["images"])
+        self.frame = B.Frame(self.ctx, width, height)
+        self.camera = Camera(np.float32(width) / np.float32(height))
+        # Raytracer::setupCamera, src/Raytracer.cpp:267-271
+        self.camera.setPosition((6.3, 4.5, -0.7))
+        self.camera.setRotation((0.0, 1.57, 0.0))
+        self.lights = LIGHT_POSITIONS
+        self.frame_index = 0
+
+    def render(self, spp: int = 1, flags: int = 0, gather: bool = True):
+        u = self.camera.uniforms(self.lights)
+        self.frame.trace(self.tlas, u, spp, self.frame_index, flags)
+        if gather and self.world_size > 1 and self.ctx is not None:
+            self.frame.gather(0)
+        self.frame_index += 1
+
+    def readback(self, aov: int = B.AOV_BGRA8, out: Optional[np.ndarray] = None) -> np.ndarray:
+        return self.frame.read(aov, out)
+
+    def close(self):
+        for o in (self.frame, self.tlas, self.blas):
+            o.close()
+        self.ctx.close()
