@@ -32,6 +32,7 @@ for p in g["meshes"][0]["primitives"]:
         "max": pos["max"],
         "material": p["material"],
         "hasTangent": "TANGENT" in a,
+        "attributes": dict(a),
     })
 mats = []
 for m in g["materials"]:

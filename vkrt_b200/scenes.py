@@ -353,6 +353,19 @@ def sponza_standin_submeshes(layout: Optional[Dict] = None) -> List[Dict]:
             verts[:, 12:16] = 0.0  # primitive 50: no TANGENT accessor -> the loader leaves zeros (src/Model.hpp:17)
         assert int(idx.max()) < 65536
         out.append({"vertices": verts.astype(np.float32), "indices": idx.astype(np.uint32), "material": int(p["material"])})
+    # primitives that share an attribute accessor in the glTF (instanced copies share NORMAL / TANGENT / TEXCOORD_0 and
+    # index data, each with its own POSITION) must carry identical data for it: the first user's data wins
+    columns = {"POSITION": (0, 3), "NORMAL": (4, 7), "TEXCOORD_0": (8, 10), "TANGENT": (12, 16)}
+    first_user = {}
+    for s, p in zip(out, prims):
+        for name, acc_id in p.get("attributes", {}).items():
+            if name not in columns:
+                continue
+            c0, c1 = columns[name]
+            if acc_id in first_user:
+                s["vertices"][:, c0:c1] = first_user[acc_id]
+            else:
+                first_user[acc_id] = s["vertices"][:, c0:c1].copy()
     return out
 
 
@@ -364,21 +377,22 @@ def find_asset_dir() -> Optional[str]:
 
 
 def load_sponza_images(layout: Optional[Dict] = None, max_size: Optional[int] = None):
-    """Returns (images, provenance).  Real textures (decoded with Pillow/libjpeg, forced to RGBA8 as tinygltf does,
+    """Returns (images, provenance).  Real textures (decoded by the host C++ decoder, forced to RGBA8 as tinygltf does,
     submodules/tinygltf/tiny_gltf.h:2363) when the files are staged; deterministic procedural textures otherwise."""
     layout = layout or load_layout()
     d = find_asset_dir()
     images = []
     if d is not None and all(os.path.isfile(os.path.join(d, im["uri"])) for im in layout["images"]):
-        from PIL import Image
+        from .model import decode_image  # host C++ decoder: bit-identical to the reference's stb_image on these files
 
         for im in layout["images"]:
-            with Image.open(os.path.join(d, im["uri"])) as f:
-                f = f.convert("RGBA")
-                if max_size and max(f.size) > max_size:
-                    f = f.resize((max_size, max_size), Image.BILINEAR)
-                images.append(np.ascontiguousarray(np.asarray(f, dtype=np.uint8)))
-        return images, "reference textures (Pillow decode)" + (f", downsized to {max_size}" if max_size else "")
+            with open(os.path.join(d, im["uri"]), "rb") as f:
+                rgba = decode_image(f.read())
+            if max_size and max(rgba.shape[:2]) > max_size:
+                step = max(rgba.shape[:2]) // max_size
+                rgba = np.ascontiguousarray(rgba[::step, ::step])
+            images.append(rgba)
+        return images, "reference textures (host decoder, == stb_image)" + (f", subsampled to {max_size}" if max_size else "")
     # procedural fall-back: role-dependent content so normal maps stay normal-like and metallic maps binary-ish
     roles = {}
     for m in layout["materials"]:
