@@ -258,8 +258,9 @@ VKRT_HD uint32_t quantExponent(float lo, float hi)
     int ex;
     frexpf(extent / 255.0f, &ex); // extent/255 = m * 2^ex, m in [0.5,1) -> 2^ex >= extent/255
     int e = ex + 127;
-    e = e < 1 ? 1 : (e > 254 ? 254 : e);
-    while (e < 254 && !(lo + 255.0f * uintAsFloat((uint32_t)e << 23) >= hi))
+    // <= 239: traversal adds 15 to the exponent byte (traverse.cuh, intersectNode); extents above 2^120 are out of range
+    e = e < 1 ? 1 : (e > 239 ? 239 : e);
+    while (e < 239 && !(lo + 255.0f * uintAsFloat((uint32_t)e << 23) >= hi))
     {
         ++e;
     }

@@ -156,18 +156,66 @@ VKRT_HD NodeWords loadNode(const Node8* nodes, uint32_t index)
 
 VKRT_HD uint32_t byteOf(uint32_t word, int i) { return (word >> (8 * i)) & 0xFFu; }
 
+// Byte i of `word` dropped into mantissa bits 8..15 of 1.0f: the float 1 + q * 2^-15.  One PRMT on the device (alu
+// pipe) instead of an I2F conversion; the 2^15 is folded into the per-node scale and the 1 into the per-node bias.
+// `one` is the bit pattern of 1.0f, passed in as a kernel parameter (SceneDev::one) so that ptxas cannot fold it: PRMT
+// then takes the selector as its immediate operand; with a literal it re-materialises a selector register per PRMT.
+template<int I>
+VKRT_HD float byteToUnitFloat(uint32_t word, uint32_t one)
+{
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(word, one, 0x7604u | (I << 4)));
+#else
+    return uintAsFloat(one | (((word >> (8 * I)) & 0xFFu) << 8));
+#endif
+}
+// Per-ray padded clamp values for the box tests.  The triangle test computes its own t with its own roundings, so a
+// box is only culled against [tmin, tmax] widened by 2^-18 relative: box culling must never reject a watertight hit.
+constexpr float kBoxRelPad = 3.8146973e-06f; // 2^-18
+VKRT_HD float padDown(float t) { return fmaExplicit(-fabsf(t), kBoxRelPad, t); }
+VKRT_HD float padUp(float t) { return fmaExplicit(fabsf(t), kBoxRelPad, t); }
+
+// Slab test of the 4 children held in one byte lane group; ORs their hit bits into `hitmask`.
+template<int I>
+VKRT_HD void testChild(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
+                       float bnx, float bny, float bnz, float bfx, float bfy, float bfz, float tminP, float tmaxP, uint32_t bits4,
+                       uint32_t index4, uint32_t one, uint32_t& hitmask)
+{
+    const float tnx = fmaExplicit(byteToUnitFloat<I>(nx, one), ax, bnx), tfx = fmaExplicit(byteToUnitFloat<I>(fx, one), ax, bfx);
+    const float tny = fmaExplicit(byteToUnitFloat<I>(ny, one), ay, bny), tfy = fmaExplicit(byteToUnitFloat<I>(fy, one), ay, bfy);
+    const float tnz = fmaExplicit(byteToUnitFloat<I>(nz, one), az, bnz), tfz = fmaExplicit(byteToUnitFloat<I>(fz, one), az, bfz);
+    const float tn = fmaxf(fmaxf(fmaxf(tnx, tny), tnz), tminP);
+    const float tf = fminf(fminf(fminf(tfx, tfy), tfz), tmaxP);
+    if (tn <= tf)
+    {
+        hitmask |= byteOf(bits4, I) << byteOf(index4, I);
+    }
+}
+
 // Intersects the ray with the 8 quantised child boxes of a node.  Returns the hit mask: bits 24..31 = internal
 // children in traversal priority order (nearest octant-order child in the highest bit), bits 0..23 = primitives.
-//   idir = safeRcp(d), octant bit k set when d_k < 0
-VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tmin, float tmax)
+//   idir = safeRcp(d), octant bit k set when d_k < 0, tminP/tmaxP = padDown(tmin)/padUp(tmax)
+//
+// Plane distance of quantised coordinate q on axis x:  t = (px + q*sx - ox) * idir.x.  With m = 1 + q*2^-15 (the PRMT
+// float above) this is  t = m*ax + b  with  ax = 2^15*sx*idir.x  and  b = (px-ox)*idir.x - ax : one FFMA per plane.
+// Rounding b costs at most 2^-24*(|b|+|ax|) <= 2^-9 of one quantisation step of t, so the near planes are pulled in
+// and the far planes pushed out by 2^-7 step (bn/bf below): the test stays conservative, and flat boxes (qlo == qhi)
+// keep tn < tf.  NaN planes (0*inf for axis-parallel rays) are dropped by fmaxf/fminf, i.e. that axis never culls.
+VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
     const uint32_t e = floatAsUint(w.n0.w);
-    const float sx = uintAsFloat((e & 0xFFu) << 23), sy = uintAsFloat(((e >> 8) & 0xFFu) << 23),
-                sz = uintAsFloat(((e >> 16) & 0xFFu) << 23);
+    // biased exponent bytes + 15 (the builder keeps them <= 239)
+    const float sx = uintAsFloat(((e << 23) & 0x7F800000u) + 0x07800000u);
+    const float sy = uintAsFloat(((e << 15) & 0x7F800000u) + 0x07800000u);
+    const float sz = uintAsFloat(((e << 7) & 0x7F800000u) + 0x07800000u);
     const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
-    const float bx = (w.n0.x - o.x) * idir.x, by = (w.n0.y - o.y) * idir.y, bz = (w.n0.z - o.z) * idir.z;
-    const uint32_t octinv = 7u - octant;
-    const float pad = 3.8146973e-06f; // 2^-18 relative padding: box culling must never reject a watertight hit
+    const float bx = fmaExplicit(w.n0.x - o.x, idir.x, -ax), by = fmaExplicit(w.n0.y - o.y, idir.y, -ay),
+                bz = fmaExplicit(w.n0.z - o.z, idir.z, -az);
+    const float slack = 2.3841858e-07f; // 2^-22 of ax = 2^-7 quantisation step
+    const float bnx = fmaExplicit(-fabsf(ax), slack, bx), bfx = fmaExplicit(fabsf(ax), slack, bx);
+    const float bny = fmaExplicit(-fabsf(ay), slack, by), bfy = fmaExplicit(fabsf(ay), slack, by);
+    const float bnz = fmaExplicit(-fabsf(az), slack, bz), bfz = fmaExplicit(fabsf(az), slack, bz);
+    const uint32_t octinv4 = (7u - octant) * 0x01010101u;
     uint32_t hitmask = 0;
     // n1 = {childBase, primBase, meta[0..3], meta[4..7]}; n2 = {qlox[0..3], qlox[4..7], qloy[0..3], qloy[4..7]}
     // n3 = {qloz lo, qloz hi, qhix lo, qhix hi};          n4 = {qhiy lo, qhiy hi, qhiz lo, qhiz hi}
@@ -175,35 +223,21 @@ VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octan
     for (int half = 0; half < 2; ++half)
     {
         const uint32_t meta4 = half ? w.n1.w : w.n1.z;
+        // internal children have meta 0b001sssss with sssss = 24 + slot: bits 3 and 4 both set
+        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t innerMask4 = (isInner4 >> 4) * 0xFFu;
+        const uint32_t index4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1F1F1F1Fu; // 24 + (slot ^ octinv) | prim offset
+        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;                      // 1 | unary triangle count; 0 = empty
         const uint32_t qlox = half ? w.n2.y : w.n2.x, qloy = half ? w.n2.w : w.n2.z, qloz = half ? w.n3.y : w.n3.x;
         const uint32_t qhix = half ? w.n3.w : w.n3.z, qhiy = half ? w.n4.y : w.n4.x, qhiz = half ? w.n4.w : w.n4.z;
         // near/far plane selection by ray direction sign
         const uint32_t nx = (octant & 1u) ? qhix : qlox, fx = (octant & 1u) ? qlox : qhix;
         const uint32_t ny = (octant & 2u) ? qhiy : qloy, fy = (octant & 2u) ? qloy : qhiy;
         const uint32_t nz = (octant & 4u) ? qhiz : qloz, fz = (octant & 4u) ? qloz : qhiz;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-        {
-            const uint32_t meta = byteOf(meta4, i);
-            if (meta == 0)
-            {
-                continue;
-            }
-            const float tnx = fmaExplicit((float)byteOf(nx, i), ax, bx), tfx = fmaExplicit((float)byteOf(fx, i), ax, bx);
-            const float tny = fmaExplicit((float)byteOf(ny, i), ay, by), tfy = fmaExplicit((float)byteOf(fy, i), ay, by);
-            const float tnz = fmaExplicit((float)byteOf(nz, i), az, bz), tfz = fmaExplicit((float)byteOf(fz, i), az, bz);
-            float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-            float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-            tn = fmaExplicit(-fabsf(tn), pad, tn);
-            tf = fmaExplicit(fabsf(tf), pad, tf);
-            if (tn <= tf)
-            {
-                const bool inner = (meta & 0xE0u) == 0x20u && (meta & 0x1Fu) >= 24u;
-                const uint32_t bits = meta >> 5;
-                const uint32_t index = inner ? (24u + (((meta & 0x1Fu) - 24u) ^ octinv)) : (meta & 0x1Fu);
-                hitmask |= bits << index;
-            }
-        }
+        testChild<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
+        testChild<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
+        testChild<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
+        testChild<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
     }
     return hitmask;
 }
@@ -238,12 +272,13 @@ struct BestHit
 // Traverses one BLAS with an object-space ray.  ANY: return true at the first accepted triangle.
 template<bool ANY>
 VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d, float tmin, uint32_t instance,
-                          BestHit& best, TraceCounters* counters)
+                          BestHit& best, TraceCounters* counters, uint32_t one)
 {
     const RayPre rp = makeRayPre(d);
     const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
     const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
     const uint32_t octinv = 7u - octant;
+    const float tminP = padDown(tmin);
 
     uint2 stack[kStackSize];
     int sp = 0;
@@ -277,7 +312,7 @@ VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d,
             {
                 ++counters->nodes;
             }
-            const uint32_t hits = intersectNode(w, o, idir, octant, tmin, best.t);
+            const uint32_t hits = intersectNode(w, o, idir, octant, tminP, padUp(best.t), one);
             const uint32_t imask = floatAsUint(w.n0.w) >> 24;
             ngroup = make_uint2(w.n1.x, (hits & 0xFF000000u) | imask);
             tgroup = make_uint2(w.n1.y, hits & 0x00FFFFFFu);
@@ -358,7 +393,7 @@ VKRT_HD bool intersectBounds(const InstanceBounds& b, F3 o, F3 idir, float tmin,
 // `best.t` must be initialised to the ray's tmax and best.tri to kInvalid.
 template<bool ANY>
 VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 d,
-                        float tmin, BestHit& best, TraceCounters* counters)
+                        float tmin, BestHit& best, TraceCounters* counters, uint32_t one = 0x3F800000u)
 {
     if (!finite3(o) || !finite3(d) || (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) || !(best.t > tmin))
     {
@@ -374,7 +409,7 @@ VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* b
         {
             return false;
         }
-        return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters);
+        return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one);
     }
     const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
     // visit instances in order of increasing entry distance: repeatedly select the nearest not yet visited one
@@ -414,7 +449,7 @@ VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* b
         {
             continue;
         }
-        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, bestIdx, best, counters))
+        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, bestIdx, best, counters, one))
         {
             found = true;
             if (ANY)

@@ -27,6 +27,7 @@ struct SceneDev
     uint32_t instanceCount;
     const VkrtSubmeshInfo* rows;
     const TextureRecord* textures;
+    uint32_t one; // 0x3F800000, see byteToUnitFloat (traverse.cuh)
 };
 
 struct WaveDev
@@ -122,7 +123,7 @@ k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* _
         best.b1 = best.b2 = 0.0f;
         best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
         traceScene<false>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z), f3(d4.x, d4.y, d4.z), o4.w, best,
-                          STATS ? &tc : nullptr);
+                          STATS ? &tc : nullptr, scene.one);
         hitA[i] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.tri));
         hitInst[i] = best.instance;
     }
@@ -261,7 +262,7 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters)
         best.b1 = best.b2 = 0.0f;
         best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
         const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
-                                               f3(d4.x, d4.y, d4.z), kRayTMin, best, STATS ? &tc : nullptr);
+                                               f3(d4.x, d4.y, d4.z), kRayTMin, best, STATS ? &tc : nullptr, scene.one);
         if (occluded)
         {
             atomicOr(&w.shadowBits[__float_as_uint(d4.w)], 1u << light);
@@ -419,7 +420,7 @@ k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* 
         best.b1 = best.b2 = 0.0f;
         best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
         const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
-                                               f3(d4.x, d4.y, d4.z), o4.w, best, STATS ? &tc : nullptr);
+                                               f3(d4.x, d4.y, d4.z), o4.w, best, STATS ? &tc : nullptr, scene.one);
         VkrtHit o;
         o.t = occluded ? best.t : 0.f, o.b1 = 0.f, o.b2 = 0.f;
         o.instance = occluded ? best.instance : kInvalid;
@@ -514,6 +515,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     scene.instanceCount = tlas->instanceCount;
     scene.rows = ctx->materials.as<VkrtSubmeshInfo>();
     scene.textures = ctx->textureRecords.as<TextureRecord>();
+    scene.one = 0x3F800000u;
 
     WaveDev w = waveDev(ctx, paths);
     FrameDev f;
@@ -695,6 +697,7 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     scene.instanceCount = tlas->instanceCount;
     scene.rows = nullptr;
     scene.textures = nullptr;
+    scene.one = 0x3F800000u;
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const uint32_t grid = persistentGrid(ctx, 8);
     if (anyHit)
