@@ -292,24 +292,40 @@ class Context:
         return bytes(buf)
 
 
+def _buffer(a, dtype=None):
+    """(pointer, bytes, elements, on_device, keepalive) of a numpy array or of a CUDA torch tensor (duck-typed: data_ptr/is_cuda)."""
+    if hasattr(a, "data_ptr") and getattr(a, "is_cuda", False):
+        a = a.contiguous()
+        return C.c_void_p(a.data_ptr()), a.numel() * a.element_size(), a.numel(), True, a
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return _ptr(a), a.nbytes, a.size, False, a
+
+
 class Blas:
-    def __init__(self, ctx: Context, vertices: np.ndarray, indices: np.ndarray, ranges: np.ndarray, flags: int = 0, stride: int = 64):
+    def __init__(self, ctx: Context, vertices, indices, ranges: np.ndarray, flags: int = 0, stride: int = 64):
         """vertices: (V,16) float32 (Model::Vertex) or raw bytes with `stride`; indices: global u32; ranges: rows of
-        (primitiveCount, maxVertex, indexByteOffset)."""
+        (primitiveCount, maxVertex, indexByteOffset).  numpy arrays (host) or CUDA torch tensors (both on the device:
+        VKRT_BUILD_INPUT_ON_DEVICE is added)."""
         self.ctx = ctx
-        v = np.ascontiguousarray(vertices)
-        idx = np.ascontiguousarray(indices, dtype=np.uint32)
+        vp, vbytes, _, vdev, vkeep = _buffer(vertices)
+        ip, _, icount, idev, ikeep = _buffer(indices, None if hasattr(indices, "data_ptr") else np.uint32)
+        if vdev != idev:
+            raise ValueError("vertices and indices must both be host arrays or both be CUDA tensors")
+        if vdev:
+            flags |= BUILD_INPUT_ON_DEVICE
         rng = (GeometryRange * len(ranges))()
         for i, r in enumerate(ranges):
             rng[i].primitiveCount, rng[i].maxVertex, rng[i].indexByteOffset = int(r[0]), int(r[1]), int(r[2])
         h = C.c_void_p()
-        ctx.check(ctx.lib.vkrt_blas_build(ctx.handle, _ptr(v), v.nbytes, stride, _ptr(idx), idx.size, rng, len(ranges), flags, C.byref(h)))
+        ctx.check(ctx.lib.vkrt_blas_build(ctx.handle, vp, vbytes, stride, ip, icount, rng, len(ranges), flags, C.byref(h)))
         self.handle = h
         self._ranges = rng
 
-    def rebuild(self, vertices: np.ndarray, flags: int = 0):
-        v = np.ascontiguousarray(vertices)
-        self.ctx.check(self.ctx.lib.vkrt_blas_rebuild(self.ctx.handle, self.handle, _ptr(v), v.nbytes, flags))
+    def rebuild(self, vertices, flags: int = 0):
+        vp, vbytes, _, vdev, vkeep = _buffer(vertices)
+        if vdev:
+            flags |= BUILD_INPUT_ON_DEVICE
+        self.ctx.check(self.ctx.lib.vkrt_blas_rebuild(self.ctx.handle, self.handle, vp, vbytes, flags))
 
     @property
     def reference(self) -> int:

@@ -278,14 +278,6 @@ k_sort_scatter(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__
     }
 }
 
-__global__ void __launch_bounds__(kThreads) k_fill_i32(int* data, uint32_t count, int value)
-{
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-    {
-        data[i] = value;
-    }
-}
-
 __global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -295,19 +287,80 @@ __global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
     }
 }
 
-__global__ void k_collapse_seed(CollapseArgs a)
+// Level-synchronous collapse without host round trips.  `range` = {first, last, ticket, levels}: wide nodes
+// [first,last) were allocated by the previous level.  Narrow levels (<= kNarrowLevel nodes) are swept by ONE block that
+// loops over levels with __syncthreads(); wide levels take one multi-block launch each, whose last block publishes
+// the next range.  Each kernel is a no-op when the current level belongs to the other kind, so the host just
+// alternates them (see buildBlasOnDevice).
+constexpr uint32_t kNarrowLevel = 1024;
+
+__global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
 {
     a.taskRef[0] = a.bvh2.count > 1 ? *a.bvh2.root : ~0;
     *a.nodeCounter = 1u;
     *a.primCounter = 0u;
+    range[0] = 0u, range[1] = 1u, range[2] = 0u, range[3] = 0u;
 }
 
-__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a, uint32_t first, uint32_t last)
+__global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a, uint32_t* range)
 {
-    const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < last)
+    __shared__ uint32_t sFirst, sLast;
+    if (threadIdx.x == 0)
+    {
+        sFirst = range[0], sLast = range[1];
+    }
+    __syncthreads();
+    uint32_t levels = 0;
+    for (;;)
+    {
+        const uint32_t first = sFirst, last = sLast;
+        if (first >= last || last - first > kNarrowLevel)
+        {
+            break;
+        }
+        if (first + threadIdx.x < last)
+        {
+            collapseNode(a, first + threadIdx.x);
+        }
+        __threadfence_block();
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            sFirst = last;
+            sLast = *(volatile uint32_t*)a.nodeCounter;
+        }
+        ++levels;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0)
+    {
+        range[0] = sFirst, range[1] = sLast, range[3] += levels;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_collapse_wide(CollapseArgs a, uint32_t* range)
+{
+    const uint32_t first = range[0], last = range[1];
+    if (last - first <= kNarrowLevel) // also covers the finished state first == last
+    {
+        return;
+    }
+    for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < last; i += gridDim.x * blockDim.x)
     {
         collapseNode(a, i);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        const uint32_t ticket = atomicAdd(&range[2], 1u);
+        if (ticket == gridDim.x - 1) // every block has read the range and finished its nodes
+        {
+            range[0] = last;
+            range[1] = atomicAdd(a.nodeCounter, 0u);
+            range[2] = 0u;
+            range[3] += 1u;
+        }
     }
 }
 
@@ -482,9 +535,9 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         bvh.root = root;
         if (n > 1)
         {
-            k_fill_i32<<<gridFor(n - 1, kThreads, sm), kThreads, 0, s>>>(bvh.flags, n - 1, -1);
+            VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0xFF, (size_t)(n - 1) * 4, s)); // -1
             k_lbvh<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
-            ctx->launches += 2;
+            ctx->launches += 1;
         }
 
         CollapseArgs ca;
@@ -497,28 +550,40 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         ca.overflow = counters + 2;
         ca.sahAccum = sahAccum;
         ca.nodeCapacity = nodeCapacity;
-        k_collapse_seed<<<1, 1, 0, s>>>(ca);
+        uint32_t* range = counters + 4; // {first, last, ticket, levels}
+        k_collapse_seed<<<1, 1, 0, s>>>(ca, range);
         ctx->launches += 1;
-        // level-synchronous collapse: wide nodes [first,last) were allocated by the previous level
-        uint32_t first = 0, last = 1;
-        while (first < last)
+        uint32_t last = 0;
+        for (int batch = 0;; ++batch)
         {
-            const uint32_t cnt = last - first;
-            k_collapse_level<<<(cnt + 127) / 128, 128, 0, s>>>(ca, first, last);
-            ctx->launches += 1;
-            uint32_t hostCounters[3];
+            // one narrow sweep, then (wide, narrow) pairs: enough for 8 wide levels per batch
+            k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+            for (int k = 0; k < 8; ++k)
+            {
+                k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range);
+                k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+            }
+            ctx->launches += 17;
+            uint32_t hostCounters[8];
             VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
             VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
             if (hostCounters[2])
             {
                 return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "BVH collapse: wide node capacity exceeded");
             }
-            first = last;
-            last = hostCounters[0];
-            if (first == last && hostCounters[1] != n)
+            if (hostCounters[4] == hostCounters[5]) // first == last: no wide node left to fill
             {
-                return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: packed " + std::to_string(hostCounters[1]) + " of " +
-                                                      std::to_string(n) + " triangles");
+                last = hostCounters[0];
+                if (hostCounters[1] != n)
+                {
+                    return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: packed " + std::to_string(hostCounters[1]) + " of " +
+                                                          std::to_string(n) + " triangles");
+                }
+                break;
+            }
+            if (batch > 64)
+            {
+                return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: did not terminate");
             }
         }
         blas->nodeCount = last;
