@@ -51,8 +51,8 @@ def test_radix_sort_matches_numpy():
     lib = C.CDLL(B.LIB_PATH)
     lib.vkrt_debug_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
     rng = np.random.default_rng(5)
-    for n in (1, 31, 4096, 4097, 100003, 1 << 20):
-        keys = rng.integers(0, 1 << 30, n, dtype=np.uint32)
+    for n in (1, 31, 4096, 4097, 100003, 1 << 20, (1 << 22) + 17):
+        keys = rng.integers(0, 1 << 32, n, dtype=np.uint32)
         if n > 1000:
             keys[: n // 2] &= 0xFF  # many duplicates: stability matters
         vals = np.arange(n, dtype=np.uint32)

@@ -210,9 +210,9 @@ int vkrt_blas_build(VkrtContext* c, const void* vertices, size_t vertexBytes, ui
         firstTri[g] = (uint32_t)n;
         n += ranges[g].primitiveCount;
     }
-    if (n >= 0x7FFFFFFFull)
+    if (n >= 0x40000000ull) // the sort's look-back words carry 30-bit counts
     {
-        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: at most 2^31-2 triangles per BLAS");
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: at most 2^30-1 triangles per BLAS");
     }
     firstTri[geometryCount] = (uint32_t)n;
     const bool onDevice = (flags & VKRT_BUILD_INPUT_ON_DEVICE) != 0;

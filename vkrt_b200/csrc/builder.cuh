@@ -291,7 +291,9 @@ VKRT_HD uint32_t quantHi(float v, float origin, float scale)
 }
 
 // Builds wide node `wideIndex` from the binary subtree taskRef[wideIndex].
-VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex)
+// `sahLocal` (device kernels): per-thread accumulators {node area, leaf area * count} that the caller reduces per warp;
+// when NULL the areas go straight to a.sahAccum.
+VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahLocal = nullptr)
 {
     const Bvh2& b = a.bvh2;
     const int rootRef = a.taskRef[wideIndex];
@@ -454,7 +456,12 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex)
         }
     }
     a.nodes[wideIndex] = node;
-    if (a.sahAccum)
+    if (sahLocal)
+    {
+        sahLocal[0] += halfArea(self.lo, self.hi);
+        sahLocal[1] += leafArea;
+    }
+    else if (a.sahAccum)
     {
         VKRT_ATOMIC_ADD(&a.sahAccum[0], halfArea(self.lo, self.hi));
         VKRT_ATOMIC_ADD(&a.sahAccum[1], leafArea);

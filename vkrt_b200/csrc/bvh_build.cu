@@ -113,10 +113,51 @@ k_tri_bounds(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t s
     }
 }
 
-__global__ void __launch_bounds__(kThreads)
-k_morton(const float4* __restrict__ triLo, const float4* __restrict__ triHi, const uint32_t* __restrict__ sceneBounds,
-         uint32_t count, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals)
+// ------------------------------------------------------------------------------------------------
+// Onesweep LSD radix sort (Adinets & Merrill 2022), key-value (u32,u32), four 8-bit digits.
+//   k_morton_hist   : Morton codes + the four global digit histograms in the same pass over the triangles
+//   k_onesweep_pass : one launch per digit.  A block takes the next tile (4096 keys) by atomic ticket, ranks its
+//                     keys (warp-level match), publishes the tile's digit counts and resolves its global offsets by
+//                     decoupled look-back over the preceding tiles (no separate scan kernel), then scatters through
+//                     shared memory so that each digit run leaves as consecutive addresses.
+// Look-back words: bits 30..31 = state (0 not ready, 1 tile count, 2 inclusive prefix), bits 0..29 = value, hence
+// fewer than 2^30 keys.  A block only ever waits for tiles with a smaller ticket, whose blocks are already running.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kThreads * kSortItems; // 4096
+constexpr int kSortWarps = kThreads / 32;
+constexpr uint32_t kLookAggregate = 0x40000000u, kLookInclusive = 0x80000000u, kLookValue = 0x3FFFFFFFu;
+
+__device__ __forceinline__ void histAccumulate(uint32_t (*hist)[256], uint32_t key)
 {
+    atomicAdd(&hist[0][key & 0xFFu], 1u);
+    atomicAdd(&hist[1][(key >> 8) & 0xFFu], 1u);
+    atomicAdd(&hist[2][(key >> 16) & 0xFFu], 1u);
+    atomicAdd(&hist[3][key >> 24], 1u);
+}
+__device__ __forceinline__ void histFlush(uint32_t (*hist)[256], uint32_t* __restrict__ globalHist)
+{
+    __syncthreads();
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x)
+    {
+        const uint32_t v = hist[i >> 8][i & 255];
+        if (v)
+        {
+            atomicAdd(&globalHist[i], v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_morton_hist(const float4* __restrict__ triLo, const float4* __restrict__ triHi, const uint32_t* __restrict__ sceneBounds,
+              uint32_t count, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ globalHist)
+{
+    __shared__ uint32_t hist[4][256];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x)
+    {
+        hist[i >> 8][i & 255] = 0u;
+    }
+    __syncthreads();
     const F3 lo = f3(floatFromOrdered(sceneBounds[6]), floatFromOrdered(sceneBounds[7]), floatFromOrdered(sceneBounds[8]));
     const F3 hi = f3(floatFromOrdered(sceneBounds[9]), floatFromOrdered(sceneBounds[10]), floatFromOrdered(sceneBounds[11]));
     const F3 inv = f3(hi.x > lo.x ? 1.0f / (hi.x - lo.x) : 0.0f, hi.y > lo.y ? 1.0f / (hi.y - lo.y) : 0.0f,
@@ -125,112 +166,84 @@ k_morton(const float4* __restrict__ triLo, const float4* __restrict__ triHi, con
     {
         const float4 l = triLo[i], h = triHi[i];
         const F3 c = f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z));
-        keys[i] = morton30(c, lo, inv);
+        const uint32_t key = morton30(c, lo, inv);
+        keys[i] = key;
         vals[i] = i;
+        histAccumulate(hist, key);
     }
+    histFlush(hist, globalHist);
 }
 
-// ------------------------------------------------------------------------------------------------
-// LSD radix sort, 8-bit digits, key-value (u32,u32).  Per pass: tile histograms -> exclusive scan ->
-// stable scatter (warp-level match ranking).  Tiles of 4096 keys, 256 threads, 16 keys per thread.
-// ------------------------------------------------------------------------------------------------
-constexpr int kSortItems = 16;
-constexpr int kSortTile = kThreads * kSortItems; // 4096
-constexpr int kSortWarps = kThreads / 32;
-
-__global__ void __launch_bounds__(kThreads)
-k_sort_hist(const uint32_t* __restrict__ keys, uint32_t count, uint32_t shift, uint32_t numTiles, uint32_t* __restrict__ tileHist)
+// histograms of arbitrary keys (debug sort entry)
+__global__ void __launch_bounds__(kThreads) k_onesweep_hist(const uint32_t* __restrict__ keys, uint32_t count, uint32_t* __restrict__ globalHist)
 {
-    __shared__ uint32_t hist[256];
-    hist[threadIdx.x] = 0;
-    __syncthreads();
-    const uint32_t base = blockIdx.x * kSortTile;
-#pragma unroll 4
-    for (int j = 0; j < kSortItems; ++j)
+    __shared__ uint32_t hist[4][256];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x)
     {
-        const uint32_t idx = base + j * kThreads + threadIdx.x;
-        if (idx < count)
-        {
-            atomicAdd(&hist[(keys[idx] >> shift) & 0xFFu], 1u);
-        }
+        hist[i >> 8][i & 255] = 0u;
     }
     __syncthreads();
-    tileHist[threadIdx.x * numTiles + blockIdx.x] = hist[threadIdx.x]; // digit-major: one scan gives global offsets
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        histAccumulate(hist, keys[i]);
+    }
+    histFlush(hist, globalHist);
 }
 
-// Single-block exclusive scan (1024 threads, contiguous chunk per thread).
-__global__ void __launch_bounds__(1024) k_exclusive_scan(uint32_t* data, uint32_t count)
+// exclusive scan of 256 values, one per thread of a 256-thread block
+__device__ __forceinline__ uint32_t blockExclusive256(uint32_t v, uint32_t* warpSums /* >= 8 */)
 {
-    __shared__ uint32_t warpSums[32];
-    __shared__ uint32_t carry;
-    const uint32_t chunk = (count + 1023u) / 1024u;
-    const uint32_t begin = min(count, threadIdx.x * chunk), end = min(count, begin + chunk);
-    uint32_t sum = 0;
-    for (uint32_t i = begin; i < end; ++i)
-    {
-        sum += data[i];
-    }
-    // block exclusive scan of `sum`
-    uint32_t incl = sum;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
     for (int o = 1; o < 32; o <<= 1)
     {
-        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if ((threadIdx.x & 31) >= o)
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o)
         {
-            incl += v;
+            incl += t;
         }
     }
-    if ((threadIdx.x & 31) == 31)
+    if (lane == 31)
     {
-        warpSums[threadIdx.x >> 5] = incl;
+        warpSums[warp] = incl;
     }
     __syncthreads();
-    if (threadIdx.x < 32)
+    uint32_t base = 0;
+    for (uint32_t w = 0; w < warp; ++w)
     {
-        uint32_t w = warpSums[threadIdx.x];
-        uint32_t wi = w;
-        for (int o = 1; o < 32; o <<= 1)
-        {
-            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, wi, o);
-            if (threadIdx.x >= o)
-            {
-                wi += v;
-            }
-        }
-        warpSums[threadIdx.x] = wi - w;
-        if (threadIdx.x == 31)
-        {
-            carry = wi;
-        }
+        base += warpSums[w];
     }
     __syncthreads();
-    uint32_t run = warpSums[threadIdx.x >> 5] + (incl - sum);
-    for (uint32_t i = begin; i < end; ++i)
-    {
-        const uint32_t v = data[i];
-        data[i] = run;
-        run += v;
-    }
-    (void)carry;
+    return base + incl - v;
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_sort_scatter(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn, uint32_t count, uint32_t shift,
-               uint32_t numTiles, const uint32_t* __restrict__ tileOffsets, uint32_t* __restrict__ keysOut,
-               uint32_t* __restrict__ valsOut)
+k_onesweep_pass(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn, uint32_t count, uint32_t shift,
+                const uint32_t* __restrict__ globalHist /* 256 counts of this digit */, uint32_t* __restrict__ ticket,
+                uint32_t* __restrict__ status /* numTiles x 256, zeroed */, uint32_t* __restrict__ keysOut, uint32_t* __restrict__ valsOut)
 {
     __shared__ uint32_t warpHist[kSortWarps][256];
-    __shared__ uint32_t digitBase[256];
+    __shared__ uint32_t stageKey[kSortTile];
+    __shared__ uint32_t stageVal[kSortTile];
+    __shared__ uint32_t localStart[256]; // first staging slot of each digit
+    __shared__ uint32_t globalStart[256]; // output position of the digit's first key of this tile
+    __shared__ uint32_t warpSums[kSortWarps];
+    __shared__ uint32_t sTile;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0)
+    {
+        sTile = atomicAdd(ticket, 1u);
+    }
     for (int w = 0; w < kSortWarps; ++w)
     {
         warpHist[w][threadIdx.x] = 0;
     }
-    digitBase[threadIdx.x] = tileOffsets[threadIdx.x * numTiles + blockIdx.x];
     __syncthreads();
+    const uint32_t tile = sTile;
 
     // warp-striped: warp w owns 512 consecutive keys; item j, lane l -> key w*512 + j*32 + l (stable order)
-    const uint32_t base = blockIdx.x * kSortTile + warp * (32 * kSortItems);
+    const uint32_t base = tile * kSortTile + warp * (32 * kSortItems);
     uint32_t key[kSortItems], rank[kSortItems];
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
@@ -253,17 +266,42 @@ k_sort_scatter(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__
         __syncwarp();
     }
     __syncthreads();
-    // per digit: exclusive prefix over the warps of this tile
+
+    // thread d owns digit d: exclusive prefix over the warps of this tile, the tile's count, look-back
+    const uint32_t d = threadIdx.x;
+    uint32_t tileCount = 0;
+    for (int w = 0; w < kSortWarps; ++w)
     {
-        uint32_t run = 0;
-        for (int w = 0; w < kSortWarps; ++w)
-        {
-            const uint32_t v = warpHist[w][threadIdx.x];
-            warpHist[w][threadIdx.x] = run;
-            run += v;
-        }
+        const uint32_t v = warpHist[w][d];
+        warpHist[w][d] = tileCount;
+        tileCount += v;
     }
+    volatile uint32_t* st = status;
+    st[(size_t)tile * 256 + d] = tileCount | (tile == 0 ? kLookInclusive : kLookAggregate);
+    const uint32_t digitBase = blockExclusive256(globalHist[d], warpSums);
+    localStart[d] = blockExclusive256(tileCount, warpSums);
+    uint32_t exclusive = 0;
+    if (tile > 0)
+    {
+        for (uint32_t t = tile - 1;; --t)
+        {
+            uint32_t w;
+            do
+            {
+                w = st[(size_t)t * 256 + d];
+            } while ((w & ~kLookValue) == 0u);
+            exclusive += w & kLookValue;
+            if (w & kLookInclusive)
+            {
+                break;
+            }
+        }
+        st[(size_t)tile * 256 + d] = (exclusive + tileCount) | kLookInclusive;
+    }
+    globalStart[d] = digitBase + exclusive;
     __syncthreads();
+
+    // stage in tile-sorted order
 #pragma unroll
     for (int j = 0; j < kSortItems; ++j)
     {
@@ -271,10 +309,20 @@ k_sort_scatter(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__
         if (idx < count)
         {
             const uint32_t digit = (key[j] >> shift) & 0xFFu;
-            const uint32_t dst = digitBase[digit] + warpHist[warp][digit] + rank[j];
-            keysOut[dst] = key[j];
-            valsOut[dst] = valsIn[idx];
+            const uint32_t slot = localStart[digit] + warpHist[warp][digit] + rank[j];
+            stageKey[slot] = key[j];
+            stageVal[slot] = valsIn[idx];
         }
+    }
+    __syncthreads();
+    const uint32_t tileKeys = min((uint32_t)kSortTile, count - tile * kSortTile);
+    for (uint32_t i = threadIdx.x; i < tileKeys; i += kThreads)
+    {
+        const uint32_t k = stageKey[i];
+        const uint32_t digit = (k >> shift) & 0xFFu;
+        const uint32_t dst = globalStart[digit] + (i - localStart[digit]);
+        keysOut[dst] = k;
+        valsOut[dst] = stageVal[i];
     }
 }
 
@@ -294,6 +342,22 @@ __global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
 // alternates them (see buildBlasOnDevice).
 constexpr uint32_t kNarrowLevel = 1024;
 
+__device__ __forceinline__ void flushSah(const CollapseArgs& a, const float* sah)
+{
+    // one atomic per warp instead of two per wide node (same-address float atomics serialise in L2)
+    float s0 = sah[0], s1 = sah[1];
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        s0 += __shfl_xor_sync(0xFFFFFFFFu, s0, o);
+        s1 += __shfl_xor_sync(0xFFFFFFFFu, s1, o);
+    }
+    if ((threadIdx.x & 31) == 0 && a.sahAccum)
+    {
+        atomicAdd(&a.sahAccum[0], s0);
+        atomicAdd(&a.sahAccum[1], s1);
+    }
+}
+
 __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
 {
     a.taskRef[0] = a.bvh2.count > 1 ? *a.bvh2.root : ~0;
@@ -311,6 +375,7 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
     }
     __syncthreads();
     uint32_t levels = 0;
+    float sah[2] = {0.0f, 0.0f};
     for (;;)
     {
         const uint32_t first = sFirst, last = sLast;
@@ -320,7 +385,7 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
         }
         if (first + threadIdx.x < last)
         {
-            collapseNode(a, first + threadIdx.x);
+            collapseNode(a, first + threadIdx.x, sah);
         }
         __threadfence_block();
         __syncthreads();
@@ -332,6 +397,7 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
         ++levels;
         __syncthreads();
     }
+    flushSah(a, sah);
     if (threadIdx.x == 0)
     {
         range[0] = sFirst, range[1] = sLast, range[3] += levels;
@@ -345,10 +411,12 @@ __global__ void __launch_bounds__(128) k_collapse_wide(CollapseArgs a, uint32_t*
     {
         return;
     }
+    float sah[2] = {0.0f, 0.0f};
     for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < last; i += gridDim.x * blockDim.x)
     {
-        collapseNode(a, i);
+        collapseNode(a, i, sah);
     }
+    flushSah(a, sah);
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0)
@@ -394,24 +462,32 @@ inline uint32_t gridFor(uint32_t count, int threads, int smCount)
 }
 } // namespace
 
-// Sorts (keys, vals) by key; result ends in keysA/valsA (4 passes ping-pong A->B->A->B->A).
-static int radixSort(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* tileHist,
+// Sorts (keys, vals) by key; result ends in keysA/valsA (4 passes ping-pong A->B->A->B->A).  `sortState` holds
+// {globalHist[4][256], ticket[4]} (the histograms already filled by k_morton_hist / k_onesweep_hist, tickets zero)
+// followed by the 4 * numTiles * 256 zeroed look-back words.
+static int radixSort(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* sortState,
                      uint32_t count)
 {
     const uint32_t numTiles = (count + kSortTile - 1) / kSortTile;
     uint32_t *kin = keysA, *vin = valsA, *kout = keysB, *vout = valsB;
+    uint32_t* globalHist = sortState;
+    uint32_t* ticket = sortState + 1024;
+    uint32_t* status = sortState + 1040;
     for (uint32_t pass = 0; pass < 4; ++pass)
     {
-        const uint32_t shift = pass * 8;
-        k_sort_hist<<<numTiles, kThreads, 0, ctx->stream>>>(kin, count, shift, numTiles, tileHist);
-        k_exclusive_scan<<<1, 1024, 0, ctx->stream>>>(tileHist, 256u * numTiles);
-        k_sort_scatter<<<numTiles, kThreads, 0, ctx->stream>>>(kin, vin, count, shift, numTiles, tileHist, kout, vout);
-        ctx->launches += 3;
+        k_onesweep_pass<<<numTiles, kThreads, 0, ctx->stream>>>(kin, vin, count, pass * 8, globalHist + 256 * pass, ticket + pass,
+                                                                   status + (size_t)pass * numTiles * 256, kout, vout);
+        ctx->launches += 1;
         std::swap(kin, kout);
         std::swap(vin, vout);
     }
     VKRT_CUDA_TRY(ctx, cudaGetLastError());
     return VKRT_SUCCESS;
+}
+static size_t sortStateBytes(uint32_t count)
+{
+    const size_t numTiles = ((size_t)count + kSortTile - 1) / kSortTile;
+    return (1040 + 4 * numTiles * 256) * sizeof(uint32_t);
 }
 
 // Debug entry used by the tests: sorts host arrays on the device with the builder's sort.
@@ -422,14 +498,19 @@ int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t coun
         return VKRT_SUCCESS;
     }
     DeviceBuffer a, b, c, d, h;
-    const uint32_t numTiles = (count + kSortTile - 1) / kSortTile;
+    if (count >= 0x40000000u)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "sort: at most 2^30-1 keys");
+    }
     VKRT_CUDA_TRY(ctx, a.reserve(count * 4ull));
     VKRT_CUDA_TRY(ctx, b.reserve(count * 4ull));
     VKRT_CUDA_TRY(ctx, c.reserve(count * 4ull));
     VKRT_CUDA_TRY(ctx, d.reserve(count * 4ull));
-    VKRT_CUDA_TRY(ctx, h.reserve(256ull * numTiles * 4ull));
+    VKRT_CUDA_TRY(ctx, h.reserve(sortStateBytes(count)));
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(h.ptr, 0, sortStateBytes(count), ctx->stream));
     VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(a.ptr, keys, count * 4ull, cudaMemcpyHostToDevice, ctx->stream));
     VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(b.ptr, vals, count * 4ull, cudaMemcpyHostToDevice, ctx->stream));
+    k_onesweep_hist<<<gridFor(count, kThreads, ctx->smCount), kThreads, 0, ctx->stream>>>(a.as<uint32_t>(), count, h.as<uint32_t>());
     int r = radixSort(ctx, a.as<uint32_t>(), b.as<uint32_t>(), c.as<uint32_t>(), d.as<uint32_t>(), h.as<uint32_t>(), count);
     if (r == VKRT_SUCCESS)
     {
@@ -465,14 +546,13 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     // scratch layout
     BuildScratch& sc = ctx->buildScratch;
     const size_t n1 = std::max<size_t>(n, 1);
-    const uint32_t numTiles = (uint32_t)((n1 + kSortTile - 1) / kSortTile);
     VKRT_CUDA_TRY(ctx, sc.triLo.reserve(n1 * sizeof(float4)));
     VKRT_CUDA_TRY(ctx, sc.triHi.reserve(n1 * sizeof(float4)));
     VKRT_CUDA_TRY(ctx, sc.keysA.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.keysB.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.valsA.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.valsB.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(256ull * numTiles * 4));
+    VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(sortStateBytes(n)));
     VKRT_CUDA_TRY(ctx, sc.children.reserve(n1 * sizeof(int2)));
     VKRT_CUDA_TRY(ctx, sc.nodeLo.reserve(n1 * sizeof(float4)));
     VKRT_CUDA_TRY(ctx, sc.nodeHi.reserve(n1 * sizeof(float4)));
@@ -512,8 +592,10 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     {
         k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices, n,
                                                                       sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds);
-        k_morton<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds, n,
-                                                                  sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>());
+        VKRT_CUDA_TRY(ctx, cudaMemsetAsync(sc.tileHist.ptr, 0, sortStateBytes(n), s));
+        k_morton_hist<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds, n,
+                                                                       sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(),
+                                                                       sc.tileHist.as<uint32_t>());
         ctx->launches += 2;
         int r = radixSort(ctx, sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(), sc.keysB.as<uint32_t>(),
                           sc.valsB.as<uint32_t>(), sc.tileHist.as<uint32_t>(), n);
