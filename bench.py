@@ -28,6 +28,7 @@ WORKLOADS = {
     "config2": (1920, 1080, 1, "Sponza 1920x1080 1 spp, camera path (W 150 frames, Z 150 frames), BVH built once"),
     "config3": (3840, 2160, 8, "Sponza 3840x2160 8 spp jittered (Halton 2,3), 64x64 interleaved tiles over ranks"),
     "config4": (3840, 2160, 1, "4x4 instanced Sponza grid (16 instances) 3840x2160 1 spp"),
+    "config5": (3840, 2160, 1, "procedural triangle soup, full BVH rebuild every frame, 3840x2160 1 spp"),
 }
 
 
@@ -83,6 +84,10 @@ class ClockSampler:
 def build_scene(workload):
     from vkrt_b200 import scenes
 
+    if workload == "config5":  # CPU arm only (the GPU arm generates the soup on the device): bounded triangle count
+        model = scenes.procedural_soup(2_000_000)
+        model["provenance"] = "procedural soup, 2,000,000 triangles (numpy generator; CPU arm is bounded to this size)"
+        return model, scenes.identity_instance(1.0)
     model = scenes.sponza_standin()
     instances = scenes.instanced_grid_transforms() if workload == "config4" else None
     return model, instances
@@ -160,6 +165,8 @@ def main():
     ap.add_argument("--impl", default="vkrt_b200", choices=["vkrt_b200", "reference"])
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--triangles", type=int, default=50_000_000, help="config5 only: triangles in the procedural soup")
+    ap.add_argument("--build-flags", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -187,8 +194,23 @@ def main():
         unique_id = ids[0]
 
     W, Hh, spp, desc = WORKLOADS[args.workload]
-    model, instances = build_scene(args.workload)
-    rt = Raytracer(model, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id)
+    soup = None
+    if args.workload == "config5":
+        from vkrt_b200 import scenes
+        from vkrt_b200.scenes_device import SoupDevice
+
+        soup = SoupDevice(args.triangles, local)
+        model = soup.model_stub()
+        instances = scenes.identity_instance(1.0)
+        flat = {"vertices": soup.vertices, "indices": soup.indices, "ranges": soup.ranges(), "rows": np.zeros((1, 4), dtype=np.int32),
+                "images": model["images"]}
+        rt = Raytracer(None, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id, flat=flat,
+                       build_flags=args.build_flags)
+    else:
+        model, instances = build_scene(args.workload)
+        rt = Raytracer(model, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id,
+                       build_flags=args.build_flags)
+    build_ms = []
     info = rt.blas.info()
     stream = torch.cuda.ExternalStream(rt.ctx.stream, device=local)
     flags = B.TRACE_NO_AOV
@@ -213,8 +235,14 @@ def main():
 
     step_counter = [0]
 
+    def rebuild_step():
+        if soup is not None:  # config 5: every frame moves all triangles and rebuilds the whole BVH
+            rt.rebuild(soup.set_frame(step_counter[0]), flags=args.build_flags)
+            build_ms.append(rt.blas.info().buildMilliseconds)
+
     def device_step():
         set_pose(rt, args.workload, step_counter[0])
+        rebuild_step()
         step_counter[0] += 1
         rt.render(spp=spp, flags=flags, gather=True)
 
@@ -246,6 +274,7 @@ def main():
 
     def e2e_step():
         set_pose(rt, args.workload, step_counter[0])
+        rebuild_step()
         step_counter[0] += 1
         rt.render(spp=spp, flags=flags, gather=True)
         if rank == 0:
@@ -297,12 +326,14 @@ def main():
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},
             "mrays_s_by_type": {"primary": rp / (ms * 1e-3) / 1e6, "shadow": rs / (ms * 1e-3) / 1e6, "reflection": rr / (ms * 1e-3) / 1e6},
             "bvh_build": {"ms": info.buildMilliseconds, "mtri_s": info.triangleCount / max(info.buildMilliseconds, 1e-9) / 1e3,
-                          "sah_cost": info.sahCost},
+                          "sah_cost": info.sahCost, "rebuilds_in_timed_region": len(build_ms),
+                          "rebuild_ms_median": float(np.median(build_ms)) if build_ms else None,
+                          "rebuild_mtri_s": info.triangleCount / float(np.median(build_ms)) / 1e3 if build_ms else None},
             "e2e": {"value": rays2 / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 256 * world,
                     "d2h_bytes_per_step": W * Hh * 4, "ms_per_step": e2e_ms / max(args.steps, 1)},
             "gpu_launches": int(launches_all), "clocks": clocks, "roofline": roofline,
         }
-        if not args.no_cpu_baseline and world == 1:
+        if not args.no_cpu_baseline and world == 1 and soup is None:
             sys.path.insert(0, os.path.join(ROOT, "tests"))
             import helpers as H
             from vkrt_b200 import scenes
@@ -318,6 +349,7 @@ def main():
                                     "bvh_build_mtri_s": info.triangleCount / max(o.build_seconds(), 1e-9) / 1e6}
         print(json.dumps(line), flush=True)
     rt.close()
+    del soup
     if dist is not None:
         dist.destroy_process_group()
 

@@ -75,7 +75,8 @@ VKRT_HD uint32_t morton30(F3 p, F3 lo, F3 invExtent)
 
 // ------------------------------------------------------------------------------------------------
 // Binary LBVH (intermediate): N-1 internal nodes, children >= 0 internal, < 0 => ~sortedLeafIndex.
-// lo.w / hi.w carry the first / last sorted leaf index of the subtree (as raw bits).
+// lo.w carries the number of leaves of the subtree (as raw bits); the leaves need not be contiguous in sorted
+// order (PLOC merges clusters that are not neighbours), so small subtrees are enumerated by walking them.
 // ------------------------------------------------------------------------------------------------
 struct Bvh2
 {
@@ -181,8 +182,8 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
         }
         lo.x = fminf(lo.x, slo.x), lo.y = fminf(lo.y, slo.y), lo.z = fminf(lo.z, slo.z);
         hi.x = fmaxf(hi.x, shi.x), hi.y = fmaxf(hi.y, shi.y), hi.z = fmaxf(hi.z, shi.z);
-        lo.w = uintAsFloat(left);
-        hi.w = uintAsFloat(right);
+        lo.w = uintAsFloat(right - left + 1u);
+        hi.w = 0.0f;
         b.lo[parent] = lo;
         b.hi[parent] = hi;
         current = (int)parent;
@@ -216,7 +217,7 @@ struct CollapseChild
 {
     int ref;
     F3 lo, hi;
-    uint32_t first, count;
+    uint32_t count;
 };
 
 VKRT_HD CollapseChild collapseFetch(const Bvh2& b, int ref)
@@ -229,16 +230,43 @@ VKRT_HD CollapseChild collapseFetch(const Bvh2& b, int ref)
         const uint32_t tri = b.vals[leaf];
         const float4 lo = b.triLo[tri], hi = b.triHi[tri];
         c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
-        c.first = leaf, c.count = 1;
+        c.count = 1;
     }
     else
     {
         const float4 lo = b.lo[ref], hi = b.hi[ref];
         c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
-        c.first = floatAsUint(lo.w);
-        c.count = floatAsUint(hi.w) - c.first + 1;
+        c.count = floatAsUint(lo.w);
     }
     return c;
+}
+
+// Sorted-leaf indices of a subtree with at most kMaxLeafTris leaves, left to right.
+VKRT_HD uint32_t collectLeaves(const Bvh2& b, int ref, uint32_t* out)
+{
+    if (ref < 0)
+    {
+        out[0] = (uint32_t)~ref;
+        return 1;
+    }
+    // at most 3 leaves: one child is a leaf, the other a leaf or a pair of leaves
+    uint32_t n = 0;
+    const int2 ch = b.children[ref];
+    const int side[2] = {ch.x, ch.y};
+    for (int k = 0; k < 2; ++k)
+    {
+        if (side[k] < 0)
+        {
+            out[n++] = (uint32_t)~side[k];
+        }
+        else
+        {
+            const int2 g = b.children[side[k]];
+            out[n++] = (uint32_t)~g.x; // grandchildren of a <= 3-leaf subtree are leaves
+            out[n++] = (uint32_t)~g.y;
+        }
+    }
+    return n;
 }
 
 VKRT_HD float halfArea(F3 lo, F3 hi)
@@ -447,9 +475,11 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
         {
             const uint32_t unary = (1u << c[k].count) - 1u; // 1 -> 001, 2 -> 011, 3 -> 111
             node.meta[s] = (uint8_t)((unary << 5) | primOffset);
+            uint32_t leaves[4];
+            collectLeaves(b, c[k].ref, leaves);
             for (uint32_t j = 0; j < c[k].count; ++j)
             {
-                a.primSource[primBase + primOffset + j] = b.vals[c[k].first + j];
+                a.primSource[primBase + primOffset + j] = b.vals[leaves[j]];
             }
             primOffset += c[k].count;
             leafArea += halfArea(c[k].lo, c[k].hi) * (float)c[k].count;

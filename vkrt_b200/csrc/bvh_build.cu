@@ -335,6 +335,281 @@ __global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// PLOC (Meister & Bittner 2018, "Parallel Locally-Ordered Clustering"): the default, higher-quality binary hierarchy.
+// Clusters live in Morton order; every round each cluster finds its nearest neighbour (smallest merged surface
+// area) within kPlocRadius positions, mutual pairs merge into a new binary node, and the survivors are compacted in
+// order.  One kernel per round (PLOC++ style): a persistent grid takes tiles of 1024 clusters by ticket, searches in
+// shared memory (tile + halo), and resolves the compaction offset by decoupled look-back.  Equal distances are
+// ordered by (i xor j) so that duplicates pair up as buddies instead of chaining.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPlocRadius = 8;
+constexpr int kPlocTile = 1024;
+constexpr int kPlocHalo = 2 * kPlocRadius;
+constexpr int kPlocThreads = 256;
+constexpr int kPlocSpan = kPlocTile + 2 * kPlocHalo;
+constexpr int kPlocPerThread = kPlocTile / kPlocThreads;
+
+struct PlocClusters
+{
+    int* id;      // binary-tree ref: >= 0 internal node, < 0 ~sortedLeaf
+    float4* lo;   // w = leaf count (raw bits)
+    float4* hi;
+};
+
+// state: [0],[1] cluster counts of buffers A/B, [2] ticket, [3] finished blocks, [4] binary nodes allocated
+__global__ void __launch_bounds__(kThreads)
+k_ploc_init(Bvh2 bvh, PlocClusters c, uint32_t* state, uint32_t* status, uint32_t statusCount)
+{
+    const uint32_t n = bvh.count;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        const uint32_t tri = bvh.vals[i];
+        float4 lo = bvh.triLo[tri], hi = bvh.triHi[tri];
+        lo.w = __uint_as_float(1u);
+        hi.w = 0.0f;
+        c.id[i] = ~(int)i;
+        c.lo[i] = lo;
+        c.hi[i] = hi;
+    }
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < statusCount; i += gridDim.x * blockDim.x)
+    {
+        status[i] = 0u;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        state[0] = n, state[1] = 0u, state[2] = 0u, state[3] = 0u, state[4] = 0u;
+    }
+}
+
+__global__ void __launch_bounds__(kPlocThreads)
+k_ploc_round(PlocClusters in, PlocClusters out, Bvh2 bvh, uint32_t* state, uint32_t* status, int parity)
+{
+    __shared__ float4 sLo[kPlocSpan];
+    __shared__ float4 sHi[kPlocSpan];
+    __shared__ int sId[kPlocSpan];
+    __shared__ short sNN[kPlocSpan];
+    __shared__ uint32_t sWarp[kPlocThreads / 32];
+    __shared__ uint32_t sTile, sExclusive, sNodeBase, sLast;
+
+    const uint32_t n = state[parity];
+    if (n <= 1u)
+    {
+        // nothing to merge: hand the (single) cluster over so that the result always sits in the buffer of the last round
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+        {
+            if (n == 1u)
+            {
+                out.id[0] = in.id[0], out.lo[0] = in.lo[0], out.hi[0] = in.hi[0];
+            }
+            state[parity ^ 1] = n;
+        }
+        return;
+    }
+    const uint32_t numTiles = (n + kPlocTile - 1) / kPlocTile;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    volatile uint32_t* st = status;
+
+    for (;;)
+    {
+        if (threadIdx.x == 0)
+        {
+            sTile = atomicAdd(&state[2], 1u);
+        }
+        __syncthreads();
+        const uint32_t tile = sTile;
+        if (tile >= numTiles)
+        {
+            break;
+        }
+        const int64_t start = (int64_t)tile * kPlocTile - kPlocHalo; // global index of span slot 0
+        for (int k = threadIdx.x; k < kPlocSpan; k += kPlocThreads)
+        {
+            const int64_t g = start + k;
+            if (g >= 0 && g < (int64_t)n)
+            {
+                sLo[k] = in.lo[g];
+                sHi[k] = in.hi[g];
+                sId[k] = in.id[g];
+            }
+        }
+        __syncthreads();
+        // nearest neighbour of every cluster whose choice can matter to the tile: slots [radius, span - radius)
+        for (int k = kPlocRadius + threadIdx.x; k < kPlocSpan - kPlocRadius; k += kPlocThreads)
+        {
+            const int64_t g = start + k;
+            if (g < 0 || g >= (int64_t)n)
+            {
+                continue;
+            }
+            const float4 lo = sLo[k], hi = sHi[k];
+            float bestD = INFINITY;
+            uint32_t bestX = 0xFFFFFFFFu;
+            int bestJ = -1;
+#pragma unroll 4
+            for (int j = k - kPlocRadius; j <= k + kPlocRadius; ++j)
+            {
+                const int64_t gj = start + j;
+                if (j == k || gj < 0 || gj >= (int64_t)n)
+                {
+                    continue;
+                }
+                const float4 l2 = sLo[j], h2 = sHi[j];
+                const float dx = fmaxf(hi.x, h2.x) - fminf(lo.x, l2.x), dy = fmaxf(hi.y, h2.y) - fminf(lo.y, l2.y),
+                            dz = fmaxf(hi.z, h2.z) - fminf(lo.z, l2.z);
+                const float d = dx * dy + dy * dz + dz * dx;
+                const uint32_t x = (uint32_t)g ^ (uint32_t)gj;
+                if (d < bestD || (d == bestD && x < bestX) || bestJ < 0)
+                {
+                    bestD = d, bestX = x, bestJ = j;
+                }
+            }
+            sNN[k] = (short)bestJ;
+        }
+        __syncthreads();
+
+        // merge decisions for the tile's own clusters, kPlocPerThread consecutive ones per thread
+        uint32_t keepMask = 0, mergeMask = 0;
+#pragma unroll
+        for (int e = 0; e < kPlocPerThread; ++e)
+        {
+            const int k = kPlocHalo + threadIdx.x * kPlocPerThread + e;
+            const int64_t g = start + k;
+            if (g < (int64_t)n)
+            {
+                const int p = sNN[k];
+                const bool mutual = p >= 0 && sNN[p] == k;
+                if (!mutual || k < p)
+                {
+                    keepMask |= 1u << e;
+                }
+                if (mutual && k < p)
+                {
+                    mergeMask |= 1u << e;
+                }
+            }
+        }
+        // block scan of (kept, merged) packed as 16 + 16 bits
+        const uint32_t mine = (uint32_t)__popc(keepMask) | ((uint32_t)__popc(mergeMask) << 16);
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= (uint32_t)o)
+            {
+                incl += t;
+            }
+        }
+        if (lane == 31)
+        {
+            sWarp[warp] = incl;
+        }
+        __syncthreads();
+        uint32_t warpBase = 0, total = 0;
+        for (uint32_t w2 = 0; w2 < kPlocThreads / 32; ++w2)
+        {
+            const uint32_t v = sWarp[w2];
+            if (w2 < warp)
+            {
+                warpBase += v;
+            }
+            total += v;
+        }
+        const uint32_t excl = warpBase + incl - mine;
+        if (threadIdx.x == 0)
+        {
+            const uint32_t tileKeep = total & 0xFFFFu, tileMerge = total >> 16;
+            st[tile] = tileKeep | (tile == 0 ? kLookInclusive : kLookAggregate);
+            uint32_t exclusive = 0;
+            if (tile > 0)
+            {
+                for (uint32_t t = tile - 1;; --t)
+                {
+                    uint32_t w2;
+                    do
+                    {
+                        w2 = st[t];
+                    } while ((w2 & ~kLookValue) == 0u);
+                    exclusive += w2 & kLookValue;
+                    if (w2 & kLookInclusive)
+                    {
+                        break;
+                    }
+                }
+                st[tile] = (exclusive + tileKeep) | kLookInclusive;
+            }
+            sExclusive = exclusive;
+            sNodeBase = tileMerge ? atomicAdd(&state[4], tileMerge) : 0u;
+            if (tile == numTiles - 1)
+            {
+                state[parity ^ 1] = exclusive + tileKeep;
+            }
+        }
+        __syncthreads();
+        uint32_t dst = sExclusive + (excl & 0xFFFFu);
+        uint32_t node = sNodeBase + (excl >> 16);
+#pragma unroll
+        for (int e = 0; e < kPlocPerThread; ++e)
+        {
+            if (!((keepMask >> e) & 1u))
+            {
+                continue;
+            }
+            const int k = kPlocHalo + threadIdx.x * kPlocPerThread + e;
+            float4 lo = sLo[k], hi = sHi[k];
+            int id = sId[k];
+            if ((mergeMask >> e) & 1u)
+            {
+                const int p = sNN[k];
+                const float4 l2 = sLo[p], h2 = sHi[p];
+                const uint32_t leaves = __float_as_uint(lo.w) + __float_as_uint(l2.w);
+                lo = make_float4(fminf(lo.x, l2.x), fminf(lo.y, l2.y), fminf(lo.z, l2.z), __uint_as_float(leaves));
+                hi = make_float4(fmaxf(hi.x, h2.x), fmaxf(hi.y, h2.y), fmaxf(hi.z, h2.z), 0.0f);
+                bvh.children[node] = make_int2(id, sId[p]);
+                bvh.lo[node] = lo;
+                bvh.hi[node] = hi;
+                id = (int)node;
+                ++node;
+            }
+            out.id[dst] = id;
+            out.lo[dst] = lo;
+            out.hi[dst] = hi;
+            ++dst;
+        }
+        __syncthreads(); // shared arrays are reused by the next tile
+    }
+
+    // the last block to finish re-arms ticket and look-back words for the next round
+    __threadfence();
+    if (threadIdx.x == 0)
+    {
+        sLast = atomicAdd(&state[3], 1u) == gridDim.x - 1 ? 1u : 0u;
+    }
+    __syncthreads();
+    if (sLast)
+    {
+        for (uint32_t i = threadIdx.x; i < numTiles; i += kPlocThreads)
+        {
+            status[i] = 0u;
+        }
+        if (threadIdx.x == 0)
+        {
+            state[2] = 0u, state[3] = 0u;
+        }
+    }
+}
+
+// root of the binary hierarchy = the single cluster left in buffer `parity`
+__global__ void k_ploc_finish(PlocClusters c, Bvh2 bvh, const uint32_t* state, int parity, uint32_t* remaining)
+{
+    *remaining = state[parity];
+    if (state[parity] == 1u && bvh.count > 1)
+    {
+        *bvh.root = c.id[0];
+    }
+}
+
 // Level-synchronous collapse without host round trips.  `range` = {first, last, ticket, levels}: wide nodes
 // [first,last) were allocated by the previous level.  Narrow levels (<= kNarrowLevel nodes) are swept by ONE block that
 // loops over levels with __syncthreads(); wide levels take one multi-block launch each, whose last block publishes
@@ -615,11 +890,55 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         bvh.triHi = sc.triHi.as<float4>();
         bvh.count = n;
         bvh.root = root;
-        if (n > 1)
+        const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
+        if (n > 1 && fast)
         {
             VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0xFF, (size_t)(n - 1) * 4, s)); // -1
             k_lbvh<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
             ctx->launches += 1;
+        }
+        else if (n > 1)
+        {
+            const uint32_t statusCount = (n + kPlocTile - 1) / kPlocTile;
+            VKRT_CUDA_TRY(ctx, sc.plocLoA.reserve(n1 * sizeof(float4)));
+            VKRT_CUDA_TRY(ctx, sc.plocHiA.reserve(n1 * sizeof(float4)));
+            VKRT_CUDA_TRY(ctx, sc.plocLoB.reserve(n1 * sizeof(float4)));
+            VKRT_CUDA_TRY(ctx, sc.plocHiB.reserve(n1 * sizeof(float4)));
+            VKRT_CUDA_TRY(ctx, sc.plocStatus.reserve((size_t)statusCount * 4 + 64));
+            PlocClusters cl[2];
+            cl[0].id = sc.flags.as<int>(), cl[0].lo = sc.plocLoA.as<float4>(), cl[0].hi = sc.plocHiA.as<float4>();
+            cl[1].id = reinterpret_cast<int*>(sc.keysB.as<uint32_t>()), cl[1].lo = sc.plocLoB.as<float4>(), cl[1].hi = sc.plocHiB.as<float4>();
+            uint32_t* state = sc.plocStatus.as<uint32_t>(); // 16 words of state, then the look-back words
+            uint32_t* status = state + 16;
+            k_ploc_init<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(bvh, cl[0], state, status, statusCount);
+            ctx->launches += 1;
+            int round = 0;
+            int batch = 6;
+            for (uint32_t m = n; m > 1; m >>= 1)
+            {
+                batch += 2; // ~2 log2(n): a round usually leaves 55-65 % of the clusters
+            }
+            for (;;)
+            {
+                for (int k = 0; k < batch; ++k, ++round)
+                {
+                    k_ploc_round<<<(uint32_t)sm * 4u, kPlocThreads, 0, s>>>(cl[round & 1], cl[(round + 1) & 1], bvh, state, status, round & 1);
+                }
+                k_ploc_finish<<<1, 1, 0, s>>>(cl[round & 1], bvh, state, round & 1, state + 8);
+                ctx->launches += batch + 1;
+                uint32_t remaining = 0;
+                VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(&remaining, state + 8, 4, cudaMemcpyDeviceToHost, s));
+                VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+                if (remaining == 1)
+                {
+                    break;
+                }
+                if (round > 4096)
+                {
+                    return ctx->fail(VKRT_ERROR_CUDA, "PLOC: did not converge");
+                }
+                batch = 8;
+            }
         }
 
         CollapseArgs ca;

@@ -24,10 +24,11 @@ namespace vkrt
 struct BuildScratch
 {
     DeviceBuffer triLo, triHi, keysA, keysB, valsA, valsB, tileHist, children, nodeLo, nodeHi, flags, taskRef, primSource, small;
+    DeviceBuffer plocLoA, plocHiA, plocLoB, plocHiB, plocStatus; // PLOC cluster boxes (ping-pong) and look-back words
     void release()
     {
         DeviceBuffer* all[] = {&triLo, &triHi, &keysA, &keysB, &valsA, &valsB, &tileHist, &children, &nodeLo, &nodeHi, &flags,
-                               &taskRef, &primSource, &small};
+                               &taskRef, &primSource, &small, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus};
         for (DeviceBuffer* b : all)
         {
             b->release();

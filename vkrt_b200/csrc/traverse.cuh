@@ -269,102 +269,163 @@ struct BestHit
     uint32_t buildIndex; // tie-break key of the current hit
 };
 
+// Per-ray traversal state inside one BLAS (object space).  Kept as plain scalars so it lives in registers.
+struct RayCtx
+{
+    F3 o, idir;
+    RayPre rp;
+    uint32_t octant;
+    float tmin, tminP;
+    uint2 ngroup; // x = base index of the internal children, y = hit bits 24..31 | imask in bits 0..7
+    uint2 tgroup; // x = first packed triangle of the node, y = hit bits 0..23
+    int sp;
+};
+
+VKRT_HD void beginTraversal(RayCtx& c, F3 o, F3 d, float tmin)
+{
+    c.o = o;
+    c.rp = makeRayPre(d);
+    c.idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    c.tmin = tmin;
+    c.tminP = padDown(tmin);
+    c.ngroup = make_uint2(0u, 0x80000000u);
+    c.tgroup = make_uint2(0u, 0u);
+    c.sp = 0;
+}
+
+constexpr int kStepDone = 1;  // nothing left in this BLAS
+constexpr int kStepFound = 2; // ANY: an occluder was accepted
+constexpr int kStepHit = 4;   // flag: at least one triangle was accepted during this step
+
+// One traversal step: pops the nearest pending internal child (if any), tests its 8 child boxes, then tests the
+// triangles the node references.  Returns 0 to continue, or kStepDone / kStepFound, optionally ORed with kStepHit.
+//
+// Triangle postponing (Ylitie et al. 2017, section 4.3; device only): when fewer than postpone/32 of the lanes that
+// entered the step have triangles to test, the triangle group goes onto the stack (entries with no bit above 23 set)
+// and the lane carries on with its nodes, so that triangle tests run with fuller warps.
+template<bool ANY>
+VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const PackedTri* tris, uint32_t instance, BestHit& best,
+                          TraceCounters* counters, uint32_t one, uint32_t postpone = 0u)
+{
+    int result = 0;
+#if defined(__CUDA_ARCH__)
+    const uint32_t postponeBelow = postpone ? ((uint32_t)__popc(__activemask()) * postpone) >> 5 : 0u;
+#else
+    (void)postpone;
+#endif
+    if (c.ngroup.y > 0x00FFFFFFu)
+    {
+        const uint32_t octinv = 7u - c.octant;
+        const uint32_t bit = highestBit(c.ngroup.y);
+        const uint32_t base = c.ngroup.x;
+        c.ngroup.y &= ~(1u << bit);
+        if (c.ngroup.y > 0x00FFFFFFu)
+        {
+            if (c.sp < kStackSize)
+            {
+                stack[c.sp++] = c.ngroup;
+            }
+            else if (counters)
+            {
+                counters->overflow = 1;
+            }
+        }
+        const uint32_t slot = (bit - 24u) ^ octinv;
+        const uint32_t rel = popCount(c.ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
+        const NodeWords w = loadNode(nodes, base + rel);
+        if (counters)
+        {
+            ++counters->nodes;
+        }
+        const uint32_t hits = intersectNode(w, c.o, c.idir, c.octant, c.tminP, padUp(best.t), one);
+        const uint32_t imask = floatAsUint(w.n0.w) >> 24;
+        c.ngroup = make_uint2(w.n1.x, (hits & 0xFF000000u) | imask);
+        c.tgroup = make_uint2(w.n1.y, hits & 0x00FFFFFFu);
+    }
+    else
+    {
+        c.tgroup = c.ngroup; // a postponed triangle group popped from the stack, or nothing
+        c.ngroup = make_uint2(0u, 0u);
+    }
+
+    while (c.tgroup.y != 0u)
+    {
+#if defined(__CUDA_ARCH__)
+        if ((uint32_t)__popc(__activemask()) < postponeBelow && c.sp < kStackSize && (c.ngroup.y > 0x00FFFFFFu || c.sp > 0))
+        {
+            if (c.ngroup.y > 0x00FFFFFFu)
+            {
+                stack[c.sp++] = c.tgroup;
+            }
+            else // nothing but the stack left: trade places with its top entry
+            {
+                c.ngroup = stack[c.sp - 1];
+                stack[c.sp - 1] = c.tgroup;
+            }
+            c.tgroup = make_uint2(0u, 0u);
+            return result;
+        }
+#endif
+        const uint32_t bit = highestBit(c.tgroup.y);
+        c.tgroup.y &= ~(1u << bit);
+        const uint32_t slotIndex = c.tgroup.x + bit;
+        F3 v0, v1, v2;
+        uint32_t geometry, primitive, buildIndex;
+        loadTriangle(tris, slotIndex, v0, v1, v2, geometry, primitive, buildIndex);
+        if (counters)
+        {
+            ++counters->tris;
+        }
+        (void)geometry;
+        (void)primitive;
+        bool tieOk = false;
+        if (!ANY)
+        {
+            tieOk = best.tri != kInvalid && (instance < best.instance || (instance == best.instance && buildIndex < best.buildIndex));
+        }
+        float t, b1, b2;
+        if (intersectTriangle(v0, v1, v2, c.o, c.rp, c.tmin, best.t, tieOk, t, b1, b2))
+        {
+            best.t = t, best.b1 = b1, best.b2 = b2;
+            best.tri = slotIndex, best.instance = instance, best.buildIndex = buildIndex;
+            result |= kStepHit;
+            if (ANY)
+            {
+                return result | kStepFound;
+            }
+        }
+    }
+
+    if (c.ngroup.y <= 0x00FFFFFFu)
+    {
+        if (c.sp == 0)
+        {
+            return result | kStepDone;
+        }
+        c.ngroup = stack[--c.sp];
+    }
+    return result;
+}
+
 // Traverses one BLAS with an object-space ray.  ANY: return true at the first accepted triangle.
 template<bool ANY>
 VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d, float tmin, uint32_t instance,
                           BestHit& best, TraceCounters* counters, uint32_t one)
 {
-    const RayPre rp = makeRayPre(d);
-    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    const uint32_t octinv = 7u - octant;
-    const float tminP = padDown(tmin);
-
+    RayCtx c;
+    beginTraversal(c, o, d, tmin);
     uint2 stack[kStackSize];
-    int sp = 0;
-    // node group: x = base index of the internal children, y = hit bits 24..31 | imask in bits 0..7
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    uint2 tgroup = make_uint2(0u, 0u);
     bool found = false;
-
     for (;;)
     {
-        if (ngroup.y > 0x00FFFFFFu)
+        const int r = traversalStep<ANY>(c, stack, nodes, tris, instance, best, counters, one);
+        found = found || (r & kStepHit);
+        if (r & (kStepDone | kStepFound))
         {
-            const uint32_t bit = highestBit(ngroup.y);
-            const uint32_t base = ngroup.x;
-            ngroup.y &= ~(1u << bit);
-            if (ngroup.y > 0x00FFFFFFu)
-            {
-                if (sp < kStackSize)
-                {
-                    stack[sp++] = ngroup;
-                }
-                else if (counters)
-                {
-                    counters->overflow = 1;
-                }
-            }
-            const uint32_t slot = (bit - 24u) ^ octinv;
-            const uint32_t rel = popCount(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
-            const NodeWords w = loadNode(nodes, base + rel);
-            if (counters)
-            {
-                ++counters->nodes;
-            }
-            const uint32_t hits = intersectNode(w, o, idir, octant, tminP, padUp(best.t), one);
-            const uint32_t imask = floatAsUint(w.n0.w) >> 24;
-            ngroup = make_uint2(w.n1.x, (hits & 0xFF000000u) | imask);
-            tgroup = make_uint2(w.n1.y, hits & 0x00FFFFFFu);
-        }
-        else
-        {
-            tgroup = make_uint2(0u, 0u);
-        }
-
-        while (tgroup.y != 0u)
-        {
-            const uint32_t bit = highestBit(tgroup.y);
-            tgroup.y &= ~(1u << bit);
-            const uint32_t slotIndex = tgroup.x + bit;
-            F3 v0, v1, v2;
-            uint32_t geometry, primitive, buildIndex;
-            loadTriangle(tris, slotIndex, v0, v1, v2, geometry, primitive, buildIndex);
-            if (counters)
-            {
-                ++counters->tris;
-            }
-            (void)geometry;
-            (void)primitive;
-            bool tieOk = false;
-            if (!ANY)
-            {
-                tieOk = best.tri != kInvalid &&
-                        (instance < best.instance || (instance == best.instance && buildIndex < best.buildIndex));
-            }
-            float t, b1, b2;
-            if (intersectTriangle(v0, v1, v2, o, rp, tmin, best.t, tieOk, t, b1, b2))
-            {
-                best.t = t, best.b1 = b1, best.b2 = b2;
-                best.tri = slotIndex, best.instance = instance, best.buildIndex = buildIndex;
-                found = true;
-                if (ANY)
-                {
-                    return true;
-                }
-            }
-        }
-
-        if (ngroup.y <= 0x00FFFFFFu)
-        {
-            if (sp == 0)
-            {
-                break;
-            }
-            ngroup = stack[--sp];
+            return found;
         }
     }
-    return found;
 }
 
 // World AABB of one instance for the top-level pass.
@@ -388,14 +449,57 @@ VKRT_HD bool intersectBounds(const InstanceBounds& b, F3 o, F3 idir, float tmin,
     return tn <= tf;
 }
 
-// traceRayEXT over the whole scene: all instances (mask 0xFF, cull disabled — src/Raytracer.cpp:1172-1177),
-// visited front to back by the entry distance of their world bounds.  Returns true on any accepted hit.
-// `best.t` must be initialised to the ray's tmax and best.tri to kInvalid.
+// Top-level pass: instances are visited front to back by the entry distance of their world bounds, ties by index.
+// The cursor remembers the last visited (distance, index); selectNextInstance returns the next one whose bounds the
+// ray still enters before `tmax`, or kInvalid.
+struct InstanceCursor
+{
+    float lastT;
+    uint32_t lastIdx;
+};
+VKRT_HD void resetCursor(InstanceCursor& cur)
+{
+    cur.lastT = -INFINITY;
+    cur.lastIdx = kInvalid; // "nothing visited yet"
+}
+VKRT_HD uint32_t selectNextInstance(const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 idir, float tmin, float tmax,
+                                    InstanceCursor& cur)
+{
+    float bestT = INFINITY;
+    uint32_t bestIdx = kInvalid;
+    const bool first = cur.lastIdx == kInvalid;
+    for (uint32_t i = 0; i < instanceCount; ++i)
+    {
+        float tn;
+        if (!intersectBounds(bounds[i], o, idir, tmin, tmax, tn))
+        {
+            continue;
+        }
+        // strict (t, index) ordering after the last visited instance
+        const bool after = first || tn > cur.lastT || (tn == cur.lastT && i > cur.lastIdx);
+        if (after && (tn < bestT || (tn == bestT && i < bestIdx)))
+        {
+            bestT = tn;
+            bestIdx = i;
+        }
+    }
+    if (bestIdx != kInvalid)
+    {
+        cur.lastT = bestT;
+        cur.lastIdx = bestIdx;
+    }
+    return bestIdx;
+}
+
+VKRT_HD bool validRay(F3 o, F3 d) { return finite3(o) && finite3(d) && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f); }
+
+// traceRayEXT over the whole scene: all instances (mask 0xFF, cull disabled — src/Raytracer.cpp:1172-1177).
+// Returns true on any accepted hit.  `best.t` must be initialised to the ray's tmax and best.tri to kInvalid.
 template<bool ANY>
 VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 d,
                         float tmin, BestHit& best, TraceCounters* counters, uint32_t one = 0x3F800000u)
 {
-    if (!finite3(o) || !finite3(d) || (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) || !(best.t > tmin))
+    if (!validRay(o, d) || !(best.t > tmin))
     {
         return false;
     }
@@ -405,51 +509,30 @@ VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* b
         const InstanceRecord& inst = instances[0];
         const F3 oo = affinePoint(inst.w2o, o);
         const F3 dd = affineDir(inst.w2o, d);
-        if (!finite3(oo) || !finite3(dd) || (dd.x == 0.0f && dd.y == 0.0f && dd.z == 0.0f))
+        if (!validRay(oo, dd))
         {
             return false;
         }
         return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one);
     }
     const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    // visit instances in order of increasing entry distance: repeatedly select the nearest not yet visited one
-    float lastT = -INFINITY;
-    uint32_t lastIdx = 0;
-    bool first = true;
+    InstanceCursor cur;
+    resetCursor(cur);
     for (;;)
     {
-        float bestT = INFINITY;
-        uint32_t bestIdx = kInvalid;
-        for (uint32_t i = 0; i < instanceCount; ++i)
-        {
-            float tn;
-            if (!intersectBounds(bounds[i], o, idir, tmin, best.t, tn))
-            {
-                continue;
-            }
-            // strict (t, index) ordering after the last visited instance
-            const bool after = first || tn > lastT || (tn == lastT && i > lastIdx);
-            if (after && (tn < bestT || (tn == bestT && i < bestIdx)))
-            {
-                bestT = tn;
-                bestIdx = i;
-            }
-        }
-        if (bestIdx == kInvalid)
+        const uint32_t idx = selectNextInstance(bounds, instanceCount, o, idir, tmin, best.t, cur);
+        if (idx == kInvalid)
         {
             break;
         }
-        first = false;
-        lastT = bestT;
-        lastIdx = bestIdx;
-        const InstanceRecord& inst = instances[bestIdx];
+        const InstanceRecord& inst = instances[idx];
         const F3 oo = affinePoint(inst.w2o, o);
         const F3 dd = affineDir(inst.w2o, d);
-        if (!finite3(oo) || !finite3(dd) || (dd.x == 0.0f && dd.y == 0.0f && dd.z == 0.0f))
+        if (!validRay(oo, dd))
         {
             continue;
         }
-        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, bestIdx, best, counters, one))
+        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, idx, best, counters, one))
         {
             found = true;
             if (ANY)

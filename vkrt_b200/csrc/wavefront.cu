@@ -11,6 +11,7 @@
 #include "traverse.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace vkrt
 {
@@ -75,7 +76,7 @@ __device__ __forceinline__ uint32_t warpAppend(uint32_t* counter, bool want)
 
 __global__ void k_reset_counters(uint32_t* counters)
 {
-    if (threadIdx.x < 8)
+    if (threadIdx.x < 16) // [0..3] shadow queue sizes, [4] reflection queue size, [8..11] ray-fetch cursors of the trace kernels
     {
         counters[threadIdx.x] = 0u;
     }
@@ -107,35 +108,265 @@ k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, ui
     }
 }
 
-template<bool STATS>
-__global__ void __launch_bounds__(kTraceThreads)
-k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
-                uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
-                int statSlot)
+// ------------------------------------------------------------------------------------------------------------
+// Persistent-thread traversal with dynamic ray fetch (Aila & Laine 2009; Ylitie et al. 2017, section 4.3).
+// A warp keeps a private pool of ray indices that it refills from the launch-wide cursor in chunks (one global
+// atomic per chunk); lanes whose ray has finished take the next pool entries, and when fewer than `refill` lanes
+// of the warp are still traversing, the busy lanes leave the traversal loop so that the idle ones can be re-armed.
+// Sources map a queue position to a ray and receive the result.
+// ------------------------------------------------------------------------------------------------------------
+struct ClosestSource
 {
-    const uint32_t count = countPtr ? *countPtr : countImm;
-    TraceCounters tc;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    const float4 *rayO, *rayD;
+    float4* hitA;
+    uint32_t* hitInst;
+    __device__ __forceinline__ uint32_t map(uint32_t i) const { return i; }
+    __device__ __forceinline__ void load(uint32_t h, F3& o, F3& d, float& tmin, float& tmax) const
     {
-        const float4 o4 = rayO[i], d4 = rayD[i];
-        BestHit best;
-        best.t = d4.w;
-        best.b1 = best.b2 = 0.0f;
-        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
-        traceScene<false>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z), f3(d4.x, d4.y, d4.z), o4.w, best,
-                          STATS ? &tc : nullptr, scene.one);
-        hitA[i] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.tri));
-        hitInst[i] = best.instance;
+        const float4 o4 = rayO[h], d4 = rayD[h];
+        o = f3(o4.x, o4.y, o4.z), d = f3(d4.x, d4.y, d4.z);
+        tmin = o4.w, tmax = d4.w;
     }
+    __device__ __forceinline__ void commit(uint32_t h, const BestHit& best, bool) const
+    {
+        hitA[h] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.tri));
+        hitInst[h] = best.instance;
+    }
+};
+
+struct ShadowSource // the four per-light queues, concatenated
+{
+    const float4 *shadowO, *shadowD;
+    uint32_t* shadowBits;
+    uint32_t c0, c01, c012, capacity;
+    __device__ __forceinline__ uint32_t map(uint32_t i) const
+    {
+        return i < c0 ? i : (i < c01 ? capacity + (i - c0) : (i < c012 ? 2u * capacity + (i - c01) : 3u * capacity + (i - c012)));
+    }
+    __device__ __forceinline__ void load(uint32_t h, F3& o, F3& d, float& tmin, float& tmax) const
+    {
+        const float4 o4 = shadowO[h], d4 = shadowD[h];
+        o = f3(o4.x, o4.y, o4.z), d = f3(d4.x, d4.y, d4.z);
+        tmin = kRayTMin, tmax = o4.w;
+    }
+    __device__ __forceinline__ void commit(uint32_t h, const BestHit&, bool occluded) const
+    {
+        if (occluded)
+        {
+            const uint32_t light = h / capacity;
+            atomicOr(&shadowBits[__float_as_uint(shadowD[h].w)], 1u << light);
+        }
+    }
+};
+
+struct ListAnySource // ray-level API, any-hit
+{
+    const float4 *rayO, *rayD;
+    VkrtHit* out;
+    __device__ __forceinline__ uint32_t map(uint32_t i) const { return i; }
+    __device__ __forceinline__ void load(uint32_t h, F3& o, F3& d, float& tmin, float& tmax) const
+    {
+        const float4 o4 = rayO[h], d4 = rayD[h];
+        o = f3(o4.x, o4.y, o4.z), d = f3(d4.x, d4.y, d4.z);
+        tmin = o4.w, tmax = d4.w;
+    }
+    __device__ __forceinline__ void commit(uint32_t h, const BestHit& best, bool occluded) const
+    {
+        VkrtHit o;
+        o.t = occluded ? best.t : 0.f, o.b1 = 0.f, o.b2 = 0.f;
+        o.instance = occluded ? best.instance : kInvalid;
+        o.geometry = o.primitive = occluded ? 0u : kInvalid;
+        out[h] = o;
+    }
+};
+
+template<bool MULTI>
+struct BlasBinding
+{
+    const Node8* nodes;
+    const PackedTri* tris;
+    uint32_t instance;
+    InstanceCursor cursor;
+};
+
+// Moves the ray into the next instance it enters (MULTI) or into instance 0; false when there is none.
+template<bool MULTI>
+__device__ __forceinline__ bool enterInstance(const SceneDev& scene, F3 o, F3 d, float tmin, float tmax, BlasBinding<MULTI>& bind, RayCtx& c)
+{
+    if (!MULTI)
+    {
+        const InstanceRecord& inst = scene.instances[0];
+        const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
+        if (!validRay(oo, dd))
+        {
+            return false;
+        }
+        beginTraversal(c, oo, dd, tmin);
+        return true;
+    }
+    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    for (;;)
+    {
+        const uint32_t idx = selectNextInstance(scene.bounds, scene.instanceCount, o, idir, tmin, tmax, bind.cursor);
+        if (idx == kInvalid)
+        {
+            return false;
+        }
+        const InstanceRecord& inst = scene.instances[idx];
+        const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
+        if (!validRay(oo, dd))
+        {
+            continue;
+        }
+        bind.instance = idx, bind.nodes = inst.nodes, bind.tris = inst.tris;
+        beginTraversal(c, oo, dd, tmin);
+        return true;
+    }
+}
+
+template<bool ANY, bool MULTI, bool STATS, typename Source>
+__device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, uint32_t refill,
+                                                uint32_t postpone, TraceCounters& tc)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
+    uint32_t chunk = (total / (warpsTotal * 8u) + 31u) & ~31u;
+    chunk = min(max(chunk, 32u), 512u);
+    uint32_t poolNext = 0, poolEnd = 0; // warp-uniform
+    bool exhausted = false;             // warp-uniform: the launch-wide cursor has passed `total`
+
+    uint2 stack[kStackSize];
+    RayCtx c;
+    BestHit best;
+    BlasBinding<MULTI> bind;
+    bind.nodes = scene.instances[0].nodes, bind.tris = scene.instances[0].tris, bind.instance = 0u;
+    uint32_t handle = 0;
+    bool active = false;
+
+    for (;;)
+    {
+        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle != 0u && !exhausted)
+        {
+            const uint32_t need = __popc(idle), avail = poolEnd - poolNext;
+            uint32_t newBase = 0;
+            if (avail < need)
+            {
+                if (lane == 0)
+                {
+                    newBase = atomicAdd(cursor, chunk);
+                }
+                newBase = __shfl_sync(0xFFFFFFFFu, newBase, 0);
+            }
+            const uint32_t k = __popc(idle & ((1u << lane) - 1u));
+            const uint32_t idx = k < avail ? poolNext + k : newBase + (k - avail);
+            if (avail < need)
+            {
+                poolNext = newBase + (need - avail), poolEnd = newBase + chunk;
+                exhausted = newBase >= total;
+            }
+            else
+            {
+                poolNext += need;
+            }
+            if (!active && idx < total)
+            {
+                handle = src.map(idx);
+                F3 o, d;
+                float tmin, tmax;
+                src.load(handle, o, d, tmin, tmax);
+                best.t = tmax, best.b1 = best.b2 = 0.0f;
+                best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
+                bool ok = validRay(o, d) && tmax > tmin;
+                if (ok)
+                {
+                    if (MULTI)
+                    {
+                        resetCursor(bind.cursor);
+                    }
+                    ok = enterInstance<MULTI>(scene, o, d, tmin, tmax, bind, c);
+                }
+                if (ok)
+                {
+                    active = true;
+                }
+                else
+                {
+                    src.commit(handle, best, false);
+                }
+            }
+        }
+        if (__ballot_sync(0xFFFFFFFFu, active) == 0u)
+        {
+            if (exhausted)
+            {
+                break;
+            }
+            continue;
+        }
+        if (active)
+        {
+            for (;;)
+            {
+                const int r = traversalStep<ANY>(c, stack, bind.nodes, bind.tris, bind.instance, best, STATS ? &tc : nullptr, scene.one,
+                                                   postpone);
+                if (r & kStepFound)
+                {
+                    src.commit(handle, best, true);
+                    active = false;
+                    break;
+                }
+                if (r & kStepDone)
+                {
+                    if (MULTI)
+                    {
+                        F3 o, d;
+                        float tmin, tmax;
+                        src.load(handle, o, d, tmin, tmax);
+                        if (enterInstance<MULTI>(scene, o, d, tmin, best.t, bind, c))
+                        {
+                            continue;
+                        }
+                    }
+                    src.commit(handle, best, best.tri != kInvalid);
+                    active = false;
+                    break;
+                }
+                if (!exhausted && (uint32_t)__popc(__activemask()) < refill)
+                {
+                    break;
+                }
+            }
+        }
+    }
+}
+
+template<bool STATS>
+__device__ __forceinline__ void flushTraceCounters(const TraceCounters& tc, unsigned long long* statCounters, int nodeSlot)
+{
     if (STATS)
     {
-        atomicAdd(&statCounters[3], (unsigned long long)tc.nodes);
-        atomicAdd(&statCounters[4], (unsigned long long)tc.tris);
+        atomicAdd(&statCounters[nodeSlot], (unsigned long long)tc.nodes);
+        atomicAdd(&statCounters[nodeSlot + 1], (unsigned long long)tc.tris);
         if (tc.overflow)
         {
             atomicAdd(&statCounters[5], 1ull);
         }
     }
+}
+
+template<bool STATS, bool MULTI>
+__global__ void __launch_bounds__(kTraceThreads)
+k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
+                uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
+                int statSlot, uint32_t* cursor, uint32_t refill, uint32_t postpone)
+{
+    const uint32_t count = countPtr ? *countPtr : countImm;
+    TraceCounters tc;
+    ClosestSource src;
+    src.rayO = rayO, src.rayD = rayD, src.hitA = hitA, src.hitInst = hitInst;
+    tracePersistent<false, MULTI, STATS>(scene, src, count, cursor, refill, postpone, tc);
+    flushTraceCounters<STATS>(tc, statCounters, 3);
     if (statSlot >= 0 && blockIdx.x == 0 && threadIdx.x == 0 && countPtr)
     {
         atomicAdd(&statCounters[statSlot], (unsigned long long)count);
@@ -229,54 +460,18 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 }
 
 // shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
-template<bool STATS>
+template<bool STATS, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads)
-k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters)
+k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor, uint32_t refill, uint32_t postpone)
 {
     const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
     const uint32_t total = c0 + c1 + c2 + c3;
     TraceCounters tc;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
-    {
-        uint32_t light, slot;
-        if (i < c0)
-        {
-            light = 0, slot = i;
-        }
-        else if (i < c0 + c1)
-        {
-            light = 1, slot = i - c0;
-        }
-        else if (i < c0 + c1 + c2)
-        {
-            light = 2, slot = i - c0 - c1;
-        }
-        else
-        {
-            light = 3, slot = i - c0 - c1 - c2;
-        }
-        const size_t src = (size_t)light * w.capacity + slot;
-        const float4 o4 = w.shadowO[src], d4 = w.shadowD[src];
-        BestHit best;
-        best.t = o4.w;
-        best.b1 = best.b2 = 0.0f;
-        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
-        const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
-                                               f3(d4.x, d4.y, d4.z), kRayTMin, best, STATS ? &tc : nullptr, scene.one);
-        if (occluded)
-        {
-            atomicOr(&w.shadowBits[__float_as_uint(d4.w)], 1u << light);
-        }
-    }
-    if (STATS)
-    {
-        atomicAdd(&statCounters[6], (unsigned long long)tc.nodes);
-        atomicAdd(&statCounters[7], (unsigned long long)tc.tris);
-        if (tc.overflow)
-        {
-            atomicAdd(&statCounters[5], 1ull);
-        }
-    }
+    ShadowSource src;
+    src.shadowO = w.shadowO, src.shadowD = w.shadowD, src.shadowBits = w.shadowBits;
+    src.c0 = c0, src.c01 = c0 + c1, src.c012 = c0 + c1 + c2, src.capacity = w.capacity;
+    tracePersistent<true, MULTI, STATS>(scene, src, total, cursor, refill, postpone, tc);
+    flushTraceCounters<STATS>(tc, statCounters, 6);
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
         atomicAdd(&statCounters[1], (unsigned long long)total);
@@ -406,32 +601,16 @@ __global__ void k_hits_export(SceneDev scene, const float4* __restrict__ hitA, c
 }
 
 // any-hit over a plain ray list (ray-level API): writes instance = 0 / kInvalid
-template<bool STATS>
+template<bool STATS, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads)
 k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, uint32_t count, VkrtHit* __restrict__ out,
-                 unsigned long long* statCounters)
+                 unsigned long long* statCounters, uint32_t* cursor, uint32_t refill, uint32_t postpone)
 {
     TraceCounters tc;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-    {
-        const float4 o4 = rayO[i], d4 = rayD[i];
-        BestHit best;
-        best.t = d4.w;
-        best.b1 = best.b2 = 0.0f;
-        best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
-        const bool occluded = traceScene<true>(scene.instances, scene.bounds, scene.instanceCount, f3(o4.x, o4.y, o4.z),
-                                               f3(d4.x, d4.y, d4.z), o4.w, best, STATS ? &tc : nullptr, scene.one);
-        VkrtHit o;
-        o.t = occluded ? best.t : 0.f, o.b1 = 0.f, o.b2 = 0.f;
-        o.instance = occluded ? best.instance : kInvalid;
-        o.geometry = o.primitive = occluded ? 0u : kInvalid;
-        out[i] = o;
-    }
-    if (STATS)
-    {
-        atomicAdd(&statCounters[6], (unsigned long long)tc.nodes);
-        atomicAdd(&statCounters[7], (unsigned long long)tc.tris);
-    }
+    ListAnySource src;
+    src.rayO = rayO, src.rayD = rayD, src.out = out;
+    tracePersistent<true, MULTI, STATS>(scene, src, count, cursor, refill, postpone, tc);
+    flushTraceCounters<STATS>(tc, statCounters, 6);
 }
 
 int reserveWave(Context* ctx, uint32_t paths)
@@ -478,6 +657,84 @@ WaveDev waveDev(Context* ctx, uint32_t paths)
 uint32_t persistentGrid(const Context* ctx, int blocksPerSm)
 {
     return (uint32_t)(ctx->smCount * blocksPerSm);
+}
+
+// lanes still traversing below which a warp re-arms its idle lanes (tunable for experiments: VKRT_REFILL_LANES)
+uint32_t refillLanes()
+{
+    static const uint32_t value = [] {
+        const char* e = getenv("VKRT_REFILL_LANES");
+        const int v = e ? atoi(e) : 0;
+        return (uint32_t)std::min(std::max(v, 0), 32);
+    }();
+    return value;
+}
+
+// fraction (n/32) of a warp's traversing lanes that must have triangles pending before they are tested (VKRT_POSTPONE)
+uint32_t postponeFraction()
+{
+    static const uint32_t value = [] {
+        const char* e = getenv("VKRT_POSTPONE");
+        const int v = e ? atoi(e) : 0;
+        return (uint32_t)std::min(std::max(v, 0), 32);
+    }();
+    return value;
+}
+
+void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const float4* o, const float4* d, const uint32_t* countPtr,
+                   uint32_t countImm, float4* hitA, uint32_t* hitInst, int statSlot, uint32_t* cursor)
+{
+    unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
+    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const uint32_t rf = refillLanes();
+    cudaStream_t s = ctx->stream;
+#define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor, rf, postponeFraction())
+    if (st)
+    {
+        multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
+    }
+    else
+    {
+        multi ? VKRT_LAUNCH(false, true) : VKRT_LAUNCH(false, false);
+    }
+#undef VKRT_LAUNCH
+}
+
+void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev& w, uint32_t* cursor)
+{
+    unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
+    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const uint32_t rf = refillLanes();
+    cudaStream_t s = ctx->stream;
+#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf, postponeFraction())
+    if (st)
+    {
+        multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
+    }
+    else
+    {
+        multi ? VKRT_LAUNCH(false, true) : VKRT_LAUNCH(false, false);
+    }
+#undef VKRT_LAUNCH
+}
+
+void launchAnyList(Context* ctx, const SceneDev& scene, uint32_t grid, const float4* o, const float4* d, uint32_t n, VkrtHit* out,
+                   uint32_t* cursor)
+{
+    unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
+    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const uint32_t rf = refillLanes();
+    cudaStream_t s = ctx->stream;
+#define VKRT_LAUNCH(S, M) k_trace_any_list<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, n, out, stat, cursor, rf, postponeFraction())
+    if (st)
+    {
+        multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
+    }
+    else
+    {
+        multi ? VKRT_LAUNCH(false, true) : VKRT_LAUNCH(false, false);
+    }
+#undef VKRT_LAUNCH
 }
 } // namespace
 
@@ -578,14 +835,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
             mark(); // 1
         }
         // depth 0: primary rays
-        if (st)
-        {
-            k_trace_closest<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, stat, -1);
-        }
-        else
-        {
-            k_trace_closest<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, stat, -1);
-        }
+        launchClosest(ctx, scene, gridTrace, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, -1, w.counters + 8);
         if (timed)
         {
             mark(); // 2
@@ -595,14 +845,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 3
         }
-        if (st)
-        {
-            k_trace_any<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
-        }
-        else
-        {
-            k_trace_any<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
-        }
+        launchAny(ctx, scene, gridTrace, w, w.counters + 9);
         if (timed)
         {
             mark(); // 4
@@ -614,14 +857,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         }
         // depth 1: the compacted reflection queue
         k_reset_counters<<<1, 4, 0, s>>>(w.counters); // only the 4 shadow queues; [4] holds the reflection count
-        if (st)
-        {
-            k_trace_closest<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.reflO, w.reflD, w.counters + 4, 0, w.hitA, w.hitInst, stat, 2);
-        }
-        else
-        {
-            k_trace_closest<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w.reflO, w.reflD, w.counters + 4, 0, w.hitA, w.hitInst, stat, 2);
-        }
+        launchClosest(ctx, scene, gridTrace, w.reflO, w.reflD, w.counters + 4, 0, w.hitA, w.hitInst, 2, w.counters + 10);
         if (timed)
         {
             mark(); // 6
@@ -631,14 +867,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 7
         }
-        if (st)
-        {
-            k_trace_any<true><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
-        }
-        else
-        {
-            k_trace_any<false><<<gridTrace, kTraceThreads, 0, s>>>(scene, w, stat);
-        }
+        launchAny(ctx, scene, gridTrace, w, w.counters + 11);
         if (timed)
         {
             mark(); // 8
@@ -700,30 +929,17 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     scene.one = 0x3F800000u;
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const uint32_t grid = persistentGrid(ctx, 8);
+    k_reset_counters<<<1, 32, 0, s>>>(w.counters);
     if (anyHit)
     {
-        if (ctx->countTraversal)
-        {
-            k_trace_any_list<true><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, n, out.as<VkrtHit>(), stat);
-        }
-        else
-        {
-            k_trace_any_list<false><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, n, out.as<VkrtHit>(), stat);
-        }
-        ctx->launches += 1;
+        launchAnyList(ctx, scene, grid, w.rayO, w.rayD, n, out.as<VkrtHit>(), w.counters + 8);
+        ctx->launches += 2;
     }
     else
     {
-        if (ctx->countTraversal)
-        {
-            k_trace_closest<true><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, n, w.hitA, w.hitInst, stat, -1);
-        }
-        else
-        {
-            k_trace_closest<false><<<grid, kTraceThreads, 0, s>>>(scene, w.rayO, w.rayD, nullptr, n, w.hitA, w.hitInst, stat, -1);
-        }
+        launchClosest(ctx, scene, grid, w.rayO, w.rayD, nullptr, n, w.hitA, w.hitInst, -1, w.counters + 8);
         k_hits_export<<<grid, 128, 0, s>>>(scene, w.hitA, w.hitInst, n, out.as<VkrtHit>());
-        ctx->launches += 2;
+        ctx->launches += 3;
     }
     cudaError_t e = cudaMemcpyAsync(hits, out.ptr, (size_t)n * sizeof(VkrtHit), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess)

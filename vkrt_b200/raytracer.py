@@ -47,9 +47,10 @@ class Raytracer:
 
     def __init__(self, model: Dict, width: int, height: int, device: int = 0, instances: Optional[np.ndarray] = None,
                  build_flags: int = 0, rank: int = 0, world_size: int = 1, unique_id: Optional[bytes] = None,
-                 emulate_ranks: bool = False):
+                 emulate_ranks: bool = False, flat: Optional[Dict] = None):
+        """`flat` (optional) is an already flattened scene whose vertices/indices may be CUDA tensors (config 5)."""
         self.width, self.height = width, height
-        self.flat = flatten_model(model)
+        self.flat = flat if flat is not None else flatten_model(model)
         self.instances = np.asarray(instances if instances is not None else REFERENCE_INSTANCE, dtype=np.float32).reshape(-1, 12)
         self.ctx = B.Context(device)
         if world_size > 1:
@@ -76,6 +77,12 @@ class Raytracer:
         if gather and self.world_size > 1 and self.ctx is not None:
             self.frame.gather(0)
         self.frame_index += 1
+
+    def rebuild(self, vertices, flags: int = 0):
+        """Per-frame full rebuild over moved vertices (BASELINE.json config 5): same storage, new BVH, new TLAS bounds."""
+        self.blas.rebuild(vertices, flags)
+        self.tlas.close()
+        self.tlas = B.Tlas(self.ctx, [self.blas], self.instances)
 
     def readback(self, aov: int = B.AOV_BGRA8, out: Optional[np.ndarray] = None) -> np.ndarray:
         return self.frame.read(aov, out)
