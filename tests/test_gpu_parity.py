@@ -63,18 +63,75 @@ def test_radix_sort_matches_numpy():
     ctx.close()
 
 
-def test_builder_invariants():
+@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD])  # PLOC / LBVH hierarchy
+def test_builder_invariants(flags):
     ctx = B.Context(0)
-    for n in (0, 1, 2, 3, 4, 5, 9, 33, 5000):
+    for n in (0, 1, 2, 3, 4, 5, 9, 33, 1023, 1025, 5000):
         flat = flatten_model(scenes.random_soup(max(n, 1), seed=n + 1, geometries=1 if n < 100 else 4))
         if n == 0:
             flat["ranges"][0, 0] = 0
             flat["indices"] = np.zeros(3, dtype=np.uint32)
-        blas = B.Blas(ctx, flat["vertices"], flat["indices"], flat["ranges"])
+        blas = B.Blas(ctx, flat["vertices"], flat["indices"], flat["ranges"], flags=flags)
         nodes, tris = blas.read()
         check_bvh8(nodes, tris, n)
         blas.close()
     ctx.close()
+
+
+@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD])
+def test_builder_duplicates(flags):
+    """Thousands of identical triangles (equal Morton codes, equal merge distances): the builder must still terminate
+    with every triangle referenced once; PLOC pairs equal-distance clusters as buddies, LBVH splits ties by index."""
+    n = 6000
+    tri = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], dtype=np.float32)
+    pos = np.tile(tri, (n, 1))
+    pos[3 * (n // 2):] += np.float32(5.0)  # two piles
+    v = scenes.make_vertex_array(pos)
+    model = {"submeshes": [{"vertices": v, "indices": np.arange(3 * n, dtype=np.uint32), "material": 0}], "materials": [(0, 0, 0)],
+             "images": [scenes.solid_image((255, 255, 255, 255), 4)]}
+    flat = flatten_model(model)
+    ctx = B.Context(0)
+    blas = B.Blas(ctx, flat["vertices"], flat["indices"], flat["ranges"], flags=flags)
+    nodes, tris = blas.read()
+    check_bvh8(nodes, tris, n)
+    tlas = B.Tlas(ctx, [blas], scenes.identity_instance(1.0))
+    rays = np.zeros(2, dtype=B.RAY_DTYPE)
+    rays["origin"] = [(0.25, 0.25, 3), (5.25, 5.25, 8)]
+    rays["direction"] = (0, 0, -1)
+    rays["tmin"], rays["tmax"] = 0.001, 1000
+    h = tlas.trace_rays(rays)
+    assert list(h["primitive"]) == [0, n // 2]  # equal t: the lowest id wins
+    tlas.close(), blas.close(), ctx.close()
+
+
+def test_device_input_build_and_rebuild():
+    """Config 5 plumbing at a small size: CUDA-tensor input (VKRT_BUILD_INPUT_ON_DEVICE), rebuild in place, hits equal
+    to the oracle's on the same vertices."""
+    import torch
+
+    from vkrt_b200.scenes_device import SoupDevice
+
+    soup = SoupDevice(50000, 0)
+    inst = scenes.identity_instance(1.0)
+    ctx = B.Context(0)
+    blas = B.Blas(ctx, soup.vertices, soup.indices, soup.ranges(), flags=B.BUILD_PREFER_FAST_BUILD)
+    rays = H.random_rays(50000, 11, (-20, 0, -12), (20, 15, 12))
+    for frame, flags in ((0, None), (3, B.BUILD_DEFAULT), (5, B.BUILD_PREFER_FAST_BUILD)):
+        verts = soup.set_frame(frame)
+        if flags is not None:
+            blas.rebuild(verts, flags)
+        tlas = B.Tlas(ctx, [blas], inst)
+        nodes, tris = blas.read()
+        check_bvh8(nodes, tris, soup.n)
+        host = {"vertices": verts.cpu().numpy(), "indices": soup.indices.cpu().numpy().astype(np.uint32), "ranges": soup.ranges(),
+                "rows": np.zeros((1, 4), dtype=np.int32), "images": soup.model_stub()["images"]}
+        o = H.OracleScene(host, inst)
+        ho, _ = o.trace_rays(rays)
+        assert np.array_equal(ho, tlas.trace_rays(rays))
+        tlas.close()
+    blas.close(), ctx.close()
+    del soup
+    torch.cuda.empty_cache()
 
 
 def test_builder_invariants_sponza(sponza_rt, sponza_flat):

@@ -170,8 +170,9 @@ int vkrt_blas_sizes(VkrtContext* c, const VkrtGeometryRange* ranges, uint32_t ge
     }
     const uint64_t nodeCap = std::max<uint64_t>(1, n / 2 + 8);
     out->accelerationStructureSize = nodeCap * sizeof(Node8) + std::max<uint64_t>(1, n) * sizeof(PackedTri);
-    // triLo/triHi 32, keys/vals x2 16, children 8, node boxes 32, flags 4, taskRef 2, primSource 4, sort histograms ~0.25
-    out->buildScratchSize = std::max<uint64_t>(1, n) * 100 + 4096;
+    // triLo/triHi 32, keys/vals x2 16, children 8, node boxes 32, flags 4, taskRef 2, primSource 4, onesweep look-back
+    // words 1 (4 passes x 256 words per 4096-key tile), PLOC cluster boxes 64 (two ping-pong float4 pairs)
+    out->buildScratchSize = std::max<uint64_t>(1, n) * 168 + 16384;
     out->geometryCopySize = vertexBytes + indexCount * 4;
     return VKRT_SUCCESS;
 }
@@ -297,6 +298,7 @@ int vkrt_blas_rebuild(VkrtContext* c, VkrtBlas* b, const void* vertices, size_t 
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_rebuild: vertex data size differs from the original build");
     }
     cudaSetDevice(ctx->device);
+    blas->flags = flags; // PLOC (default) or LBVH (VKRT_BUILD_PREFER_FAST_BUILD) may change between rebuilds
     int r = uploadGeometry(ctx, blas, vertices, vertexBytes, nullptr, 0, (flags & VKRT_BUILD_INPUT_ON_DEVICE) != 0);
     if (r != VKRT_SUCCESS)
     {
