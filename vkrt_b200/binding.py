@@ -7,7 +7,8 @@ from typing import Optional, Sequence
 
 import numpy as np
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libvkrt_b200.so")
+# VKRT_B200_LIB: developer override to time experimental builds of the same library; there is still no CPU fallback
+LIB_PATH = os.environ.get("VKRT_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libvkrt_b200.so")
 
 AOV_BGRA8, AOV_RGB32F, AOV_TRIANGLE_ID, AOV_SHADOW_MASK = 0, 1, 2, 3
 BUILD_DEFAULT, BUILD_PREFER_FAST_BUILD, BUILD_INPUT_ON_DEVICE = 0, 1, 2

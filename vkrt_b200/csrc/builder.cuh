@@ -198,7 +198,10 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
 // ------------------------------------------------------------------------------------------------
 // Collapse to 8-wide nodes
 // ------------------------------------------------------------------------------------------------
-constexpr uint32_t kMaxLeafTris = 3; // a child slot references at most 3 triangles (unary count in 3 bits)
+#ifndef VKRT_MAX_LEAF_TRIS
+#define VKRT_MAX_LEAF_TRIS 3
+#endif
+constexpr uint32_t kMaxLeafTris = VKRT_MAX_LEAF_TRIS; // a child slot references at most 3 triangles (unary count in 3 bits)
 
 struct CollapseArgs
 {

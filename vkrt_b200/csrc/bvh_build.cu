@@ -814,7 +814,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     VKRT_CUDA_TRY(ctx, cudaEventRecord(ev0, s));
 
     // node capacity: every wide node with internal children covers > 3 triangles per child
-    const uint32_t nodeCapacity = std::max(1u, n / 2u + 8u);
+    const uint32_t nodeCapacity = kMaxLeafTris >= 3 ? std::max(1u, n / 2u + 8u) : n + 8u;
     VKRT_CUDA_TRY(ctx, blas->nodes.reserve((size_t)nodeCapacity * sizeof(Node8)));
     VKRT_CUDA_TRY(ctx, blas->tris.reserve(std::max<size_t>(1, n) * sizeof(PackedTri)));
 

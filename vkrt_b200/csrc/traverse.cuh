@@ -300,20 +300,11 @@ constexpr int kStepHit = 4;   // flag: at least one triangle was accepted during
 
 // One traversal step: pops the nearest pending internal child (if any), tests its 8 child boxes, then tests the
 // triangles the node references.  Returns 0 to continue, or kStepDone / kStepFound, optionally ORed with kStepHit.
-//
-// Triangle postponing (Ylitie et al. 2017, section 4.3; device only): when fewer than postpone/32 of the lanes that
-// entered the step have triangles to test, the triangle group goes onto the stack (entries with no bit above 23 set)
-// and the lane carries on with its nodes, so that triangle tests run with fuller warps.
 template<bool ANY>
 VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const PackedTri* tris, uint32_t instance, BestHit& best,
-                          TraceCounters* counters, uint32_t one, uint32_t postpone = 0u)
+                          TraceCounters* counters, uint32_t one)
 {
     int result = 0;
-#if defined(__CUDA_ARCH__)
-    const uint32_t postponeBelow = postpone ? ((uint32_t)__popc(__activemask()) * postpone) >> 5 : 0u;
-#else
-    (void)postpone;
-#endif
     if (c.ngroup.y > 0x00FFFFFFu)
     {
         const uint32_t octinv = 7u - c.octant;
@@ -345,28 +336,11 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
     }
     else
     {
-        c.tgroup = c.ngroup; // a postponed triangle group popped from the stack, or nothing
-        c.ngroup = make_uint2(0u, 0u);
+        c.tgroup = make_uint2(0u, 0u);
     }
 
     while (c.tgroup.y != 0u)
     {
-#if defined(__CUDA_ARCH__)
-        if ((uint32_t)__popc(__activemask()) < postponeBelow && c.sp < kStackSize && (c.ngroup.y > 0x00FFFFFFu || c.sp > 0))
-        {
-            if (c.ngroup.y > 0x00FFFFFFu)
-            {
-                stack[c.sp++] = c.tgroup;
-            }
-            else // nothing but the stack left: trade places with its top entry
-            {
-                c.ngroup = stack[c.sp - 1];
-                stack[c.sp - 1] = c.tgroup;
-            }
-            c.tgroup = make_uint2(0u, 0u);
-            return result;
-        }
-#endif
         const uint32_t bit = highestBit(c.tgroup.y);
         c.tgroup.y &= ~(1u << bit);
         const uint32_t slotIndex = c.tgroup.x + bit;

@@ -111,8 +111,9 @@ k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, ui
 // ------------------------------------------------------------------------------------------------------------
 // Persistent-thread traversal with dynamic ray fetch (Aila & Laine 2009; Ylitie et al. 2017, section 4.3).
 // A warp keeps a private pool of ray indices that it refills from the launch-wide cursor in chunks (one global
-// atomic per chunk); lanes whose ray has finished take the next pool entries, and when fewer than `refill` lanes
-// of the warp are still traversing, the busy lanes leave the traversal loop so that the idle ones can be re-armed.
+// atomic per chunk) and re-arms all 32 lanes together once every lane's ray has finished.  Re-arming idle lanes
+// while others are still traversing (per-lane replacement below 4..28 busy lanes) and triangle postponing were both
+// measured slower on B200 (config 2: 2014 Mrays/s without, 1690-1900 with), so neither is compiled in.
 // Sources map a queue position to a ray and receive the result.
 // ------------------------------------------------------------------------------------------------------------
 struct ClosestSource
@@ -225,8 +226,7 @@ __device__ __forceinline__ bool enterInstance(const SceneDev& scene, F3 o, F3 d,
 }
 
 template<bool ANY, bool MULTI, bool STATS, typename Source>
-__device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, uint32_t refill,
-                                                uint32_t postpone, TraceCounters& tc)
+__device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, TraceCounters& tc)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
@@ -308,8 +308,7 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
         {
             for (;;)
             {
-                const int r = traversalStep<ANY>(c, stack, bind.nodes, bind.tris, bind.instance, best, STATS ? &tc : nullptr, scene.one,
-                                                   postpone);
+                const int r = traversalStep<ANY>(c, stack, bind.nodes, bind.tris, bind.instance, best, STATS ? &tc : nullptr, scene.one);
                 if (r & kStepFound)
                 {
                     src.commit(handle, best, true);
@@ -330,10 +329,6 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                     }
                     src.commit(handle, best, best.tri != kInvalid);
                     active = false;
-                    break;
-                }
-                if (!exhausted && (uint32_t)__popc(__activemask()) < refill)
-                {
                     break;
                 }
             }
@@ -359,13 +354,13 @@ template<bool STATS, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads)
 k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
                 uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
-                int statSlot, uint32_t* cursor, uint32_t refill, uint32_t postpone)
+                int statSlot, uint32_t* cursor)
 {
     const uint32_t count = countPtr ? *countPtr : countImm;
     TraceCounters tc;
     ClosestSource src;
     src.rayO = rayO, src.rayD = rayD, src.hitA = hitA, src.hitInst = hitInst;
-    tracePersistent<false, MULTI, STATS>(scene, src, count, cursor, refill, postpone, tc);
+    tracePersistent<false, MULTI, STATS>(scene, src, count, cursor, tc);
     flushTraceCounters<STATS>(tc, statCounters, 3);
     if (statSlot >= 0 && blockIdx.x == 0 && threadIdx.x == 0 && countPtr)
     {
@@ -462,7 +457,7 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 // shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
 template<bool STATS, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads)
-k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor, uint32_t refill, uint32_t postpone)
+k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor)
 {
     const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
     const uint32_t total = c0 + c1 + c2 + c3;
@@ -470,7 +465,7 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_
     ShadowSource src;
     src.shadowO = w.shadowO, src.shadowD = w.shadowD, src.shadowBits = w.shadowBits;
     src.c0 = c0, src.c01 = c0 + c1, src.c012 = c0 + c1 + c2, src.capacity = w.capacity;
-    tracePersistent<true, MULTI, STATS>(scene, src, total, cursor, refill, postpone, tc);
+    tracePersistent<true, MULTI, STATS>(scene, src, total, cursor, tc);
     flushTraceCounters<STATS>(tc, statCounters, 6);
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
@@ -604,12 +599,12 @@ __global__ void k_hits_export(SceneDev scene, const float4* __restrict__ hitA, c
 template<bool STATS, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads)
 k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, uint32_t count, VkrtHit* __restrict__ out,
-                 unsigned long long* statCounters, uint32_t* cursor, uint32_t refill, uint32_t postpone)
+                 unsigned long long* statCounters, uint32_t* cursor)
 {
     TraceCounters tc;
     ListAnySource src;
     src.rayO = rayO, src.rayD = rayD, src.out = out;
-    tracePersistent<true, MULTI, STATS>(scene, src, count, cursor, refill, postpone, tc);
+    tracePersistent<true, MULTI, STATS>(scene, src, count, cursor, tc);
     flushTraceCounters<STATS>(tc, statCounters, 6);
 }
 
@@ -659,36 +654,13 @@ uint32_t persistentGrid(const Context* ctx, int blocksPerSm)
     return (uint32_t)(ctx->smCount * blocksPerSm);
 }
 
-// lanes still traversing below which a warp re-arms its idle lanes (tunable for experiments: VKRT_REFILL_LANES)
-uint32_t refillLanes()
-{
-    static const uint32_t value = [] {
-        const char* e = getenv("VKRT_REFILL_LANES");
-        const int v = e ? atoi(e) : 0;
-        return (uint32_t)std::min(std::max(v, 0), 32);
-    }();
-    return value;
-}
-
-// fraction (n/32) of a warp's traversing lanes that must have triangles pending before they are tested (VKRT_POSTPONE)
-uint32_t postponeFraction()
-{
-    static const uint32_t value = [] {
-        const char* e = getenv("VKRT_POSTPONE");
-        const int v = e ? atoi(e) : 0;
-        return (uint32_t)std::min(std::max(v, 0), 32);
-    }();
-    return value;
-}
-
 void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const float4* o, const float4* d, const uint32_t* countPtr,
                    uint32_t countImm, float4* hitA, uint32_t* hitInst, int statSlot, uint32_t* cursor)
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
-    const uint32_t rf = refillLanes();
     cudaStream_t s = ctx->stream;
-#define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor, rf, postponeFraction())
+#define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor)
     if (st)
     {
         multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
@@ -704,9 +676,8 @@ void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
-    const uint32_t rf = refillLanes();
     cudaStream_t s = ctx->stream;
-#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf, postponeFraction())
+#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor)
     if (st)
     {
         multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
@@ -723,9 +694,8 @@ void launchAnyList(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
-    const uint32_t rf = refillLanes();
     cudaStream_t s = ctx->stream;
-#define VKRT_LAUNCH(S, M) k_trace_any_list<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, n, out, stat, cursor, rf, postponeFraction())
+#define VKRT_LAUNCH(S, M) k_trace_any_list<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, n, out, stat, cursor)
     if (st)
     {
         multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
