@@ -916,7 +916,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
             int batch = 6;
             for (uint32_t m = n; m > 1; m >>= 1)
             {
-                batch += 2; // ~2 log2(n): a round usually leaves 55-65 % of the clusters
+                batch += 4; // ~4 log2(n): measured, a round leaves ~84 % of the clusters (262 k triangles: 74 rounds)
             }
             for (;;)
             {
@@ -937,7 +937,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
                 {
                     return ctx->fail(VKRT_ERROR_CUDA, "PLOC: did not converge");
                 }
-                batch = 8;
+                batch = 16;
             }
         }
 

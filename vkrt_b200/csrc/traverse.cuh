@@ -20,39 +20,63 @@ struct TraceCounters
     uint32_t nodes = 0, tris = 0, overflow = 0;
 };
 
-struct RayPre // watertight per-ray constants
+// Watertight per-ray constants.  The shear of Woop et al. 2013 is  A' = (A[kx] - Sx*A[kz], A[ky] - Sy*A[kz], Sz*A[kz]).
+// Instead of selecting vertex components by the runtime axis indices (two SEL per component on the saturated alu
+// pipe), each output is evaluated as a dot product with a per-ray vector whose entries are 1 at kx (ky), -Sx (-Sy) at
+// kz and 0 elsewhere: the products by 1 and 0 are exact, adding +-0 is exact, and -(S*a) == (-S)*a, so every result
+// is bit-identical to the selected form (finite vertices) while the work moves to the fma pipe.
+struct RayPre
 {
-    int kx, ky, kz;
-    float Sx, Sy, Sz;
+    F3 mx, my, mz;
 };
+
+VKRT_HD void setComp3(F3& v, int k, float value)
+{
+    if (k == 0)
+    {
+        v.x = value;
+    }
+    else if (k == 1)
+    {
+        v.y = value;
+    }
+    else
+    {
+        v.z = value;
+    }
+}
 
 VKRT_HD RayPre makeRayPre(F3 d)
 {
-    RayPre r;
     const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-    r.kz = 0;
+    int kz = 0;
     float best = ax;
     if (ay > best)
     {
-        r.kz = 1;
+        kz = 1;
         best = ay;
     }
     if (az > best)
     {
-        r.kz = 2;
+        kz = 2;
     }
-    r.kx = r.kz + 1 == 3 ? 0 : r.kz + 1;
-    r.ky = r.kx + 1 == 3 ? 0 : r.kx + 1;
-    if (comp3(d, r.kz) < 0.0f)
+    int kx = kz + 1 == 3 ? 0 : kz + 1;
+    int ky = kx + 1 == 3 ? 0 : kx + 1;
+    if (comp3(d, kz) < 0.0f)
     {
-        const int t = r.kx;
-        r.kx = r.ky;
-        r.ky = t;
+        const int t = kx;
+        kx = ky;
+        ky = t;
     }
-    const float dz = comp3(d, r.kz);
-    r.Sx = comp3(d, r.kx) / dz;
-    r.Sy = comp3(d, r.ky) / dz;
-    r.Sz = 1.0f / dz;
+    const float dz = comp3(d, kz);
+    const float Sx = comp3(d, kx) / dz, Sy = comp3(d, ky) / dz, Sz = 1.0f / dz;
+    RayPre r;
+    r.mx = r.my = r.mz = f3(0.0f, 0.0f, 0.0f);
+    setComp3(r.mx, kx, 1.0f);
+    setComp3(r.mx, kz, -Sx);
+    setComp3(r.my, ky, 1.0f);
+    setComp3(r.my, kz, -Sy);
+    setComp3(r.mz, kz, Sz);
     return r;
 }
 
@@ -62,10 +86,9 @@ VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, floa
                                float& b1, float& b2)
 {
     const F3 A = v0 - o, B = v1 - o, C = v2 - o;
-    const float Akz = comp3(A, rp.kz), Bkz = comp3(B, rp.kz), Ckz = comp3(C, rp.kz);
-    const float Ax = comp3(A, rp.kx) - rp.Sx * Akz, Ay = comp3(A, rp.ky) - rp.Sy * Akz;
-    const float Bx = comp3(B, rp.kx) - rp.Sx * Bkz, By = comp3(B, rp.ky) - rp.Sy * Bkz;
-    const float Cx = comp3(C, rp.kx) - rp.Sx * Ckz, Cy = comp3(C, rp.ky) - rp.Sy * Ckz;
+    const float Ax = dot3(A, rp.mx), Ay = dot3(A, rp.my);
+    const float Bx = dot3(B, rp.mx), By = dot3(B, rp.my);
+    const float Cx = dot3(C, rp.mx), Cy = dot3(C, rp.my);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -84,7 +107,7 @@ VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, floa
     {
         return false;
     }
-    const float Az = rp.Sz * Akz, Bz = rp.Sz * Bkz, Cz = rp.Sz * Ckz;
+    const float Az = dot3(A, rp.mz), Bz = dot3(B, rp.mz), Cz = dot3(C, rp.mz);
     const float T = (U * Az + V * Bz) + W * Cz;
     const float rcp = 1.0f / det;
     const float t = T * rcp;
