@@ -32,6 +32,16 @@ WORKLOADS = {
 }
 
 
+def read_traffic(workload):
+    """Measured DRAM bytes per launch of the dominant kernel for this workload (ncu capture summarised under profiles/)."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        e = json.load(open(p)).get(workload)
+        return (float(e["bytes_per_launch_avg"]), e["capture"]) if e else (None, None)
+    except Exception:
+        return None, None
+
+
 def read_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -311,7 +321,9 @@ def main():
         any_ms = max(stage["trace_any"], 1e-9)
         achieved = any_rays_per_sample * b_any / (any_ms * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": "k_trace_any (2 launches per sample)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "frac_of_8tbs_nominal": achieved / 8000.0, "peak_source": peak_src, "traffic": None,
+                    "frac": achieved / peak, "frac_of_8tbs_nominal": achieved / 8000.0, "peak_source": peak_src,
+                    "traffic": read_traffic(args.workload)[0], "traffic_source": read_traffic(args.workload)[1],
+                    "algorithmic_bytes_per_launch": any_rays_per_sample * b_any / 2,
                     "bytes_per_ray_any": b_any, "bytes_per_ray_closest": b_cl,
                     "n_node_any": n_node_any, "n_tri_any": n_tri_any, "n_node_closest": n_node_cl, "n_tri_closest": n_tri_cl,
                     "launch_ms_avg": any_ms / 2, "stage_ms_sample0": stage}

@@ -19,6 +19,9 @@ namespace vkrt
 namespace
 {
 constexpr int kTraceThreads = 128;
+#ifndef VKRT_TRACE_MIN_BLOCKS
+#define VKRT_TRACE_MIN_BLOCKS 7
+#endif
 constexpr int kShadeThreads = 128;
 
 struct SceneDev
@@ -351,7 +354,7 @@ __device__ __forceinline__ void flushTraceCounters(const TraceCounters& tc, unsi
 }
 
 template<bool STATS, bool MULTI>
-__global__ void __launch_bounds__(kTraceThreads)
+__global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
 k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
                 uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
                 int statSlot, uint32_t* cursor)
@@ -456,7 +459,7 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 
 // shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
 template<bool STATS, bool MULTI>
-__global__ void __launch_bounds__(kTraceThreads)
+__global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
 k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor)
 {
     const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
