@@ -240,7 +240,9 @@ typedef struct VkrtStats
     uint64_t nodesVisited, trianglesTested; /* closest-hit + any-hit; only counted when enabled with vkrt_stats_enable */
     uint64_t nodesVisitedAny, trianglesTestedAny; /* the any-hit (shadow ray) share of the two totals above */
     uint64_t kernelLaunches;                /* kernels launched by this library */
-    float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* last vkrt_trace, if timing enabled */
+    float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* first wave of the last vkrt_trace, if timing enabled */
+    uint32_t samplesPerWave; /* samples per pixel that went through the pipeline together in the last vkrt_trace */
+    uint32_t reserved;
 } VkrtStats;
 VKRT_API int vkrt_stats_enable(VkrtContext* ctx, int countTraversal, int timeStages);
 VKRT_API int vkrt_stats_reset(VkrtContext* ctx);

@@ -96,6 +96,8 @@ class Stats(C.Structure):
         ("msTraceAny", C.c_float),
         ("msResolve", C.c_float),
         ("msTotal", C.c_float),
+        ("samplesPerWave", C.c_uint32),
+        ("reserved", C.c_uint32),
     ]
 
 

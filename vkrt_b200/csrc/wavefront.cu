@@ -87,27 +87,30 @@ __global__ void k_reset_counters(uint32_t* counters)
 
 // shader.rgen:32-47 — one primary ray per owned pixel path
 __global__ void __launch_bounds__(kShadeThreads)
-k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, uint32_t sample, uint32_t spp, float4* __restrict__ rayO,
-         float4* __restrict__ rayD, float4* __restrict__ pathAccum)
+k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, uint32_t sampleBase, uint32_t samples, uint32_t spp,
+         float4* __restrict__ rayO, float4* __restrict__ rayD, float4* __restrict__ pathAccum)
 {
-    float jx, jy;
-    sampleOffset(sample, spp, jx, jy);
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < paths; p += gridDim.x * blockDim.x)
+    // a wave holds `samples` consecutive samples of every owned pixel path, sample-major: index = s * paths + path
+    const uint32_t total = paths * samples;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
     {
+        const uint32_t p = i % paths;
+        float jx, jy;
+        sampleOffset(sampleBase + i / paths, spp, jx, jy);
         uint32_t x, y, tl, pit;
         if (pathToPixel(map, p, x, y, tl, pit))
         {
             F3 o, d;
             primaryRay(u, map.width, map.height, x, y, jx, jy, o, d);
-            rayO[p] = make_float4(o.x, o.y, o.z, kRayTMin);
-            rayD[p] = make_float4(d.x, d.y, d.z, kRayTMax);
+            rayO[i] = make_float4(o.x, o.y, o.z, kRayTMin);
+            rayD[i] = make_float4(d.x, d.y, d.z, kRayTMax);
         }
         else
         {
-            rayO[p] = make_float4(0.f, 0.f, 0.f, kRayTMin);
-            rayD[p] = make_float4(0.f, 0.f, 0.f, -1.0f); // inactive path
+            rayO[i] = make_float4(0.f, 0.f, 0.f, kRayTMin);
+            rayD[i] = make_float4(0.f, 0.f, 0.f, -1.0f); // inactive path
         }
-        pathAccum[p] = make_float4(0.f, 0.f, 0.f, 1.0f); // finalHitValue = 0, attenuation = 1 (rgen:42-45)
+        pathAccum[i] = make_float4(0.f, 0.f, 0.f, 1.0f); // finalHitValue = 0, attenuation = 1 (rgen:42-45)
     }
 }
 
@@ -374,7 +377,7 @@ k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* _
 // shader.rchit:88-129 for every hit; shader.rmiss:17 for every miss.  Emits shadow rays.
 __global__ void __launch_bounds__(kShadeThreads)
 k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
-                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, int writeAov)
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovPaths)
 {
     const uint32_t count = countPtr ? *countPtr : countImm;
     const uint32_t rounded = (count + 31u) & ~31u; // whole warps stay in the loop for the ballots
@@ -404,7 +407,7 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 acc.x += 0.8f, acc.y += 0.8f, acc.z += 1.0f; // rmiss:17, rgen:63
                 w.pathAccum[p] = acc;
                 w.surfGeom[q] = kInvalid;
-                if (writeAov && depth == 0)
+                if (depth == 0 && p < aovPaths) // sample 0 of the frame only
                 {
                     uint32_t x, y, tl, pit;
                     pathToPixel(f.map, p, x, y, tl, pit);
@@ -432,7 +435,7 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 w.surfB[q] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.v);
                 w.surfGeom[q] = geometry;
                 w.shadowBits[q] = castMask << 4;
-                if (writeAov && depth == 0)
+                if (depth == 0 && p < aovPaths) // sample 0 of the frame only
                 {
                     uint32_t x, y, tl, pit;
                     pathToPixel(f.map, p, x, y, tl, pit);
@@ -479,7 +482,7 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_
 // shader.rchit:144-171 and the bounce bookkeeping of shader.rgen:63-73
 __global__ void __launch_bounds__(kShadeThreads)
 k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
-                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, int writeAov)
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovPaths)
 {
     const uint32_t count = countPtr ? *countPtr : countImm;
     const uint32_t rounded = (count + 31u) & ~31u;
@@ -511,7 +514,7 @@ k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
             w.pathAccum[p] = acc;
             reflect = r.reflect && depth == 0; // rgen:65-69: maxDepth 2
             origin = sp.worldPos, dir = r.rayDir;
-            if (writeAov && depth == 0)
+            if (depth == 0 && p < aovPaths) // sample 0 of the frame only
             {
                 uint32_t x, y, tl, pit;
                 pathToPixel(f.map, p, x, y, tl, pit);
@@ -530,22 +533,35 @@ k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 
 // shader.rgen:76 imageStore + sample averaging; writes the linear image and/or the tile-major send buffer
 __global__ void __launch_bounds__(kShadeThreads)
-k_resolve_sample(WaveDev w, FrameDev f, uint32_t paths, uint32_t sample, uint32_t spp)
+k_resolve_sample(WaveDev w, FrameDev f, uint32_t paths, uint32_t sampleBase, uint32_t samples, uint32_t spp)
 {
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < paths; p += gridDim.x * blockDim.x)
     {
         uint32_t x, y, tl, pit;
         const bool valid = pathToPixel(f.map, p, x, y, tl, pit);
-        const float4 acc = w.pathAccum[p];
-        F3 sum = f3(acc.x, acc.y, acc.z);
+        // samples are summed in sample order (the running sum crosses waves through sampleSum), then divided by spp
+        F3 sum = f3(0.f, 0.f, 0.f);
+        for (uint32_t j = 0; j < samples; ++j)
+        {
+            const float4 acc = w.pathAccum[(size_t)j * paths + p];
+            const F3 a = f3(acc.x, acc.y, acc.z);
+            if (j == 0 && sampleBase == 0)
+            {
+                sum = a;
+            }
+            else if (j == 0)
+            {
+                const float4 sprev = w.sampleSum[p];
+                sum = f3(sprev.x, sprev.y, sprev.z) + a;
+            }
+            else
+            {
+                sum = sum + a;
+            }
+        }
         if (spp > 1)
         {
-            if (sample > 0)
-            {
-                const float4 s = w.sampleSum[p];
-                sum = f3(s.x, s.y, s.z) + sum;
-            }
-            if (sample + 1 < spp)
+            if (sampleBase + samples < spp)
             {
                 w.sampleSum[p] = make_float4(sum.x, sum.y, sum.z, 0.f);
                 continue;
@@ -724,7 +740,26 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_trace: materials and textures must be set first");
     }
     const uint32_t paths = frame->paths;
-    int r = reserveWave(ctx, paths);
+    // Samples per wave: all samples of a pixel that fit the queue budget go through the pipeline together, so a frame
+    // costs 12 launches per WAVE instead of per sample (at 8 GPUs the per-launch ramp and tail were 10 % of a sample).
+    uint32_t waveSamples = 1;
+    {
+        size_t freeBytes = 0, totalBytes = 0;
+        cudaMemGetInfo(&freeBytes, &totalBytes);
+        const size_t held = ctx->wave.rayO.capacity * 18; // the wave buffers already reserved count as available
+        const size_t budget = std::min<size_t>((size_t)24 << 30, (freeBytes + held) / 3);
+        const size_t perSample = (size_t)std::max<uint32_t>(paths, 32) * 288;
+        size_t fit = std::max<size_t>(1, budget / perSample);
+        fit = std::min<size_t>(fit, (size_t)0x0FFFFFFF / std::max<uint32_t>(paths, 1)); // queue indices stay below 2^30
+        const char* e = getenv("VKRT_WAVE_SAMPLES");
+        if (e && atoi(e) > 0)
+        {
+            fit = (size_t)atoi(e);
+        }
+        waveSamples = (uint32_t)std::max<size_t>(1, std::min<size_t>(fit, spp));
+    }
+    ctx->stats.samplesPerWave = waveSamples;
+    int r = reserveWave(ctx, paths * waveSamples);
     if (r != VKRT_SUCCESS)
     {
         return r;
@@ -747,7 +782,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     scene.textures = ctx->textureRecords.as<TextureRecord>();
     scene.one = 0x3F800000u;
 
-    WaveDev w = waveDev(ctx, paths);
+    WaveDev w = waveDev(ctx, paths * waveSamples);
     FrameDev f;
     f.map.width = frame->width, f.map.height = frame->height;
     f.map.tilesX = frame->tilesX, f.map.tilesY = frame->tilesY;
@@ -793,27 +828,29 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     ctx->stats.msRaygen = ctx->stats.msTraceClosest = ctx->stats.msShade = ctx->stats.msTraceAny = ctx->stats.msResolve = 0.f;
     ctx->stats.msTotal = 0.f;
 
-    for (uint32_t sample = 0; sample < spp; ++sample)
+    for (uint32_t sample = 0; sample < spp; sample += waveSamples)
     {
-        const int writeAov = (aov && sample == 0) ? 1 : 0;
+        const uint32_t samples = std::min(waveSamples, spp - sample);
+        const uint32_t wavePaths = paths * samples;
+        const uint32_t aovPaths = (aov && sample == 0) ? paths : 0u; // AOVs describe sample 0
         const bool timed = ctx->timeStages && sample == 0;
         if (timed)
         {
             mark(); // 0
         }
         k_reset_counters<<<1, 32, 0, s>>>(w.counters);
-        k_raygen<<<gridShade, kShadeThreads, 0, s>>>(u, f.map, paths, sample, spp, w.rayO, w.rayD, w.pathAccum);
+        k_raygen<<<gridShade, kShadeThreads, 0, s>>>(u, f.map, paths, sample, samples, spp, w.rayO, w.rayD, w.pathAccum);
         if (timed)
         {
             mark(); // 1
         }
         // depth 0: primary rays
-        launchClosest(ctx, scene, gridTrace, w.rayO, w.rayD, nullptr, paths, w.hitA, w.hitInst, -1, w.counters + 8);
+        launchClosest(ctx, scene, gridTrace, w.rayO, w.rayD, nullptr, wavePaths, w.hitA, w.hitInst, -1, w.counters + 8);
         if (timed)
         {
             mark(); // 2
         }
-        k_shade_surface<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, paths, 0, writeAov);
+        k_shade_surface<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovPaths);
         if (timed)
         {
             mark(); // 3
@@ -823,7 +860,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 4
         }
-        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, paths, 0, writeAov);
+        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovPaths);
         if (timed)
         {
             mark(); // 5
@@ -850,7 +887,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 9
         }
-        k_resolve_sample<<<gridShade, kShadeThreads, 0, s>>>(w, f, paths, sample, spp);
+        k_resolve_sample<<<gridShade, kShadeThreads, 0, s>>>(w, f, paths, sample, samples, spp);
         if (timed)
         {
             mark(); // 10
