@@ -177,6 +177,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--triangles", type=int, default=50_000_000, help="config5 only: triangles in the procedural soup")
     ap.add_argument("--build-flags", type=int, default=0)
+    ap.add_argument("--lane-refill", type=int, default=-1, help="vkrt_trace_set_lane_refill; default 0, config5 20")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -221,6 +222,8 @@ def main():
         rt = Raytracer(model, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id,
                        build_flags=args.build_flags)
     build_ms = []
+    lane_refill = args.lane_refill if args.lane_refill >= 0 else (20 if args.workload == "config5" else 0)
+    rt.ctx.set_lane_refill(lane_refill)
     info = rt.blas.info()
     stream = torch.cuda.ExternalStream(rt.ctx.stream, device=local)
     flags = B.TRACE_NO_AOV
@@ -328,7 +331,7 @@ def main():
                     "algorithmic_bytes_per_launch": any_rays_per_sample * b_any / 2,
                     "bytes_per_ray_any": b_any, "bytes_per_ray_closest": b_cl,
                     "n_node_any": n_node_any, "n_tri_any": n_tri_any, "n_node_closest": n_node_cl, "n_tri_closest": n_tri_cl,
-                    "launch_ms_avg": any_ms / 2, "samples_per_wave": wave_samples, "stage_ms_sample0": stage}
+                    "launch_ms_avg": any_ms / 2, "samples_per_wave": wave_samples, "lane_refill": lane_refill, "stage_ms_sample0": stage}
         line = {
             "metric": "Sponza 4K Mrays/s (prim+shadow+refl)", "value": total_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",

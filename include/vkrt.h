@@ -212,6 +212,12 @@ VKRT_API int vkrt_frame_read(VkrtContext* ctx, VkrtFrame* frame, int aov, void* 
 /* Device pointer of the assembled BGRA8 image (width*height*4), valid until the frame is destroyed. */
 VKRT_API void* vkrt_frame_device_bgra8(VkrtFrame* frame);
 
+/* Scheduling knob of the persistent trace kernels (no counterpart in the reference; results do not depend on it).
+ * lanes == 0 (default): a warp takes 32 new rays once all of its rays have finished - fastest on coherent scenes.
+ * lanes in 1..32: lanes whose ray has finished are re-armed as soon as fewer than `lanes` lanes of the warp are still
+ * traversing - pays on incoherent scenes (the config-5 triangle soup). */
+VKRT_API int vkrt_trace_set_lane_refill(VkrtContext* ctx, uint32_t lanes);
+
 /* Ray-level entry (ray-query style; used by the parity tests and per-ray-type benchmarks).  `rays` are
  * 32-byte records {origin[3], tmin, direction[3], tmax}; `hits` 24-byte records {t, b1, b2, instance, geometry,
  * primitive}; instance == 0xFFFFFFFF on miss.  anyHit != 0 → gl_RayFlagsTerminateOnFirstHitEXT semantics

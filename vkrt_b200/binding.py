@@ -130,6 +130,7 @@ EXPORTS = [
     "vkrt_last_error",
     "vkrt_context_synchronize",
     "vkrt_context_stream",
+    "vkrt_trace_set_lane_refill",
     "vkrt_blas_sizes",
     "vkrt_blas_build",
     "vkrt_blas_rebuild",
@@ -179,6 +180,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_last_error": (C.c_char_p, [vp]),
         "vkrt_context_synchronize": (i32, [vp]),
         "vkrt_context_stream": (vp, [vp]),
+        "vkrt_trace_set_lane_refill": (i32, [vp, u32]),
         "vkrt_blas_sizes": (i32, [vp, C.POINTER(GeometryRange), u32, u64, u64, C.POINTER(BuildSizes)]),
         "vkrt_blas_build": (i32, [vp, vp, sz, u32, vp, sz, C.POINTER(GeometryRange), u32, u32, C.POINTER(vp)]),
         "vkrt_blas_rebuild": (i32, [vp, vp, vp, sz, u32]),
@@ -269,6 +271,9 @@ class Context:
 
     def stats_enable(self, count_traversal: bool, time_stages: bool = False):
         self.check(self.lib.vkrt_stats_enable(self.handle, int(count_traversal), int(time_stages)))
+
+    def set_lane_refill(self, lanes: int):
+        self.check(self.lib.vkrt_trace_set_lane_refill(self.handle, lanes))
 
     def stats_reset(self):
         self.check(self.lib.vkrt_stats_reset(self.handle))

@@ -661,6 +661,21 @@ void* vkrt_frame_device_bgra8(VkrtFrame* fr)
     return fr ? F(fr)->bgra8.ptr : nullptr;
 }
 
+int vkrt_trace_set_lane_refill(VkrtContext* c, uint32_t lanes)
+{
+    Context* ctx = C(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (lanes > 32)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_set_lane_refill: lanes must be in 0..32");
+    }
+    ctx->refillLanes = lanes;
+    return VKRT_SUCCESS;
+}
+
 int vkrt_trace_rays(VkrtContext* c, const VkrtTlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits)
 {
     Context* ctx = C(c);

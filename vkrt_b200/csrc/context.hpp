@@ -84,6 +84,7 @@ struct Context : VkrtContext
     WaveBuffers wave;
 
     // stats
+    uint32_t refillLanes = 0; // vkrt_trace_set_lane_refill: 0 = whole-warp re-arm (default)
     bool countTraversal = false;
     bool timeStages = false;
     VkrtStats stats{};

@@ -117,9 +117,11 @@ k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, ui
 // ------------------------------------------------------------------------------------------------------------
 // Persistent-thread traversal with dynamic ray fetch (Aila & Laine 2009; Ylitie et al. 2017, section 4.3).
 // A warp keeps a private pool of ray indices that it refills from the launch-wide cursor in chunks (one global
-// atomic per chunk) and re-arms all 32 lanes together once every lane's ray has finished.  Re-arming idle lanes
-// while others are still traversing (per-lane replacement below 4..28 busy lanes) and triangle postponing were both
-// measured slower on B200 (config 2: 2014 Mrays/s without, 1690-1900 with), so neither is compiled in.
+// atomic per chunk) and by default re-arms all 32 lanes together once every lane's ray has finished: on coherent
+// workloads (Sponza) per-lane replacement below 4..28 busy lanes was measured slower (config 2: 2014 Mrays/s without,
+// 1690-1900 with), as was triangle postponing.  The REFILL variant (vkrt_trace_set_lane_refill) re-arms idle lanes
+// as soon as fewer than `refill` lanes are traversing; it pays on incoherent scenes such as the config-5 soup, where
+// only 13-15 of 32 lanes are busy otherwise.
 // Sources map a queue position to a ray and receive the result.
 // ------------------------------------------------------------------------------------------------------------
 struct ClosestSource
@@ -231,8 +233,9 @@ __device__ __forceinline__ bool enterInstance(const SceneDev& scene, F3 o, F3 d,
     }
 }
 
-template<bool ANY, bool MULTI, bool STATS, typename Source>
-__device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, TraceCounters& tc)
+template<bool ANY, bool MULTI, bool STATS, bool REFILL, typename Source>
+__device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, uint32_t refill,
+                                                TraceCounters& tc)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
@@ -337,6 +340,10 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                     active = false;
                     break;
                 }
+                if (REFILL && !exhausted && (uint32_t)__popc(__activemask()) < refill)
+                {
+                    break; // too few lanes still traversing: leave so that the idle lanes can take new rays
+                }
             }
         }
     }
@@ -356,17 +363,19 @@ __device__ __forceinline__ void flushTraceCounters(const TraceCounters& tc, unsi
     }
 }
 
-template<bool STATS, bool MULTI>
+// MODE: 0 plain, 1 counting nodes/triangles (stats pass), 2 per-lane ray replacement
+template<int MODE, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
 k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint32_t* __restrict__ countPtr,
                 uint32_t countImm, float4* __restrict__ hitA, uint32_t* __restrict__ hitInst, unsigned long long* statCounters,
-                int statSlot, uint32_t* cursor)
+                int statSlot, uint32_t* cursor, uint32_t refill)
 {
+    constexpr bool STATS = MODE == 1;
     const uint32_t count = countPtr ? *countPtr : countImm;
     TraceCounters tc;
     ClosestSource src;
     src.rayO = rayO, src.rayD = rayD, src.hitA = hitA, src.hitInst = hitInst;
-    tracePersistent<false, MULTI, STATS>(scene, src, count, cursor, tc);
+    tracePersistent<false, MULTI, STATS, MODE == 2>(scene, src, count, cursor, refill, tc);
     flushTraceCounters<STATS>(tc, statCounters, 3);
     if (statSlot >= 0 && blockIdx.x == 0 && threadIdx.x == 0 && countPtr)
     {
@@ -461,17 +470,18 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 }
 
 // shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
-template<bool STATS, bool MULTI>
+template<int MODE, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
-k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor)
+k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor, uint32_t refill)
 {
+    constexpr bool STATS = MODE == 1;
     const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
     const uint32_t total = c0 + c1 + c2 + c3;
     TraceCounters tc;
     ShadowSource src;
     src.shadowO = w.shadowO, src.shadowD = w.shadowD, src.shadowBits = w.shadowBits;
     src.c0 = c0, src.c01 = c0 + c1, src.c012 = c0 + c1 + c2, src.capacity = w.capacity;
-    tracePersistent<true, MULTI, STATS>(scene, src, total, cursor, tc);
+    tracePersistent<true, MULTI, STATS, MODE == 2>(scene, src, total, cursor, refill, tc);
     flushTraceCounters<STATS>(tc, statCounters, 6);
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
@@ -623,7 +633,7 @@ k_trace_any_list(SceneDev scene, const float4* __restrict__ rayO, const float4* 
     TraceCounters tc;
     ListAnySource src;
     src.rayO = rayO, src.rayD = rayD, src.out = out;
-    tracePersistent<true, MULTI, STATS>(scene, src, count, cursor, tc);
+    tracePersistent<true, MULTI, STATS, false>(scene, src, count, cursor, 0u, tc);
     flushTraceCounters<STATS>(tc, statCounters, 6);
 }
 
@@ -679,14 +689,19 @@ void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
     cudaStream_t s = ctx->stream;
-#define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor)
+    const uint32_t rf = ctx->refillLanes;
+#define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor, rf)
     if (st)
     {
-        multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
+        multi ? VKRT_LAUNCH(1, true) : VKRT_LAUNCH(1, false);
+    }
+    else if (rf)
+    {
+        multi ? VKRT_LAUNCH(2, true) : VKRT_LAUNCH(2, false);
     }
     else
     {
-        multi ? VKRT_LAUNCH(false, true) : VKRT_LAUNCH(false, false);
+        multi ? VKRT_LAUNCH(0, true) : VKRT_LAUNCH(0, false);
     }
 #undef VKRT_LAUNCH
 }
@@ -696,14 +711,19 @@ void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
     cudaStream_t s = ctx->stream;
-#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor)
+    const uint32_t rf = ctx->refillLanes;
+#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf)
     if (st)
     {
-        multi ? VKRT_LAUNCH(true, true) : VKRT_LAUNCH(true, false);
+        multi ? VKRT_LAUNCH(1, true) : VKRT_LAUNCH(1, false);
+    }
+    else if (rf)
+    {
+        multi ? VKRT_LAUNCH(2, true) : VKRT_LAUNCH(2, false);
     }
     else
     {
-        multi ? VKRT_LAUNCH(false, true) : VKRT_LAUNCH(false, false);
+        multi ? VKRT_LAUNCH(0, true) : VKRT_LAUNCH(0, false);
     }
 #undef VKRT_LAUNCH
 }
