@@ -1,6 +1,8 @@
 """GPU tier (`-m gpu`): the CUDA path, called through the C ABI (include/vkrt.h), against the CPU oracle.
 Bars (BASELINE.json north_star): closest-hit primitive id >= 99.9 %, shadow mask >= 99.9 %, RGB within 1/255 on
 matching pixels.  The design goal is stronger — bit equality — and is asserted where it is expected to hold."""
+import os
+
 import numpy as np
 import pytest
 
@@ -9,6 +11,8 @@ from bvh_check import check_bvh8
 from vkrt_b200 import binding as B
 from vkrt_b200 import camera, scenes
 from vkrt_b200.raytracer import Raytracer, flatten_model
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -319,3 +323,33 @@ def test_rebuild_and_linearity_properties():
     nodes, tris = blas.read()
     check_bvh8(nodes, tris, 300000)
     tlas.close(), tlas2.close(), blas.close(), ctx.close()
+
+
+def test_headless_host_executable(tmp_path, sponza_flat):
+    """The C++ host mirror (vkrt_b200/host: Context / Model / Camera / Raytracer / main over the C ABI) renders the staged
+    Sponza through its own glTF + image loader; frame 0 must match the Python-side render of the same scene (texture
+    decoders differ by at most an LSB or two, geometry is identical)."""
+    import json
+    import subprocess
+
+    exe = os.path.join(ROOT, "vkrt_b200", "host", "vkrt_headless")
+    assets = scenes.find_asset_dir()
+    if not os.path.exists(exe) or assets is None or not os.path.exists(os.path.join(assets, "Sponza.bin")):
+        pytest.skip("headless executable or staged assets missing (run __graft_entry__.build())")
+    W, Hh = 640, 360
+    prefix = str(tmp_path / "frame_")
+    r = subprocess.run([exe, "--width", str(W), "--height", str(Hh), "--frames", "3", "--models",
+                        os.path.dirname(assets), "--out", prefix], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["frames"] == 3 and line["blas_triangles"] == 262267 and line["rays_shadow"] > line["rays_primary"] > 0
+    with open(prefix + "0000.ppm", "rb") as f:
+        assert f.readline() == b"P6\n" and f.readline() == f"{W} {Hh}\n".encode() and f.readline() == b"255\n"
+        rgb = np.frombuffer(f.read(), dtype=np.uint8).reshape(Hh, W, 3)
+    rt = Raytracer(scenes.sponza_standin(), W, Hh, device=0)
+    rt.render()
+    bgra = rt.readback(B.AOV_BGRA8)
+    rt.close()
+    diff = np.abs(rgb.astype(np.int16) - bgra[:, :, 2::-1].astype(np.int16))
+    # stb-style JPEG decode (host loader) vs Pillow/libjpeg (Python side): texel LSBs differ, geometry does not
+    assert (diff <= 4).mean() > 0.99 and diff.mean() < 1.0, (float((diff <= 4).mean()), float(diff.mean()))

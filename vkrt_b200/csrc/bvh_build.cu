@@ -406,8 +406,148 @@ k_ploc_round(PlocClusters in, PlocClusters out, Bvh2 bvh, uint32_t* state, uint3
         }
         return;
     }
-    const uint32_t numTiles = (n + kPlocTile - 1) / kPlocTile;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (n <= (uint32_t)kPlocTile)
+    {
+        // Tail: everything fits one tile, so block 0 runs all remaining rounds out of shared memory in this launch
+        // (about 40 of the 74 rounds of a 262 k-triangle build are this small; as launches they cost ~8 us each).
+        if (blockIdx.x != 0)
+        {
+            return;
+        }
+        for (uint32_t k = threadIdx.x; k < n; k += kPlocThreads)
+        {
+            sLo[k] = in.lo[k], sHi[k] = in.hi[k], sId[k] = in.id[k];
+        }
+        uint32_t m = n, nodeNext = state[4];
+        __syncthreads();
+        while (m > 1u)
+        {
+            for (uint32_t k = threadIdx.x; k < m; k += kPlocThreads)
+            {
+                const float4 lo = sLo[k], hi = sHi[k];
+                float bestD = INFINITY;
+                uint32_t bestX = 0xFFFFFFFFu;
+                int bestJ = -1;
+                const int j0 = max((int)k - kPlocRadius, 0), j1 = min((int)k + kPlocRadius, (int)m - 1);
+                for (int j = j0; j <= j1; ++j)
+                {
+                    if (j == (int)k)
+                    {
+                        continue;
+                    }
+                    const float4 l2 = sLo[j], h2 = sHi[j];
+                    const float dx = fmaxf(hi.x, h2.x) - fminf(lo.x, l2.x), dy = fmaxf(hi.y, h2.y) - fminf(lo.y, l2.y),
+                                dz = fmaxf(hi.z, h2.z) - fminf(lo.z, l2.z);
+                    const float d = dx * dy + dy * dz + dz * dx;
+                    const uint32_t x = k ^ (uint32_t)j;
+                    if (d < bestD || (d == bestD && x < bestX) || bestJ < 0)
+                    {
+                        bestD = d, bestX = x, bestJ = j;
+                    }
+                }
+                sNN[k] = (short)bestJ;
+            }
+            __syncthreads();
+            // kPlocPerThread consecutive clusters per thread, results held in registers until everyone has read
+            uint32_t keepMask = 0, mergeMask = 0;
+            float4 rLo[kPlocPerThread], rHi[kPlocPerThread];
+            int rId[kPlocPerThread], rP[kPlocPerThread];
+#pragma unroll
+            for (int e = 0; e < kPlocPerThread; ++e)
+            {
+                const uint32_t k = threadIdx.x * kPlocPerThread + e;
+                rP[e] = -1;
+                if (k < m)
+                {
+                    const int p = sNN[k];
+                    const bool mutual = sNN[p] == (short)k;
+                    rLo[e] = sLo[k], rHi[e] = sHi[k], rId[e] = sId[k];
+                    if (!mutual || (int)k < p)
+                    {
+                        keepMask |= 1u << e;
+                    }
+                    if (mutual && (int)k < p)
+                    {
+                        mergeMask |= 1u << e;
+                        rP[e] = p;
+                        const float4 l2 = sLo[p], h2 = sHi[p];
+                        const uint32_t leaves = __float_as_uint(rLo[e].w) + __float_as_uint(l2.w);
+                        rLo[e] = make_float4(fminf(rLo[e].x, l2.x), fminf(rLo[e].y, l2.y), fminf(rLo[e].z, l2.z), __uint_as_float(leaves));
+                        rHi[e] = make_float4(fmaxf(rHi[e].x, h2.x), fmaxf(rHi[e].y, h2.y), fmaxf(rHi[e].z, h2.z), 0.0f);
+                    }
+                }
+            }
+            const uint32_t mine = (uint32_t)__popc(keepMask) | ((uint32_t)__popc(mergeMask) << 16);
+            uint32_t incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= (uint32_t)o)
+                {
+                    incl += t;
+                }
+            }
+            if (lane == 31)
+            {
+                sWarp[warp] = incl;
+            }
+            __syncthreads(); // also: every thread has finished reading the shared cluster arrays
+            uint32_t warpBase = 0, total = 0;
+            for (uint32_t w2 = 0; w2 < kPlocThreads / 32; ++w2)
+            {
+                const uint32_t v = sWarp[w2];
+                if (w2 < warp)
+                {
+                    warpBase += v;
+                }
+                total += v;
+            }
+            const uint32_t excl = warpBase + incl - mine;
+            uint32_t dst = excl & 0xFFFFu, node = nodeNext + (excl >> 16);
+#pragma unroll
+            for (int e = 0; e < kPlocPerThread; ++e)
+            {
+                if (!((keepMask >> e) & 1u))
+                {
+                    continue;
+                }
+                int id = rId[e];
+                if ((mergeMask >> e) & 1u)
+                {
+                    bvh.children[node] = make_int2(id, sId[rP[e]]);
+                    bvh.lo[node] = rLo[e];
+                    bvh.hi[node] = rHi[e];
+                    id = (int)node;
+                    ++node;
+                }
+                rId[e] = id;
+                rP[e] = (int)dst; // destination slot
+                ++dst;
+            }
+            __syncthreads(); // partner ids (sId) have been read
+#pragma unroll
+            for (int e = 0; e < kPlocPerThread; ++e)
+            {
+                if ((keepMask >> e) & 1u)
+                {
+                    sLo[rP[e]] = rLo[e], sHi[rP[e]] = rHi[e], sId[rP[e]] = rId[e];
+                }
+            }
+            m = total & 0xFFFFu;
+            nodeNext += total >> 16;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0)
+        {
+            out.id[0] = sId[0], out.lo[0] = sLo[0], out.hi[0] = sHi[0];
+            state[4] = nodeNext;
+            state[parity ^ 1] = 1u;
+        }
+        return;
+    }
+    const uint32_t numTiles = (n + kPlocTile - 1) / kPlocTile;
     volatile uint32_t* st = status;
 
     for (;;)
@@ -633,6 +773,268 @@ __device__ __forceinline__ void flushSah(const CollapseArgs& a, const float* sah
     }
 }
 
+// Cooperative form of collapseNode (builder.cuh): 8 lanes build one wide node, lane k holding child k, so the
+// dependent chain of child fetches, the greedy slot assignment and the quantisation run across lanes instead of as
+// ~500-step loops over local arrays in one thread.  Same decisions as the scalar form (lowest index wins ties).
+// All 32 lanes of a warp must call it; `valid` marks groups that have a node.  `stage` = 80 bytes per group.
+__device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t wideIndex, bool valid, uint8_t* stage, float* sahLocal)
+{
+    const Bvh2& b = a.bvh2;
+    const uint32_t lane = threadIdx.x & 31u, l8 = lane & 7u, base = lane & ~7u;
+    const unsigned full = 0xFFFFFFFFu;
+
+    int rootRef = ~0;
+    CollapseChild self;
+    self.ref = 0, self.lo = self.hi = f3(0.f, 0.f, 0.f), self.count = 0;
+    if (valid)
+    {
+        rootRef = a.taskRef[wideIndex];
+        self = collapseFetch(b, rootRef);
+    }
+    // children: lane k holds child k while k < n
+    CollapseChild c;
+    c.ref = 0, c.lo = c.hi = f3(0.f, 0.f, 0.f), c.count = 0;
+    uint32_t n = 0;
+    if (valid)
+    {
+        if (rootRef < 0 || self.count <= kMaxLeafTris)
+        {
+            n = 1;
+            if (l8 == 0)
+            {
+                c = self;
+            }
+        }
+        else
+        {
+            n = 2;
+            const int2 ch = b.children[rootRef];
+            if (l8 < 2)
+            {
+                c = collapseFetch(b, l8 == 0 ? ch.x : ch.y);
+            }
+        }
+    }
+    // open children: first those that must become inner nodes otherwise (> 3 triangles), then multi-triangle leaves
+    bool opening = valid && n >= 2;
+#pragma unroll 1
+    for (int iter = 0; iter < 6; ++iter)
+    {
+        const uint32_t cat = (l8 < n && opening) ? (c.count > kMaxLeafTris ? 2u : (c.count > 1u ? 1u : 0u)) : 0u;
+        float area = cat ? halfArea(c.lo, c.hi) : -1.0f;
+        uint32_t bestCat = cat, bestIdx = l8;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1)
+        {
+            const uint32_t oc = __shfl_xor_sync(full, bestCat, o);
+            const float oa = __shfl_xor_sync(full, area, o);
+            const uint32_t oi = __shfl_xor_sync(full, bestIdx, o);
+            const bool take = oc > bestCat || (oc == bestCat && (oa > area || (oa == area && oi < bestIdx)));
+            if (take)
+            {
+                bestCat = oc, area = oa, bestIdx = oi;
+            }
+        }
+        if (bestCat == 0u)
+        {
+            opening = false;
+        }
+        const int pickRef = __shfl_sync(full, c.ref, base + bestIdx);
+        if (opening && n < 8)
+        {
+            const int2 ch = b.children[pickRef];
+            if (l8 == bestIdx)
+            {
+                c = collapseFetch(b, ch.x);
+            }
+            else if (l8 == n)
+            {
+                c = collapseFetch(b, ch.y);
+            }
+            ++n;
+            if (n == 8)
+            {
+                opening = false;
+            }
+        }
+        if (!__any_sync(full, opening))
+        {
+            break;
+        }
+    }
+
+    // octant-ordered slot assignment: greedy maximum of +-cx +-cy +-cz over (child, free slot)
+    const bool has = valid && l8 < n;
+    const float ox = 0.5f * (c.lo.x + c.hi.x) - 0.5f * (self.lo.x + self.hi.x);
+    const float oy = 0.5f * (c.lo.y + c.hi.y) - 0.5f * (self.lo.y + self.hi.y);
+    const float oz = 0.5f * (c.lo.z + c.hi.z) - 0.5f * (self.lo.z + self.hi.z);
+    uint32_t freeMask = 0xFFu;
+    int mySlot = -1;
+#pragma unroll 1
+    for (int iter = 0; iter < 8; ++iter)
+    {
+        float cost = -INFINITY;
+        int slot = -1;
+        if (has && mySlot < 0)
+        {
+#pragma unroll
+            for (int sidx = 0; sidx < 8; ++sidx)
+            {
+                if ((freeMask >> sidx) & 1u)
+                {
+                    const float v = ((sidx & 1) ? ox : -ox) + ((sidx & 2) ? oy : -oy) + ((sidx & 4) ? oz : -oz);
+                    if (v > cost || slot < 0)
+                    {
+                        cost = v, slot = sidx;
+                    }
+                }
+            }
+        }
+        float bestCost = cost;
+        int bestSlot = slot;
+        uint32_t bestK = slot >= 0 ? l8 : 8u;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1)
+        {
+            const float oc = __shfl_xor_sync(full, bestCost, o);
+            const int os = __shfl_xor_sync(full, bestSlot, o);
+            const uint32_t ok = __shfl_xor_sync(full, bestK, o);
+            const bool take = ok < 8u && (bestK >= 8u || oc > bestCost || (oc == bestCost && ok < bestK));
+            if (take)
+            {
+                bestCost = oc, bestSlot = os, bestK = ok;
+            }
+        }
+        if (bestK < 8u)
+        {
+            if (l8 == bestK)
+            {
+                mySlot = bestSlot;
+            }
+            freeMask &= ~(1u << bestSlot);
+        }
+        if (!__any_sync(full, bestK < 8u))
+        {
+            break;
+        }
+    }
+
+    // bring the children into slot order: lane s takes the child whose slot is s
+    int src = -1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+    {
+        const int sj = __shfl_sync(full, mySlot, base + j);
+        if (sj == (int)l8)
+        {
+            src = j;
+        }
+    }
+    const uint32_t from = base + (src < 0 ? 0 : src);
+    CollapseChild d;
+    d.ref = __shfl_sync(full, c.ref, from);
+    d.lo.x = __shfl_sync(full, c.lo.x, from), d.lo.y = __shfl_sync(full, c.lo.y, from), d.lo.z = __shfl_sync(full, c.lo.z, from);
+    d.hi.x = __shfl_sync(full, c.hi.x, from), d.hi.y = __shfl_sync(full, c.hi.y, from), d.hi.z = __shfl_sync(full, c.hi.z, from);
+    d.count = __shfl_sync(full, c.count, from);
+    const bool present = src >= 0;
+    const bool inner = present && d.count > kMaxLeafTris;
+    const bool leaf = present && !inner;
+
+    const uint32_t innerMask = (__ballot_sync(full, inner) >> base) & 0xFFu;
+    const uint32_t innerCount = __popc(innerMask), innerRank = __popc(innerMask & ((1u << l8) - 1u));
+    uint32_t leafIncl = leaf ? d.count : 0u;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1)
+    {
+        const uint32_t t = __shfl_up_sync(full, leafIncl, o, 8);
+        if (l8 >= (uint32_t)o)
+        {
+            leafIncl += t;
+        }
+    }
+    const uint32_t primOffset = leafIncl - (leaf ? d.count : 0u);
+    const uint32_t primCount = __shfl_sync(full, leafIncl, base + 7);
+
+    // allocation: one pair of atomics per warp (4 nodes)
+    uint32_t needNodes = (l8 == 0 && valid) ? innerCount : 0u, needPrims = (l8 == 0 && valid) ? primCount : 0u;
+    uint32_t nodesBefore = 0, primsBefore = 0, nodesTotal = 0, primsTotal = 0;
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+    {
+        const uint32_t gn = __shfl_sync(full, needNodes, g * 8), gp = __shfl_sync(full, needPrims, g * 8);
+        if ((uint32_t)g * 8u < base)
+        {
+            nodesBefore += gn, primsBefore += gp;
+        }
+        nodesTotal += gn, primsTotal += gp;
+    }
+    uint32_t warpNodeBase = 0, warpPrimBase = 0;
+    if (lane == 0)
+    {
+        warpNodeBase = nodesTotal ? atomicAdd(a.nodeCounter, nodesTotal) : 0u;
+        warpPrimBase = primsTotal ? atomicAdd(a.primCounter, primsTotal) : 0u;
+    }
+    warpNodeBase = __shfl_sync(full, warpNodeBase, 0), warpPrimBase = __shfl_sync(full, warpPrimBase, 0);
+    const uint32_t childBase = innerCount ? warpNodeBase + nodesBefore : 0u;
+    const uint32_t primBase = primCount ? warpPrimBase + primsBefore : 0u;
+    const bool overflow = valid && childBase + innerCount > a.nodeCapacity;
+    if (overflow && l8 == 0)
+    {
+        *a.overflow = 1u;
+    }
+
+    if (valid && !overflow)
+    {
+        const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
+                       ez = quantExponent(self.lo.z, self.hi.z);
+        const float sx = __uint_as_float(ex << 23), sy = __uint_as_float(ey << 23), sz = __uint_as_float(ez << 23);
+        uint8_t meta = 0, q[6] = {0, 0, 0, 0, 0, 0};
+        if (present)
+        {
+            q[0] = (uint8_t)quantLo(d.lo.x, self.lo.x, sx), q[1] = (uint8_t)quantLo(d.lo.y, self.lo.y, sy);
+            q[2] = (uint8_t)quantLo(d.lo.z, self.lo.z, sz), q[3] = (uint8_t)quantHi(d.hi.x, self.lo.x, sx);
+            q[4] = (uint8_t)quantHi(d.hi.y, self.lo.y, sy), q[5] = (uint8_t)quantHi(d.hi.z, self.lo.z, sz);
+        }
+        if (inner)
+        {
+            meta = (uint8_t)(0x20u | (24u + l8));
+            a.taskRef[childBase + innerRank] = d.ref;
+        }
+        else if (leaf)
+        {
+            meta = (uint8_t)((((1u << d.count) - 1u) << 5) | primOffset);
+            uint32_t leaves[4];
+            collectLeaves(b, d.ref, leaves);
+            for (uint32_t j = 0; j < d.count; ++j)
+            {
+                a.primSource[primBase + primOffset + j] = b.vals[leaves[j]];
+            }
+            sahLocal[1] += halfArea(d.lo, d.hi) * (float)d.count;
+        }
+        stage[24 + l8] = meta;
+#pragma unroll
+        for (int f = 0; f < 6; ++f)
+        {
+            stage[32 + 8 * f + l8] = q[f];
+        }
+        if (l8 == 0)
+        {
+            float* hf = reinterpret_cast<float*>(stage);
+            uint32_t* hu = reinterpret_cast<uint32_t*>(stage);
+            hf[0] = self.lo.x, hf[1] = self.lo.y, hf[2] = self.lo.z;
+            hu[3] = ex | (ey << 8) | (ez << 16) | (innerMask << 24);
+            hu[4] = childBase, hu[5] = primBase;
+            sahLocal[0] += halfArea(self.lo, self.hi);
+        }
+    }
+    __syncwarp();
+    if (valid && !overflow && l8 < 5)
+    {
+        reinterpret_cast<uint4*>(a.nodes + wideIndex)[l8] = reinterpret_cast<const uint4*>(stage)[l8];
+    }
+    __syncwarp();
+}
+
 __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
 {
     a.taskRef[0] = a.bvh2.count > 1 ? *a.bvh2.root : ~0;
@@ -644,6 +1046,7 @@ __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
 __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a, uint32_t* range)
 {
     __shared__ uint32_t sFirst, sLast;
+    __shared__ __align__(16) uint8_t sStage[kNarrowLevel / 8][80];
     if (threadIdx.x == 0)
     {
         sFirst = range[0], sLast = range[1];
@@ -651,6 +1054,7 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
     __syncthreads();
     uint32_t levels = 0;
     float sah[2] = {0.0f, 0.0f};
+    const uint32_t group = threadIdx.x >> 3;
     for (;;)
     {
         const uint32_t first = sFirst, last = sLast;
@@ -658,9 +1062,10 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
         {
             break;
         }
-        if (first + threadIdx.x < last)
+        for (uint32_t chunk = first; chunk < last; chunk += kNarrowLevel / 8)
         {
-            collapseNode(a, first + threadIdx.x, sah);
+            const uint32_t i = chunk + group;
+            collapseNodeCoop(a, i, i < last, sStage[group], sah);
         }
         __threadfence_block();
         __syncthreads();
@@ -686,10 +1091,25 @@ __global__ void __launch_bounds__(128) k_collapse_wide(CollapseArgs a, uint32_t*
     {
         return;
     }
+    __shared__ __align__(16) uint8_t sStage[128 / 8][80];
     float sah[2] = {0.0f, 0.0f};
-    for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < last; i += gridDim.x * blockDim.x)
+    const uint32_t groupsPerBlock = blockDim.x >> 3, group = threadIdx.x >> 3;
+    if (last - first <= gridDim.x * blockDim.x)
     {
-        collapseNode(a, i, sah);
+        // latency-bound level: 8 lanes per node
+        for (uint32_t chunk = first + blockIdx.x * groupsPerBlock; chunk < last; chunk += gridDim.x * groupsPerBlock)
+        {
+            const uint32_t i = chunk + group;
+            collapseNodeCoop(a, i, i < last, sStage[group], sah);
+        }
+    }
+    else
+    {
+        // throughput-bound level (more nodes than threads): one thread per node costs fewer instructions in total
+        for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < last; i += gridDim.x * blockDim.x)
+        {
+            collapseNode(a, i, sah);
+        }
     }
     flushSah(a, sah);
     __threadfence();
@@ -913,10 +1333,10 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
             k_ploc_init<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(bvh, cl[0], state, status, statusCount);
             ctx->launches += 1;
             int round = 0;
-            int batch = 6;
-            for (uint32_t m = n; m > 1; m >>= 1)
+            int batch = 8;
+            for (uint32_t m = n; m > (uint32_t)kPlocTile; m >>= 1)
             {
-                batch += 4; // ~4 log2(n): measured, a round leaves ~84 % of the clusters (262 k triangles: 74 rounds)
+                batch += 4; // measured: a round leaves ~84 % of the clusters; the last <= 1024 take one launch
             }
             for (;;)
             {
