@@ -62,6 +62,8 @@ class ClockSampler:
         self.rows, self.proc, self.index = [], None, index
 
     def start(self):
+        if os.environ.get("VKRT_BENCH_NO_SMI"):  # diagnostic: does the nvidia-smi poller perturb the timed region?
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
                                           str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -176,7 +178,7 @@ def main():
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--triangles", type=int, default=50_000_000, help="config5 only: triangles in the procedural soup")
-    ap.add_argument("--build-flags", type=int, default=0)
+    ap.add_argument("--build-flags", type=int, default=-1, help="VkrtBuildFlags; default 0 (PLOC), config5 1 (LBVH: faster rebuild and, on the soup, fewer nodes per ray)")
     ap.add_argument("--lane-refill", type=int, default=-1, help="vkrt_trace_set_lane_refill; default 0, config5 20")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -205,6 +207,8 @@ def main():
         unique_id = ids[0]
 
     W, Hh, spp, desc = WORKLOADS[args.workload]
+    if args.build_flags < 0:
+        args.build_flags = 1 if args.workload == "config5" else 0
     soup = None
     if args.workload == "config5":
         from vkrt_b200 import scenes
@@ -343,7 +347,7 @@ def main():
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},
             "mrays_s_by_type": {"primary": rp / (ms * 1e-3) / 1e6, "shadow": rs / (ms * 1e-3) / 1e6, "reflection": rr / (ms * 1e-3) / 1e6},
             "bvh_build": {"ms": info.buildMilliseconds, "mtri_s": info.triangleCount / max(info.buildMilliseconds, 1e-9) / 1e3,
-                          "sah_cost": info.sahCost, "rebuilds_in_timed_region": len(build_ms),
+                          "sah_cost": info.sahCost, "build_flags": args.build_flags, "rebuilds_in_timed_region": len(build_ms),
                           "rebuild_ms_median": float(np.median(build_ms)) if build_ms else None,
                           "rebuild_mtri_s": info.triangleCount / float(np.median(build_ms)) / 1e3 if build_ms else None},
             "e2e": {"value": rays2 / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 256 * world,

@@ -84,6 +84,7 @@ struct Context : VkrtContext
     WaveBuffers wave;
 
     // stats
+    uint32_t waveKeyPaths = 0, waveKeySpp = 0, waveSamples = 1; // cached samples-per-wave decision (wavefront.cu)
     uint32_t refillLanes = 0; // vkrt_trace_set_lane_refill: 0 = whole-warp re-arm (default)
     bool countTraversal = false;
     bool timeStages = false;

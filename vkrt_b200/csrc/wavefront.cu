@@ -763,6 +763,11 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     // Samples per wave: all samples of a pixel that fit the queue budget go through the pipeline together, so a frame
     // costs 12 launches per WAVE instead of per sample (at 8 GPUs the per-launch ramp and tail were 10 % of a sample).
     uint32_t waveSamples = 1;
+    if (ctx->waveKeyPaths == paths && ctx->waveKeySpp == spp)
+    {
+        waveSamples = ctx->waveSamples; // cudaMemGetInfo costs up to milliseconds: ask once per frame shape
+    }
+    else
     {
         size_t freeBytes = 0, totalBytes = 0;
         cudaMemGetInfo(&freeBytes, &totalBytes);
@@ -777,6 +782,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
             fit = (size_t)atoi(e);
         }
         waveSamples = (uint32_t)std::max<size_t>(1, std::min<size_t>(fit, spp));
+        ctx->waveKeyPaths = paths, ctx->waveKeySpp = spp, ctx->waveSamples = waveSamples;
     }
     ctx->stats.samplesPerWave = waveSamples;
     int r = reserveWave(ctx, paths * waveSamples);
