@@ -87,7 +87,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     }
 
     // k_tri_bounds
-    std::vector<float4> triLo(n), triHi(n);
+    std::vector<float4> triBox(2 * (size_t)n);
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (uint32_t i = 0; i < n; ++i)
@@ -97,7 +97,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
         fetchTriangle(geo, b->vertices.data(), stride, b->indices.data(), i, v0, v1, v2, g, p);
         const float4 l = make_float4(fminf(fminf(v0.x, v1.x), v2.x), fminf(fminf(v0.y, v1.y), v2.y), fminf(fminf(v0.z, v1.z), v2.z), 0.f);
         const float4 h = make_float4(fmaxf(fmaxf(v0.x, v1.x), v2.x), fmaxf(fmaxf(v0.y, v1.y), v2.y), fmaxf(fmaxf(v0.z, v1.z), v2.z), 0.f);
-        triLo[i] = l, triHi[i] = h;
+        triBox[2 * (size_t)i] = l, triBox[2 * (size_t)i + 1] = h;
         const float lv[3] = {l.x, l.y, l.z}, hv[3] = {h.x, h.y, h.z};
         for (int k = 0; k < 3; ++k)
         {
@@ -117,7 +117,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
                       chi[2] > clo[2] ? 1.0f / (chi[2] - clo[2]) : 0.f);
     for (uint32_t i = 0; i < n; ++i)
     {
-        const float4 l = triLo[i], h = triHi[i];
+        const float4 l = triBox[2 * (size_t)i], h = triBox[2 * (size_t)i + 1];
         keys[i] = morton30(f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)), clo3, inv);
         vals[i] = i;
     }
@@ -131,13 +131,12 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
         sk[i] = keys[perm[i]], sv[i] = vals[perm[i]];
     }
     // k_lbvh
-    std::vector<int2> children(std::max(1u, n));
-    std::vector<float4> nlo(std::max(1u, n)), nhi(std::max(1u, n));
+    std::vector<BinNode> binNodes(std::max(1u, n));
     std::vector<int> flags(std::max(1u, n), -1);
     int root = 0;
     Bvh2 bvh;
-    bvh.children = children.data(), bvh.lo = nlo.data(), bvh.hi = nhi.data(), bvh.flags = flags.data();
-    bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triLo = triLo.data(), bvh.triHi = triHi.data();
+    bvh.nodes = binNodes.data(), bvh.flags = flags.data();
+    bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
     bvh.count = n, bvh.root = &root;
     if (n > 1)
     {

@@ -170,9 +170,9 @@ int vkrt_blas_sizes(VkrtContext* c, const VkrtGeometryRange* ranges, uint32_t ge
     }
     const uint64_t nodeCap = std::max<uint64_t>(1, n / 2 + 8);
     out->accelerationStructureSize = nodeCap * sizeof(Node8) + std::max<uint64_t>(1, n) * sizeof(PackedTri);
-    // triLo/triHi 32, keys/vals x2 16, children 8, node boxes 32, flags 4, taskRef 2, primSource 4, onesweep look-back
-    // words 1 (4 passes x 256 words per 4096-key tile), PLOC cluster boxes 64 (two ping-pong float4 pairs)
-    out->buildScratchSize = std::max<uint64_t>(1, n) * 168 + 16384;
+    // triangle boxes 32, build-order packed triangles 48, keys/vals x2 16, binary nodes 64, flags 4, taskRef 2-4,
+    // primSource 4, onesweep look-back words 1, PLOC cluster boxes 64 (two ping-pong float4 pairs)
+    out->buildScratchSize = std::max<uint64_t>(1, n) * 240 + 16384;
     out->geometryCopySize = vertexBytes + indexCount * 4;
     return VKRT_SUCCESS;
 }

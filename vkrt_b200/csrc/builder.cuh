@@ -78,16 +78,25 @@ VKRT_HD uint32_t morton30(F3 p, F3 lo, F3 invExtent)
 // lo.w carries the number of leaves of the subtree (as raw bits); the leaves need not be contiguous in sorted
 // order (PLOC merges clusters that are not neighbours), so small subtrees are enumerated by walking them.
 // ------------------------------------------------------------------------------------------------
+// One 64-byte record per binary node (one DRAM burst per visit; three separate arrays cost three), and one 32-byte
+// box per triangle: at 50 M triangles the collapse and the LBVH climb are bound by exactly these random fetches.
+struct alignas(64) BinNode
+{
+    float4 lo; // w = leaf count (raw bits)
+    float4 hi;
+    int2 children;
+    int2 pad0;
+    float4 pad1;
+};
+static_assert(sizeof(BinNode) == 64, "BinNode must be 64 bytes");
+
 struct Bvh2
 {
-    int2* children;
-    float4* lo;
-    float4* hi;
+    BinNode* nodes;
     int* flags;        // init -1; Apetrei range hand-off
     const uint32_t* keys;  // sorted Morton codes
     const uint32_t* vals;  // sorted build indices
-    const float4* triLo;   // per build index
-    const float4* triHi;
+    const float4* triBox;  // per build index: [2i] = min, [2i+1] = max
     uint32_t count;    // number of leaves
     int* root;
 };
@@ -131,7 +140,7 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
     uint32_t left = leaf, right = leaf;
     int current = ~(int)leaf;
     const uint32_t tri = b.vals[leaf];
-    float4 lo = b.triLo[tri], hi = b.triHi[tri];
+    float4 lo = b.triBox[2 * tri], hi = b.triBox[2 * tri + 1];
     for (;;)
     {
         uint32_t parent;
@@ -141,7 +150,7 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
         {
             parent = right;
             isLeftChild = true;
-            b.children[parent].x = current;
+            b.nodes[parent].children.x = current;
             VKRT_FENCE();
             prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)left);
             if (prev != -1)
@@ -153,7 +162,7 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
         {
             parent = left - 1;
             isLeftChild = false;
-            b.children[parent].y = current;
+            b.nodes[parent].children.y = current;
             VKRT_FENCE();
             prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)right);
             if (prev != -1)
@@ -167,25 +176,25 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
         }
         VKRT_FENCE();
         // fetch the sibling's box (written before its fence)
-        const int sibling = isLeftChild ? ((volatile int2*)b.children)[parent].y : ((volatile int2*)b.children)[parent].x;
+        const int sibling = isLeftChild ? ((volatile BinNode*)b.nodes)[parent].children.y : ((volatile BinNode*)b.nodes)[parent].children.x;
         float4 slo, shi;
         if (sibling < 0)
         {
             const uint32_t st = b.vals[~sibling];
-            slo = b.triLo[st];
-            shi = b.triHi[st];
+            slo = b.triBox[2 * st];
+            shi = b.triBox[2 * st + 1];
         }
         else
         {
-            slo = VKRT_LOAD_CG_F4(&b.lo[sibling]);
-            shi = VKRT_LOAD_CG_F4(&b.hi[sibling]);
+            slo = VKRT_LOAD_CG_F4(&b.nodes[sibling].lo);
+            shi = VKRT_LOAD_CG_F4(&b.nodes[sibling].hi);
         }
         lo.x = fminf(lo.x, slo.x), lo.y = fminf(lo.y, slo.y), lo.z = fminf(lo.z, slo.z);
         hi.x = fmaxf(hi.x, shi.x), hi.y = fmaxf(hi.y, shi.y), hi.z = fmaxf(hi.z, shi.z);
         lo.w = uintAsFloat(right - left + 1u);
         hi.w = 0.0f;
-        b.lo[parent] = lo;
-        b.hi[parent] = hi;
+        b.nodes[parent].lo = lo;
+        b.nodes[parent].hi = hi;
         current = (int)parent;
         if (left == 0 && right == n - 1)
         {
@@ -231,13 +240,13 @@ VKRT_HD CollapseChild collapseFetch(const Bvh2& b, int ref)
     {
         const uint32_t leaf = (uint32_t)~ref;
         const uint32_t tri = b.vals[leaf];
-        const float4 lo = b.triLo[tri], hi = b.triHi[tri];
+        const float4 lo = b.triBox[2 * tri], hi = b.triBox[2 * tri + 1];
         c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
         c.count = 1;
     }
     else
     {
-        const float4 lo = b.lo[ref], hi = b.hi[ref];
+        const float4 lo = b.nodes[ref].lo, hi = b.nodes[ref].hi;
         c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
         c.count = floatAsUint(lo.w);
     }
@@ -254,7 +263,7 @@ VKRT_HD uint32_t collectLeaves(const Bvh2& b, int ref, uint32_t* out)
     }
     // at most 3 leaves: one child is a leaf, the other a leaf or a pair of leaves
     uint32_t n = 0;
-    const int2 ch = b.children[ref];
+    const int2 ch = b.nodes[ref].children;
     const int side[2] = {ch.x, ch.y};
     for (int k = 0; k < 2; ++k)
     {
@@ -264,7 +273,7 @@ VKRT_HD uint32_t collectLeaves(const Bvh2& b, int ref, uint32_t* out)
         }
         else
         {
-            const int2 g = b.children[side[k]];
+            const int2 g = b.nodes[side[k]].children;
             out[n++] = (uint32_t)~g.x; // grandchildren of a <= 3-leaf subtree are leaves
             out[n++] = (uint32_t)~g.y;
         }
@@ -340,8 +349,8 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     }
     else
     {
-        c[0] = collapseFetch(b, b.children[rootRef].x);
-        c[1] = collapseFetch(b, b.children[rootRef].y);
+        c[0] = collapseFetch(b, b.nodes[rootRef].children.x);
+        c[1] = collapseFetch(b, b.nodes[rootRef].children.y);
         n = 2;
         while (n < 8)
         {
@@ -363,7 +372,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             {
                 break;
             }
-            const int2 ch = b.children[c[pick].ref];
+            const int2 ch = b.nodes[c[pick].ref].children;
             c[pick] = collapseFetch(b, ch.x);
             c[n++] = collapseFetch(b, ch.y);
         }
@@ -389,7 +398,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             {
                 break;
             }
-            const int2 ch = b.children[c[pick].ref];
+            const int2 ch = b.nodes[c[pick].ref].children;
             c[pick] = collapseFetch(b, ch.x);
             c[n++] = collapseFetch(b, ch.y);
         }

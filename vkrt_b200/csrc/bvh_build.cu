@@ -76,7 +76,7 @@ __device__ __forceinline__ float warpMax(float v)
 // Per-triangle AABB + reduction of the scene and centroid bounds (warp shuffle -> one atomic per warp).
 __global__ void __launch_bounds__(kThreads)
 k_tri_bounds(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t stride, const uint32_t* __restrict__ indices,
-             uint32_t count, float4* __restrict__ triLo, float4* __restrict__ triHi, uint32_t* sceneBounds)
+             uint32_t count, float4* __restrict__ triBox, float4* __restrict__ packedBuild, uint32_t* sceneBounds)
 {
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
@@ -89,8 +89,14 @@ k_tri_bounds(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t s
                                      fminf(fminf(v0.z, v1.z), v2.z), 0.0f);
         const float4 h = make_float4(fmaxf(fmaxf(v0.x, v1.x), v2.x), fmaxf(fmaxf(v0.y, v1.y), v2.y),
                                      fmaxf(fmaxf(v0.z, v1.z), v2.z), 0.0f);
-        triLo[i] = l;
-        triHi[i] = h;
+        triBox[2 * (size_t)i] = l;
+        triBox[2 * (size_t)i + 1] = h;
+        // the packed triangle in build order: k_pack_tris then only permutes 48-byte records instead of gathering the
+        // three (64-byte stride) vertices a second time
+        float4* dst = packedBuild + 3 * (size_t)i;
+        dst[0] = make_float4(v0.x, v0.y, v0.z, v1.x);
+        dst[1] = make_float4(v1.y, v1.z, v2.x, v2.y);
+        dst[2] = make_float4(v2.z, __uint_as_float(g), __uint_as_float(p), __uint_as_float(i));
         const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
         lo[0] = fminf(lo[0], l.x), lo[1] = fminf(lo[1], l.y), lo[2] = fminf(lo[2], l.z);
         hi[0] = fmaxf(hi[0], h.x), hi[1] = fmaxf(hi[1], h.y), hi[2] = fmaxf(hi[2], h.z);
@@ -149,7 +155,7 @@ __device__ __forceinline__ void histFlush(uint32_t (*hist)[256], uint32_t* __res
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_morton_hist(const float4* __restrict__ triLo, const float4* __restrict__ triHi, const uint32_t* __restrict__ sceneBounds,
+k_morton_hist(const float4* __restrict__ triBox, const uint32_t* __restrict__ sceneBounds,
               uint32_t count, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ globalHist)
 {
     __shared__ uint32_t hist[4][256];
@@ -164,7 +170,7 @@ k_morton_hist(const float4* __restrict__ triLo, const float4* __restrict__ triHi
                       hi.z > lo.z ? 1.0f / (hi.z - lo.z) : 0.0f);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
     {
-        const float4 l = triLo[i], h = triHi[i];
+        const float4 l = triBox[2 * (size_t)i], h = triBox[2 * (size_t)i + 1];
         const F3 c = f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z));
         const uint32_t key = morton30(c, lo, inv);
         keys[i] = key;
@@ -365,7 +371,7 @@ k_ploc_init(Bvh2 bvh, PlocClusters c, uint32_t* state, uint32_t* status, uint32_
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     {
         const uint32_t tri = bvh.vals[i];
-        float4 lo = bvh.triLo[tri], hi = bvh.triHi[tri];
+        float4 lo = bvh.triBox[2 * (size_t)tri], hi = bvh.triBox[2 * (size_t)tri + 1];
         lo.w = __uint_as_float(1u);
         hi.w = 0.0f;
         c.id[i] = ~(int)i;
@@ -516,9 +522,9 @@ k_ploc_round(PlocClusters in, PlocClusters out, Bvh2 bvh, uint32_t* state, uint3
                 int id = rId[e];
                 if ((mergeMask >> e) & 1u)
                 {
-                    bvh.children[node] = make_int2(id, sId[rP[e]]);
-                    bvh.lo[node] = rLo[e];
-                    bvh.hi[node] = rHi[e];
+                    bvh.nodes[node].lo = rLo[e];
+                    bvh.nodes[node].hi = rHi[e];
+                    bvh.nodes[node].children = make_int2(id, sId[rP[e]]);
                     id = (int)node;
                     ++node;
                 }
@@ -706,9 +712,9 @@ k_ploc_round(PlocClusters in, PlocClusters out, Bvh2 bvh, uint32_t* state, uint3
                 const uint32_t leaves = __float_as_uint(lo.w) + __float_as_uint(l2.w);
                 lo = make_float4(fminf(lo.x, l2.x), fminf(lo.y, l2.y), fminf(lo.z, l2.z), __uint_as_float(leaves));
                 hi = make_float4(fmaxf(hi.x, h2.x), fmaxf(hi.y, h2.y), fmaxf(hi.z, h2.z), 0.0f);
-                bvh.children[node] = make_int2(id, sId[p]);
-                bvh.lo[node] = lo;
-                bvh.hi[node] = hi;
+                bvh.nodes[node].lo = lo;
+                bvh.nodes[node].hi = hi;
+                bvh.nodes[node].children = make_int2(id, sId[p]);
                 id = (int)node;
                 ++node;
             }
@@ -808,7 +814,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         else
         {
             n = 2;
-            const int2 ch = b.children[rootRef];
+            const int2 ch = b.nodes[rootRef].children;
             if (l8 < 2)
             {
                 c = collapseFetch(b, l8 == 0 ? ch.x : ch.y);
@@ -842,7 +848,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         const int pickRef = __shfl_sync(full, c.ref, base + bestIdx);
         if (opening && n < 8)
         {
-            const int2 ch = b.children[pickRef];
+            const int2 ch = b.nodes[pickRef].children;
             if (l8 == bestIdx)
             {
                 c = collapseFetch(b, ch.x);
@@ -1136,16 +1142,14 @@ __global__ void k_empty_root(Node8* nodes)
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_pack_tris(GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t stride, const uint32_t* __restrict__ indices,
-            const uint32_t* __restrict__ primSource, uint32_t count, PackedTri* __restrict__ out)
+k_pack_tris(const float4* __restrict__ packedBuild, const uint32_t* __restrict__ primSource, uint32_t count, PackedTri* __restrict__ out)
 {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
     {
-        const PackedTri t = packTriangle(geo, vertices, stride, indices, primSource[i]);
+        const float4* src = packedBuild + 3 * (size_t)primSource[i];
+        const float4 a = src[0], b = src[1], c = src[2];
         float4* dst = reinterpret_cast<float4*>(out + i);
-        dst[0] = make_float4(t.v0x, t.v0y, t.v0z, t.v1x);
-        dst[1] = make_float4(t.v1y, t.v1z, t.v2x, t.v2y);
-        dst[2] = make_float4(t.v2z, __uint_as_float(t.geometry), __uint_as_float(t.primitive), __uint_as_float(t.buildIndex));
+        dst[0] = a, dst[1] = b, dst[2] = c;
     }
 }
 
@@ -1241,16 +1245,14 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     // scratch layout
     BuildScratch& sc = ctx->buildScratch;
     const size_t n1 = std::max<size_t>(n, 1);
-    VKRT_CUDA_TRY(ctx, sc.triLo.reserve(n1 * sizeof(float4)));
-    VKRT_CUDA_TRY(ctx, sc.triHi.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.triBox.reserve(n1 * 2 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.packedBuild.reserve(n1 * sizeof(PackedTri)));
     VKRT_CUDA_TRY(ctx, sc.keysA.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.keysB.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.valsA.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.valsB.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(sortStateBytes(n)));
-    VKRT_CUDA_TRY(ctx, sc.children.reserve(n1 * sizeof(int2)));
-    VKRT_CUDA_TRY(ctx, sc.nodeLo.reserve(n1 * sizeof(float4)));
-    VKRT_CUDA_TRY(ctx, sc.nodeHi.reserve(n1 * sizeof(float4)));
+    VKRT_CUDA_TRY(ctx, sc.binNodes.reserve(n1 * sizeof(BinNode)));
     VKRT_CUDA_TRY(ctx, sc.flags.reserve(n1 * 4));
     VKRT_CUDA_TRY(ctx, sc.taskRef.reserve((size_t)nodeCapacity * 4));
     VKRT_CUDA_TRY(ctx, sc.primSource.reserve(n1 * 4));
@@ -1286,9 +1288,9 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     else
     {
         k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices, n,
-                                                                      sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds);
+                                                                      sc.triBox.as<float4>(), sc.packedBuild.as<float4>(), sceneBounds);
         VKRT_CUDA_TRY(ctx, cudaMemsetAsync(sc.tileHist.ptr, 0, sortStateBytes(n), s));
-        k_morton_hist<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triLo.as<float4>(), sc.triHi.as<float4>(), sceneBounds, n,
+        k_morton_hist<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triBox.as<float4>(), sceneBounds, n,
                                                                        sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(),
                                                                        sc.tileHist.as<uint32_t>());
         ctx->launches += 2;
@@ -1300,14 +1302,11 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         }
 
         Bvh2 bvh;
-        bvh.children = sc.children.as<int2>();
-        bvh.lo = sc.nodeLo.as<float4>();
-        bvh.hi = sc.nodeHi.as<float4>();
+        bvh.nodes = sc.binNodes.as<BinNode>();
         bvh.flags = sc.flags.as<int>();
         bvh.keys = sc.keysA.as<uint32_t>();
         bvh.vals = sc.valsA.as<uint32_t>();
-        bvh.triLo = sc.triLo.as<float4>();
-        bvh.triHi = sc.triHi.as<float4>();
+        bvh.triBox = sc.triBox.as<float4>();
         bvh.count = n;
         bvh.root = root;
         const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
@@ -1408,8 +1407,8 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
             }
         }
         blas->nodeCount = last;
-        k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices,
-                                                                     sc.primSource.as<uint32_t>(), n, blas->tris.as<PackedTri>());
+        k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
+                                                                     blas->tris.as<PackedTri>());
         ctx->launches += 1;
 
         uint32_t hb[12];

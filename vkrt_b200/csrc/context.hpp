@@ -23,11 +23,11 @@ namespace vkrt
 
 struct BuildScratch
 {
-    DeviceBuffer triLo, triHi, keysA, keysB, valsA, valsB, tileHist, children, nodeLo, nodeHi, flags, taskRef, primSource, small;
+    DeviceBuffer triBox, packedBuild, keysA, keysB, valsA, valsB, tileHist, binNodes, flags, taskRef, primSource, small;
     DeviceBuffer plocLoA, plocHiA, plocLoB, plocHiB, plocStatus; // PLOC cluster boxes (ping-pong) and look-back words
     void release()
     {
-        DeviceBuffer* all[] = {&triLo, &triHi, &keysA, &keysB, &valsA, &valsB, &tileHist, &children, &nodeLo, &nodeHi, &flags,
+        DeviceBuffer* all[] = {&triBox, &packedBuild, &keysA, &keysB, &valsA, &valsB, &tileHist, &binNodes, &flags,
                                &taskRef, &primSource, &small, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus};
         for (DeviceBuffer* b : all)
         {
