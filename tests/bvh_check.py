@@ -34,22 +34,18 @@ def check_bvh8(nodes, tris, expected_triangles):
         max_depth = max(max_depth, depth)
         node = nodes[ni]
         imask = int(node["imask"])
+        leaf_bits = int(node["leafBits"])
+        assert leaf_bits < (1 << 24)
         for s in range(8):
-            meta = int(node["meta"][s])
-            if meta == 0:
-                assert not (imask >> s) & 1
-                continue
-            if (meta & 0xE0) == 0x20 and (meta & 0x1F) >= 24:
-                assert (meta & 0x1F) == 24 + s
-                assert (imask >> s) & 1
+            unary = (leaf_bits >> (3 * s)) & 7
+            if (imask >> s) & 1:
+                assert unary == 0, "a slot is internal or leaf, not both"
                 child = int(node["childBase"]) + bin(imask & ((1 << s) - 1)).count("1")
                 assert 0 < child < len(nodes)
                 stack.append((child, depth + 1))
-            else:
-                assert not (imask >> s) & 1
-                count = {1: 1, 3: 2, 7: 3}[meta >> 5]
-                off = meta & 0x1F
-                assert off + count <= 24
+            elif unary:
+                count = {1: 1, 3: 2, 7: 3}[unary]
+                off = bin(leaf_bits & ((1 << (3 * s)) - 1)).count("1")  # leaves are stored in slot order
                 for k in range(count):
                     seen_slot[int(node["primBase"]) + off + k] += 1
     assert (seen_node == 1).all(), "every node reachable exactly once"
@@ -61,17 +57,18 @@ def check_bvh8(nodes, tris, expected_triangles):
         node = nodes[ni]
         lo, hi = decode_child_boxes(node)
         imask = int(node["imask"])
+        leaf_bits = int(node["leafBits"])
         for s in range(8):
-            meta = int(node["meta"][s])
-            if meta == 0:
-                continue
+            unary = (leaf_bits >> (3 * s)) & 7
             if (imask >> s) & 1:
                 child = int(node["childBase"]) + bin(imask & ((1 << s) - 1)).count("1")
                 clo, chi = node_lo[child], node_hi[child]
-            else:
-                count = {1: 1, 3: 2, 7: 3}[meta >> 5]
-                first = int(node["primBase"]) + (meta & 0x1F)
+            elif unary:
+                count = {1: 1, 3: 2, 7: 3}[unary]
+                first = int(node["primBase"]) + bin(leaf_bits & ((1 << (3 * s)) - 1)).count("1")
                 clo, chi = tri_lo[first:first + count].min(axis=0), tri_hi[first:first + count].max(axis=0)
+            else:
+                continue
             assert (lo[s] <= clo).all() and (hi[s] >= chi).all(), (ni, s, lo[s], clo, hi[s], chi)
             node_lo[ni] = np.minimum(node_lo[ni], clo)
             node_hi[ni] = np.maximum(node_hi[ni], chi)

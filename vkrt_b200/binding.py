@@ -110,7 +110,8 @@ NODE_DTYPE = np.dtype(
         ("imask", "u1"),
         ("childBase", "<u4"),
         ("primBase", "<u4"),
-        ("meta", "u1", 8),
+        ("leafBits", "<u4"),
+        ("reserved", "<u4"),
         ("qlox", "u1", 8),
         ("qloy", "u1", 8),
         ("qloz", "u1", 8),

@@ -484,6 +484,8 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     node.imask = 0;
     node.childBase = childBase;
     node.primBase = primBase;
+    node.leafBits = 0;
+    node.reserved = 0;
     uint32_t innerSeen = 0, primOffset = 0;
     float leafArea = 0.0f;
     for (int s = 0; s < 8; ++s)
@@ -491,7 +493,6 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
         const int k = childInSlot[s];
         if (k < 0)
         {
-            node.meta[s] = 0;
             node.qlox[s] = node.qloy[s] = node.qloz[s] = 0;
             node.qhix[s] = node.qhiy[s] = node.qhiz[s] = 0;
             continue;
@@ -505,14 +506,13 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
         if (c[k].count > kMaxLeafTris)
         {
             node.imask |= (uint8_t)(1u << s);
-            node.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
             a.taskRef[childBase + innerSeen] = c[k].ref;
             ++innerSeen;
         }
         else
         {
             const uint32_t unary = (1u << c[k].count) - 1u; // 1 -> 001, 2 -> 011, 3 -> 111
-            node.meta[s] = (uint8_t)((unary << 5) | primOffset);
+            node.leafBits |= unary << (3 * s);
             uint32_t leaves[4];
             collectLeaves(b, c[k].ref, leaves);
             for (uint32_t j = 0; j < c[k].count; ++j)

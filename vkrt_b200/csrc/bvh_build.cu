@@ -989,12 +989,20 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         *a.overflow = 1u;
     }
 
+    // Node8::leafBits: slot l8 contributes its unary triangle count at bit 3*l8; OR over the 8 lanes of the group
+    uint32_t leafBits = leaf ? ((1u << d.count) - 1u) << (3u * l8) : 0u;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1)
+    {
+        leafBits |= __shfl_xor_sync(full, leafBits, o, 8);
+    }
+
     if (valid && !overflow)
     {
         const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
                        ez = quantExponent(self.lo.z, self.hi.z);
         const float sx = __uint_as_float(ex << 23), sy = __uint_as_float(ey << 23), sz = __uint_as_float(ez << 23);
-        uint8_t meta = 0, q[6] = {0, 0, 0, 0, 0, 0};
+        uint8_t q[6] = {0, 0, 0, 0, 0, 0};
         if (present)
         {
             q[0] = (uint8_t)quantLo(d.lo.x, self.lo.x, sx), q[1] = (uint8_t)quantLo(d.lo.y, self.lo.y, sy);
@@ -1003,12 +1011,10 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         }
         if (inner)
         {
-            meta = (uint8_t)(0x20u | (24u + l8));
             a.taskRef[childBase + innerRank] = d.ref;
         }
         else if (leaf)
         {
-            meta = (uint8_t)((((1u << d.count) - 1u) << 5) | primOffset);
             uint32_t leaves[4];
             collectLeaves(b, d.ref, leaves);
             for (uint32_t j = 0; j < d.count; ++j)
@@ -1017,7 +1023,6 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             }
             sahLocal[1] += halfArea(d.lo, d.hi) * (float)d.count;
         }
-        stage[24 + l8] = meta;
 #pragma unroll
         for (int f = 0; f < 6; ++f)
         {
@@ -1029,7 +1034,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             uint32_t* hu = reinterpret_cast<uint32_t*>(stage);
             hf[0] = self.lo.x, hf[1] = self.lo.y, hf[2] = self.lo.z;
             hu[3] = ex | (ey << 8) | (ez << 16) | (innerMask << 24);
-            hu[4] = childBase, hu[5] = primBase;
+            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits, hu[7] = 0u;
             sahLocal[0] += halfArea(self.lo, self.hi);
         }
     }

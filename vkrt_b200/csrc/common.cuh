@@ -28,7 +28,9 @@ struct alignas(16) Node8
     uint8_t imask;        // bit s set: slot s holds an internal child
     uint32_t childBase;   // index of the first internal child node
     uint32_t primBase;    // index of the first primitive (packed triangle or instance) of this node
-    uint8_t meta[8];      // per slot: 0 empty | internal: 0b001xxxxx (low5 = 24+slot) | leaf: unary count<<5 | offset
+    uint32_t leafBits;    // bit 3*s+j set: slot s is a leaf holding a j-th triangle (j < 3); its packed triangle is
+                          // primBase + popcount(leafBits below that bit): leaves are stored in slot order
+    uint32_t reserved;
     uint8_t qlox[8], qloy[8], qloz[8];
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };

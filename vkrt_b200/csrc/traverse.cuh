@@ -128,7 +128,9 @@ VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, floa
 VKRT_HD uint32_t highestBit(uint32_t v) // index of the most significant set bit, v != 0
 {
 #if defined(__CUDA_ARCH__)
-    return 31u - (uint32_t)__clz((int)v);
+    uint32_t bit;
+    asm("bfind.u32 %0, %1;" : "=r"(bit) : "r"(v)); // FLO.U32 already is the bit index; 31 - clz costs two more ops
+    return bit;
 #else
     return 31u - (uint32_t)__builtin_clz(v);
 #endif
@@ -198,12 +200,14 @@ constexpr float kBoxRelPad = 3.8146973e-06f; // 2^-18
 VKRT_HD float padDown(float t) { return fmaExplicit(-fabsf(t), kBoxRelPad, t); }
 VKRT_HD float padUp(float t) { return fmaExplicit(fabsf(t), kBoxRelPad, t); }
 
-// Slab test of the 4 children held in one byte lane group; ORs their hit bits into `hitmask`.
-template<int I>
+// Slab test of child J (byte J & 3 of its half's plane words); sets bit J of `hitSlots` when the padded interval is
+// not empty.
+template<int J>
 VKRT_HD void testChild(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
-                       float bnx, float bny, float bnz, float bfx, float bfy, float bfz, float tminP, float tmaxP, uint32_t bits4,
-                       uint32_t index4, uint32_t one, uint32_t& hitmask)
+                       float bnx, float bny, float bnz, float bfx, float bfy, float bfz, float tminP, float tmaxP, uint32_t one,
+                       uint32_t& hitSlots)
 {
+    constexpr int I = J & 3;
     const float tnx = fmaExplicit(byteToUnitFloat<I>(nx, one), ax, bnx), tfx = fmaExplicit(byteToUnitFloat<I>(fx, one), ax, bfx);
     const float tny = fmaExplicit(byteToUnitFloat<I>(ny, one), ay, bny), tfy = fmaExplicit(byteToUnitFloat<I>(fy, one), ay, bfy);
     const float tnz = fmaExplicit(byteToUnitFloat<I>(nz, one), az, bnz), tfz = fmaExplicit(byteToUnitFloat<I>(fz, one), az, bfz);
@@ -211,12 +215,33 @@ VKRT_HD void testChild(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint3
     const float tf = fminf(fminf(fminf(tfx, tfy), tfz), tmaxP);
     if (tn <= tf)
     {
-        hitmask |= byteOf(bits4, I) << byteOf(index4, I);
+        hitSlots |= 1u << J;
     }
 }
 
+// Moves bit s of an 8-bit slot mask to bit s ^ octinv (three conditional swap stages, written as variable shifts so
+// that no select is needed).  Children are stored in octant order, so after this the highest bit is the nearest child.
+VKRT_HD uint32_t permuteSlots(uint32_t x, uint32_t octinv)
+{
+    const uint32_t s4 = octinv & 4u, s2 = octinv & 2u, s1 = octinv & 1u;
+    x = ((x * 0x101u) >> s4) & 0xFFu;
+    x = ((x << s2) & 0xCCu) | ((x >> s2) & 0x33u);
+    x = ((x << s1) & 0xAAu) | ((x >> s1) & 0x55u);
+    return x;
+}
+
+// Bit s of an 8-bit slot mask -> bits 3s, 3s+1, 3s+2 (the layout of Node8::leafBits).
+VKRT_HD uint32_t spreadSlots(uint32_t x)
+{
+    x = (x * 0x101u) & 0xF00Fu;
+    x = (x * 0x11u) & 0xC30C3u;
+    x = (x * 0x5u) & 0x249249u;
+    return x * 7u;
+}
+
 // Intersects the ray with the 8 quantised child boxes of a node.  Returns the hit mask: bits 24..31 = internal
-// children in traversal priority order (nearest octant-order child in the highest bit), bits 0..23 = primitives.
+// children in traversal priority order (nearest octant-order child in the highest bit), bits 0..23 = the leafBits of
+// the leaf children whose boxes are hit.
 //   idir = safeRcp(d), octant bit k set when d_k < 0, tminP/tmaxP = padDown(tmin)/padUp(tmax)
 //
 // Plane distance of quantised coordinate q on axis x:  t = (px + q*sx - ox) * idir.x.  With m = 1 + q*2^-15 (the PRMT
@@ -224,6 +249,7 @@ VKRT_HD void testChild(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint3
 // Rounding b costs at most 2^-24*(|b|+|ax|) <= 2^-9 of one quantisation step of t, so the near planes are pulled in
 // and the far planes pushed out by 2^-7 step (bn/bf below): the test stays conservative, and flat boxes (qlo == qhi)
 // keep tn < tf.  NaN planes (0*inf for axis-parallel rays) are dropped by fmaxf/fminf, i.e. that axis never culls.
+// Empty slots carry a zero box that a ray may well hit: they drop out because neither imask nor leafBits names them.
 VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
     const uint32_t e = floatAsUint(w.n0.w);
@@ -238,31 +264,30 @@ VKRT_HD uint32_t intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octan
     const float bnx = fmaExplicit(-fabsf(ax), slack, bx), bfx = fmaExplicit(fabsf(ax), slack, bx);
     const float bny = fmaExplicit(-fabsf(ay), slack, by), bfy = fmaExplicit(fabsf(ay), slack, by);
     const float bnz = fmaExplicit(-fabsf(az), slack, bz), bfz = fmaExplicit(fabsf(az), slack, bz);
-    const uint32_t octinv4 = (7u - octant) * 0x01010101u;
-    uint32_t hitmask = 0;
-    // n1 = {childBase, primBase, meta[0..3], meta[4..7]}; n2 = {qlox[0..3], qlox[4..7], qloy[0..3], qloy[4..7]}
+    uint32_t hitSlots = 0;
+    // n1 = {childBase, primBase, leafBits, reserved};     n2 = {qlox[0..3], qlox[4..7], qloy[0..3], qloy[4..7]}
     // n3 = {qloz lo, qloz hi, qhix lo, qhix hi};          n4 = {qhiy lo, qhiy hi, qhiz lo, qhiz hi}
-#pragma unroll
-    for (int half = 0; half < 2; ++half)
     {
-        const uint32_t meta4 = half ? w.n1.w : w.n1.z;
-        // internal children have meta 0b001sssss with sssss = 24 + slot: bits 3 and 4 both set
-        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t innerMask4 = (isInner4 >> 4) * 0xFFu;
-        const uint32_t index4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1F1F1F1Fu; // 24 + (slot ^ octinv) | prim offset
-        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;                      // 1 | unary triangle count; 0 = empty
-        const uint32_t qlox = half ? w.n2.y : w.n2.x, qloy = half ? w.n2.w : w.n2.z, qloz = half ? w.n3.y : w.n3.x;
-        const uint32_t qhix = half ? w.n3.w : w.n3.z, qhiy = half ? w.n4.y : w.n4.x, qhiz = half ? w.n4.w : w.n4.z;
         // near/far plane selection by ray direction sign
-        const uint32_t nx = (octant & 1u) ? qhix : qlox, fx = (octant & 1u) ? qlox : qhix;
-        const uint32_t ny = (octant & 2u) ? qhiy : qloy, fy = (octant & 2u) ? qloy : qhiy;
-        const uint32_t nz = (octant & 4u) ? qhiz : qloz, fz = (octant & 4u) ? qloz : qhiz;
-        testChild<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
-        testChild<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
-        testChild<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
-        testChild<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, bits4, index4, one, hitmask);
+        const uint32_t nx = (octant & 1u) ? w.n3.z : w.n2.x, fx = (octant & 1u) ? w.n2.x : w.n3.z;
+        const uint32_t ny = (octant & 2u) ? w.n4.x : w.n2.z, fy = (octant & 2u) ? w.n2.z : w.n4.x;
+        const uint32_t nz = (octant & 4u) ? w.n4.z : w.n3.x, fz = (octant & 4u) ? w.n3.x : w.n4.z;
+        testChild<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
     }
-    return hitmask;
+    {
+        const uint32_t nx = (octant & 1u) ? w.n3.w : w.n2.y, fx = (octant & 1u) ? w.n2.y : w.n3.w;
+        const uint32_t ny = (octant & 2u) ? w.n4.y : w.n2.w, fy = (octant & 2u) ? w.n2.w : w.n4.y;
+        const uint32_t nz = (octant & 4u) ? w.n4.w : w.n3.y, fz = (octant & 4u) ? w.n3.y : w.n4.w;
+        testChild<4>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<5>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<6>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+        testChild<7>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
+    }
+    const uint32_t inner = permuteSlots(hitSlots & (e >> 24), 7u - octant);
+    return (inner << 24) | (spreadSlots(hitSlots) & w.n1.z);
 }
 
 VKRT_HD void loadTriangle(const PackedTri* tris, uint32_t index, F3& v0, F3& v1, F3& v2, uint32_t& geometry,
@@ -328,6 +353,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
                           TraceCounters* counters, uint32_t one)
 {
     int result = 0;
+    uint32_t leafBits = 0;
     if (c.ngroup.y > 0x00FFFFFFu)
     {
         const uint32_t octinv = 7u - c.octant;
@@ -345,7 +371,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
                 counters->overflow = 1;
             }
         }
-        const uint32_t slot = (bit - 24u) ^ octinv;
+        const uint32_t slot = (bit ^ octinv) & 7u; // bit is 24..31
         const uint32_t rel = popCount(c.ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
         const NodeWords w = loadNode(nodes, base + rel);
         if (counters)
@@ -356,6 +382,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
         const uint32_t imask = floatAsUint(w.n0.w) >> 24;
         c.ngroup = make_uint2(w.n1.x, (hits & 0xFF000000u) | imask);
         c.tgroup = make_uint2(w.n1.y, hits & 0x00FFFFFFu);
+        leafBits = w.n1.z;
     }
     else
     {
@@ -365,8 +392,9 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
     while (c.tgroup.y != 0u)
     {
         const uint32_t bit = highestBit(c.tgroup.y);
-        c.tgroup.y &= ~(1u << bit);
-        const uint32_t slotIndex = c.tgroup.x + bit;
+        const uint32_t below = (1u << bit) - 1u;
+        c.tgroup.y &= below;
+        const uint32_t slotIndex = c.tgroup.x + popCount(leafBits & below); // leaves are stored in slot order
         F3 v0, v1, v2;
         uint32_t geometry, primitive, buildIndex;
         loadTriangle(tris, slotIndex, v0, v1, v2, geometry, primitive, buildIndex);
