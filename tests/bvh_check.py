@@ -4,7 +4,9 @@ import numpy as np
 
 def decode_child_boxes(node):
     p = node["p"].astype(np.float32)
-    scale = (node["e"].astype(np.uint32) << 23).view(np.float32)
+    # sx, sy, sz hold the upper half of the float 2^15 * scale
+    half = np.array([node["sx"], node["sy"], node["sz"]], dtype=np.uint32)
+    scale = ((half << 16).view(np.float32) * np.float32(2.0 ** -15)).astype(np.float32)
     lo = np.stack([p[0] + node["qlox"].astype(np.float32) * scale[0], p[1] + node["qloy"].astype(np.float32) * scale[1],
                    p[2] + node["qloz"].astype(np.float32) * scale[2]], axis=1)
     hi = np.stack([p[0] + node["qhix"].astype(np.float32) * scale[0], p[1] + node["qhiy"].astype(np.float32) * scale[1],

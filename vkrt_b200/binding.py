@@ -106,12 +106,14 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "
 NODE_DTYPE = np.dtype(
     [
         ("p", "<f4", 3),
-        ("e", "u1", 3),
-        ("imask", "u1"),
+        ("sx", "<u2"),
+        ("sy", "<u2"),
         ("childBase", "<u4"),
         ("primBase", "<u4"),
         ("leafBits", "<u4"),
-        ("reserved", "<u4"),
+        ("sz", "<u2"),
+        ("imask", "u1"),
+        ("reserved", "u1"),
         ("qlox", "u1", 8),
         ("qloy", "u1", 8),
         ("qloz", "u1", 8),

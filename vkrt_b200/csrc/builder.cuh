@@ -479,7 +479,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     node.px = self.lo.x, node.py = self.lo.y, node.pz = self.lo.z;
     const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
                    ez = quantExponent(self.lo.z, self.hi.z);
-    node.ex = (uint8_t)ex, node.ey = (uint8_t)ey, node.ez = (uint8_t)ez;
+    node.sx = packScaleExponent(ex), node.sy = packScaleExponent(ey), node.sz = packScaleExponent(ez);
     const float sx = uintAsFloat(ex << 23), sy = uintAsFloat(ey << 23), sz = uintAsFloat(ez << 23);
     node.imask = 0;
     node.childBase = childBase;

@@ -1033,8 +1033,9 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             float* hf = reinterpret_cast<float*>(stage);
             uint32_t* hu = reinterpret_cast<uint32_t*>(stage);
             hf[0] = self.lo.x, hf[1] = self.lo.y, hf[2] = self.lo.z;
-            hu[3] = ex | (ey << 8) | (ez << 16) | (innerMask << 24);
-            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits, hu[7] = 0u;
+            hu[3] = (uint32_t)packScaleExponent(ex) | ((uint32_t)packScaleExponent(ey) << 16);
+            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits;
+            hu[7] = (uint32_t)packScaleExponent(ez) | (innerMask << 16);
             sahLocal[0] += halfArea(self.lo, self.hi);
         }
     }
@@ -1142,7 +1143,7 @@ __global__ void k_empty_root(Node8* nodes)
 {
     Node8 n;
     memset(&n, 0, sizeof(n));
-    n.ex = n.ey = n.ez = 1;
+    n.sx = n.sy = n.sz = packScaleExponent(1);
     nodes[0] = n;
 }
 

@@ -24,16 +24,19 @@ namespace vkrt
 struct alignas(16) Node8
 {
     float px, py, pz;     // quantisation origin (node box minimum)
-    uint8_t ex, ey, ez;   // per-axis scale exponents (biased IEEE exponent bytes: scale = 2^(e-127))
-    uint8_t imask;        // bit s set: slot s holds an internal child
+    uint16_t sx, sy;      // per-axis scale 2^(e-127) as the upper half of the float 2^(e-127+15): (e + 15) << 7
     uint32_t childBase;   // index of the first internal child node
     uint32_t primBase;    // index of the first primitive (packed triangle or instance) of this node
     uint32_t leafBits;    // bit 3*s+j set: slot s is a leaf holding a j-th triangle (j < 3); its packed triangle is
                           // primBase + popcount(leafBits below that bit): leaves are stored in slot order
-    uint32_t reserved;
+    uint16_t sz;          // as sx, sy
+    uint8_t imask;        // bit s set: slot s holds an internal child
+    uint8_t reserved;     // 0
     uint8_t qlox[8], qloy[8], qloz[8];
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };
+// Packs a scale exponent byte the way Node8 stores it; the builder keeps e <= 239.
+inline __host__ __device__ uint16_t packScaleExponent(uint32_t e) { return (uint16_t)((e + 15u) << 7); }
 static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 
 // Packed triangle, 48 bytes: raw vertex positions (the watertight test needs all three) + Vulkan ids.

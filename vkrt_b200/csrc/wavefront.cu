@@ -237,6 +237,7 @@ template<bool ANY, bool MULTI, bool STATS, bool REFILL, typename Source>
 __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, uint32_t refill,
                                                 TraceCounters& tc)
 {
+    initSlotTables();
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
     uint32_t chunk = (total / (warpsTotal * 8u) + 31u) & ~31u;
