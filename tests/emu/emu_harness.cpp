@@ -138,11 +138,45 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     bvh.nodes = binNodes.data(), bvh.flags = flags.data();
     bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
     bvh.count = n, bvh.root = &root;
+    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
     if (n > 1)
     {
         for (uint32_t i = 0; i < n; ++i)
         {
             lbvhClimb(bvh, i);
+        }
+    }
+    // cost-optimal collapse: children before parents (the GPU climbs from the leaves with arrival counters)
+    std::vector<uint32_t> dpChoice;
+    const char* dpEnv = getenv("VKRT_EMU_DP_PRIM_COST");
+    const float dpPrimCost = dpEnv ? (float)atof(dpEnv) : 0.5f;
+    if (n > 1 && dpPrimCost > 0.0f)
+    {
+        dpChoice.assign(n, 0u);
+        bvh.dpChoice = dpChoice.data(), bvh.dpPrimCost = dpPrimCost;
+        std::vector<std::pair<int, int>> work; // (node, state)
+        work.emplace_back(root, 0);
+        while (!work.empty())
+        {
+            auto [node, state] = work.back();
+            if (state == 0)
+            {
+                work.back().second = 1;
+                const int2 ch = binNodes[node].children;
+                if (ch.x >= 0)
+                {
+                    work.emplace_back(ch.x, 0);
+                }
+                if (ch.y >= 0)
+                {
+                    work.emplace_back(ch.y, 0);
+                }
+            }
+            else
+            {
+                dpSolve(bvh, node);
+                work.pop_back();
+            }
         }
     }
     // collapse

@@ -172,7 +172,7 @@ int vkrt_blas_sizes(VkrtContext* c, const VkrtGeometryRange* ranges, uint32_t ge
     out->accelerationStructureSize = nodeCap * sizeof(Node8) + std::max<uint64_t>(1, n) * sizeof(PackedTri);
     // triangle boxes 32, build-order packed triangles 48, keys/vals x2 16, binary nodes 64, flags 4, taskRef 2-4,
     // primSource 4, onesweep look-back words 1, PLOC cluster boxes 64 (two ping-pong float4 pairs)
-    out->buildScratchSize = std::max<uint64_t>(1, n) * 240 + 16384;
+    out->buildScratchSize = std::max<uint64_t>(1, n) * 252 + 16384;
     out->geometryCopySize = vertexBytes + indexCount * 4;
     return VKRT_SUCCESS;
 }

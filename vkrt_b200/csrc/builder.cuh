@@ -99,6 +99,10 @@ struct Bvh2
     const float4* triBox;  // per build index: [2i] = min, [2i+1] = max
     uint32_t count;    // number of leaves
     int* root;
+    // cost-optimal collapse (dpSolve / dpExpand below); dpChoice == nullptr selects the greedy collapse
+    uint32_t* dpChoice; // per binary node: split decisions
+    int* dpParent;      // [0, count): parent of sorted leaf i; [count, 2*count-1): parent of binary node i - count
+    float dpPrimCost;   // cost of one triangle test relative to one node test
 };
 
 VKRT_HD uint64_t lbvhDelta(const Bvh2& b, uint32_t j) // distance between sorted leaves j and j+1
@@ -287,6 +291,154 @@ VKRT_HD float halfArea(F3 lo, F3 hi)
     return dx * dy + dy * dz + dz * dx;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Cost-optimal distribution of a binary subtree over wide-node slots (Ylitie, Karras, Laine 2017, section 3.1).
+// c[i], i = 1..7, is the cheapest SAH cost of the subtree represented as a forest of at most i slot entries:
+//   c[1]  = leaf (<= 3 triangles): area * count * primCost;  else: area * 1 + dist[8]   (one wide node)
+//   c[i]  = min(dist[i], c[i-1]),   dist[j] = min over k of cLeft[k] + cRight[j-k]
+// The seven costs live in the padding of the 64-byte BinNode (pad1, pad0, hi.w), the decisions in one word:
+//   bits 3(j-2)..3(j-2)+2 = k chosen for dist[j], j = 2..8;  bit 21+(i-2) set: c[i] == c[i-1] (use fewer entries).
+// A subtree is an internal wide node exactly when it holds more than 3 triangles, as in the greedy collapse.
+// ------------------------------------------------------------------------------------------------
+constexpr float kDpPrimCost = 0.5f; // triangle test relative to node test; chosen on the Sponza stand-in (tools/bvh_quality.py)
+VKRT_HD void dpFetch(const Bvh2& b, int ref, float* c)
+{
+    if (ref < 0)
+    {
+        const uint32_t tri = b.vals[(uint32_t)~ref];
+        const float4 lo = b.triBox[2 * tri], hi = b.triBox[2 * tri + 1];
+        const float a = halfArea(f3(lo.x, lo.y, lo.z), f3(hi.x, hi.y, hi.z)) * b.dpPrimCost;
+        for (int i = 1; i < 8; ++i)
+        {
+            c[i] = a;
+        }
+    }
+    else
+    {
+        // written by another thread of the same launch (dpClimb): read past L1
+        const BinNode& n = b.nodes[ref];
+        const float4 p1 = VKRT_LOAD_CG_F4(&n.pad1), hi = VKRT_LOAD_CG_F4(&n.hi);
+        const float4 p0 = VKRT_LOAD_CG_F4(reinterpret_cast<const float4*>(&n.children)); // children, pad0
+        c[1] = p1.x, c[2] = p1.y, c[3] = p1.z, c[4] = p1.w;
+        c[5] = p0.z, c[6] = p0.w, c[7] = hi.w;
+    }
+}
+
+VKRT_HD void dpSolve(const Bvh2& b, int ref)
+{
+    BinNode& n = b.nodes[ref];
+    float cl[8], cr[8];
+    dpFetch(b, n.children.x, cl);
+    dpFetch(b, n.children.y, cr);
+    uint32_t choice = 0;
+    float dist[9];
+    for (int j = 2; j <= 8; ++j)
+    {
+        float best = INFINITY;
+        int bk = j - 7 > 1 ? j - 7 : 1;
+        for (int k = bk; k <= 7 && k < j; ++k)
+        {
+            const float v = cl[k] + cr[j - k];
+            if (v < best)
+            {
+                best = v, bk = k;
+            }
+        }
+        dist[j] = best;
+        choice |= (uint32_t)bk << (3 * (j - 2));
+    }
+    const float4 lo = n.lo, hi = n.hi;
+    const float area = halfArea(f3(lo.x, lo.y, lo.z), f3(hi.x, hi.y, hi.z));
+    const uint32_t count = floatAsUint(lo.w);
+    float c[8];
+    c[1] = count <= kMaxLeafTris ? area * (float)count * b.dpPrimCost : area + dist[8];
+    for (int i = 2; i < 8; ++i)
+    {
+        if (dist[i] < c[i - 1])
+        {
+            c[i] = dist[i];
+        }
+        else
+        {
+            c[i] = c[i - 1];
+            choice |= 1u << (21 + (i - 2));
+        }
+    }
+    n.pad1 = make_float4(c[1], c[2], c[3], c[4]);
+    n.pad0 = make_int2((int)floatAsUint(c[5]), (int)floatAsUint(c[6]));
+    n.hi.w = c[7];
+    b.dpChoice[ref] = choice;
+}
+
+// Parent links for the climb: one thread per binary node.
+VKRT_HD void dpLinkParents(const Bvh2& b, uint32_t node)
+{
+    const int2 ch = b.nodes[node].children;
+    b.dpParent[ch.x < 0 ? (uint32_t)~ch.x : b.count + (uint32_t)ch.x] = (int)node;
+    b.dpParent[ch.y < 0 ? (uint32_t)~ch.y : b.count + (uint32_t)ch.y] = (int)node;
+}
+
+// One thread per sorted leaf: climbs towards the root; the second thread to arrive at a node solves it (both children
+// are final then).  b.flags must be zero on entry.
+VKRT_HD void dpClimb(const Bvh2& b, uint32_t leaf)
+{
+    const int root = *b.root;
+    int node = b.dpParent[leaf];
+    for (;;)
+    {
+        VKRT_FENCE();
+        if (VKRT_ATOMIC_ADD(&b.flags[node], 1) == 0)
+        {
+            return;
+        }
+        VKRT_FENCE();
+        dpSolve(b, node);
+        if (node == root)
+        {
+            return;
+        }
+        node = b.dpParent[b.count + (uint32_t)node];
+    }
+}
+
+// Slot entries of the wide node that covers binary node `ref` (more than 3 triangles), left to right.
+VKRT_HD int dpExpand(const Bvh2& b, int ref, int* out)
+{
+    int stackRef[8], stackSlots[8];
+    int sp = 0, n = 0;
+    {
+        const int2 ch = b.nodes[ref].children;
+        const int k = (int)(b.dpChoice[ref] >> 18) & 7; // dist[8]
+        stackRef[sp] = ch.y, stackSlots[sp++] = 8 - k;
+        stackRef[sp] = ch.x, stackSlots[sp++] = k;
+    }
+    while (sp > 0)
+    {
+        const int m = stackRef[--sp];
+        int i = stackSlots[sp];
+        if (m < 0)
+        {
+            out[n++] = m;
+            continue;
+        }
+        const uint32_t choice = b.dpChoice[m];
+        while (i > 1 && ((choice >> (21 + (i - 2))) & 1u))
+        {
+            --i;
+        }
+        if (i == 1)
+        {
+            out[n++] = m;
+            continue;
+        }
+        const int2 ch = b.nodes[m].children;
+        const int k = (int)(choice >> (3 * (i - 2))) & 7;
+        stackRef[sp] = ch.y, stackSlots[sp++] = i - k;
+        stackRef[sp] = ch.x, stackSlots[sp++] = k;
+    }
+    return n;
+}
+
 // Smallest biased exponent byte e such that lo + 255 * 2^(e-127) >= hi (evaluated in float, as traversal decodes it)
 VKRT_HD uint32_t quantExponent(float lo, float hi)
 {
@@ -349,10 +501,22 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     }
     else
     {
-        c[0] = collapseFetch(b, b.nodes[rootRef].children.x);
-        c[1] = collapseFetch(b, b.nodes[rootRef].children.y);
-        n = 2;
-        while (n < 8)
+        if (b.dpChoice)
+        {
+            int refs[8];
+            n = dpExpand(b, rootRef, refs);
+            for (int k = 0; k < n; ++k)
+            {
+                c[k] = collapseFetch(b, refs[k]);
+            }
+        }
+        else
+        {
+            c[0] = collapseFetch(b, b.nodes[rootRef].children.x);
+            c[1] = collapseFetch(b, b.nodes[rootRef].children.y);
+            n = 2;
+        }
+        while (n < 8 && !b.dpChoice)
         {
             int pick = -1;
             float bestArea = -1.0f;

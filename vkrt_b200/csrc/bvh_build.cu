@@ -811,7 +811,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
                 c = self;
             }
         }
-        else
+        else if (!b.dpChoice)
         {
             n = 2;
             const int2 ch = b.nodes[rootRef].children;
@@ -821,12 +821,43 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             }
         }
     }
+    if (b.dpChoice)
+    {
+        // cost-optimal collapse: lane 0 of the group walks the decisions, then every lane fetches its entry
+        int refs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        uint32_t m = 0;
+        if (valid && n == 0 && l8 == 0)
+        {
+            m = (uint32_t)dpExpand(b, rootRef, refs);
+        }
+        m = __shfl_sync(full, m, base);
+        int myRef = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+        {
+            const int r = __shfl_sync(full, refs[j], base);
+            if (l8 == (uint32_t)j)
+            {
+                myRef = r;
+            }
+        }
+        if (m > 0)
+        {
+            n = m;
+            if (l8 < n)
+            {
+                c = collapseFetch(b, myRef);
+            }
+        }
+    }
     // open children: first those that must become inner nodes otherwise (> 3 triangles), then multi-triangle leaves
+    // (with the cost-optimal collapse only the latter: which subtrees become nodes is already decided)
+    const uint32_t innerCat = b.dpChoice ? 0u : 2u;
     bool opening = valid && n >= 2;
 #pragma unroll 1
     for (int iter = 0; iter < 6; ++iter)
     {
-        const uint32_t cat = (l8 < n && opening) ? (c.count > kMaxLeafTris ? 2u : (c.count > 1u ? 1u : 0u)) : 0u;
+        const uint32_t cat = (l8 < n && opening) ? (c.count > kMaxLeafTris ? innerCat : (c.count > 1u ? 1u : 0u)) : 0u;
         float area = cat ? halfArea(c.lo, c.hi) : -1.0f;
         uint32_t bestCat = cat, bestIdx = l8;
 #pragma unroll
@@ -1045,6 +1076,24 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         reinterpret_cast<uint4*>(a.nodes + wideIndex)[l8] = reinterpret_cast<const uint4*>(stage)[l8];
     }
     __syncwarp();
+}
+
+__global__ void __launch_bounds__(kThreads) k_dp_parents(Bvh2 bvh)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < bvh.count)
+    {
+        dpLinkParents(bvh, i);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_dp_climb(Bvh2 bvh)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < bvh.count)
+    {
+        dpClimb(bvh, i);
+    }
 }
 
 __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
@@ -1308,6 +1357,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         }
 
         Bvh2 bvh;
+        bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
         bvh.nodes = sc.binNodes.as<BinNode>();
         bvh.flags = sc.flags.as<int>();
         bvh.keys = sc.keysA.as<uint32_t>();
@@ -1364,6 +1414,24 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
                 }
                 batch = 16;
             }
+        }
+
+        // cost-optimal collapse (default; the fast-build path keeps the greedy one): parents, then a bottom-up climb
+        float dpPrimCost = fast ? 0.0f : kDpPrimCost;
+        if (const char* e = getenv("VKRT_BUILD_DP_PRIM_COST"))
+        {
+            dpPrimCost = (float)atof(e);
+        }
+        if (n > kMaxLeafTris && dpPrimCost > 0.0f)
+        {
+            VKRT_CUDA_TRY(ctx, sc.dp.reserve((size_t)n * 12));
+            bvh.dpChoice = sc.dp.as<uint32_t>();
+            bvh.dpParent = reinterpret_cast<int*>(sc.dp.as<uint32_t>() + n);
+            bvh.dpPrimCost = dpPrimCost;
+            VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0, (size_t)(n - 1) * 4, s));
+            k_dp_parents<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+            k_dp_climb<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+            ctx->launches += 2;
         }
 
         CollapseArgs ca;
