@@ -341,7 +341,7 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "scene": model["provenance"], "width": W, "height": Hh, "spp": spp,
-                       "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "instances": 1 if instances is None else len(instances),
+                       "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "instances": 1 if instances is None else int(np.asarray(instances).size // 12),
                        "parallelism": f"interleaved 64x64 tiles over {world} rank(s), scene replicated, NCCL send/recv gather to rank 0",
                        "l2": "per-frame ray/hit/shading queues (>2 GB at 4K) exceed the 126 MB L2; no explicit flush"},
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},

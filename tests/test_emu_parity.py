@@ -35,6 +35,25 @@ def test_builder_invariants_soup_and_duplicates():
     check_bvh8(nodes, tris, 300)
 
 
+def test_cost_optimal_collapse(monkeypatch):
+    """The cost-optimal collapse (dpSolve / dpExpand in builder.cuh) against the greedy one on the same binary tree:
+    both give valid trees and identical closest hits; the optimal one has the lower SAH cost and tests fewer triangles."""
+    flat = flatten_model(scenes.random_soup(20000, seed=11, geometries=3))
+    inst = scenes.identity_instance(1.0)
+    rays = H.random_rays(20000, 5, (-12, -8, -10), (12, 8, 10))
+    out = {}
+    for name, cost in (("greedy", "0"), ("optimal", "0.5")):
+        monkeypatch.setenv("VKRT_EMU_DP_PRIM_COST", cost)
+        e = H.EmuScene(flat, inst)
+        nodes, tris = e.read_blas()
+        check_bvh8(nodes, tris, 20000)
+        hits, n_nodes, n_tris = e.trace_rays(rays)
+        out[name] = (e.sah(), len(nodes), hits, n_nodes, n_tris)
+    assert np.array_equal(out["greedy"][2], out["optimal"][2])
+    assert out["optimal"][0] < out["greedy"][0]
+    assert out["optimal"][3] * 0.5 + out["optimal"][4] < out["greedy"][3] * 0.5 + out["greedy"][4]
+
+
 def test_builder_invariants_sponza(sponza_flat):
     e = H.EmuScene(sponza_flat, scenes.REFERENCE_INSTANCE)
     nodes, tris = e.read_blas()

@@ -82,6 +82,31 @@ def test_builder_invariants(flags):
     ctx.close()
 
 
+def test_collapse_modes(monkeypatch):
+    """PLOC hierarchy with the greedy collapse (VKRT_BUILD_DP_PRIM_COST=0) and with the cost-optimal one (default), and
+    the cost-optimal one on the LBVH hierarchy: valid trees, identical hits, lower SAH cost for the optimal collapse."""
+    flat = flatten_model(scenes.random_soup(30000, seed=21, geometries=3))
+    inst = scenes.identity_instance(1.0)
+    rays = H.random_rays(100000, 6, (-12, -8, -10), (12, 8, 10))
+    ctx = B.Context(0)
+    res = {}
+    for name, env, flags in (("greedy", "0", B.BUILD_DEFAULT), ("optimal", None, B.BUILD_DEFAULT), ("lbvh_optimal", "0.5", B.BUILD_PREFER_FAST_BUILD)):
+        if env is None:
+            monkeypatch.delenv("VKRT_BUILD_DP_PRIM_COST", raising=False)
+        else:
+            monkeypatch.setenv("VKRT_BUILD_DP_PRIM_COST", env)
+        blas = B.Blas(ctx, flat["vertices"], flat["indices"], flat["ranges"], flags=flags)
+        nodes, tris = blas.read()
+        check_bvh8(nodes, tris, 30000)
+        tlas = B.Tlas(ctx, [blas], inst)
+        res[name] = (float(blas.info().sahCost), tlas.trace_rays(rays))
+        tlas.close(), blas.close()
+    monkeypatch.delenv("VKRT_BUILD_DP_PRIM_COST", raising=False)
+    ctx.close()
+    assert np.array_equal(res["greedy"][1], res["optimal"][1]) and np.array_equal(res["greedy"][1], res["lbvh_optimal"][1])
+    assert res["optimal"][0] < res["greedy"][0]
+
+
 @pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD])
 def test_builder_duplicates(flags):
     """Thousands of identical triangles (equal Morton codes, equal merge distances): the builder must still terminate
