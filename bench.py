@@ -3,8 +3,10 @@
 
 Step   = one frame of the hot path (vkrt_trace [+ NCCL tile gather]) over the resident scene.
 value  = rays traced by all ranks / device time (CUDA events on the library's stream), inputs resident in HBM.
-e2e    = same metric through the reference-facing call (Raytracer.render + frame readback): the 256-byte uniform
-         block goes host->device and the B8G8R8A8 frame comes back to pinned host memory every step.
+e2e    = same metric through the reference-facing calls (Raytracer.render + present): the 256-byte uniform block goes
+         host->device and the B8G8R8A8 frame comes back to page-locked host memory every step, through a ring of 3
+         images like the reference's swapchain (the copy of frame k overlaps the traversal of frame k+1; the timed
+         region ends when the last copy has landed).
 --impl reference times the CPU oracle (oracle/, the restatement of the reference's shaders; the reference's own
 Vulkan path and Mesa lavapipe are unavailable on this box) on the host cores, on a bounded pixel subset per step.
 """
@@ -286,25 +288,38 @@ def main():
              "resolve": st.msResolve, "sample_total": st.msTotal}
 
     # end to end through the reference-facing call: render + readback into pinned host memory every step
-    host = torch.empty((Hh, W, 4), dtype=torch.uint8, pin_memory=True)
-    host_np = host.numpy()
+    ring = [rt.ctx.host_array((Hh, W, 4)) for _ in range(3)] if rank == 0 else []
+    tickets = [None, None, None]
     rt.ctx.stats_enable(False, False)
 
-    def e2e_step():
+    def e2e_step(k):
         set_pose(rt, args.workload, step_counter[0])
         rebuild_step()
         step_counter[0] += 1
+        if rank == 0 and tickets[k % 3] is not None:  # acquire: the ring image's previous copy has landed
+            rt.present_wait(tickets[k % 3])
         rt.render(spp=spp, flags=flags, gather=True)
         if rank == 0:
-            rt.readback(B.AOV_BGRA8, host_np)
+            tickets[k % 3] = rt.present(ring[k % 3])
 
-    for _ in range(2):
-        e2e_step()
+    def e2e_drain():
+        for i, t in enumerate(tickets):
+            if t is not None:
+                rt.present_wait(t)
+                tickets[i] = None
+        rt.ctx.synchronize()
+
+    # restart the camera path so that the timed e2e steps walk the same frames as the device-timed steps did
+    step_counter[0] = (step_counter[0] + 299) // 300 * 300
+    for k in range(max(args.warmup, 2)):
+        e2e_step(k)
+    e2e_drain()
     barrier()
     rt.ctx.stats_reset()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
+    for k in range(args.steps):
+        e2e_step(k)
+    e2e_drain()
     barrier()
     e2e_s = time.perf_counter() - t0
     st2 = rt.ctx.stats()

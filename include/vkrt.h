@@ -209,6 +209,19 @@ typedef enum VkrtAov
  * swapchain image (src/Raytracer.cpp:175-185) in the headless mode.  Synchronises the stream.  With a
  * communicator, valid on the root rank after vkrt_tiles_gather (BGRA8) and on every rank for owned tiles. */
 VKRT_API int vkrt_frame_read(VkrtContext* ctx, VkrtFrame* frame, int aov, void* dst, size_t pitch);
+/* Presentation ring, the headless form of the reference's swapchain (acquire / submit / present with 3 images in
+ * flight, src/Context.cpp:141-180; image copy src/Raytracer.cpp:175-185).  vkrt_frame_present queues a copy of the
+ * BGRA8 image into `dst` (`pitch` = bytes per row, 0 = tight) on the library's copy stream, ordered after everything
+ * queued on the context so far, and returns without waiting; `*ticket` identifies the copy.  `dst` should be page-locked
+ * (vkrt_host_alloc) or the copy degrades to a synchronous one.  The next vkrt_trace / vkrt_tiles_gather into the same
+ * frame may be queued at once: only its final image write waits (on the device) for outstanding copies, so the copy
+ * overlaps the next frame's traversal.  vkrt_frame_present_wait blocks the host until the copy `ticket` has landed
+ * (the wait a swapchain image needs before it is reused).  At most 8 copies per frame are kept in flight. */
+VKRT_API int vkrt_frame_present(VkrtContext* ctx, VkrtFrame* frame, void* dst, size_t pitch, uint64_t* ticket);
+VKRT_API int vkrt_frame_present_wait(VkrtContext* ctx, VkrtFrame* frame, uint64_t ticket);
+/* Page-locked host memory for vkrt_frame_present / vkrt_frame_read destinations. */
+VKRT_API int vkrt_host_alloc(VkrtContext* ctx, size_t bytes, void** out);
+VKRT_API void vkrt_host_free(VkrtContext* ctx, void* ptr);
 /* Device pointer of the assembled BGRA8 image (width*height*4), valid until the frame is destroyed. */
 VKRT_API void* vkrt_frame_device_bgra8(VkrtFrame* frame);
 

@@ -350,6 +350,40 @@ def test_rebuild_and_linearity_properties():
     tlas.close(), tlas2.close(), blas.close(), ctx.close()
 
 
+def test_present_ring():
+    """vkrt_frame_present (the swapchain stand-in): five frames with different poses go through a ring of three
+    page-locked images without a host wait between render and present; every image must equal the synchronous
+    read-back of the same pose, i.e. frame k+1's image write waited for frame k's copy."""
+    W, Hh = 512, 288
+    rt = Raytracer(scenes.analytic_scene(metallic_floor=True), W, Hh, device=0)
+    poses = [((0.0, 1.5, 4.0 + 0.5 * k), (0.0, 0.1 * k, 0.0)) for k in range(5)]
+    want = []
+    for pos, rot in poses:
+        rt.camera.setPosition(pos), rt.camera.setRotation(rot)
+        rt.render()
+        want.append(rt.readback(B.AOV_BGRA8).copy())
+    assert not np.array_equal(want[0], want[4])
+    ring = [rt.ctx.host_array((Hh, W, 4)) for _ in range(3)]
+    tickets, got = [None] * 3, {}
+    for k, (pos, rot) in enumerate(poses):
+        s = k % 3
+        if tickets[s] is not None:
+            rt.present_wait(tickets[s])
+            got[k - 3] = ring[s].copy()
+        rt.camera.setPosition(pos), rt.camera.setRotation(rot)
+        rt.render()
+        tickets[s] = rt.present(ring[s])
+    for k in range(2, 5):
+        rt.present_wait(tickets[k % 3])
+        got[k] = ring[k % 3].copy()
+    rt.present_wait(0)  # long finished: returns at once
+    with pytest.raises(B.VkrtError):
+        rt.present_wait(99)
+    for k in range(5):
+        assert np.array_equal(got[k], want[k]), k
+    rt.close()
+
+
 def test_headless_host_executable(tmp_path, sponza_flat):
     """The C++ host mirror (vkrt_b200/host: Context / Model / Camera / Raytracer / main over the C ABI) renders the staged
     Sponza through its own glTF + image loader; frame 0 must match the Python-side render of the same scene (texture

@@ -149,6 +149,10 @@ EXPORTS = [
     "vkrt_frame_destroy",
     "vkrt_trace",
     "vkrt_frame_read",
+    "vkrt_frame_present",
+    "vkrt_frame_present_wait",
+    "vkrt_host_alloc",
+    "vkrt_host_free",
     "vkrt_frame_device_bgra8",
     "vkrt_trace_rays",
     "vkrt_stats_enable",
@@ -199,6 +203,10 @@ def load_library(path: Optional[str] = None):
         "vkrt_frame_destroy": (None, [vp, vp]),
         "vkrt_trace": (i32, [vp, vp, C.POINTER(Uniforms), u32, u32, u32, vp]),
         "vkrt_frame_read": (i32, [vp, vp, i32, vp, sz]),
+        "vkrt_frame_present": (i32, [vp, vp, vp, sz, C.POINTER(C.c_uint64)]),
+        "vkrt_frame_present_wait": (i32, [vp, vp, C.c_uint64]),
+        "vkrt_host_alloc": (i32, [vp, sz, C.POINTER(vp)]),
+        "vkrt_host_free": (None, [vp, vp]),
         "vkrt_frame_device_bgra8": (vp, [vp]),
         "vkrt_trace_rays": (i32, [vp, vp, vp, u64, i32, vp]),
         "vkrt_stats_enable": (i32, [vp, i32, i32]),
@@ -235,6 +243,7 @@ class Context:
             raise VkrtError(r, (self.lib.vkrt_last_error(None) or b"").decode())
         self.handle = h
         self._keep = []
+        self._pinned = {}
 
     def check(self, r: int):
         if r != 0:
@@ -242,6 +251,9 @@ class Context:
 
     def close(self):
         if self.handle:
+            for p in list(getattr(self, "_pinned", {}).values()):
+                self.lib.vkrt_host_free(self.handle, C.c_void_p(p))
+            self._pinned = {}
             self.lib.vkrt_context_destroy(self.handle)
             self.handle = None
 
@@ -271,6 +283,21 @@ class Context:
             keep.append(im)
             arr[i].width, arr[i].height, arr[i].rgba8 = im.shape[1], im.shape[0], im.ctypes.data
         self.check(self.lib.vkrt_textures_set(self.handle, arr, len(images)))
+
+    def host_array(self, shape, dtype=np.uint8) -> np.ndarray:
+        """numpy view of page-locked host memory (vkrt_host_alloc); released with host_free(array) or with the context."""
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        self.check(self.lib.vkrt_host_alloc(self.handle, nbytes, C.byref(p)))
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        self._pinned[arr.ctypes.data] = p.value
+        return arr
+
+    def host_free(self, arr: np.ndarray):
+        p = self._pinned.pop(arr.ctypes.data, None)
+        if p:
+            self.lib.vkrt_host_free(self.handle, C.c_void_p(p))
 
     def stats_enable(self, count_traversal: bool, time_stages: bool = False):
         self.check(self.lib.vkrt_stats_enable(self.handle, int(count_traversal), int(time_stages)))
@@ -430,6 +457,17 @@ class Frame:
             out = np.empty(shape, dtype=dt)
         self.ctx.check(self.ctx.lib.vkrt_frame_read(self.ctx.handle, self.handle, aov, _ptr(out), 0))
         return out
+
+    def present(self, out: np.ndarray) -> int:
+        """Queues the BGRA8 image copy into `out` (page-locked host memory: Context.host_array or a pinned torch tensor)
+        and returns its ticket at once; the next trace may be queued immediately (vkrt_frame_present)."""
+        assert out.nbytes >= self.width * self.height * 4 and out.flags["C_CONTIGUOUS"]
+        t = C.c_uint64()
+        self.ctx.check(self.ctx.lib.vkrt_frame_present(self.ctx.handle, self.handle, _ptr(out), 0, C.byref(t)))
+        return int(t.value)
+
+    def present_wait(self, ticket: int):
+        self.ctx.check(self.ctx.lib.vkrt_frame_present_wait(self.ctx.handle, self.handle, ticket))
 
     @property
     def device_bgra8(self) -> int:

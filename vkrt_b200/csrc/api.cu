@@ -134,6 +134,11 @@ void vkrt_context_destroy(VkrtContext* c)
             cudaEventDestroy(ev);
         }
     }
+    if (ctx->copyStream)
+    {
+        cudaStreamSynchronize(ctx->copyStream);
+        cudaStreamDestroy(ctx->copyStream);
+    }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -594,6 +599,21 @@ void vkrt_frame_destroy(VkrtContext* c, VkrtFrame* fr)
         cudaStreamSynchronize(C(c)->stream);
     }
     Frame* f = F(fr);
+    if (c && C(c)->copyStream)
+    {
+        cudaStreamSynchronize(C(c)->copyStream);
+    }
+    if (f->presentReady)
+    {
+        cudaEventDestroy(f->presentReady);
+    }
+    for (cudaEvent_t e : f->presentDone)
+    {
+        if (e)
+        {
+            cudaEventDestroy(e);
+        }
+    }
     f->bgra8.release(), f->tileBgra8.release(), f->rgb32f.release(), f->triangleId.release(), f->shadowMask.release();
     delete f;
 }
@@ -654,6 +674,103 @@ int vkrt_frame_read(VkrtContext* c, VkrtFrame* fr, int aov, void* dst, size_t pi
     VKRT_CUDA_TRY(ctx, cudaMemcpy2DAsync(dst, pitch, src, row, row, f->height, cudaMemcpyDeviceToHost, ctx->stream));
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return VKRT_SUCCESS;
+}
+
+int vkrt_frame_present(VkrtContext* c, VkrtFrame* fr, void* dst, size_t pitch, uint64_t* ticket)
+{
+    Context* ctx = C(c);
+    Frame* f = F(fr);
+    if (!f || !dst || !ticket)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_present: NULL argument");
+    }
+    if (!f->bgra8.ptr)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_frame_present: no image");
+    }
+    const size_t row = (size_t)f->width * 4;
+    if (pitch == 0)
+    {
+        pitch = row;
+    }
+    if (pitch < row)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_present: pitch smaller than a row");
+    }
+    cudaSetDevice(ctx->device);
+    if (!ctx->copyStream)
+    {
+        VKRT_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+    }
+    if (!f->presentReady)
+    {
+        VKRT_CUDA_TRY(ctx, cudaEventCreateWithFlags(&f->presentReady, cudaEventDisableTiming));
+    }
+    const uint64_t n = f->presentNext;
+    cudaEvent_t& done = f->presentDone[n % Frame::kPresentRing];
+    if (!done)
+    {
+        VKRT_CUDA_TRY(ctx, cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    }
+    else if (n >= (uint64_t)Frame::kPresentRing && f->presentWaited + Frame::kPresentRing <= n)
+    {
+        // the event is about to be reused: the copy it stood for (ticket n - ring) has to be over
+        VKRT_CUDA_TRY(ctx, cudaEventSynchronize(done));
+        f->presentWaited = n - Frame::kPresentRing + 1;
+    }
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(f->presentReady, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copyStream, f->presentReady, 0));
+    VKRT_CUDA_TRY(ctx, cudaMemcpy2DAsync(dst, pitch, f->bgra8.ptr, row, row, f->height, cudaMemcpyDeviceToHost, ctx->copyStream));
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(done, ctx->copyStream));
+    *ticket = n;
+    f->presentNext = n + 1;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_frame_present_wait(VkrtContext* c, VkrtFrame* fr, uint64_t ticket)
+{
+    Context* ctx = C(c);
+    Frame* f = F(fr);
+    if (!f)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_present_wait: NULL argument");
+    }
+    if (ticket >= f->presentNext)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_present_wait: unknown ticket");
+    }
+    if (ticket < f->presentWaited || ticket + Frame::kPresentRing < f->presentNext)
+    {
+        return VKRT_SUCCESS; // already waited for (copies finish in order; reused events were synchronised)
+    }
+    cudaSetDevice(ctx->device);
+    VKRT_CUDA_TRY(ctx, cudaEventSynchronize(f->presentDone[ticket % Frame::kPresentRing]));
+    f->presentWaited = ticket + 1;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_host_alloc(VkrtContext* c, size_t bytes, void** out)
+{
+    Context* ctx = C(c);
+    if (!out)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_host_alloc: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    VKRT_CUDA_TRY(ctx, cudaHostAlloc(out, std::max<size_t>(bytes, 1), cudaHostAllocDefault));
+    return VKRT_SUCCESS;
+}
+
+void vkrt_host_free(VkrtContext* c, void* ptr)
+{
+    if (ptr)
+    {
+        if (c)
+        {
+            cudaSetDevice(C(c)->device);
+        }
+        cudaFreeHost(ptr);
+    }
 }
 
 void* vkrt_frame_device_bgra8(VkrtFrame* fr)

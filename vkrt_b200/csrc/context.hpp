@@ -70,6 +70,7 @@ struct Context : VkrtContext
     int device = 0;
     int smCount = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copyStream = nullptr; // vkrt_frame_present copies (created on first use)
     std::string lastError;
     uint64_t launches = 0;
 
@@ -143,7 +144,15 @@ struct Frame : VkrtFrame
     DeviceBuffer triangleId;  // width*height u32 (AOV)
     DeviceBuffer shadowMask;  // width*height u8 (AOV)
     bool gathered = false;
+    // presentation ring (vkrt_frame_present): copy n uses presentDone[n % kPresentRing]
+    static constexpr int kPresentRing = 8;
+    cudaEvent_t presentReady = nullptr;              // recorded on the context stream when a present is queued
+    cudaEvent_t presentDone[kPresentRing] = {};      // recorded on the copy stream after each copy
+    uint64_t presentNext = 0;                        // tickets handed out so far
+    uint64_t presentWaited = 0;                      // every ticket below this has been waited for on the host
 };
+// Makes the context stream wait for the outstanding presents of `frame` before its image is overwritten.
+int waitPresents(Context* ctx, Frame* frame);
 
 int buildBlasOnDevice(Context* ctx, Blas* blas);
 int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count);

@@ -793,6 +793,16 @@ void launchAnyList(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
 }
 } // namespace
 
+int waitPresents(Context* ctx, Frame* f)
+{
+    if (f->presentNext > f->presentWaited)
+    {
+        // copies run in order on one stream: the newest event covers all of them
+        VKRT_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, f->presentDone[(f->presentNext - 1) % Frame::kPresentRing], 0));
+    }
+    return VKRT_SUCCESS;
+}
+
 int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
                Frame* frame)
 {
@@ -959,6 +969,10 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         if (timed)
         {
             mark(); // 9
+        }
+        if (int r = waitPresents(ctx, frame)) // the image is about to be overwritten: outstanding vkrt_frame_present copies first
+        {
+            return r;
         }
         k_resolve_sample<<<gridShade, kShadeThreads, 0, s>>>(w, f, paths, sample, samples, spp);
         if (timed)

@@ -38,6 +38,10 @@ Context::Context(const Options& options) : m_options(options)
 
 Context::~Context()
 {
+    for (void* image : m_swapchainImages)
+    {
+        vkrt_host_free(m_device, image);
+    }
     vkrt_context_destroy(m_device);
 }
 
@@ -133,10 +137,43 @@ void Context::pushKeyEvent(int key, int action)
 
 uint32_t Context::acquireNextSwapchainImage()
 {
+    if (m_imageIndex < m_pending.size() && m_pending[m_imageIndex].frame)
+    {
+        VKRT_CHECK(m_device, vkrt_frame_present_wait(m_device, m_pending[m_imageIndex].frame, m_pending[m_imageIndex].ticket));
+        m_pending[m_imageIndex].frame = nullptr;
+    }
     return m_imageIndex;
 }
 
-void Context::submitCommandBuffers()
+void Context::submitCommandBuffers(VkrtFrame* presented)
 {
+    if (presented)
+    {
+        if (m_swapchainImages.empty())
+        {
+            m_swapchainImages.assign(c_swapchainImageCount, nullptr);
+            m_pending.assign(c_swapchainImageCount, Pending{});
+            for (void*& image : m_swapchainImages)
+            {
+                VKRT_CHECK(m_device, vkrt_host_alloc(m_device, static_cast<size_t>(m_options.width) * m_options.height * 4, &image));
+            }
+        }
+        Pending& p = m_pending[m_imageIndex];
+        VKRT_CHECK(m_device, vkrt_frame_present(m_device, presented, m_swapchainImages[m_imageIndex], 0, &p.ticket));
+        p.frame = presented;
+        m_lastPresented = m_imageIndex;
+    }
     m_imageIndex = (m_imageIndex + 1) % c_swapchainImageCount;
+}
+
+void Context::waitIdle()
+{
+    for (Pending& p : m_pending)
+    {
+        if (p.frame)
+        {
+            VKRT_CHECK(m_device, vkrt_frame_present_wait(m_device, p.frame, p.ticket));
+            p.frame = nullptr;
+        }
+    }
 }

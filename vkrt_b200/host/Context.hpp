@@ -52,8 +52,14 @@ public:
     bool update();                          // src/Context.cpp:122-127 (poll events, report whether to keep running)
     std::vector<KeyEvent> getKeyEvents();   // src/Context.cpp:129-139 (drains the queue)
     void pushKeyEvent(int key, int action);
-    uint32_t acquireNextSwapchainImage();   // src/Context.cpp:141-152: 3 frames in flight -> ring index
-    void submitCommandBuffers();            // src/Context.cpp:154-180: headless "present" = advance the ring
+    // src/Context.cpp:141-152: 3 images in flight -> ring index; waits until the image's previous present has landed
+    uint32_t acquireNextSwapchainImage();
+    // src/Context.cpp:154-180: submit + present.  Headless: the finished image of `presented` (rank 0; nullptr = nothing
+    // to show) is copied asynchronously into the acquired ring image (page-locked host memory), then the ring advances.
+    void submitCommandBuffers(VkrtFrame* presented = nullptr);
+    const std::vector<void*>& getSwapchainImages() const { return m_swapchainImages; } // BGRA8, width*height*4 each
+    uint32_t getLastPresentedImage() const { return m_lastPresented; }
+    void waitIdle(); // every queued present has landed (vkDeviceWaitIdle for the presentation ring)
     uint64_t getFrameNumber() const { return m_frame; }
 
 private:
@@ -74,5 +80,13 @@ private:
     int m_heldKey = -1;
     uint64_t m_frame = 0;
     uint32_t m_imageIndex = 0;
+    uint32_t m_lastPresented = 0;
+    std::vector<void*> m_swapchainImages;
+    struct Pending
+    {
+        VkrtFrame* frame = nullptr;
+        uint64_t ticket = 0;
+    };
+    std::vector<Pending> m_pending; // per ring image: the present that last wrote it
     bool m_shouldQuit = false;
 };

@@ -38,6 +38,7 @@ Raytracer::Raytracer(Context& context) :
 
 Raytracer::~Raytracer()
 {
+    m_context.waitIdle();
     vkrt_context_synchronize(m_device);
     vkrt_frame_destroy(m_device, m_frame);
     vkrt_tlas_destroy(m_device, m_tlas);
@@ -59,7 +60,8 @@ bool Raytracer::render()
         VKRT_CHECK(m_device, vkrt_tiles_gather(m_device, m_frame, 0));
     }
     ++m_frameIndex;
-    m_context.submitCommandBuffers();
+    // the copy to the acquired swapchain image + present: asynchronous, the next frame's traversal overlaps it
+    m_context.submitCommandBuffers(m_context.getOptions().rank == 0 ? m_frame : nullptr);
     return true;
 }
 
@@ -269,6 +271,14 @@ void Raytracer::updateMaterialIndexDescriptorSet()
 void Raytracer::readback(std::vector<uint8_t>& bgra8)
 {
     bgra8.resize(static_cast<size_t>(m_context.getWidth()) * m_context.getHeight() * 4);
+    const std::vector<void*>& images = m_context.getSwapchainImages();
+    if (!images.empty())
+    {
+        // the last frame was presented: take it from its ring image once the copy has landed
+        m_context.waitIdle();
+        memcpy(bgra8.data(), images[m_context.getLastPresentedImage()], bgra8.size());
+        return;
+    }
     VKRT_CHECK(m_device, vkrt_frame_read(m_device, m_frame, VKRT_AOV_BGRA8, bgra8.data(), 0));
 }
 

@@ -87,6 +87,15 @@ class Raytracer:
     def readback(self, aov: int = B.AOV_BGRA8, out: Optional[np.ndarray] = None) -> np.ndarray:
         return self.frame.read(aov, out)
 
+    def present(self, out: np.ndarray) -> int:
+        """Asynchronous copy of the finished image into page-locked `out`; mirrors the copy to the acquired swapchain
+        image + vkQueuePresentKHR (src/Raytracer.cpp:175-185, src/Context.cpp:154-180).  Returns a ticket."""
+        return self.frame.present(out)
+
+    def present_wait(self, ticket: int):
+        """The wait acquireNextSwapchainImage implies before a ring image is reused (src/Context.cpp:141-152)."""
+        self.frame.present_wait(ticket)
+
     def close(self):
         for o in (self.frame, self.tlas, self.blas):
             o.close()
