@@ -21,8 +21,12 @@ from vkrt_b200 import binding as B  # noqa: E402
 
 
 def _ensure(path: str, makedir: str):
-    if not os.path.exists(path):
+    # always ask make: the harnesses include the library's headers, a stale build would test yesterday's logic
+    try:
         subprocess.check_call(["make", "-C", makedir], stdout=subprocess.DEVNULL)
+    except (OSError, subprocess.CalledProcessError):
+        if not os.path.exists(path):
+            raise
     return path
 
 
