@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Run under torchrun on N GPUs: renders the Sponza stand-in split into interleaved tiles over N ranks, gathers the
-BGRA8 frame on rank 0 over NCCL (vkrt_tiles_gather) and checks it is byte-identical to a single-GPU render.
+BGRA8 frame on rank 0 over NCCL (vkrt_tiles_gather) and checks that it, and the copy that vkrt_frame_present makes while
+the next frame is being traced, are byte-identical to a single-GPU render.
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/multigpu_check.py"""
 import os
 import sys
@@ -27,16 +28,25 @@ def main():
         rt = Raytracer(model, w, h, device=local, rank=rank, world_size=world, unique_id=ids[0])
         rt.render(spp=spp)
         rt.ctx.synchronize()
+        presented = None
         if rank == 0:
             got = rt.readback(B.AOV_BGRA8)
+            # presentation ring on the root: the copy of this frame overlaps the next frame's trace + gather
+            presented = rt.ctx.host_array((h, w, 4))
+            ticket = rt.present(presented)
+        rt.render(spp=spp)
+        if rank == 0:
+            rt.present_wait(ticket)
+            presented = presented.copy()
+        rt.ctx.synchronize()
         rt.close()
         if rank == 0:
             single = Raytracer(model, w, h, device=local)
             single.render(spp=spp)
             ref = single.readback(B.AOV_BGRA8)
             single.close()
-            same = np.array_equal(got, ref)
-            print(f"multigpu_check {w}x{h} spp={spp} ranks={world}: gathered == single-GPU: {same}", flush=True)
+            same = np.array_equal(got, ref) and np.array_equal(presented, ref)
+            print(f"multigpu_check {w}x{h} spp={spp} ranks={world}: gathered == presented == single-GPU: {same}", flush=True)
             ok = ok and same
         dist.barrier()
     dist.destroy_process_group()
