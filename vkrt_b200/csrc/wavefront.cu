@@ -133,13 +133,15 @@ __global__ void __launch_bounds__(kShadeThreads)
 k_raygen(const __grid_constant__ VkrtUniforms u, TileMap map, uint32_t paths, uint32_t sampleBase, uint32_t samples, uint32_t spp,
          float4* __restrict__ rayO, float4* __restrict__ rayD, float4* __restrict__ pathAccum)
 {
-    // a wave holds `samples` consecutive samples of every owned pixel path, sample-major: index = s * paths + path
+    // a wave holds `samples` consecutive samples of every owned pixel path, pixel-major: index = path * samples + s, so a
+    // warp traces the samples of a few neighbouring pixels together (near-identical rays: they visit the same nodes and
+    // triangles in step; sample-major order left the triangle test at 13-16 of 32 lanes)
     const uint32_t total = paths * samples;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
     {
-        const uint32_t p = i % paths;
+        const uint32_t p = i / samples;
         float jx, jy;
-        sampleOffset(sampleBase + i / paths, spp, jx, jy);
+        sampleOffset(sampleBase + i % samples, spp, jx, jy);
         uint32_t x, y, tl, pit;
         if (pathToPixel(map, p, x, y, tl, pit))
         {
@@ -430,7 +432,7 @@ k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* _
 // shader.rchit:88-129 for every hit; shader.rmiss:17 for every miss.  Emits shadow rays.
 __global__ void __launch_bounds__(kShadeWarps * 32)
 k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
-                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovPaths)
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
 {
     __shared__ AppendStage stage;
     const uint32_t count = countPtr ? *countPtr : countImm;
@@ -462,10 +464,10 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 acc.x += 0.8f, acc.y += 0.8f, acc.z += 1.0f; // rmiss:17, rgen:63
                 w.pathAccum[p] = acc;
                 w.surfGeom[q] = kInvalid;
-                if (depth == 0 && p < aovPaths) // sample 0 of the frame only
+                if (depth == 0 && aovSamples && p % aovSamples == 0) // sample 0 of the frame only
                 {
                     uint32_t x, y, tl, pit;
-                    pathToPixel(f.map, p, x, y, tl, pit);
+                    pathToPixel(f.map, p / aovSamples, x, y, tl, pit);
                     f.triangleId[(size_t)y * f.map.width + x] = kInvalid;
                     f.shadowMask[(size_t)y * f.map.width + x] = 0;
                 }
@@ -490,10 +492,10 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 w.surfB[q] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.v);
                 w.surfGeom[q] = geometry;
                 w.shadowBits[q] = castMask << 4;
-                if (depth == 0 && p < aovPaths) // sample 0 of the frame only
+                if (depth == 0 && aovSamples && p % aovSamples == 0) // sample 0 of the frame only
                 {
                     uint32_t x, y, tl, pit;
-                    pathToPixel(f.map, p, x, y, tl, pit);
+                    pathToPixel(f.map, p / aovSamples, x, y, tl, pit);
                     f.triangleId[(size_t)y * f.map.width + x] =
                         (instance << 24) + (uint32_t)scene.rows[geometry].indexBufferOffset + primitive;
                 }
@@ -538,7 +540,7 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_
 // shader.rchit:144-171 and the bounce bookkeeping of shader.rgen:63-73
 __global__ void __launch_bounds__(kShadeThreads)
 k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
-                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovPaths)
+                const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
 {
     const uint32_t count = countPtr ? *countPtr : countImm;
     const uint32_t rounded = (count + 31u) & ~31u;
@@ -570,10 +572,10 @@ k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
             w.pathAccum[p] = acc;
             reflect = r.reflect && depth == 0; // rgen:65-69: maxDepth 2
             origin = sp.worldPos, dir = r.rayDir;
-            if (depth == 0 && p < aovPaths) // sample 0 of the frame only
+            if (depth == 0 && aovSamples && p % aovSamples == 0) // sample 0 of the frame only
             {
                 uint32_t x, y, tl, pit;
-                pathToPixel(f.map, p, x, y, tl, pit);
+                pathToPixel(f.map, p / aovSamples, x, y, tl, pit);
                 f.shadowMask[(size_t)y * f.map.width + x] = (uint8_t)bits;
             }
         }
@@ -599,7 +601,7 @@ k_resolve_sample(WaveDev w, FrameDev f, uint32_t paths, uint32_t sampleBase, uin
         F3 sum = f3(0.f, 0.f, 0.f);
         for (uint32_t j = 0; j < samples; ++j)
         {
-            const float4 acc = w.pathAccum[(size_t)j * paths + p];
+            const float4 acc = w.pathAccum[(size_t)p * samples + j];
             const F3 a = f3(acc.x, acc.y, acc.z);
             if (j == 0 && sampleBase == 0)
             {
@@ -915,7 +917,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     {
         const uint32_t samples = std::min(waveSamples, spp - sample);
         const uint32_t wavePaths = paths * samples;
-        const uint32_t aovPaths = (aov && sample == 0) ? paths : 0u; // AOVs describe sample 0
+        const uint32_t aovSamples = (aov && sample == 0) ? samples : 0u; // AOVs describe sample 0 = every samples-th entry
         const bool timed = ctx->timeStages && sample == 0;
         if (timed)
         {
@@ -933,7 +935,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 2
         }
-        k_shade_surface<<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovPaths);
+        k_shade_surface<<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
         if (timed)
         {
             mark(); // 3
@@ -943,7 +945,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 4
         }
-        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovPaths);
+        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
         if (timed)
         {
             mark(); // 5
