@@ -260,7 +260,10 @@ VKRT_HD bool pathToPixel(const TileMap& m, uint32_t path, uint32_t& x, uint32_t&
     const uint32_t within = path % (uint32_t)kTilePixels;
     const uint32_t block = within >> 5, lane = within & 31u;
     const uint32_t bx = block & 7u, by = block >> 3; // 8 blocks across, 16 down
-    const uint32_t px = bx * 8u + (lane & 7u), py = by * 4u + (lane >> 3);
+    // pixels of a block along a Morton curve: 4 consecutive paths are a 2x2 quad, 8 a 4x2 patch (with several samples
+    // per pixel in adjacent lanes a warp then covers a compact patch rather than a row)
+    const uint32_t lx = (lane & 1u) | ((lane >> 1) & 2u) | ((lane >> 2) & 4u), ly = ((lane >> 1) & 1u) | ((lane >> 2) & 2u);
+    const uint32_t px = bx * 8u + lx, py = by * 4u + ly;
     const uint32_t tile = m.rank + tileLocal * m.size;
     const uint32_t tx = tile % m.tilesX, ty = tile / m.tilesX;
     x = tx * (uint32_t)kTile + px;
