@@ -353,7 +353,7 @@ def main():
                     "launch_ms_avg": any_ms / 2, "samples_per_wave": wave_samples, "lane_refill": lane_refill, "stage_ms_sample0": stage,
                     "note": "achieved = algorithmic bytes (32 ray + 4 result + 80/node + 48/triangle) / kernel time; it can exceed the HBM "
                             "peak because the BVH is served from L1/L2 (see traffic = measured DRAM bytes per launch); ncu shows the kernel "
-                            "bound by instruction issue (profiles/r01_ncu_trace_kernels_v4.txt: issue slots 80 % busy, DRAM 2 %)"}
+                            "bound by instruction issue (profiles/r01_ncu_trace_kernels_v5.txt: issue slots 79 % busy, DRAM 2 %)"}
         line = {
             "metric": "Sponza 4K Mrays/s (prim+shadow+refl)", "value": total_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
