@@ -281,6 +281,30 @@ def test_frame_parity_sponza_other_pose_and_spp8(sponza_rt, sponza_flat):
     assert_contract(H.compare_frames(a, g, sel))
 
 
+def test_multi_wave_equals_single_wave(monkeypatch):
+    """spp = 8 traced as one wave of 8 samples, as waves of 3 + 3 + 2 (VKRT_WAVE_SAMPLES=3) and one sample at a time:
+    the running sample sum crosses waves in sample order, so every output plane must be bit-equal."""
+    model = scenes.analytic_scene(metallic_floor=True)
+    W, Hh = 333, 190  # ragged tiles
+    frames = {}
+    for waves in ("", "3", "1"):
+        if waves:
+            monkeypatch.setenv("VKRT_WAVE_SAMPLES", waves)
+        else:
+            monkeypatch.delenv("VKRT_WAVE_SAMPLES", raising=False)
+        rt = Raytracer(model, W, Hh, device=0)
+        rt.camera.setPosition((0.3, 1.4, 4.2)), rt.camera.setRotation((0.05, 0.2, 0.0))
+        rt.render(spp=8)
+        frames[waves] = gpu_frame(rt)
+        if waves:
+            assert rt.ctx.stats().samplesPerWave == int(waves)
+        rt.close()
+    monkeypatch.delenv("VKRT_WAVE_SAMPLES", raising=False)
+    for waves in ("3", "1"):
+        for plane in ("rgb", "bgra", "tri", "mask"):
+            assert np.array_equal(frames[""][plane], frames[waves][plane], equal_nan=(plane == "rgb")), (waves, plane)
+
+
 def test_frame_parity_instanced_grid_config4(sponza_flat):
     """BASELINE.json config 4 at reduced resolution: 16 instances of the BLAS, two-level traversal."""
     model = scenes.sponza_standin(max_texture_size=256)

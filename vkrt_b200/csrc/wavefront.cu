@@ -880,7 +880,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
 
     const VkrtUniforms u = *uniforms;
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
-    const uint32_t gridTrace = persistentGrid(ctx, 8);
+    const uint32_t gridTrace = persistentGrid(ctx, VKRT_TRACE_MIN_BLOCKS); // exactly the resident blocks: a persistent kernel gains nothing from more
     const uint32_t gridShade = persistentGrid(ctx, 8);
     const uint32_t gridSurface = persistentGrid(ctx, 4); // 256-thread blocks at 64 registers: 4 per SM
     const bool st = ctx->countTraversal;
