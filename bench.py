@@ -172,6 +172,11 @@ def run_reference(args):
 
 
 def main():
+    # stdout carries exactly one JSON line: this image exports NCCL_DEBUG=VERSION, which makes NCCL printf its version banner
+    # to stdout; other NCCL_DEBUG levels (a user asking for INFO) are left alone but sent to stderr
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
