@@ -216,6 +216,30 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     return b;
 }
 
+// pathToPixel of shading.cuh for one (rank, size): x, y, pixel-in-tile per path; returns the number of valid paths
+uint32_t emu_path_to_pixel(uint32_t width, uint32_t height, uint32_t rank, uint32_t size, uint32_t paths, uint32_t* x, uint32_t* y,
+                           uint32_t* pit)
+{
+    TileMap m;
+    m.width = width, m.height = height;
+    m.tilesX = (width + kTile - 1) / kTile, m.tilesY = (height + kTile - 1) / kTile;
+    m.rank = rank, m.size = size;
+    const uint32_t tiles = m.tilesX * m.tilesY;
+    m.ownedTiles = tiles > rank ? (tiles - rank + size - 1) / size : 0u;
+    uint32_t valid = 0;
+    for (uint32_t p = 0; p < paths; ++p)
+    {
+        uint32_t tl;
+        const bool ok = pathToPixel(m, p, x[p], y[p], tl, pit[p]);
+        if (!ok)
+        {
+            x[p] = y[p] = 0xFFFFFFFFu;
+        }
+        valid += ok ? 1u : 0u;
+    }
+    return valid;
+}
+
 void emu_blas_destroy(EmuBlas* b) { delete b; }
 uint32_t emu_blas_node_count(const EmuBlas* b) { return (uint32_t)b->nodes.size(); }
 uint32_t emu_blas_triangle_count(const EmuBlas* b) { return b->triangleCount; }

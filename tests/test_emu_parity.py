@@ -35,6 +35,35 @@ def test_builder_invariants_soup_and_duplicates():
     check_bvh8(nodes, tris, 300)
 
 
+def test_path_to_pixel_partition():
+    """pathToPixel (shading.cuh): over the ranks every pixel of a ragged frame is produced exactly once, a warp of 32
+    consecutive paths is one 8x4 block and 4 consecutive paths a 2x2 quad (the layout the pixel-major waves rely on)."""
+    import ctypes as C
+
+    lib = H.emu_lib()
+    lib.emu_path_to_pixel.restype = C.c_uint32
+    lib.emu_path_to_pixel.argtypes = [C.c_uint32] * 5 + [C.c_void_p] * 3
+    W, Hh, size = 333, 190, 3
+    seen = np.zeros((Hh, W), dtype=np.int32)
+    for rank in range(size):
+        tiles = ((W + 63) // 64) * ((Hh + 63) // 64)
+        owned = len(range(rank, tiles, size))
+        n = owned * 4096
+        x, y, pit = (np.zeros(n, dtype=np.uint32) for _ in range(3))
+        valid = lib.emu_path_to_pixel(W, Hh, rank, size, n, x.ctypes.data, y.ctypes.data, pit.ctypes.data)
+        ok = x != 0xFFFFFFFF
+        assert valid == ok.sum()
+        np.add.at(seen, (y[ok], x[ok]), 1)
+        # geometry of a warp / quad, checked on the paths of the first (full) tile of rank 0
+        if rank == 0:
+            bx, by = x[:4096].reshape(128, 32), y[:4096].reshape(128, 32)
+            assert ((bx.max(1) - bx.min(1)) == 7).all() and ((by.max(1) - by.min(1)) == 3).all()
+            qx, qy = x[:4096].reshape(1024, 4), y[:4096].reshape(1024, 4)
+            assert ((qx.max(1) - qx.min(1)) == 1).all() and ((qy.max(1) - qy.min(1)) == 1).all()
+            assert np.array_equal(pit[:4096], (y[:4096] % 64) * 64 + x[:4096] % 64)
+    assert (seen == 1).all()
+
+
 def test_cost_optimal_collapse(monkeypatch):
     """The cost-optimal collapse (dpSolve / dpExpand in builder.cuh) against the greedy one on the same binary tree:
     both give valid trees and identical closest hits; the optimal one has the lower SAH cost and tests fewer triangles."""
