@@ -186,6 +186,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--triangles", type=int, default=50_000_000, help="config5 only: triangles in the procedural soup")
     ap.add_argument("--build-flags", type=int, default=-1, help="VkrtBuildFlags; default 0 (PLOC), config5 1 (LBVH: faster rebuild and, on the soup, fewer nodes per ray)")
+    ap.add_argument("--texture-lod", default="zero", choices=["zero", "cones"],
+                    help="zero: every texture() samples level 0 as the reference's ray-tracing shaders do (default, the parity mode); "
+                         "cones: ray-cone level of detail over the generated mip chain (SURVEY 8 f3)")
     ap.add_argument("--lane-refill", type=int, default=-1, help="vkrt_trace_set_lane_refill; default 0, config5 20")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -235,6 +238,7 @@ def main():
     build_ms = []
     lane_refill = args.lane_refill if args.lane_refill >= 0 else (20 if args.workload == "config5" else 0)
     rt.ctx.set_lane_refill(lane_refill)
+    rt.set_texture_lod(B.TEXTURE_LOD_RAY_CONES if args.texture_lod == "cones" else B.TEXTURE_LOD_ZERO)
     info = rt.blas.info()
     stream = torch.cuda.ExternalStream(rt.ctx.stream, device=local)
     flags = B.TRACE_NO_AOV
@@ -364,7 +368,7 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "scene": model["provenance"], "width": W, "height": Hh, "spp": spp,
-                       "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "instances": 1 if instances is None else int(np.asarray(instances).size // 12),
+                       "texture_lod": args.texture_lod, "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "instances": 1 if instances is None else int(np.asarray(instances).size // 12),
                        "parallelism": f"interleaved 64x64 tiles over {world} rank(s), scene replicated, NCCL send/recv gather to rank 0",
                        "l2": "per-frame ray/hit/shading queues (>2 GB at 4K) exceed the 126 MB L2; no explicit flush"},
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},

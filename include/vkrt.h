@@ -163,6 +163,27 @@ typedef struct VkrtImage
 /* Replaces createTextures + createSampler + updateTexturesDescriptorSets (src/Raytracer.cpp:436-570, :1444-1467):
  * bindless array of RGBA8 images sampled LINEAR / REPEAT at LOD 0 (shaders/shader.rchit:76,107,157,162). */
 VKRT_API int vkrt_textures_set(VkrtContext* ctx, const VkrtImage* images, uint32_t count);
+/* Replaces Raytracer::createMipmaps (src/Raytracer.cpp:572-640): the full mip chain of every image,
+ * floor(log2(max(w,h))) + 1 levels (:467-468), level k = max(w>>k,1) x max(h>>k,1), each level a
+ * vkCmdBlitImage(VK_FILTER_LINEAR) of the previous one (:610-625).  Built on the device; complete on return.
+ * vkrt_textures_set discards the chain. */
+VKRT_API int vkrt_textures_generate_mips(VkrtContext* ctx);
+/* Extent of `level` of image `image` and its level count (1 until the chain has been generated). */
+VKRT_API int vkrt_texture_info(VkrtContext* ctx, uint32_t image, uint32_t level, uint32_t* width, uint32_t* height,
+                               uint32_t* levels);
+/* Copies one level (tightly packed RGBA8 rows) to host memory; for the parity tests of the chain. */
+VKRT_API int vkrt_texture_read(VkrtContext* ctx, uint32_t image, uint32_t level, void* dst, size_t bytes);
+
+typedef enum VkrtTextureLod
+{
+    VKRT_TEXTURE_LOD_ZERO = 0,     /* every texture() samples level 0: what the reference's ray-tracing shaders get
+                                      (no derivatives in rchit; sampler src/Raytracer.cpp:436-458) - default, parity mode */
+    VKRT_TEXTURE_LOD_RAY_CONES = 1 /* trilinear at the ray-cone level of detail (Ray Tracing Gems ch. 20): cone width =
+                                      pixel spread angle x distance travelled, per-triangle texel density, |n.d| term */
+} VkrtTextureLod;
+/* Texture level-of-detail mode of the shading kernels (no counterpart in the reference: its mip chain is built but
+ * never sampled on the ray-tracing path).  RAY_CONES needs vkrt_textures_generate_mips first. */
+VKRT_API int vkrt_trace_set_texture_lod(VkrtContext* ctx, int mode);
 
 /* ------------------------------------------------------------------------------------------------
  * Frames and tracing

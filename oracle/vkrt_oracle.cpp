@@ -144,6 +144,13 @@ struct Image
     std::vector<uint8_t> px;
 };
 
+/* One generated mip level (levels 1.. of an Image; level 0 is the Image itself). */
+struct MipLevel
+{
+    uint32_t w, h;
+    std::vector<uint8_t> px;
+};
+
 struct Instance
 {
     float o2w[12];
@@ -251,6 +258,8 @@ struct OrcScene
     std::vector<OrcGeometryRange> ranges;
     std::vector<OrcSubmeshInfo> rows;
     std::vector<Image> images;
+    std::vector<std::vector<MipLevel>> mips; /* per image: levels 1.. (orc_scene_generate_mips) */
+    int lodMode = 0;                         /* 0 = LOD 0 (the reference's ray-tracing path), 1 = ray cones */
     std::vector<Instance> instances;
     std::vector<Tri> tris;       /* in (geometry, primitive) order */
     std::vector<uint32_t> order; /* BVH leaf order -> index into tris */
@@ -266,6 +275,8 @@ struct OrcScene
                      Counters& c) const;
     Hit trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, Counters& c) const;
     void sample(uint32_t index, float u, float v, float rgba[4]) const;
+    void sampleLod(uint32_t index, float u, float v, float footprint2, float rgba[4]) const;
+    void generateMips();
 };
 
 void OrcScene::buildTriangles()
@@ -612,12 +623,11 @@ Hit OrcScene::trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, C
     return hit;
 }
 
-/* Bilinear, REPEAT, LOD 0, texel = u8/255 (UNORM). Vulkan texel addressing: u*W - 0.5. */
-void OrcScene::sample(uint32_t index, float u, float v, float rgba[4]) const
+/* Bilinear, REPEAT, texel = u8/255 (UNORM). Vulkan texel addressing: u*W - 0.5. */
+static void bilinearRepeat(const uint8_t* px, uint32_t iw, uint32_t ih, float u, float v, float rgba[4])
 {
-    const Image& img = images[index];
-    float x = u * (float)img.w - 0.5f;
-    float y = v * (float)img.h - 0.5f;
+    float x = u * (float)iw - 0.5f;
+    float y = v * (float)ih - 0.5f;
     if (!std::isfinite(x))
     {
         x = -0.5f;
@@ -638,18 +648,139 @@ void OrcScene::sample(uint32_t index, float u, float v, float rgba[4]) const
         uint32_t i = (uint32_t)m;
         return i >= n ? 0u : i;
     };
-    const uint32_t x0 = wrap(fx, img.w), y0 = wrap(fy, img.h);
-    const uint32_t x1 = (x0 + 1 == img.w) ? 0u : x0 + 1, y1 = (y0 + 1 == img.h) ? 0u : y0 + 1;
+    const uint32_t x0 = wrap(fx, iw), y0 = wrap(fy, ih);
+    const uint32_t x1 = (x0 + 1 == iw) ? 0u : x0 + 1, y1 = (y0 + 1 == ih) ? 0u : y0 + 1;
     const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
-    const uint8_t* p00 = &img.px[((size_t)y0 * img.w + x0) * 4];
-    const uint8_t* p10 = &img.px[((size_t)y0 * img.w + x1) * 4];
-    const uint8_t* p01 = &img.px[((size_t)y1 * img.w + x0) * 4];
-    const uint8_t* p11 = &img.px[((size_t)y1 * img.w + x1) * 4];
+    const uint8_t* p00 = &px[((size_t)y0 * iw + x0) * 4];
+    const uint8_t* p10 = &px[((size_t)y0 * iw + x1) * 4];
+    const uint8_t* p01 = &px[((size_t)y1 * iw + x0) * 4];
+    const uint8_t* p11 = &px[((size_t)y1 * iw + x1) * 4];
     for (int ch = 0; ch < 4; ++ch)
     {
         const float t00 = (float)p00[ch] / 255.0f, t10 = (float)p10[ch] / 255.0f;
         const float t01 = (float)p01[ch] / 255.0f, t11 = (float)p11[ch] / 255.0f;
         rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+    }
+}
+
+/* texture() at LOD 0: what rchit:107,157,162 get on the ray-tracing path (no derivatives). */
+void OrcScene::sample(uint32_t index, float u, float v, float rgba[4]) const
+{
+    const Image& img = images[index];
+    bilinearRepeat(img.px.data(), img.w, img.h, u, v, rgba);
+}
+
+/*
+ * Mip chain of Raytracer::createMipmaps (src/Raytracer.cpp:572-640): floor(log2(max(w,h)))+1 levels (:467-468), level k
+ * = vkCmdBlitImage(level k-1 -> k, VK_FILTER_LINEAR) with extents max(w/2,1) x max(h/2,1) (:612,629-630).
+ * Blit addressing (Vulkan spec, "Image Copies with Scaling"): source coordinate of destination texel centre i is
+ * (i + 0.5) * srcExtent/dstExtent; linear filter = bilinear around coordinate - 0.5, clamp to edge; UNORM8 store rounds
+ * to nearest.
+ */
+void OrcScene::generateMips()
+{
+    mips.assign(images.size(), {});
+    for (size_t n = 0; n < images.size(); ++n)
+    {
+        const Image& img = images[n];
+        const uint32_t levelCount = (uint32_t)std::floor(std::log2((double)std::max(img.w, img.h))) + 1u;
+        const uint8_t* src = img.px.data();
+        uint32_t sw = img.w, sh = img.h;
+        for (uint32_t level = 1; level < levelCount; ++level)
+        {
+            MipLevel out;
+            out.w = sw > 1 ? sw / 2 : 1, out.h = sh > 1 ? sh / 2 : 1;
+            out.px.resize((size_t)out.w * out.h * 4);
+            const float scaleX = (float)sw / (float)out.w, scaleY = (float)sh / (float)out.h;
+            for (uint32_t j = 0; j < out.h; ++j)
+            {
+                for (uint32_t i = 0; i < out.w; ++i)
+                {
+                    const float cx = ((float)i + 0.5f) * scaleX - 0.5f, cy = ((float)j + 0.5f) * scaleY - 0.5f;
+                    const float fx = std::floor(cx), fy = std::floor(cy);
+                    const float a = cx - fx, b = cy - fy;
+                    auto edge = [](long c, uint32_t n) -> uint32_t { return (uint32_t)std::min<long>(std::max<long>(c, 0), (long)n - 1); };
+                    const uint32_t x0 = edge((long)fx, sw), x1 = edge((long)fx + 1, sw);
+                    const uint32_t y0 = edge((long)fy, sh), y1 = edge((long)fy + 1, sh);
+                    const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+                    for (int ch = 0; ch < 4; ++ch)
+                    {
+                        const float t00 = (float)src[((size_t)y0 * sw + x0) * 4 + ch] / 255.0f;
+                        const float t10 = (float)src[((size_t)y0 * sw + x1) * 4 + ch] / 255.0f;
+                        const float t01 = (float)src[((size_t)y1 * sw + x0) * 4 + ch] / 255.0f;
+                        const float t11 = (float)src[((size_t)y1 * sw + x1) * 4 + ch] / 255.0f;
+                        const float c = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+                        out.px[((size_t)j * out.w + i) * 4 + ch] = (uint8_t)(clamp01(c) * 255.0f + 0.5f);
+                    }
+                }
+            }
+            mips[n].push_back(std::move(out));
+            const MipLevel& made = mips[n].back();
+            src = made.px.data(), sw = made.w, sh = made.h;
+        }
+    }
+}
+
+/*
+ * log2 for the level-of-detail computation: exponent + cubic-corrected mantissa term, + and * only in a fixed order
+ * (|error| < 1.5e-4).  Part of the numerical contract of the ray-cone mode: libm's log2f and the
+ * GPU's differ in the last bits, this does not.
+ */
+static float lodLog2(float x)
+{
+    uint32_t bits;
+    std::memcpy(&bits, &x, 4);
+    const float e = (float)((int)(bits >> 23) - 127);
+    const uint32_t mantissaBits = (bits & 0x007FFFFFu) | 0x3F800000u;
+    float m;
+    std::memcpy(&m, &mantissaBits, 4);
+    const float f = m - 1.0f;
+    const float poly = 0.4380733f + f * (-0.2366934f + f * 0.0803073f);
+    return e + (f + (f * (1.0f - f)) * poly);
+}
+
+/*
+ * Trilinear sample at the ray-cone level of detail (Akenine-Moller et al., Ray Tracing Gems 2019, ch. 20):
+ * lambda = 0.5 * log2(footprint2 * W * H), clamped to the chain; footprints of at most one texel (and NaN) take level 0.
+ */
+void OrcScene::sampleLod(uint32_t index, float u, float v, float footprint2, float rgba[4]) const
+{
+    const Image& img = images[index];
+    const std::vector<MipLevel>& chain = mips[index];
+    const float texels2 = (footprint2 * (float)img.w) * (float)img.h;
+    if (!(texels2 > 1.0f) || !std::isfinite(texels2) || chain.empty())
+    {
+        bilinearRepeat(img.px.data(), img.w, img.h, u, v, rgba);
+        return;
+    }
+    float lambda = 0.5f * lodLog2(texels2);
+    const float top = (float)chain.size(); /* index of the last level */
+    if (lambda > top)
+    {
+        lambda = top;
+    }
+    const float fl = std::floor(lambda);
+    const float frac = lambda - fl;
+    const uint32_t l0 = (uint32_t)fl;
+    auto level = [&](uint32_t l, float out[4]) {
+        if (l == 0)
+        {
+            bilinearRepeat(img.px.data(), img.w, img.h, u, v, out);
+        }
+        else
+        {
+            bilinearRepeat(chain[l - 1].px.data(), chain[l - 1].w, chain[l - 1].h, u, v, out);
+        }
+    };
+    level(l0, rgba);
+    if (frac > 0.0f)
+    {
+        float hi[4];
+        level(l0 + 1, hi);
+        for (int ch = 0; ch < 4; ++ch)
+        {
+            rgba[ch] = rgba[ch] * (1.0f - frac) + hi[ch] * frac;
+        }
     }
 }
 
@@ -680,7 +811,7 @@ struct Payload
 
 /* shader.rchit main(), lines 86-172. Returns the 8-bit shadow mask of this hit. */
 uint8_t closestHit(const OrcScene& s, const OrcUniforms& u, const Hit& hit, V3 worldRayDir, Payload& payload, int mode,
-                   Counters& c)
+                   Counters& c, float coneWidth)
 {
     const OrcSubmeshInfo& mat = s.rows[hit.geometry];
     const uint64_t tri = (uint64_t)(uint32_t)mat.indexBufferOffset + hit.primitive; /* rchit:88-89 */
@@ -712,7 +843,33 @@ uint8_t closestHit(const OrcScene& s, const OrcUniforms& u, const Hit& hit, V3 w
     const V3 T = normalize(tangent);
     const V3 B = cross(T, N);
     float texel[4];
-    s.sample((uint32_t)mat.normalTextureIndex, uvx, uvy, texel); /* rchit:106-107 */
+    /* Ray-cone mode (not in the reference): squared uv footprint of the cone on this triangle =
+     * (uv double area / world double area) * (coneWidth / |n.d|)^2, n the geometric normal. */
+    float footprint2 = 0.0f;
+    const bool lod = s.lodMode == 1;
+    if (lod)
+    {
+        const V3 q0 = affinePoint(inst.o2w, mk(v0[0], v0[1], v0[2]));
+        const V3 q1 = affinePoint(inst.o2w, mk(v1[0], v1[1], v1[2]));
+        const V3 q2 = affinePoint(inst.o2w, mk(v2[0], v2[1], v2[2]));
+        const V3 areaVec = cross(q1 - q0, q2 - q0);
+        const float worldArea2 = length(areaVec);
+        const float uvArea2 = std::fabs((v1[8] - v0[8]) * (v2[9] - v0[9]) - (v2[8] - v0[8]) * (v1[9] - v0[9]));
+        const float ndotd = std::fabs(dot(areaVec, worldRayDir)) / (worldArea2 * length(worldRayDir));
+        const float wn = coneWidth / ndotd;
+        footprint2 = (uvArea2 / worldArea2) * (wn * wn);
+    }
+    auto fetch = [&](int32_t textureIndex, float out[4]) {
+        if (lod)
+        {
+            s.sampleLod((uint32_t)textureIndex, uvx, uvy, footprint2, out);
+        }
+        else
+        {
+            s.sample((uint32_t)textureIndex, uvx, uvy, out);
+        }
+    };
+    fetch(mat.normalTextureIndex, texel); /* rchit:106-107 */
     const V3 mapN = mk(texel[0] * 2.0f - 1.0f, texel[1] * 2.0f - 1.0f, texel[2] * 2.0f - 1.0f);
     const V3 mn = normalize(mapN);
     const V3 perturbed = normalize((T * mn.x + B * mn.y) + N * mn.z); /* rchit:108 */
@@ -744,11 +901,11 @@ uint8_t closestHit(const OrcScene& s, const OrcUniforms& u, const Hit& hit, V3 w
     }
 
     const float ambient = 0.1f;
-    s.sample((uint32_t)mat.baseColorTextureIndex, uvx, uvy, texel); /* rchit:156-157 */
+    fetch(mat.baseColorTextureIndex, texel); /* rchit:156-157 */
     const V3 baseColor = mk(texel[0], texel[1], texel[2]);
     payload.hitValue = (baseColor * totalLightAmount) * payload.attenuation + baseColor * ambient; /* rchit:158 */
 
-    s.sample((uint32_t)mat.metallicRoughnessTextureIndex, uvx, uvy, texel); /* rchit:161-162 */
+    fetch(mat.metallicRoughnessTextureIndex, texel); /* rchit:161-162 */
     const float metallic = texel[2];
     if (metallic > 0.1f) /* rchit:163-171 */
     {
@@ -852,6 +1009,38 @@ void orc_affine_inverse(const float m[12], float inv[12])
     affineInverse(m, inv);
 }
 
+void orc_scene_generate_mips(OrcScene* scene)
+{
+    scene->generateMips();
+}
+
+void orc_scene_set_texture_lod(OrcScene* scene, int mode)
+{
+    scene->lodMode = (mode == 1 && scene->mips.size() == scene->images.size()) ? 1 : 0;
+}
+
+uint32_t orc_texture_level_count(const OrcScene* scene, uint32_t index)
+{
+    return scene->mips.size() == scene->images.size() ? (uint32_t)scene->mips[index].size() + 1u : 1u;
+}
+
+const uint8_t* orc_texture_level(const OrcScene* scene, uint32_t index, uint32_t level, uint32_t* width, uint32_t* height)
+{
+    if (level == 0)
+    {
+        *width = scene->images[index].w, *height = scene->images[index].h;
+        return scene->images[index].px.data();
+    }
+    const MipLevel& m = scene->mips[index][level - 1];
+    *width = m.w, *height = m.h;
+    return m.px.data();
+}
+
+void orc_sample_texture_lod(const OrcScene* scene, uint32_t index, float u, float v, float footprint2, float rgba[4])
+{
+    scene->sampleLod(index, u, v, footprint2, rgba);
+}
+
 void orc_sample_texture(const OrcScene* scene, uint32_t index, float u, float v, float rgba[4])
 {
     scene->sample(index, u, v, rgba);
@@ -906,6 +1095,10 @@ void orc_render(OrcScene* scene, const OrcUniforms* uniforms, uint32_t width, ui
                     p.hitValue = mk(0, 0, 0), p.attenuation = 1.0f, p.depth = 0, p.done = 1; /* rgen:44-47 */
                     p.rayOrigin = mk(0, 0, 0), p.rayDir = mk(0, 0, 0);
                     const int maxDepth = 2;
+                    /* ray cones: spread angle 2 tan(fovy/2) / height, tan(fovy/2) = |projInverse[1][1]|; the cone
+                     * width at a hit is the spread angle times the distance travelled along the whole path */
+                    const float spreadAngle = (2.0f * std::fabs(u.projInverse[5])) / (float)height;
+                    float travelled = 0.0f;
                     for (;;) /* rgen:49-74 */
                     {
                         if (p.depth == 0)
@@ -920,7 +1113,8 @@ void orc_render(OrcScene* scene, const OrcUniforms* uniforms, uint32_t width, ui
                         uint8_t mask = 0;
                         if (hit.valid)
                         {
-                            mask = closestHit(s, u, hit, direction, p, mode, c);
+                            travelled = p.depth == 0 ? hit.t : travelled + hit.t;
+                            mask = closestHit(s, u, hit, direction, p, mode, c, spreadAngle * travelled);
                         }
                         else
                         {

@@ -133,6 +133,15 @@ void orc_trace_rays(OrcScene* scene, const OrcRay* rays, uint64_t count, int any
 /* Bilinear REPEAT LOD-0 sample of image `index` (rchit:107,157,162 + sampler Raytracer.cpp:436-458). */
 void orc_sample_texture(const OrcScene* scene, uint32_t index, float u, float v, float rgba[4]);
 
+/* Mip chain as Raytracer::createMipmaps builds it (src/Raytracer.cpp:572-640): level k = linear blit of level k-1. */
+void orc_scene_generate_mips(OrcScene* scene);
+/* 0 = every texture() samples level 0 (the reference's ray-tracing path, default); 1 = ray-cone level of detail
+ * (needs orc_scene_generate_mips; not in the reference: checks the product's optional VKRT_TEXTURE_LOD_RAY_CONES). */
+void orc_scene_set_texture_lod(OrcScene* scene, int mode);
+uint32_t orc_texture_level_count(const OrcScene* scene, uint32_t index);
+const uint8_t* orc_texture_level(const OrcScene* scene, uint32_t index, uint32_t level, uint32_t* width, uint32_t* height);
+void orc_sample_texture_lod(const OrcScene* scene, uint32_t index, float u, float v, float footprint2, float rgba[4]);
+
 /* Halton(2,3) sample s in [0,1)^2 used instead of +0.5 when spp > 1. */
 void orc_halton23(uint32_t s, float out[2]);
 

@@ -41,6 +41,9 @@ struct EmuScene
     std::vector<VkrtSubmeshInfo> rows;
     std::vector<std::vector<uint8_t>> texels;
     std::vector<TextureRecord> textures;
+    std::vector<std::vector<uint8_t>> mipTexels; // levels 1.. packed, as textures.cu lays them out
+    std::vector<TextureMips> mips;
+    bool lod = false;
 };
 
 extern "C" {
@@ -299,6 +302,66 @@ EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t insta
 
 void emu_scene_destroy(EmuScene* s) { delete s; }
 
+// Sequential form of generateMips (textures.cu): blitTexel per destination texel, level after level.
+void emu_scene_generate_mips(EmuScene* s)
+{
+    const size_t n = s->textures.size();
+    s->mipTexels.assign(n, {});
+    s->mips.assign(n, TextureMips{nullptr, 1u, 0u});
+    for (size_t i = 0; i < n; ++i)
+    {
+        const TextureRecord& t = s->textures[i];
+        const uint32_t levels = mipLevelCount(t.width, t.height);
+        size_t bytes = 0;
+        for (uint32_t k = 1; k < levels; ++k)
+        {
+            bytes += (size_t)mipExtent(t.width, k) * mipExtent(t.height, k) * 4;
+        }
+        s->mipTexels[i].resize(std::max<size_t>(bytes, 4));
+        const uint8_t* src = t.texels;
+        uint8_t* dst = s->mipTexels[i].data();
+        for (uint32_t k = 1; k < levels; ++k)
+        {
+            const uint32_t sw = mipExtent(t.width, k - 1), sh = mipExtent(t.height, k - 1), dw = mipExtent(t.width, k), dh = mipExtent(t.height, k);
+            for (uint32_t j = 0; j < dh; ++j)
+            {
+                for (uint32_t x = 0; x < dw; ++x)
+                {
+                    const uint32_t px = blitTexel(src, sw, sh, dw, dh, x, j);
+                    memcpy(dst + ((size_t)j * dw + x) * 4, &px, 4);
+                }
+            }
+            src = dst;
+            dst += (size_t)dw * dh * 4;
+        }
+        s->mips[i].texels = s->mipTexels[i].data();
+        s->mips[i].levels = levels;
+    }
+}
+
+void emu_scene_set_texture_lod(EmuScene* s, int mode) { s->lod = mode == 1 && s->mips.size() == s->textures.size(); }
+
+const uint8_t* emu_texture_level(const EmuScene* s, uint32_t image, uint32_t level, uint32_t* width, uint32_t* height)
+{
+    const TextureRecord& t = s->textures[image];
+    *width = mipExtent(t.width, level), *height = mipExtent(t.height, level);
+    if (level == 0)
+    {
+        return t.texels;
+    }
+    const uint8_t* p = s->mips[image].texels;
+    for (uint32_t k = 1; k < level; ++k)
+    {
+        p += (size_t)mipExtent(t.width, k) * mipExtent(t.height, k) * 4;
+    }
+    return p;
+}
+
+void emu_sample_texture_lod(const EmuScene* s, uint32_t image, float u, float v, float footprint2, float rgba[4])
+{
+    sampleTextureLod(s->textures[image], s->mips[image], u, v, footprint2, rgba);
+}
+
 void emu_trace_rays(const EmuScene* s, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits, uint64_t* nodesVisited,
                     uint64_t* trisTested)
 {
@@ -374,6 +437,7 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                 primaryRay(*u, width, height, x, y, jx, jy, o, d);
                 F3 acc = f3(0, 0, 0);
                 float attenuation = 1.0f;
+                float travelled = 0.0f; // ray cones: k_shade_surface keeps the primary hit distance in coneT
                 for (int depth = 0; depth < 2; ++depth)
                 {
                     BestHit best;
@@ -386,8 +450,21 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                         break;
                     }
                     const PackedTri& t = inst[best.instance].tris[best.tri];
-                    const SurfacePoint sp = shadeSurface(inst[best.instance], s->rows.data(), s->textures.data(), t.geometry, t.primitive,
-                                                         best.b1, best.b2);
+                    SurfacePoint sp;
+                    if (s->lod)
+                    {
+                        travelled = depth == 0 ? best.t : travelled + best.t;
+                        LodInput lod;
+                        lod.mips = s->mips.data(), lod.worldRayDir = d;
+                        lod.coneWidth = pixelSpreadAngle(*u, height) * travelled;
+                        sp = shadeSurface<true>(inst[best.instance], s->rows.data(), s->textures.data(), t.geometry, t.primitive, best.b1,
+                                                best.b2, &lod);
+                    }
+                    else
+                    {
+                        sp = shadeSurface<false>(inst[best.instance], s->rows.data(), s->textures.data(), t.geometry, t.primitive, best.b1,
+                                                 best.b2);
+                    }
                     uint32_t bits = 0, cast = 0;
                     for (int i = 0; i < 4; ++i)
                     {
@@ -409,7 +486,8 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                         aovTri = (best.instance << 24) + (uint32_t)s->rows[t.geometry].indexBufferOffset + t.primitive;
                         aovMask = (uint8_t)(bits | (cast << 4));
                     }
-                    const ResolveOut r = shadeResolve(*u, s->rows.data(), s->textures.data(), sp, bits, attenuation, d);
+                    const ResolveOut r = s->lod ? shadeResolve<true>(*u, s->rows.data(), s->textures.data(), sp, bits, attenuation, d, s->mips.data())
+                                                : shadeResolve<false>(*u, s->rows.data(), s->textures.data(), sp, bits, attenuation, d);
                     acc.x += r.hitValue.x, acc.y += r.hitValue.y, acc.z += r.hitValue.z;
                     attenuation = r.attenuation;
                     if (!r.reflect)

@@ -64,6 +64,13 @@ def oracle_lib():
         lib.orc_halton23.argtypes = [u32, vp]
         lib.orc_primary_ray.argtypes = [vp, u32, u32, u32, u32, C.c_float, C.c_float, vp]
         lib.orc_affine_inverse.argtypes = [vp, vp]
+        lib.orc_scene_generate_mips.argtypes = [vp]
+        lib.orc_scene_set_texture_lod.argtypes = [vp, i32]
+        lib.orc_texture_level_count.restype = u32
+        lib.orc_texture_level_count.argtypes = [vp, u32]
+        lib.orc_texture_level.restype = vp
+        lib.orc_texture_level.argtypes = [vp, u32, u32, C.POINTER(u32), C.POINTER(u32)]
+        lib.orc_sample_texture_lod.argtypes = [vp, u32, C.c_float, C.c_float, C.c_float, vp]
         _oracle = lib
     return _oracle
 
@@ -126,6 +133,25 @@ class OracleScene:
         self.lib.orc_sample_texture(self.h, index, np.float32(u), np.float32(v), _p(out))
         return out
 
+    def generate_mips(self):
+        self.lib.orc_scene_generate_mips(self.h)
+
+    def set_texture_lod(self, mode):
+        self.lib.orc_scene_set_texture_lod(self.h, int(mode))
+
+    def level_count(self, index):
+        return self.lib.orc_texture_level_count(self.h, index)
+
+    def texture_level(self, index, level):
+        w, h = C.c_uint32(), C.c_uint32()
+        p = self.lib.orc_texture_level(self.h, index, level, C.byref(w), C.byref(h))
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(h.value, w.value, 4)).copy()
+
+    def sample_texture_lod(self, index, u, v, footprint2):
+        out = np.zeros(4, dtype=np.float32)
+        self.lib.orc_sample_texture_lod(self.h, index, np.float32(u), np.float32(v), np.float32(footprint2), _p(out))
+        return out
+
 
 _emu = None
 
@@ -153,6 +179,11 @@ def emu_lib():
         lib.emu_scene_destroy.argtypes = [vp]
         lib.emu_trace_rays.argtypes = [vp, vp, u64, i32, vp, C.POINTER(u64), C.POINTER(u64)]
         lib.emu_render.argtypes = [vp, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32, vp, vp, vp, vp]
+        lib.emu_scene_generate_mips.argtypes = [vp]
+        lib.emu_scene_set_texture_lod.argtypes = [vp, i32]
+        lib.emu_texture_level.restype = vp
+        lib.emu_texture_level.argtypes = [vp, u32, u32, C.POINTER(u32), C.POINTER(u32)]
+        lib.emu_sample_texture_lod.argtypes = [vp, u32, C.c_float, C.c_float, C.c_float, vp]
         _emu = lib
     return _emu
 
@@ -186,6 +217,22 @@ class EmuScene:
                 self.h = None
         except Exception:
             pass
+
+    def generate_mips(self):
+        self.lib.emu_scene_generate_mips(self.h)
+
+    def set_texture_lod(self, mode):
+        self.lib.emu_scene_set_texture_lod(self.h, int(mode))
+
+    def texture_level(self, image, level):
+        w, h = C.c_uint32(), C.c_uint32()
+        p = self.lib.emu_texture_level(self.h, image, level, C.byref(w), C.byref(h))
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(h.value, w.value, 4)).copy()
+
+    def sample_texture_lod(self, image, u, v, footprint2):
+        out = np.zeros(4, dtype=np.float32)
+        self.lib.emu_sample_texture_lod(self.h, image, np.float32(u), np.float32(v), np.float32(footprint2), _p(out))
+        return out
 
     def read_blas(self):
         n, t = self.lib.emu_blas_node_count(self.blas), self.lib.emu_blas_triangle_count(self.blas)

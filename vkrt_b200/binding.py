@@ -13,6 +13,7 @@ LIB_PATH = os.environ.get("VKRT_B200_LIB") or os.path.join(os.path.dirname(os.pa
 AOV_BGRA8, AOV_RGB32F, AOV_TRIANGLE_ID, AOV_SHADOW_MASK = 0, 1, 2, 3
 BUILD_DEFAULT, BUILD_PREFER_FAST_BUILD, BUILD_INPUT_ON_DEVICE = 0, 1, 2
 TRACE_DEFAULT, TRACE_NO_AOV = 0, 1
+TEXTURE_LOD_ZERO, TEXTURE_LOD_RAY_CONES = 0, 1
 TILE = 64
 UNIQUE_ID_BYTES = 128
 
@@ -134,6 +135,10 @@ EXPORTS = [
     "vkrt_context_synchronize",
     "vkrt_context_stream",
     "vkrt_trace_set_lane_refill",
+    "vkrt_trace_set_texture_lod",
+    "vkrt_textures_generate_mips",
+    "vkrt_texture_info",
+    "vkrt_texture_read",
     "vkrt_blas_sizes",
     "vkrt_blas_build",
     "vkrt_blas_rebuild",
@@ -199,6 +204,10 @@ def load_library(path: Optional[str] = None):
         "vkrt_tlas_destroy": (None, [vp, vp]),
         "vkrt_materials_set": (i32, [vp, C.POINTER(SubmeshInfo), u32]),
         "vkrt_textures_set": (i32, [vp, C.POINTER(Image), u32]),
+        "vkrt_textures_generate_mips": (i32, [vp]),
+        "vkrt_texture_info": (i32, [vp, u32, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]),
+        "vkrt_texture_read": (i32, [vp, u32, u32, vp, sz]),
+        "vkrt_trace_set_texture_lod": (i32, [vp, i32]),
         "vkrt_frame_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
         "vkrt_frame_destroy": (None, [vp, vp]),
         "vkrt_trace": (i32, [vp, vp, C.POINTER(Uniforms), u32, u32, u32, vp]),
@@ -283,6 +292,26 @@ class Context:
             keep.append(im)
             arr[i].width, arr[i].height, arr[i].rgba8 = im.shape[1], im.shape[0], im.ctypes.data
         self.check(self.lib.vkrt_textures_set(self.handle, arr, len(images)))
+
+    def generate_mips(self):
+        """Raytracer::createMipmaps (src/Raytracer.cpp:572-640) for every image, on the device."""
+        self.check(self.lib.vkrt_textures_generate_mips(self.handle))
+
+    def texture_info(self, image: int, level: int = 0):
+        """(width, height, level count) of one level of one image."""
+        w, h, n = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self.check(self.lib.vkrt_texture_info(self.handle, image, level, C.byref(w), C.byref(h), C.byref(n)))
+        return w.value, h.value, n.value
+
+    def read_texture(self, image: int, level: int = 0) -> np.ndarray:
+        w, h, _ = self.texture_info(image, level)
+        out = np.empty((h, w, 4), dtype=np.uint8)
+        self.check(self.lib.vkrt_texture_read(self.handle, image, level, _ptr(out), out.nbytes))
+        return out
+
+    def set_texture_lod(self, mode: int):
+        """TEXTURE_LOD_ZERO (the reference's ray-tracing path, default) or TEXTURE_LOD_RAY_CONES."""
+        self.check(self.lib.vkrt_trace_set_texture_lod(self.handle, int(mode)))
 
     def host_array(self, shape, dtype=np.uint8) -> np.ndarray:
         """numpy view of page-locked host memory (vkrt_host_alloc); released with host_free(array) or with the context."""

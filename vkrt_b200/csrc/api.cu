@@ -122,6 +122,8 @@ void vkrt_context_destroy(VkrtContext* c)
     }
     ctx->materials.release();
     ctx->textureRecords.release();
+    ctx->textureMips.release();
+    ctx->mipPool.release();
     ctx->uniforms.release();
     ctx->buildScratch.release();
     ctx->wave.release();
@@ -520,6 +522,9 @@ int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
     }
     ctx->textureAllocs.clear();
     ctx->textureCount = 0;
+    ctx->textureHost.clear();
+    ctx->mipsHost.clear();
+    ctx->mipsReady = false; // a new texture set invalidates the mip chain
     // one allocation for all texels (256-byte aligned sub-ranges)
     std::vector<size_t> offsets(count);
     size_t total = 0;
@@ -544,6 +549,102 @@ int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
     VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->textureRecords.ptr, recs.data(), recs.size() * sizeof(TextureRecord), cudaMemcpyHostToDevice, ctx->stream));
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->textureCount = count;
+    ctx->textureHost = recs;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_textures_generate_mips(VkrtContext* c)
+{
+    Context* ctx = C(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (ctx->textureCount == 0)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_textures_generate_mips: vkrt_textures_set must come first");
+    }
+    cudaSetDevice(ctx->device);
+    return generateMips(ctx);
+}
+
+int vkrt_texture_info(VkrtContext* c, uint32_t image, uint32_t level, uint32_t* width, uint32_t* height, uint32_t* levels)
+{
+    Context* ctx = C(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (image >= ctx->textureCount)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_texture_info: no image " + std::to_string(image));
+    }
+    const TextureRecord& t = ctx->textureHost[image];
+    const uint32_t n = ctx->mipsReady ? ctx->mipsHost[image].levels : 1u;
+    if (level >= n)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_texture_info: image " + std::to_string(image) + " has " + std::to_string(n) + " level(s)");
+    }
+    if (width)
+    {
+        *width = std::max(t.width >> level, 1u);
+    }
+    if (height)
+    {
+        *height = std::max(t.height >> level, 1u);
+    }
+    if (levels)
+    {
+        *levels = n;
+    }
+    return VKRT_SUCCESS;
+}
+
+int vkrt_texture_read(VkrtContext* c, uint32_t image, uint32_t level, void* dst, size_t bytes)
+{
+    Context* ctx = C(c);
+    uint32_t w = 0, h = 0;
+    if (int r = vkrt_texture_info(c, image, level, &w, &h, nullptr))
+    {
+        return r;
+    }
+    const size_t need = (size_t)w * h * 4;
+    if (!dst || bytes < need)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_texture_read: destination smaller than " + std::to_string(need) + " bytes");
+    }
+    const TextureRecord& t = ctx->textureHost[image];
+    const uint8_t* src = t.texels;
+    if (level > 0)
+    {
+        src = ctx->mipsHost[image].texels;
+        for (uint32_t k = 1; k < level; ++k)
+        {
+            src += (size_t)std::max(t.width >> k, 1u) * std::max(t.height >> k, 1u) * 4;
+        }
+    }
+    cudaSetDevice(ctx->device);
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, need, cudaMemcpyDeviceToHost, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return VKRT_SUCCESS;
+}
+
+int vkrt_trace_set_texture_lod(VkrtContext* c, int mode)
+{
+    Context* ctx = C(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (mode != VKRT_TEXTURE_LOD_ZERO && mode != VKRT_TEXTURE_LOD_RAY_CONES)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_set_texture_lod: unknown mode " + std::to_string(mode));
+    }
+    if (mode == VKRT_TEXTURE_LOD_RAY_CONES && !ctx->mipsReady)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_trace_set_texture_lod: vkrt_textures_generate_mips must come first");
+    }
+    ctx->textureLod = mode;
     return VKRT_SUCCESS;
 }
 

@@ -70,6 +70,15 @@ struct TextureRecord
     uint32_t width, height;
 };
 
+// Mip levels 1.. of a texture (vkrt_textures_generate_mips), tightly packed one after the other; a parallel array to
+// TextureRecord so that the LOD-0 path reads exactly what it read before mips existed.
+struct TextureMips
+{
+    const uint8_t* texels; // level 1 starts here
+    uint32_t levels;       // floor(log2(max(w,h))) + 1, level 0 included
+    uint32_t pad;
+};
+
 // Hit record written by the closest-hit traversal.
 struct HitRecord
 {

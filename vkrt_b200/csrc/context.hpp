@@ -52,10 +52,11 @@ struct WaveBuffers
     DeviceBuffer pathAccum;          // float4[P] finalHitValue of the current sample (xyz) + attenuation (w)
     DeviceBuffer sampleSum;          // float4[P] sum over samples
     DeviceBuffer counters;           // u32[16]: [0..3] shadow queue sizes, [4] reflection queue size, [8..] stats
+    DeviceBuffer coneT, surfFoot;    // float[P] each, reserved only in the ray-cone texture LOD mode
     void release()
     {
         DeviceBuffer* all[] = {&rayO, &rayD, &reflO, &reflD, &reflPath, &hitA, &hitInst, &surfA, &surfB, &surfGeom, &shadowBits,
-                               &shadowO, &shadowD, &pathAccum, &sampleSum, &counters};
+                               &shadowO, &shadowD, &pathAccum, &sampleSum, &counters, &coneT, &surfFoot};
         for (DeviceBuffer* b : all)
         {
             b->release();
@@ -80,6 +81,12 @@ struct Context : VkrtContext
     DeviceBuffer textureRecords; // TextureRecord[]
     std::vector<void*> textureAllocs;
     uint32_t textureCount = 0;
+    std::vector<TextureRecord> textureHost; // host copy of the records (device pointers), for vkrt_texture_info / _read
+    DeviceBuffer textureMips;               // TextureMips[], parallel to textureRecords (vkrt_textures_generate_mips)
+    std::vector<TextureMips> mipsHost;
+    DeviceBuffer mipPool;                   // levels 1.. of every image
+    bool mipsReady = false;
+    int textureLod = VKRT_TEXTURE_LOD_ZERO; // vkrt_trace_set_texture_lod
     DeviceBuffer uniforms; // VkrtUniforms
 
     BuildScratch buildScratch;
@@ -159,6 +166,7 @@ int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t coun
 int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
                Frame* frame);
 int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits);
+int generateMips(Context* ctx); // textures.cu
 int gatherTiles(Context* ctx, Frame* frame, int root);
 int commInit(Context* ctx, const uint8_t* id, int rank, int size);
 int commDestroy(Context* ctx);

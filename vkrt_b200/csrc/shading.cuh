@@ -20,6 +20,15 @@ struct SurfacePoint
     F3 normal; // perturbedNormal (may be NaN when the tangent is zero, see SURVEY §7 "NaN path")
     float u, v;
     uint32_t geometry;
+    float footprint2; // ray-cone mode only: squared uv-space footprint of the ray's cone (coneFootprint2)
+};
+
+// Ray-cone level-of-detail inputs of one hit (VKRT_TEXTURE_LOD_RAY_CONES); unused in the default LOD-0 mode.
+struct LodInput
+{
+    const TextureMips* mips; // parallel to the texture array
+    F3 worldRayDir;
+    float coneWidth; // spread angle times the distance travelled along the path
 };
 
 // Halton radical inverse, digits accumulated in FP32 exactly as the oracle does.
@@ -63,6 +72,13 @@ VKRT_HD void primaryRay(const VkrtUniforms& u, uint32_t width, uint32_t height, 
     origin = mat4MulVec(u.viewInverse, 0.0f, 0.0f, 0.0f, 1.0f);
 }
 
+// Pixel spread angle of the primary rays for the ray cones: 2 tan(fovy/2) / height (small-angle form of RTG ch. 20
+// eq. 30); tan(fovy/2) is |projInverse[1][1]|.
+VKRT_HD float pixelSpreadAngle(const VkrtUniforms& u, uint32_t height)
+{
+    return (2.0f * fabsf(u.projInverse[5])) / (float)height;
+}
+
 VKRT_HD uint32_t wrapRepeat(float f, uint32_t n) // f integral; REPEAT addressing
 {
     float m = fmodf(f, (float)n);
@@ -85,11 +101,12 @@ VKRT_HD uint32_t loadTexel(const uint8_t* texels, size_t index)
 #endif
 }
 
-// texture(sampler2D, uv) at LOD 0: LINEAR, REPEAT, RGBA8 UNORM (src/Raytracer.cpp:436-458,467).
-VKRT_HD void sampleTexture(const TextureRecord& tex, float u, float v, float rgba[4])
+// Bilinear REPEAT sample of one RGBA8 image level (LINEAR mag/min, src/Raytracer.cpp:436-458,467); Vulkan texel
+// addressing u*W - 0.5.
+VKRT_HD void sampleLevel(const uint8_t* texels, uint32_t width, uint32_t height, float u, float v, float rgba[4])
 {
-    float x = u * (float)tex.width - 0.5f;
-    float y = v * (float)tex.height - 0.5f;
+    float x = u * (float)width - 0.5f;
+    float y = v * (float)height - 0.5f;
     if (!finite1(x))
     {
         x = -0.5f;
@@ -100,18 +117,141 @@ VKRT_HD void sampleTexture(const TextureRecord& tex, float u, float v, float rgb
     }
     const float fx = floorf(x), fy = floorf(y);
     const float a = x - fx, b = y - fy;
-    const uint32_t x0 = wrapRepeat(fx, tex.width), y0 = wrapRepeat(fy, tex.height);
-    const uint32_t x1 = (x0 + 1 == tex.width) ? 0u : x0 + 1, y1 = (y0 + 1 == tex.height) ? 0u : y0 + 1;
+    const uint32_t x0 = wrapRepeat(fx, width), y0 = wrapRepeat(fy, height);
+    const uint32_t x1 = (x0 + 1 == width) ? 0u : x0 + 1, y1 = (y0 + 1 == height) ? 0u : y0 + 1;
     const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
-    const uint32_t p00 = loadTexel(tex.texels, (size_t)y0 * tex.width + x0);
-    const uint32_t p10 = loadTexel(tex.texels, (size_t)y0 * tex.width + x1);
-    const uint32_t p01 = loadTexel(tex.texels, (size_t)y1 * tex.width + x0);
-    const uint32_t p11 = loadTexel(tex.texels, (size_t)y1 * tex.width + x1);
+    const uint32_t p00 = loadTexel(texels, (size_t)y0 * width + x0);
+    const uint32_t p10 = loadTexel(texels, (size_t)y0 * width + x1);
+    const uint32_t p01 = loadTexel(texels, (size_t)y1 * width + x0);
+    const uint32_t p11 = loadTexel(texels, (size_t)y1 * width + x1);
     for (int ch = 0; ch < 4; ++ch)
     {
         const float t00 = (float)((p00 >> (8 * ch)) & 0xFFu) / 255.0f, t10 = (float)((p10 >> (8 * ch)) & 0xFFu) / 255.0f;
         const float t01 = (float)((p01 >> (8 * ch)) & 0xFFu) / 255.0f, t11 = (float)((p11 >> (8 * ch)) & 0xFFu) / 255.0f;
         rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+    }
+}
+
+// texture(sampler2D, uv) at LOD 0 (what the reference's ray-tracing shaders get: no derivatives).
+VKRT_HD void sampleTexture(const TextureRecord& tex, float u, float v, float rgba[4])
+{
+    sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba);
+}
+
+// ---- Mip chain and ray-cone level of detail (off by default, the parity frames sample LOD 0) ----------
+// Level k of a WxH image is max(W>>k,1) x max(H>>k,1) (src/Raytracer.cpp:467-468,612,629-630); levels 1.. follow each
+// other tightly packed in TextureMips::texels.
+VKRT_HD uint32_t mipExtent(uint32_t extent, uint32_t level)
+{
+    const uint32_t e = extent >> level;
+    return e ? e : 1u;
+}
+
+VKRT_HD uint32_t mipLevelCount(uint32_t width, uint32_t height) // floor(log2(max(w,h))) + 1, src/Raytracer.cpp:467
+{
+    uint32_t m = width > height ? width : height, levels = 0;
+    while (m)
+    {
+        ++levels;
+        m >>= 1;
+    }
+    return levels ? levels : 1u;
+}
+
+// One destination texel of vkCmdBlitImage(level-1 -> level, VK_FILTER_LINEAR) (src/Raytracer.cpp:610-625): the source
+// coordinate of destination texel centre i is (i + 0.5) * srcExtent / dstExtent, filtered bilinearly with
+// clamp-to-edge; for an even source extent that is the mean of a 2x2 block.  UNORM8 store as packBgra8 rounds.
+VKRT_HD uint32_t blitTexel(const uint8_t* src, uint32_t srcW, uint32_t srcH, uint32_t dstW, uint32_t dstH, uint32_t i, uint32_t j)
+{
+    const float sx = ((float)i + 0.5f) * ((float)srcW / (float)dstW) - 0.5f;
+    const float sy = ((float)j + 0.5f) * ((float)srcH / (float)dstH) - 0.5f;
+    const float fx = floorf(sx), fy = floorf(sy);
+    const float a = sx - fx, b = sy - fy;
+    const int ix = (int)fx, iy = (int)fy;
+    const uint32_t x0 = (uint32_t)(ix < 0 ? 0 : (ix >= (int)srcW ? (int)srcW - 1 : ix));
+    const uint32_t y0 = (uint32_t)(iy < 0 ? 0 : (iy >= (int)srcH ? (int)srcH - 1 : iy));
+    const uint32_t x1 = (ix + 1 >= (int)srcW) ? srcW - 1 : (uint32_t)(ix + 1 < 0 ? 0 : ix + 1);
+    const uint32_t y1 = (iy + 1 >= (int)srcH) ? srcH - 1 : (uint32_t)(iy + 1 < 0 ? 0 : iy + 1);
+    const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+    const uint32_t p00 = loadTexel(src, (size_t)y0 * srcW + x0), p10 = loadTexel(src, (size_t)y0 * srcW + x1);
+    const uint32_t p01 = loadTexel(src, (size_t)y1 * srcW + x0), p11 = loadTexel(src, (size_t)y1 * srcW + x1);
+    uint32_t out = 0;
+    for (int ch = 0; ch < 4; ++ch)
+    {
+        const float t00 = (float)((p00 >> (8 * ch)) & 0xFFu) / 255.0f, t10 = (float)((p10 >> (8 * ch)) & 0xFFu) / 255.0f;
+        const float t01 = (float)((p01 >> (8 * ch)) & 0xFFu) / 255.0f, t11 = (float)((p11 >> (8 * ch)) & 0xFFu) / 255.0f;
+        const float c = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+        out |= (uint32_t)(clamp01(c) * 255.0f + 0.5f) << (8 * ch);
+    }
+    return out;
+}
+
+// log2 of a finite x > 0 from its exponent and a cubic-corrected mantissa term (|error| < 1.5e-4): only + and *, fixed
+// order, so the CPU oracle and the device agree bit for bit (libm's log2f and CUDA's do not).
+VKRT_HD float lodLog2(float x)
+{
+    uint32_t bits;
+    memcpy(&bits, &x, 4);
+    const float e = (float)((int)(bits >> 23) - 127);
+    const uint32_t mb = (bits & 0x007FFFFFu) | 0x3F800000u;
+    float m;
+    memcpy(&m, &mb, 4);
+    const float f = m - 1.0f;
+    const float poly = 0.4380733f + f * (-0.2366934f + f * 0.0803073f);
+    return e + (f + (f * (1.0f - f)) * poly);
+}
+
+// Ray-cone footprint (Akenine-Moller et al., "Texture Level of Detail Strategies for Real-Time Ray Tracing", Ray Tracing
+// Gems 2019, ch. 20): squared uv-space footprint of a cone of width `coneWidth` on a triangle =
+// (uv double area / world double area) * (coneWidth / |n.d|)^2.  A texture of WxH texels then takes
+// lambda = 0.5 * log2(footprint2 * W * H).
+VKRT_HD float coneFootprint2(F3 p0, F3 p1, F3 p2, float u0, float v0, float u1, float v1, float u2, float v2, F3 rayDir, float coneWidth)
+{
+    const F3 c = cross3(p1 - p0, p2 - p0);
+    const float worldArea2 = length3(c);
+    const float uvArea2 = fabsf((u1 - u0) * (v2 - v0) - (u2 - u0) * (v1 - v0));
+    const float ndotd = fabsf(dot3(c, rayDir)) / (worldArea2 * length3(rayDir));
+    const float wn = coneWidth / ndotd;
+    return (uvArea2 / worldArea2) * (wn * wn);
+}
+
+// Trilinear sample at the ray-cone level of detail; footprint2 that is not > 1 texel (magnification, degenerate
+// triangles or uv, NaN) samples level 0 exactly as sampleTexture does.
+VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips, float u, float v, float footprint2, float rgba[4])
+{
+    const float texels2 = (footprint2 * (float)tex.width) * (float)tex.height;
+    if (!(texels2 > 1.0f) || !finite1(texels2) || mips.levels <= 1u)
+    {
+        sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba);
+        return;
+    }
+    float lambda = 0.5f * lodLog2(texels2);
+    const float top = (float)(mips.levels - 1u);
+    if (lambda > top)
+    {
+        lambda = top;
+    }
+    const float fl = floorf(lambda);
+    const float frac = lambda - fl;
+    const uint32_t l0 = (uint32_t)fl;
+    // byte offset of level l0 inside mips.texels (levels 1.. packed)
+    size_t offset = 0;
+    for (uint32_t k = 1; k < l0; ++k)
+    {
+        offset += (size_t)mipExtent(tex.width, k) * mipExtent(tex.height, k) * 4;
+    }
+    const uint8_t* base0 = l0 == 0 ? tex.texels : mips.texels + offset;
+    const uint32_t w0 = mipExtent(tex.width, l0), h0 = mipExtent(tex.height, l0);
+    sampleLevel(base0, w0, h0, u, v, rgba);
+    if (frac > 0.0f) // l0 < levels - 1 here, because lambda <= levels - 1
+    {
+        const uint8_t* base1 = l0 == 0 ? mips.texels : base0 + (size_t)w0 * h0 * 4;
+        float hi[4];
+        sampleLevel(base1, mipExtent(tex.width, l0 + 1), mipExtent(tex.height, l0 + 1), u, v, hi);
+        for (int ch = 0; ch < 4; ++ch)
+        {
+            rgba[ch] = rgba[ch] * (1.0f - frac) + hi[ch] * frac;
+        }
     }
 }
 
@@ -126,12 +266,14 @@ VKRT_HD float4 loadF4(const uint8_t* base, size_t byteOffset)
 #endif
 }
 
-// shader.rchit:88-108
+// shader.rchit:88-108.  LOD = false is the reference's behaviour (every texture() call samples level 0).
+template<bool LOD = false>
 VKRT_HD SurfacePoint shadeSurface(const InstanceRecord& inst, const VkrtSubmeshInfo* rows, const TextureRecord* textures,
-                                  uint32_t geometry, uint32_t primitive, float b1, float b2)
+                                  uint32_t geometry, uint32_t primitive, float b1, float b2, const LodInput* lod = nullptr)
 {
     SurfacePoint sp;
     sp.geometry = geometry;
+    sp.footprint2 = 0.0f;
     const VkrtSubmeshInfo row = rows[geometry];
     const uint64_t tri = (uint64_t)(uint32_t)row.indexBufferOffset + primitive; // rchit:88-89
     const uint32_t i0 = inst.indices[3 * tri + 0], i1 = inst.indices[3 * tri + 1], i2 = inst.indices[3 * tri + 2];
@@ -162,7 +304,18 @@ VKRT_HD SurfacePoint shadeSurface(const InstanceRecord& inst, const VkrtSubmeshI
     const F3 T = normalize3(tangent);
     const F3 B = cross3(T, N);
     float texel[4];
-    sampleTexture(textures[(uint32_t)row.normalTextureIndex], sp.u, sp.v, texel); // rchit:106-107
+    if (LOD)
+    {
+        sp.footprint2 = coneFootprint2(affinePoint(inst.o2w, f3(p0.x, p0.y, p0.z)), affinePoint(inst.o2w, f3(p1.x, p1.y, p1.z)),
+                                       affinePoint(inst.o2w, f3(p2.x, p2.y, p2.z)), uv0.x, uv0.y, uv1.x, uv1.y, uv2.x, uv2.y,
+                                       lod->worldRayDir, lod->coneWidth);
+        const uint32_t ti = (uint32_t)row.normalTextureIndex;
+        sampleTextureLod(textures[ti], lod->mips[ti], sp.u, sp.v, sp.footprint2, texel);
+    }
+    else
+    {
+        sampleTexture(textures[(uint32_t)row.normalTextureIndex], sp.u, sp.v, texel); // rchit:106-107
+    }
     const F3 mapN = f3(texel[0] * 2.0f - 1.0f, texel[1] * 2.0f - 1.0f, texel[2] * 2.0f - 1.0f);
     const F3 mn = normalize3(mapN);
     sp.normal = normalize3((T * mn.x + B * mn.y) + N * mn.z); // rchit:108
@@ -201,8 +354,10 @@ struct ResolveOut
 };
 
 // shader.rchit:130-171. shadowBits: bit i set = light i occluded.
+template<bool LOD = false>
 VKRT_HD ResolveOut shadeResolve(const VkrtUniforms& u, const VkrtSubmeshInfo* rows, const TextureRecord* textures,
-                                const SurfacePoint& sp, uint32_t shadowBits, float attenuation, F3 worldRayDir)
+                                const SurfacePoint& sp, uint32_t shadowBits, float attenuation, F3 worldRayDir,
+                                const TextureMips* mips = nullptr)
 {
     ResolveOut out;
     float totalLightAmount = 0.0f;
@@ -215,10 +370,26 @@ VKRT_HD ResolveOut shadeResolve(const VkrtUniforms& u, const VkrtSubmeshInfo* ro
     const VkrtSubmeshInfo row = rows[sp.geometry];
     const float ambient = 0.1f;
     float texel[4];
-    sampleTexture(textures[(uint32_t)row.baseColorTextureIndex], sp.u, sp.v, texel); // rchit:156-157
+    if (LOD)
+    {
+        const uint32_t ti = (uint32_t)row.baseColorTextureIndex;
+        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel);
+    }
+    else
+    {
+        sampleTexture(textures[(uint32_t)row.baseColorTextureIndex], sp.u, sp.v, texel); // rchit:156-157
+    }
     const F3 baseColor = f3(texel[0], texel[1], texel[2]);
     out.hitValue = (baseColor * totalLightAmount) * attenuation + baseColor * ambient; // rchit:158
-    sampleTexture(textures[(uint32_t)row.metallicRoughnessTextureIndex], sp.u, sp.v, texel); // rchit:161-162
+    if (LOD)
+    {
+        const uint32_t ti = (uint32_t)row.metallicRoughnessTextureIndex;
+        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel);
+    }
+    else
+    {
+        sampleTexture(textures[(uint32_t)row.metallicRoughnessTextureIndex], sp.u, sp.v, texel); // rchit:161-162
+    }
     const float metallic = texel[2];
     out.attenuation = attenuation;
     out.reflect = false;

@@ -32,6 +32,7 @@ struct SceneDev
     const VkrtSubmeshInfo* rows;
     const TextureRecord* textures;
     uint32_t one; // 0x3F800000, see byteToUnitFloat (traverse.cuh)
+    const TextureMips* mips; // ray-cone LOD mode only, else nullptr
 };
 
 struct WaveDev
@@ -46,6 +47,7 @@ struct WaveDev
     float4 *pathAccum, *sampleSum;
     uint32_t* counters; // [0..3] shadow queue sizes, [4] reflection queue size
     uint32_t capacity;  // P
+    float *coneT, *surfFoot; // ray-cone LOD mode only: primary hit distance per path, squared uv footprint per surface
 };
 
 struct FrameDev
@@ -429,7 +431,9 @@ k_trace_closest(SceneDev scene, const float4* __restrict__ rayO, const float4* _
     }
 }
 
-// shader.rchit:88-129 for every hit; shader.rmiss:17 for every miss.  Emits shadow rays.
+// shader.rchit:88-129 for every hit; shader.rmiss:17 for every miss.  Emits shadow rays.  LOD = true is the ray-cone
+// texture mode (vkrt_trace_set_texture_lod); the default instantiation is the reference's LOD-0 sampling.
+template<bool LOD>
 __global__ void __launch_bounds__(kShadeWarps * 32)
 k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
                 const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
@@ -479,7 +483,28 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 const float4 tag = __ldg(reinterpret_cast<const float4*>(inst.tris + tri) + 2);
                 const uint32_t geometry = __float_as_uint(tag.y);
                 primitive = __float_as_uint(tag.z);
-                sp = shadeSurface(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z);
+                if (LOD)
+                {
+                    const float4 d4 = rayD[q];
+                    float travelled = h.x; // cone width = spread angle x distance along the path (surface spread ignored)
+                    if (depth == 0)
+                    {
+                        w.coneT[q] = h.x;
+                    }
+                    else
+                    {
+                        travelled = w.coneT[p] + h.x;
+                    }
+                    LodInput lod;
+                    lod.mips = scene.mips, lod.worldRayDir = f3(d4.x, d4.y, d4.z);
+                    lod.coneWidth = pixelSpreadAngle(u, f.map.height) * travelled;
+                    sp = shadeSurface<true>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z, &lod);
+                    w.surfFoot[q] = sp.footprint2;
+                }
+                else
+                {
+                    sp = shadeSurface<false>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z);
+                }
                 for (int i = 0; i < 4; ++i)
                 {
                     lt[i] = lightTerm(u, i, sp.worldPos, sp.normal);
@@ -538,6 +563,7 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_
 }
 
 // shader.rchit:144-171 and the bounce bookkeeping of shader.rgen:63-73
+template<bool LOD>
 __global__ void __launch_bounds__(kShadeThreads)
 k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
                 const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
@@ -563,10 +589,11 @@ k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
             SurfacePoint sp;
             sp.worldPos = f3(a.x, a.y, a.z), sp.normal = f3(b.x, b.y, b.z);
             sp.u = a.w, sp.v = b.w, sp.geometry = geometry;
+            sp.footprint2 = LOD ? w.surfFoot[q] : 0.0f;
             const uint32_t bits = w.shadowBits[q];
             float4 acc = w.pathAccum[p];
             const float4 d4 = rayD[q];
-            const ResolveOut r = shadeResolve(u, scene.rows, scene.textures, sp, bits & 0xFu, acc.w, f3(d4.x, d4.y, d4.z));
+            const ResolveOut r = shadeResolve<LOD>(u, scene.rows, scene.textures, sp, bits & 0xFu, acc.w, f3(d4.x, d4.y, d4.z), scene.mips);
             acc.x += r.hitValue.x, acc.y += r.hitValue.y, acc.z += r.hitValue.z; // rgen:63
             acc.w = r.attenuation;
             w.pathAccum[p] = acc;
@@ -706,6 +733,11 @@ int reserveWave(Context* ctx, uint32_t paths)
     VKRT_CUDA_TRY(ctx, w.sampleSum.reserve(p * 16));
     VKRT_CUDA_TRY(ctx, w.counters.reserve(64));
     VKRT_CUDA_TRY(ctx, ctx->statCounters.reserve(64));
+    if (ctx->textureLod == VKRT_TEXTURE_LOD_RAY_CONES)
+    {
+        VKRT_CUDA_TRY(ctx, w.coneT.reserve(p * 4));
+        VKRT_CUDA_TRY(ctx, w.surfFoot.reserve(p * 4));
+    }
     return VKRT_SUCCESS;
 }
 
@@ -722,6 +754,7 @@ WaveDev waveDev(Context* ctx, uint32_t paths)
     w.shadowO = b.shadowO.as<float4>(), w.shadowD = b.shadowD.as<float4>();
     w.pathAccum = b.pathAccum.as<float4>(), w.sampleSum = b.sampleSum.as<float4>();
     w.counters = b.counters.as<uint32_t>();
+    w.coneT = b.coneT.as<float>(), w.surfFoot = b.surfFoot.as<float>();
     w.capacity = std::max<uint32_t>(paths, 32);
     return w;
 }
@@ -865,6 +898,12 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     scene.rows = ctx->materials.as<VkrtSubmeshInfo>();
     scene.textures = ctx->textureRecords.as<TextureRecord>();
     scene.one = 0x3F800000u;
+    const bool lod = ctx->textureLod == VKRT_TEXTURE_LOD_RAY_CONES;
+    if (lod && !ctx->mipsReady)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_trace: VKRT_TEXTURE_LOD_RAY_CONES needs vkrt_textures_generate_mips first");
+    }
+    scene.mips = lod ? ctx->textureMips.as<TextureMips>() : nullptr;
 
     WaveDev w = waveDev(ctx, paths * waveSamples);
     FrameDev f;
@@ -935,7 +974,14 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 2
         }
-        k_shade_surface<<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        if (lod)
+        {
+            k_shade_surface<true><<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        }
+        else
+        {
+            k_shade_surface<false><<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        }
         if (timed)
         {
             mark(); // 3
@@ -945,7 +991,14 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 4
         }
-        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        if (lod)
+        {
+            k_shade_resolve<true><<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        }
+        else
+        {
+            k_shade_resolve<false><<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.rayD, nullptr, nullptr, wavePaths, 0, aovSamples);
+        }
         if (timed)
         {
             mark(); // 5
@@ -957,7 +1010,14 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 6
         }
-        k_shade_surface<<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        if (lod)
+        {
+            k_shade_surface<true><<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        }
+        else
+        {
+            k_shade_surface<false><<<gridSurface, kShadeWarps * 32, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        }
         if (timed)
         {
             mark(); // 7
@@ -967,7 +1027,14 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 8
         }
-        k_shade_resolve<<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        if (lod)
+        {
+            k_shade_resolve<true><<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        }
+        else
+        {
+            k_shade_resolve<false><<<gridShade, kShadeThreads, 0, s>>>(u, scene, w, f, w.reflD, w.reflPath, w.counters + 4, 0, 1, 0);
+        }
         if (timed)
         {
             mark(); // 9
@@ -1026,6 +1093,7 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     scene.rows = nullptr;
     scene.textures = nullptr;
     scene.one = 0x3F800000u;
+    scene.mips = nullptr;
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const uint32_t grid = persistentGrid(ctx, 8);
     k_reset_counters<<<1, 32, 0, s>>>(w.counters);

@@ -168,6 +168,20 @@ void Raytracer::createTextures()
         images[i].rgba8 = m_model->images[i].data.data();
     }
     VKRT_CHECK(m_device, vkrt_textures_set(m_device, images.data(), ui32Size(images)));
+    createMipmaps();
+}
+
+void Raytracer::createMipmaps()
+{
+    // src/Raytracer.cpp:572-640, called per image from createTextures (:562): here one call builds every chain on the
+    // device.  The chain is sampled only after setTextureLod(VKRT_TEXTURE_LOD_RAY_CONES); the default is the reference's
+    // level-0 sampling.
+    VKRT_CHECK(m_device, vkrt_textures_generate_mips(m_device));
+}
+
+void Raytracer::setTextureLod(int mode)
+{
+    VKRT_CHECK(m_device, vkrt_trace_set_texture_lod(m_device, mode));
 }
 
 void Raytracer::createVertexAndIndexBuffer()

@@ -23,6 +23,7 @@ public:
 
     // Headless mode (BASELINE.json north_star: "a headless offscreen mode ... so frames can be read back")
     void setSamplesPerPixel(uint32_t spp) { m_spp = spp; }
+    void setTextureLod(int mode); // VKRT_TEXTURE_LOD_ZERO (reference behaviour, default) or VKRT_TEXTURE_LOD_RAY_CONES
     void setInstances(const std::vector<VkrtInstance>& instances); // config 4; default = the reference's single 0.01-scale instance
     void readback(std::vector<uint8_t>& bgra8);                     // B8G8R8A8, tightly packed (root rank after the gather)
     void readbackAov(int aov, void* dst);
@@ -46,6 +47,7 @@ private:
     void updateCamera(double deltaTime);
     void createColorImage();
     void createTextures();
+    void createMipmaps();
     void createVertexAndIndexBuffer();
     void createBLAS();
     void createTLAS();

@@ -14,6 +14,7 @@ int main(int argc, char** argv)
     Context::Options options;
     options.width = 1280, options.height = 720; // BASELINE.json config 1
     uint32_t spp = 1;
+    int textureLod = VKRT_TEXTURE_LOD_ZERO;
     std::string out;
     for (int i = 1; i < argc; ++i)
     {
@@ -28,10 +29,11 @@ int main(int argc, char** argv)
         else if (a == "--models") Model::setModelsFolder(next());
         else if (a == "--out") out = next();
         else if (a == "--comm-file") options.commFile = next();
+        else if (a == "--texture-lod") textureLod = std::string(next()) == "cones" ? VKRT_TEXTURE_LOD_RAY_CONES : VKRT_TEXTURE_LOD_ZERO;
         else
         {
             printf("usage: %s [--width W] [--height H] [--frames N] [--spp S] [--device D] [--script W:150,Z:150] [--models DIR] "
-                   "[--out frame_prefix] [--comm-file PATH]\n", argv[0]);
+                   "[--out frame_prefix] [--comm-file PATH] [--texture-lod zero|cones]\n", argv[0]);
             return a == "--help" ? 0 : 2;
         }
     }
@@ -43,6 +45,7 @@ int main(int argc, char** argv)
     Context context(options);
     Raytracer graphicsApp(context);
     graphicsApp.setSamplesPerPixel(spp);
+    graphicsApp.setTextureLod(textureLod);
 
     const auto t0 = std::chrono::steady_clock::now();
     bool running = true;

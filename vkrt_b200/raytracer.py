@@ -63,6 +63,7 @@ class Raytracer:
         self.tlas = B.Tlas(self.ctx, [self.blas], self.instances)
         self.ctx.set_materials(self.flat["rows"])
         self.ctx.set_textures(self.flat["images"])
+        self.ctx.generate_mips()  # createTextures -> createMipmaps, src/Raytracer.cpp:562 (sampled only in the ray-cone mode)
         self.frame = B.Frame(self.ctx, width, height)
         self.camera = Camera(np.float32(width) / np.float32(height))
         # Raytracer::setupCamera, src/Raytracer.cpp:267-271
@@ -77,6 +78,11 @@ class Raytracer:
         if gather and self.world_size > 1 and self.ctx is not None:
             self.frame.gather(0)
         self.frame_index += 1
+
+    def set_texture_lod(self, mode: int):
+        """B.TEXTURE_LOD_ZERO: every texture() samples level 0, as the reference's ray-tracing shaders do (default);
+        B.TEXTURE_LOD_RAY_CONES: trilinear at the ray-cone level of detail over the generated mip chain."""
+        self.ctx.set_texture_lod(mode)
 
     def rebuild(self, vertices, flags: int = 0):
         """Per-frame full rebuild over moved vertices (BASELINE.json config 5): same storage, new BVH, new TLAS bounds."""
