@@ -246,6 +246,20 @@ VKRT_API void vkrt_host_free(VkrtContext* ctx, void* ptr);
 /* Device pointer of the assembled BGRA8 image (width*height*4), valid until the frame is destroyed. */
 VKRT_API void* vkrt_frame_device_bgra8(VkrtFrame* frame);
 
+/* ------------------------------------------------------------------------------------------------
+ * Rasteriser — the reference's second renderer, `Rasterizer` (src/Rasterizer.cpp; `main` instantiates the ray tracer,
+ * src/main.cpp:8).  One call replaces the render pass of Rasterizer::render (:119-147): clear to (0,0,0.2,1) / depth 1,
+ * one indexed draw per geometry of `geometry` with shaders/shader.vert + shader.frag (base-colour texture with its mip
+ * chain, alpha test at 0.1), back-face culling with counter-clockwise front faces, depth test LESS on D24, 8x MSAA
+ * without sample shading, resolve into the frame's B8G8R8A8 image (pipeline state :779-829).
+ * `geometry` supplies the vertex and index data (positions + uv of the 64-byte Model::Vertex, draw order = geometry order,
+ * :1054-1075); `wvp` is the column-major proj * view * world matrix of Rasterizer::update (:189-191).  Materials, textures
+ * and the mip chain must have been set.  Stream-ordered like vkrt_trace; with AOVs, VKRT_AOV_TRIANGLE_ID_U32 holds the
+ * triangle (cumulative index over the geometries) seen by sample 0 of every pixel, ~0 where the clear colour shows.
+ * Single-GPU frames only.  The ImGui overlay (:149-159) is not drawn.
+ * ---------------------------------------------------------------------------------------------- */
+VKRT_API int vkrt_rasterize(VkrtContext* ctx, const VkrtBlas* geometry, const float* wvp, uint32_t flags, VkrtFrame* frame);
+
 /* Scheduling knob of the persistent trace kernels (no counterpart in the reference; results do not depend on it).
  * lanes == 0 (default): a warp takes 32 new rays once all of its rays have finished - fastest on coherent scenes.
  * lanes in 1..32: lanes whose ray has finished are re-armed as soon as fewer than `lanes` lanes of the warp are still

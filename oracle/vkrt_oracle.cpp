@@ -276,6 +276,7 @@ struct OrcScene
     Hit trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, Counters& c) const;
     void sample(uint32_t index, float u, float v, float rgba[4]) const;
     void sampleLod(uint32_t index, float u, float v, float footprint2, float rgba[4]) const;
+    void sampleTexels2(uint32_t index, float u, float v, float texels2, float rgba[4]) const;
     void generateMips();
 };
 
@@ -746,8 +747,15 @@ static float lodLog2(float x)
 void OrcScene::sampleLod(uint32_t index, float u, float v, float footprint2, float rgba[4]) const
 {
     const Image& img = images[index];
-    const std::vector<MipLevel>& chain = mips[index];
-    const float texels2 = (footprint2 * (float)img.w) * (float)img.h;
+    sampleTexels2(index, u, v, (footprint2 * (float)img.w) * (float)img.h, rgba);
+}
+
+/* Trilinear sample for a squared footprint of `texels2` level-0 texels (mip LINEAR, minLod 0, all levels). */
+void OrcScene::sampleTexels2(uint32_t index, float u, float v, float texels2, float rgba[4]) const
+{
+    const Image& img = images[index];
+    static const std::vector<MipLevel> none;
+    const std::vector<MipLevel>& chain = mips.size() == images.size() ? mips[index] : none;
     if (!(texels2 > 1.0f) || !std::isfinite(texels2) || chain.empty())
     {
         bilinearRepeat(img.px.data(), img.w, img.h, u, v, rgba);
@@ -1180,6 +1188,262 @@ void orc_render(OrcScene* scene, const OrcUniforms* uniforms, uint32_t width, ui
         stats->raysReflection = total.raysReflection;
         stats->nodesVisited = total.nodes, stats->trianglesTested = total.tris;
         stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - tStart).count();
+    }
+}
+
+/*
+ * The reference's second renderer: Rasterizer::render (src/Rasterizer.cpp:100-170) with shaders/shader.vert and
+ * shaders/shader.frag, restated as a scalar z-buffer rasteriser.
+ *   vertex shader      gl_Position = wvp * (position, 1), uv passed through                      (shader.vert:18-23)
+ *   fixed function     viewport (0,0,W,H), depth [0,1]; back faces culled, front = counter-clockwise; 8x MSAA at the
+ *                      Vulkan standard sample locations, no sample shading (one fragment per pixel and triangle, attributes
+ *                      at the pixel centre); top-left rule; depth test LESS with writes on D24; no blending
+ *                                                                                                (Rasterizer.cpp:779-829)
+ *   fragment shader    colour = texture(baseColor, uv), discard when alpha < 0.1                 (shader.frag:13-22)
+ *   sampler            LINEAR / REPEAT / mip LINEAR over the whole chain, implicit derivatives   (Rasterizer.cpp:484-498)
+ *   clears, resolve    colour (0,0,0.2,1), depth 1 (:119-120); 8 samples averaged into B8G8R8A8
+ * Triangles are drawn in order (geometry after geometry, :140-146), so at equal depth the earlier triangle keeps the
+ * sample.  Numerical contract shared with the product: edge functions in 2D homogeneous
+ * coordinates (Olano & Greer 1997), planes evaluated as (a*x + b*y) + c, FP32, no FMA contraction.
+ */
+namespace
+{
+struct RasterPlanes
+{
+    float ea[3], eb[3], ec[3]; /* edge functions, >= 0 inside */
+    float z[3], u[3], v[3], s[3];
+    uint32_t texture;
+    int x0, y0, x1, y1;
+    bool drawn;
+};
+
+inline float evalPlane(const float p[3], float x, float y)
+{
+    return (p[0] * x + p[1] * y) + p[2];
+}
+
+const int kSampleX16[8] = {9, 7, 13, 5, 3, 1, 11, 15}; /* Vulkan standard sample locations, 8 samples, in 1/16 pixel */
+const int kSampleY16[8] = {5, 11, 9, 3, 13, 7, 15, 1};
+
+RasterPlanes rasterPlanes(const float* wvp, const float* a, const float* b, const float* c, uint32_t texture, uint32_t width, uint32_t height)
+{
+    RasterPlanes r;
+    r.drawn = false, r.texture = texture;
+    const float* vtx[3] = {a, b, c};
+    float cx[3], cy[3], cz[3], cw[3];
+    for (int i = 0; i < 3; ++i)
+    {
+        const float px = vtx[i][0], py = vtx[i][1], pz = vtx[i][2];
+        cx[i] = ((wvp[0] * px + wvp[4] * py) + wvp[8] * pz) + wvp[12];
+        cy[i] = ((wvp[1] * px + wvp[5] * py) + wvp[9] * pz) + wvp[13];
+        cz[i] = ((wvp[2] * px + wvp[6] * py) + wvp[10] * pz) + wvp[14];
+        cw[i] = ((wvp[3] * px + wvp[7] * py) + wvp[11] * pz) + wvp[15];
+    }
+    auto all = [&](auto pred) { return pred(0) && pred(1) && pred(2); };
+    if (all([&](int i) { return cx[i] < -cw[i]; }) || all([&](int i) { return cx[i] > cw[i]; }) || all([&](int i) { return cy[i] < -cw[i]; }) ||
+        all([&](int i) { return cy[i] > cw[i]; }) || all([&](int i) { return cz[i] < 0.0f; }) || all([&](int i) { return cz[i] > cw[i]; }))
+    {
+        return r; /* outside one frustum plane */
+    }
+    const float halfW = 0.5f * (float)width, halfH = 0.5f * (float)height;
+    V3 h[3]; /* (x_fb * w, y_fb * w, w) */
+    for (int i = 0; i < 3; ++i)
+    {
+        h[i] = mk((cx[i] + cw[i]) * halfW, (cy[i] + cw[i]) * halfH, cw[i]);
+    }
+    const V3 n[3] = {cross(h[2], h[1]), cross(h[0], h[2]), cross(h[1], h[0])};
+    const float det = dot(h[0], n[0]);
+    if (!(det > 0.0f) || !std::isfinite(det))
+    {
+        return r; /* back-facing (clockwise in the y-down framebuffer) or degenerate */
+    }
+    const float tu[3] = {a[8], b[8], c[8]}, tv[3] = {a[9], b[9], c[9]};
+    for (int k = 0; k < 3; ++k)
+    {
+        const float nk[3] = {comp(n[0], k), comp(n[1], k), comp(n[2], k)};
+        if (k == 0)
+        {
+            r.ea[0] = nk[0], r.ea[1] = nk[1], r.ea[2] = nk[2];
+        }
+        else if (k == 1)
+        {
+            r.eb[0] = nk[0], r.eb[1] = nk[1], r.eb[2] = nk[2];
+        }
+        else
+        {
+            r.ec[0] = nk[0], r.ec[1] = nk[1], r.ec[2] = nk[2];
+        }
+        r.z[k] = ((cz[0] * nk[0] + cz[1] * nk[1]) + cz[2] * nk[2]) / det;
+        r.u[k] = (tu[0] * nk[0] + tu[1] * nk[1]) + tu[2] * nk[2];
+        r.v[k] = (tv[0] * nk[0] + tv[1] * nk[1]) + tv[2] * nk[2];
+        r.s[k] = (nk[0] + nk[1]) + nk[2];
+    }
+    r.x0 = 0, r.y0 = 0, r.x1 = (int)width - 1, r.y1 = (int)height - 1;
+    if (cw[0] > 0.0f && cw[1] > 0.0f && cw[2] > 0.0f)
+    {
+        float lox = INFINITY, hix = -INFINITY, loy = INFINITY, hiy = -INFINITY;
+        for (int i = 0; i < 3; ++i)
+        {
+            const float fx = h[i].x / h[i].z, fy = h[i].y / h[i].z;
+            lox = std::fmin(lox, fx), hix = std::fmax(hix, fx), loy = std::fmin(loy, fy), hiy = std::fmax(hiy, fy);
+        }
+        if (!(hix >= 0.0f) || !(lox < (float)width) || !(hiy >= 0.0f) || !(loy < (float)height))
+        {
+            return r;
+        }
+        r.x0 = (int)std::fmax(std::floor(lox), 0.0f), r.y0 = (int)std::fmax(std::floor(loy), 0.0f);
+        r.x1 = (int)std::fmin(std::floor(hix), (float)(width - 1)), r.y1 = (int)std::fmin(std::floor(hiy), (float)(height - 1));
+    }
+    r.drawn = true;
+    return r;
+}
+} // namespace
+
+/* Fragment colour of triangle planes `t` at pixel (px,py); false = discarded. */
+static bool rasterFragmentColour(const OrcScene& s, const RasterPlanes& t, int px, int py, float rgba[4])
+{
+    const float x = (float)px + 0.5f, y = (float)py + 0.5f;
+    const float U = evalPlane(t.u, x, y), V = evalPlane(t.v, x, y), S = evalPlane(t.s, x, y);
+    const float u = U / S, v = V / S;
+    const float S2 = S * S;
+    /* implicit derivatives, analytic: d(U/S)/dx = (U_x S - U S_x) / S^2 */
+    const float dudx = (t.u[0] * S - U * t.s[0]) / S2, dudy = (t.u[1] * S - U * t.s[1]) / S2;
+    const float dvdx = (t.v[0] * S - V * t.s[0]) / S2, dvdy = (t.v[1] * S - V * t.s[1]) / S2;
+    const Image& img = s.images[t.texture];
+    const float w = (float)img.w, h = (float)img.h;
+    const float rx2 = (dudx * w) * (dudx * w) + (dvdx * h) * (dvdx * h);
+    const float ry2 = (dudy * w) * (dudy * w) + (dvdy * h) * (dvdy * h);
+    s.sampleTexels2(t.texture, u, v, std::fmax(rx2, ry2), rgba);
+    return !(rgba[3] < 0.1f);
+}
+
+void orc_rasterize(OrcScene* scene, const float* wvp, uint32_t width, uint32_t height, int threads, uint8_t* bgra8, uint32_t* triangleId)
+{
+    const OrcScene& s = *scene;
+    if (threads <= 0)
+    {
+        threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    }
+    /* vertex shader + set-up for every triangle, in draw order */
+    std::vector<RasterPlanes> planes(s.tris.size());
+    {
+        size_t t = 0;
+        for (size_t g = 0; g < s.ranges.size(); ++g)
+        {
+            const uint64_t first = s.ranges[g].indexByteOffset / 4;
+            const int32_t baseColor = s.rows[g].baseColorTextureIndex;
+            const uint32_t texture = (baseColor < 0 || (size_t)baseColor >= s.images.size()) ? 0u : (uint32_t)baseColor;
+            for (uint32_t p = 0; p < s.ranges[g].primitiveCount; ++p, ++t)
+            {
+                const float* a = &s.vertices[(size_t)s.indices[first + 3 * p + 0] * 16];
+                const float* b = &s.vertices[(size_t)s.indices[first + 3 * p + 1] * 16];
+                const float* c = &s.vertices[(size_t)s.indices[first + 3 * p + 2] * 16];
+                planes[t] = rasterPlanes(wvp, a, b, c, texture, width, height);
+            }
+        }
+    }
+    const size_t sampleCount = (size_t)width * height * 8;
+    std::vector<uint32_t> depth(sampleCount, 0xFFFFFFu); /* cleared to 1.0 (src/Rasterizer.cpp:120) */
+    std::vector<uint32_t> colour(sampleCount, 0u | (0u << 8) | (51u << 16) | (255u << 24)); /* (0,0,0.2,1) as UNORM8 */
+    std::vector<uint32_t> owner(sampleCount, 0xFFFFFFFFu);
+    auto band = [&](int tid) {
+        for (size_t t = 0; t < planes.size(); ++t)
+        {
+            const RasterPlanes& tp = planes[t];
+            if (!tp.drawn)
+            {
+                continue;
+            }
+            for (int py = tp.y0; py <= tp.y1; ++py)
+            {
+                if (py % threads != tid)
+                {
+                    continue;
+                }
+                for (int px = tp.x0; px <= tp.x1; ++px)
+                {
+                    uint32_t covered = 0;
+                    for (int k = 0; k < 8; ++k)
+                    {
+                        const float x = (float)px + (float)kSampleX16[k] * 0.0625f, y = (float)py + (float)kSampleY16[k] * 0.0625f;
+                        bool inside = true;
+                        for (int e = 0; e < 3; ++e)
+                        {
+                            const float val = (tp.ea[e] * x + tp.eb[e] * y) + tp.ec[e];
+                            const bool topLeft = tp.ea[e] > 0.0f || (tp.ea[e] == 0.0f && tp.eb[e] > 0.0f);
+                            inside = inside && (val > 0.0f || (val == 0.0f && topLeft));
+                        }
+                        covered |= inside ? 1u << k : 0u;
+                    }
+                    if (!covered)
+                    {
+                        continue;
+                    }
+                    float rgba[4];
+                    if (!rasterFragmentColour(s, tp, px, py, rgba))
+                    {
+                        continue; /* discard */
+                    }
+                    uint32_t q = 0;
+                    for (int ch = 0; ch < 4; ++ch)
+                    {
+                        q |= (uint32_t)unorm8(rgba[ch]) << (8 * ch);
+                    }
+                    for (int k = 0; k < 8; ++k)
+                    {
+                        if (!((covered >> k) & 1u))
+                        {
+                            continue;
+                        }
+                        const float x = (float)px + (float)kSampleX16[k] * 0.0625f, y = (float)py + (float)kSampleY16[k] * 0.0625f;
+                        const float z = evalPlane(tp.z, x, y);
+                        if (!(z >= 0.0f && z <= 1.0f))
+                        {
+                            continue; /* near / far clip */
+                        }
+                        const uint32_t d24 = (uint32_t)(z * 16777215.0f + 0.5f);
+                        const size_t idx = ((size_t)py * width + px) * 8 + k;
+                        if (d24 < depth[idx]) /* VK_COMPARE_OP_LESS */
+                        {
+                            depth[idx] = d24, colour[idx] = q, owner[idx] = (uint32_t)t;
+                        }
+                    }
+                }
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t)
+    {
+        pool.emplace_back(band, t);
+    }
+    band(0);
+    for (auto& t : pool)
+    {
+        t.join();
+    }
+    for (size_t pix = 0; pix < (size_t)width * height; ++pix)
+    {
+        uint32_t sum[4] = {0, 0, 0, 0};
+        for (int k = 0; k < 8; ++k)
+        {
+            for (int ch = 0; ch < 4; ++ch)
+            {
+                sum[ch] += (colour[pix * 8 + k] >> (8 * ch)) & 0xFFu;
+            }
+        }
+        if (bgra8)
+        {
+            const int order[4] = {2, 1, 0, 3}; /* B, G, R, A */
+            for (int ch = 0; ch < 4; ++ch)
+            {
+                bgra8[pix * 4 + ch] = (uint8_t)((float)sum[order[ch]] / 8.0f + 0.5f);
+            }
+        }
+        if (triangleId)
+        {
+            triangleId[pix] = owner[pix * 8];
+        }
     }
 }
 

@@ -142,6 +142,12 @@ uint32_t orc_texture_level_count(const OrcScene* scene, uint32_t index);
 const uint8_t* orc_texture_level(const OrcScene* scene, uint32_t index, uint32_t level, uint32_t* width, uint32_t* height);
 void orc_sample_texture_lod(const OrcScene* scene, uint32_t index, float u, float v, float footprint2, float rgba[4]);
 
+/* The reference's rasteriser (src/Rasterizer.cpp:100-170, shaders/shader.vert, shaders/shader.frag): one frame through
+ * the column-major `wvp` matrix; needs orc_scene_generate_mips.  bgra8: width*height*4 (resolved image); triangleId:
+ * width*height u32, triangle (draw order) that owns sample 0 of the pixel, 0xFFFFFFFF where the clear colour shows. */
+void orc_rasterize(OrcScene* scene, const float* wvp, uint32_t width, uint32_t height, int threads, uint8_t* bgra8,
+                   uint32_t* triangleId);
+
 /* Halton(2,3) sample s in [0,1)^2 used instead of +0.5 when spp > 1. */
 void orc_halton23(uint32_t s, float out[2]);
 

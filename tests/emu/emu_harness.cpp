@@ -9,6 +9,7 @@
  */
 #include "../../vkrt_b200/csrc/builder.cuh"
 #include "../../vkrt_b200/csrc/shading.cuh"
+#include "../../vkrt_b200/csrc/raster.cuh"
 #include "../../vkrt_b200/csrc/traverse.cuh"
 
 #include <algorithm>
@@ -336,6 +337,61 @@ void emu_scene_generate_mips(EmuScene* s)
         }
         s->mips[i].texels = s->mipTexels[i].data();
         s->mips[i].levels = levels;
+    }
+}
+
+// Sequential form of rasterizeFrame (raster.cu): set-up of every triangle, rasterPixel over its bounding box (the
+// small/large split and the tile rejection of the kernels only skip pixels that rasterPixel would reject), resolve.
+void emu_rasterize(const EmuScene* s, const float* wvp, uint32_t width, uint32_t height, uint8_t* bgra8, uint32_t* triangleId)
+{
+    const EmuBlas* b = s->blas;
+    GeometryTable geo;
+    geo.firstTri = b->firstTri.data(), geo.indexBase = b->indexBase.data();
+    geo.geometryCount = (uint32_t)b->firstTri.size() - 1u;
+    const uint32_t n = b->triangleCount;
+    std::vector<RasterSetup> setups(std::max(n, 1u));
+    std::vector<uint64_t> visibility((size_t)width * height * kRasterSamples, kRasterEmpty);
+    auto minKey = [](uint64_t* key, uint64_t candidate) { *key = std::min(*key, candidate); };
+    // triangles are visited in REVERSE draw order on purpose: the keys make the result independent of the order
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        const uint32_t t = n - 1u - k;
+        const uint32_t g = findGeometry(geo, t);
+        const uint64_t base = geo.indexBase[g] + 3ull * (t - geo.firstTri[g]);
+        const uint32_t i0 = b->indices[base], i1 = b->indices[base + 1], i2 = b->indices[base + 2];
+        const uint8_t* vb = b->vertices.data();
+        const float4 p0 = loadF4(vb, (size_t)i0 * b->stride), p1 = loadF4(vb, (size_t)i1 * b->stride), p2 = loadF4(vb, (size_t)i2 * b->stride);
+        const float4 t0 = loadF4(vb, (size_t)i0 * b->stride + 32), t1 = loadF4(vb, (size_t)i1 * b->stride + 32), t2 = loadF4(vb, (size_t)i2 * b->stride + 32);
+        const int32_t baseColor = s->rows[g].baseColorTextureIndex;
+        const uint32_t texture = (baseColor < 0 || (size_t)baseColor >= s->textures.size()) ? 0u : (uint32_t)baseColor;
+        RasterSetup& rs = setups[t];
+        if (!rasterSetup(wvp, f3(p0.x, p0.y, p0.z), f3(p1.x, p1.y, p1.z), f3(p2.x, p2.y, p2.z), t0.x, t0.y, t1.x, t1.y, t2.x, t2.y, texture, width,
+                         height, rs))
+        {
+            continue;
+        }
+        const uint32_t x0 = rs.bboxX & 0xFFFFu, x1 = rs.bboxX >> 16, y0 = rs.bboxY & 0xFFFFu, y1 = rs.bboxY >> 16;
+        for (uint32_t py = y0; py <= y1; ++py)
+        {
+            for (uint32_t px = x0; px <= x1; ++px)
+            {
+                rasterPixel(rs, t, s->textures.data(), s->mips.data(), width, px, py, visibility.data(), minKey);
+            }
+        }
+    }
+    for (uint32_t py = 0; py < height; ++py)
+    {
+        for (uint32_t px = 0; px < width; ++px)
+        {
+            uint32_t first;
+            const uint32_t c = rasterResolve(setups.data(), s->textures.data(), s->mips.data(), width, px, py, visibility.data(), first);
+            const size_t pix = (size_t)py * width + px;
+            memcpy(bgra8 + pix * 4, &c, 4);
+            if (triangleId)
+            {
+                triangleId[pix] = first;
+            }
+        }
     }
 }
 

@@ -64,6 +64,7 @@ def oracle_lib():
         lib.orc_halton23.argtypes = [u32, vp]
         lib.orc_primary_ray.argtypes = [vp, u32, u32, u32, u32, C.c_float, C.c_float, vp]
         lib.orc_affine_inverse.argtypes = [vp, vp]
+        lib.orc_rasterize.argtypes = [vp, vp, u32, u32, i32, vp, vp]
         lib.orc_scene_generate_mips.argtypes = [vp]
         lib.orc_scene_set_texture_lod.argtypes = [vp, i32]
         lib.orc_texture_level_count.restype = u32
@@ -136,6 +137,14 @@ class OracleScene:
     def generate_mips(self):
         self.lib.orc_scene_generate_mips(self.h)
 
+    def rasterize(self, wvp, width, height, threads=0):
+        """The reference's Rasterizer frame (needs generate_mips): {"bgra", "tri"}."""
+        wvp = np.ascontiguousarray(wvp, dtype=np.float32).reshape(16)
+        bgra = np.zeros((height, width, 4), dtype=np.uint8)
+        tri = np.zeros((height, width), dtype=np.uint32)
+        self.lib.orc_rasterize(self.h, _p(wvp), width, height, threads, _p(bgra), _p(tri))
+        return {"bgra": bgra, "tri": tri}
+
     def set_texture_lod(self, mode):
         self.lib.orc_scene_set_texture_lod(self.h, int(mode))
 
@@ -179,6 +188,7 @@ def emu_lib():
         lib.emu_scene_destroy.argtypes = [vp]
         lib.emu_trace_rays.argtypes = [vp, vp, u64, i32, vp, C.POINTER(u64), C.POINTER(u64)]
         lib.emu_render.argtypes = [vp, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32, vp, vp, vp, vp]
+        lib.emu_rasterize.argtypes = [vp, vp, u32, u32, vp, vp]
         lib.emu_scene_generate_mips.argtypes = [vp]
         lib.emu_scene_set_texture_lod.argtypes = [vp, i32]
         lib.emu_texture_level.restype = vp
@@ -220,6 +230,13 @@ class EmuScene:
 
     def generate_mips(self):
         self.lib.emu_scene_generate_mips(self.h)
+
+    def rasterize(self, wvp, width, height):
+        wvp = np.ascontiguousarray(wvp, dtype=np.float32).reshape(16)
+        bgra = np.zeros((height, width, 4), dtype=np.uint8)
+        tri = np.zeros((height, width), dtype=np.uint32)
+        self.lib.emu_rasterize(self.h, _p(wvp), width, height, _p(bgra), _p(tri))
+        return {"bgra": bgra, "tri": tri}
 
     def set_texture_lod(self, mode):
         self.lib.emu_scene_set_texture_lod(self.h, int(mode))

@@ -135,6 +135,7 @@ EXPORTS = [
     "vkrt_context_synchronize",
     "vkrt_context_stream",
     "vkrt_trace_set_lane_refill",
+    "vkrt_rasterize",
     "vkrt_trace_set_texture_lod",
     "vkrt_textures_generate_mips",
     "vkrt_texture_info",
@@ -208,6 +209,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_texture_info": (i32, [vp, u32, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]),
         "vkrt_texture_read": (i32, [vp, u32, u32, vp, sz]),
         "vkrt_trace_set_texture_lod": (i32, [vp, i32]),
+        "vkrt_rasterize": (i32, [vp, vp, vp, u32, vp]),
         "vkrt_frame_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
         "vkrt_frame_destroy": (None, [vp, vp]),
         "vkrt_trace": (i32, [vp, vp, C.POINTER(Uniforms), u32, u32, u32, vp]),
@@ -471,6 +473,11 @@ class Frame:
 
     def trace(self, tlas: Tlas, uniforms: Uniforms, spp: int = 1, frame_index: int = 0, flags: int = 0):
         self.ctx.check(self.ctx.lib.vkrt_trace(self.ctx.handle, tlas.handle, C.byref(uniforms), spp, frame_index, flags, self.handle))
+
+    def rasterize(self, blas: "Blas", wvp: np.ndarray, flags: int = 0):
+        """One frame of the reference's Rasterizer (src/Rasterizer.cpp:119-147) through the column-major wvp matrix."""
+        m = np.ascontiguousarray(wvp, dtype=np.float32).reshape(16)
+        self.ctx.check(self.ctx.lib.vkrt_rasterize(self.ctx.handle, blas.handle, _ptr(m), flags, self.handle))
 
     def gather(self, root: int = 0):
         self.ctx.check(self.ctx.lib.vkrt_tiles_gather(self.ctx.handle, self.handle, root))

@@ -34,6 +34,7 @@ def load_host():
         lib.vkrt_host_camera_set_aspect.argtypes = [vp, f]
         lib.vkrt_host_camera_axes.argtypes = [vp, vp]
         lib.vkrt_host_camera_matrices.argtypes = [vp, vp]
+        lib.vkrt_host_camera_wvp.argtypes = [vp, f, vp]
         lib.vkrt_host_fill_uniforms.argtypes = [vp, vp, C.POINTER(Uniforms)]
         _host = lib
     return _host
@@ -97,6 +98,12 @@ class Camera:
 
     def getProjectionMatrix(self):
         return self._matrices()[16:].copy()
+
+    def wvp(self, scale: float = 0.01) -> np.ndarray:
+        """proj * view * scale(s), column-major 16 floats: the rasteriser's uniform (src/Rasterizer.cpp:189-191)."""
+        out = np.zeros(16, dtype=np.float32)
+        self._lib.vkrt_host_camera_wvp(self._h, np.float32(scale), out.ctypes.data)
+        return out
 
     def uniforms(self, lights: np.ndarray = LIGHT_POSITIONS) -> Uniforms:
         """The 256-byte block Raytracer::update fills (src/Raytracer.cpp:224-235)."""

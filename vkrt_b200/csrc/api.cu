@@ -127,6 +127,7 @@ void vkrt_context_destroy(VkrtContext* c)
     ctx->uniforms.release();
     ctx->buildScratch.release();
     ctx->wave.release();
+    ctx->raster.release();
     ctx->statCounters.release();
     ctx->gatherStaging.release();
     if (ctx->eventsCreated)
@@ -715,7 +716,7 @@ void vkrt_frame_destroy(VkrtContext* c, VkrtFrame* fr)
             cudaEventDestroy(e);
         }
     }
-    f->bgra8.release(), f->tileBgra8.release(), f->rgb32f.release(), f->triangleId.release(), f->shadowMask.release();
+    f->bgra8.release(), f->tileBgra8.release(), f->rgb32f.release(), f->triangleId.release(), f->shadowMask.release(), f->visibility.release();
     delete f;
 }
 
@@ -877,6 +878,21 @@ void vkrt_host_free(VkrtContext* c, void* ptr)
 void* vkrt_frame_device_bgra8(VkrtFrame* fr)
 {
     return fr ? F(fr)->bgra8.ptr : nullptr;
+}
+
+int vkrt_rasterize(VkrtContext* c, const VkrtBlas* b, const float* wvp, uint32_t flags, VkrtFrame* fr)
+{
+    Context* ctx = C(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (!b || !wvp || !fr)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_rasterize: NULL argument");
+    }
+    cudaSetDevice(ctx->device);
+    return rasterizeFrame(ctx, static_cast<const Blas*>(b), wvp, flags, F(fr));
 }
 
 int vkrt_trace_set_lane_refill(VkrtContext* c, uint32_t lanes)

@@ -64,6 +64,22 @@ struct WaveBuffers
     }
 };
 
+// Scratch of the software rasteriser (raster.cu); grow-only, reused across frames.
+struct RasterBuffers
+{
+    DeviceBuffer setups;                          // RasterSetup[triangles]
+    DeviceBuffer smallList, largeList, largeTiles; // u32[triangles] each
+    DeviceBuffer counters;                        // u32[16]
+    void release()
+    {
+        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &counters};
+        for (DeviceBuffer* b : all)
+        {
+            b->release();
+        }
+    }
+};
+
 struct NcclApi; // dlopen'ed NCCL entry points (comm.cpp)
 
 struct Context : VkrtContext
@@ -91,6 +107,7 @@ struct Context : VkrtContext
 
     BuildScratch buildScratch;
     WaveBuffers wave;
+    RasterBuffers raster;
 
     // stats
     uint32_t waveKeyPaths = 0, waveKeySpp = 0, waveSamples = 1; // cached samples-per-wave decision (wavefront.cu)
@@ -150,6 +167,7 @@ struct Frame : VkrtFrame
     DeviceBuffer rgb32f;      // width*height*3 floats (AOV)
     DeviceBuffer triangleId;  // width*height u32 (AOV)
     DeviceBuffer shadowMask;  // width*height u8 (AOV)
+    DeviceBuffer visibility;  // width*height*8 u64 (depth24 << 32 | triangle) keys of the rasteriser (raster.cu)
     bool gathered = false;
     // presentation ring (vkrt_frame_present): copy n uses presentDone[n % kPresentRing]
     static constexpr int kPresentRing = 8;
@@ -167,6 +185,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
                Frame* frame);
 int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits);
 int generateMips(Context* ctx); // textures.cu
+int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t flags, Frame* frame); // raster.cu
 int gatherTiles(Context* ctx, Frame* frame, int root);
 int commInit(Context* ctx, const uint8_t* id, int rank, int size);
 int commDestroy(Context* ctx);

@@ -215,11 +215,11 @@ VKRT_HD float coneFootprint2(F3 p0, F3 p1, F3 p2, float u0, float v0, float u1, 
     return (uvArea2 / worldArea2) * (wn * wn);
 }
 
-// Trilinear sample at the ray-cone level of detail; footprint2 that is not > 1 texel (magnification, degenerate
-// triangles or uv, NaN) samples level 0 exactly as sampleTexture does.
-VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips, float u, float v, float footprint2, float rgba[4])
+// Trilinear sample (mip LINEAR, minLod 0, no maxLod: src/Raytracer.cpp:436-458, src/Rasterizer.cpp:484-498) for a squared
+// footprint of `texels2` level-0 texels: lambda = 0.5 * log2(texels2), clamped to the chain.  A footprint that is not
+// > 1 texel (magnification, degenerate triangles or uv, NaN, inf) samples level 0 exactly as sampleTexture does.
+VKRT_HD void sampleTrilinear(const TextureRecord& tex, const TextureMips& mips, float u, float v, float texels2, float rgba[4])
 {
-    const float texels2 = (footprint2 * (float)tex.width) * (float)tex.height;
     if (!(texels2 > 1.0f) || !finite1(texels2) || mips.levels <= 1u)
     {
         sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba);
@@ -253,6 +253,12 @@ VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips,
             rgba[ch] = rgba[ch] * (1.0f - frac) + hi[ch] * frac;
         }
     }
+}
+
+// Ray-cone level of detail: the squared uv footprint covers footprint2 * W * H texels of this texture.
+VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips, float u, float v, float footprint2, float rgba[4])
+{
+    sampleTrilinear(tex, mips, u, v, (footprint2 * (float)tex.width) * (float)tex.height, rgba);
 }
 
 VKRT_HD float4 loadF4(const uint8_t* base, size_t byteOffset)

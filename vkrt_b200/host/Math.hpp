@@ -66,6 +66,25 @@ inline vec4 operator*(const mat4& m, vec4 v)
     return add0 + add1;
 }
 
+// glm mat4 * mat4: every result column is m1 * (column of m2), terms added left to right
+inline mat4 operator*(const mat4& m1, const mat4& m2)
+{
+    mat4 r;
+    for (int j = 0; j < 4; ++j)
+    {
+        r[j] = ((m1[0] * m2[j].x + m1[1] * m2[j].y) + m1[2] * m2[j].z) + m1[3] * m2[j].w;
+    }
+    return r;
+}
+
+// glm::scale(vec3) from <glm/gtx/transform.hpp>: identity with the diagonal scaled
+inline mat4 scale(vec3 v)
+{
+    mat4 r(1.0f);
+    r[0] = r[0] * v.x, r[1] = r[1] * v.y, r[2] = r[2] * v.z;
+    return r;
+}
+
 inline mat4 perspective(float fovy, float aspect, float zNear, float zFar)
 {
     const float tanHalfFovy = std::tan(fovy / 2.0f);

@@ -58,6 +58,16 @@ HOST_API void vkrt_host_camera_matrices(void* c, float* out)
         out[16 + i] = (&p.col[0].x)[i];
     }
 }
+// out: proj * view * scale(s), column-major: the matrix Rasterizer::update uploads (src/Rasterizer.cpp:189-191)
+HOST_API void vkrt_host_camera_wvp(void* c, float s, float* out)
+{
+    const Camera* cam = static_cast<Camera*>(c);
+    const vkrt::mat4 wvp = cam->getProjectionMatrix() * cam->getViewMatrix() * vkrt::scale(vkrt::vec3(s, s, s));
+    for (int i = 0; i < 16; ++i)
+    {
+        out[i] = (&wvp.col[0].x)[i];
+    }
+}
 HOST_API void vkrt_host_fill_uniforms(void* c, const float* lights16, VkrtUniforms* out)
 {
     float lights[4][4];

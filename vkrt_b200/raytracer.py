@@ -106,3 +106,39 @@ class Raytracer:
         for o in (self.frame, self.tlas, self.blas):
             o.close()
         self.ctx.close()
+
+
+class Rasterizer:
+    """Headless mirror of the reference's second renderer (src/Rasterizer.hpp:11-17, src/Rasterizer.cpp): the scene is
+    uploaded in the constructor, `render()` draws one frame with shader.vert / shader.frag semantics (base-colour texture
+    through its mip chain, alpha test, 8x MSAA, depth test LESS) on the GPU via vkrt_rasterize."""
+
+    def __init__(self, model: Dict, width: int, height: int, device: int = 0, flat: Optional[Dict] = None):
+        self.width, self.height = width, height
+        self.flat = flat if flat is not None else flatten_model(model)
+        self.ctx = B.Context(device)
+        # vertex/index buffers (createVertexAndIndexBuffer, src/Rasterizer.cpp:1040-1085); the BLAS object holds the device copy
+        self.blas = B.Blas(self.ctx, self.flat["vertices"], self.flat["indices"], self.flat["ranges"], flags=B.BUILD_PREFER_FAST_BUILD)
+        self.ctx.set_materials(self.flat["rows"])
+        self.ctx.set_textures(self.flat["images"])
+        self.ctx.generate_mips()  # createTextures -> createMipmaps, src/Rasterizer.cpp:560-700
+        self.frame = B.Frame(self.ctx, width, height)
+        self.camera = Camera(np.float32(width) / np.float32(height))
+        # Rasterizer::setupCamera, src/Rasterizer.cpp:207-211
+        self.camera.setPosition((-4.0, 2.0, -0.2))
+        self.camera.setRotation((0.0, 1.51, 0.0))
+        self.scale = 0.01  # Rasterizer::update, src/Rasterizer.cpp:189
+
+    def wvp(self) -> np.ndarray:
+        return self.camera.wvp(self.scale)
+
+    def render(self, flags: int = 0):
+        self.frame.rasterize(self.blas, self.wvp(), flags)
+
+    def readback(self, aov: int = B.AOV_BGRA8, out: Optional[np.ndarray] = None) -> np.ndarray:
+        return self.frame.read(aov, out)
+
+    def close(self):
+        for o in (self.frame, self.blas):
+            o.close()
+        self.ctx.close()
