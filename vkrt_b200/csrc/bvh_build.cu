@@ -1244,6 +1244,24 @@ static size_t sortStateBytes(uint32_t count)
     return (1040 + 4 * numTiles * 256) * sizeof(uint32_t);
 }
 
+// Device-resident (key, value) sort for other parts of the library (the rasteriser orders its large triangles front to
+// back with it).  Everything is stream-ordered; the sorted pairs end up in keysA / valsA.
+size_t sortPairsStateBytes(uint32_t count)
+{
+    return sortStateBytes(count);
+}
+int sortPairsDevice(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* state, uint32_t count)
+{
+    if (count == 0)
+    {
+        return VKRT_SUCCESS;
+    }
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(state, 0, sortStateBytes(count), ctx->stream));
+    k_onesweep_hist<<<gridFor(count, kThreads, ctx->smCount), kThreads, 0, ctx->stream>>>(keysA, count, state);
+    ctx->launches += 1;
+    return radixSort(ctx, keysA, valsA, keysB, valsB, state, count);
+}
+
 // Debug entry used by the tests: sorts host arrays on the device with the builder's sort.
 int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count)
 {

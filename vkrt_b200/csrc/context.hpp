@@ -69,10 +69,11 @@ struct RasterBuffers
 {
     DeviceBuffer setups;                          // RasterSetup[triangles]
     DeviceBuffer smallList, largeList, largeTiles; // u32[triangles] each
+    DeviceBuffer sortKeys, sortKeysB, sortValsB, sortState; // front-to-back order of the large triangles
     DeviceBuffer counters;                        // u32[16]
     void release()
     {
-        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &counters};
+        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &sortKeys, &sortKeysB, &sortValsB, &sortState, &counters};
         for (DeviceBuffer* b : all)
         {
             b->release();
@@ -181,6 +182,8 @@ int waitPresents(Context* ctx, Frame* frame);
 
 int buildBlasOnDevice(Context* ctx, Blas* blas);
 int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count);
+size_t sortPairsStateBytes(uint32_t count);
+int sortPairsDevice(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* state, uint32_t count);
 int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uint32_t spp, uint32_t frameIndex, uint32_t flags,
                Frame* frame);
 int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit, VkrtHit* hits);

@@ -18,6 +18,7 @@
 #include "raster.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace vkrt
 {
@@ -64,7 +65,7 @@ __global__ void __launch_bounds__(256)
 k_raster_setup(const __grid_constant__ Mat4 wvpHolder, GeometryTable geo, const uint8_t* __restrict__ vertices, uint32_t stride,
                const uint32_t* __restrict__ indices, const VkrtSubmeshInfo* __restrict__ rows, uint32_t textureCount, uint32_t triangles, uint32_t width, uint32_t height,
                RasterSetup* __restrict__ setups, uint32_t* __restrict__ smallList, uint32_t* __restrict__ largeList, uint32_t* __restrict__ largeTiles,
-               uint32_t* __restrict__ counters)
+               uint32_t* __restrict__ sortKeys, uint32_t* __restrict__ counters)
 {
     const float* wvp = wvpHolder.m;
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < triangles; t += gridDim.x * blockDim.x)
@@ -89,6 +90,10 @@ k_raster_setup(const __grid_constant__ Mat4 wvpHolder, GeometryTable geo, const 
         {
             dst[k] = src[k];
         }
+        if (sortKeys)
+        {
+            sortKeys[t] = 0xFFFFFFFFu, largeList[t] = t; // the sort moves the large triangles to the front, nearest first
+        }
         if (!drawn)
         {
             continue;
@@ -98,6 +103,16 @@ k_raster_setup(const __grid_constant__ Mat4 wvpHolder, GeometryTable geo, const 
         {
             smallList[atomicAdd(&counters[0], 1u)] = t;
         }
+        else if (sortKeys)
+        {
+            // nearest depth the triangle reaches on screen, as ordered bits: min over the bounding-box corners of the depth
+            // plane (it is linear in x, y), clamped to [0, 1]
+            const float fx0 = (float)x0, fx1 = (float)(x1 + 1u), fy0 = (float)y0, fy1 = (float)(y1 + 1u);
+            const float zmin = fminf(fminf(plane3(s.za, s.zb, s.zc, fx0, fy0), plane3(s.za, s.zb, s.zc, fx1, fy0)),
+                                     fminf(plane3(s.za, s.zb, s.zc, fx0, fy1), plane3(s.za, s.zb, s.zc, fx1, fy1)));
+            sortKeys[t] = __float_as_uint(fminf(fmaxf(zmin, 0.0f), 1.0f));
+            atomicAdd(&counters[1], 1u);
+        }
         else
         {
             const uint32_t tiles = (x1 / kRasterTile - x0 / kRasterTile + 1u) * (y1 / kRasterTile - y0 / kRasterTile + 1u);
@@ -105,6 +120,21 @@ k_raster_setup(const __grid_constant__ Mat4 wvpHolder, GeometryTable geo, const 
             largeList[slot] = t;
             largeTiles[slot] = tiles;
         }
+    }
+}
+
+// Tile counts of the large triangles in their sorted order.
+__global__ void __launch_bounds__(256)
+k_raster_tiles(const RasterSetup* __restrict__ setups, const uint32_t* __restrict__ largeList, uint32_t* __restrict__ largeTiles,
+               const uint32_t* __restrict__ counters)
+{
+    const uint32_t n = counters[1];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        const RasterSetup* s = setups + largeList[i];
+        const uint32_t bx = s->bboxX, by = s->bboxY;
+        const uint32_t x0 = bx & 0xFFFFu, x1 = bx >> 16, y0 = by & 0xFFFFu, y1 = by >> 16;
+        largeTiles[i] = (x1 / kRasterTile - x0 / kRasterTile + 1u) * (y1 / kRasterTile - y0 / kRasterTile + 1u);
     }
 }
 
@@ -304,6 +334,16 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     VKRT_CUDA_TRY(ctx, b.largeList.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.largeTiles.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.counters.reserve(64));
+    // Large triangles are rasterised nearest first, so that later ones are mostly rejected by the keys already in place
+    // (fewer atomics and fragment evaluations); the image does not depend on the order.  VKRT_RASTER_SORT=0 turns it off.
+    static const bool sortLarge = !(getenv("VKRT_RASTER_SORT") && atoi(getenv("VKRT_RASTER_SORT")) == 0);
+    if (sortLarge && n > 0)
+    {
+        VKRT_CUDA_TRY(ctx, b.sortKeys.reserve((size_t)n * 4));
+        VKRT_CUDA_TRY(ctx, b.sortKeysB.reserve((size_t)n * 4));
+        VKRT_CUDA_TRY(ctx, b.sortValsB.reserve((size_t)n * 4));
+        VKRT_CUDA_TRY(ctx, b.sortState.reserve(sortPairsStateBytes(n)));
+    }
     const bool aov = !(flags & VKRT_TRACE_NO_AOV);
     if (aov)
     {
@@ -331,7 +371,17 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     {
         k_raster_setup<<<grid, 256, 0, s>>>(holder, geo, blas->vertices.as<uint8_t>(), blas->vertexStride, blas->indices.as<uint32_t>(),
                                             ctx->materials.as<VkrtSubmeshInfo>(), ctx->textureCount, n, W, H, b.setups.as<RasterSetup>(), b.smallList.as<uint32_t>(),
-                                            b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+                                            b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), sortLarge ? b.sortKeys.as<uint32_t>() : nullptr, counters);
+        if (sortLarge)
+        {
+            if (int e = sortPairsDevice(ctx, b.sortKeys.as<uint32_t>(), b.largeList.as<uint32_t>(), b.sortKeysB.as<uint32_t>(), b.sortValsB.as<uint32_t>(),
+                                        b.sortState.as<uint32_t>(), n))
+            {
+                return e;
+            }
+            k_raster_tiles<<<grid, 256, 0, s>>>(b.setups.as<RasterSetup>(), b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            ctx->launches += 1;
+        }
         k_raster_scan<<<1, 1024, 0, s>>>(b.largeTiles.as<uint32_t>(), counters);
         k_raster_small<<<grid, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         k_raster_large<<<grid, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);

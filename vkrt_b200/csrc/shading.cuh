@@ -161,7 +161,9 @@ VKRT_HD uint32_t mipLevelCount(uint32_t width, uint32_t height) // floor(log2(ma
 // One destination texel of vkCmdBlitImage(level-1 -> level, VK_FILTER_LINEAR) (src/Raytracer.cpp:610-625): the source
 // coordinate of destination texel centre i is (i + 0.5) * srcExtent / dstExtent, filtered bilinearly with
 // clamp-to-edge; for an even source extent that is the mean of a 2x2 block.  UNORM8 store as packBgra8 rounds.
-VKRT_HD uint32_t blitTexel(const uint8_t* src, uint32_t srcW, uint32_t srcH, uint32_t dstW, uint32_t dstH, uint32_t i, uint32_t j)
+// `unorm` (optional) is a 256-entry table of c / 255.0f: the same IEEE quotients, looked up instead of divided.
+VKRT_HD uint32_t blitTexel(const uint8_t* src, uint32_t srcW, uint32_t srcH, uint32_t dstW, uint32_t dstH, uint32_t i, uint32_t j,
+                           const float* unorm = nullptr)
 {
     const float sx = ((float)i + 0.5f) * ((float)srcW / (float)dstW) - 0.5f;
     const float sy = ((float)j + 0.5f) * ((float)srcH / (float)dstH) - 0.5f;
@@ -178,8 +180,9 @@ VKRT_HD uint32_t blitTexel(const uint8_t* src, uint32_t srcW, uint32_t srcH, uin
     uint32_t out = 0;
     for (int ch = 0; ch < 4; ++ch)
     {
-        const float t00 = (float)((p00 >> (8 * ch)) & 0xFFu) / 255.0f, t10 = (float)((p10 >> (8 * ch)) & 0xFFu) / 255.0f;
-        const float t01 = (float)((p01 >> (8 * ch)) & 0xFFu) / 255.0f, t11 = (float)((p11 >> (8 * ch)) & 0xFFu) / 255.0f;
+        const uint32_t c00 = (p00 >> (8 * ch)) & 0xFFu, c10 = (p10 >> (8 * ch)) & 0xFFu, c01 = (p01 >> (8 * ch)) & 0xFFu, c11 = (p11 >> (8 * ch)) & 0xFFu;
+        const float t00 = unorm ? unorm[c00] : (float)c00 / 255.0f, t10 = unorm ? unorm[c10] : (float)c10 / 255.0f;
+        const float t01 = unorm ? unorm[c01] : (float)c01 / 255.0f, t11 = unorm ? unorm[c11] : (float)c11 / 255.0f;
         const float c = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
         out |= (uint32_t)(clamp01(c) * 255.0f + 0.5f) << (8 * ch);
     }
