@@ -90,4 +90,4 @@ def test_raster_cross_checks_ray_traced_visibility(sponza_flat):
     both = (tri_rt != 0xFFFFFFFF) & (tri_rz != 0xFFFFFFFF)
     agree = float((tri_rt[both] == tri_rz[both]).mean())
     print("raster vs ray-traced primary visibility:", agree, float(both.mean()))
-    assert both.mean() > 0.5 and agree > 0.8
+    assert both.mean() > 0.9 and agree > 0.85

@@ -197,6 +197,14 @@ __global__ void __launch_bounds__(1024) k_raster_scan(uint32_t* __restrict__ lar
     }
 }
 
+// c / 255.0f for every byte value in shared memory (blocks of 256 threads): the texture filter of a fragment converts 32
+// texels' channels; ncu showed the resolve kernel with the xu pipe (conversions, reciprocals of the IEEE divisions) at 58 %.
+__device__ __forceinline__ void fillUnormTable(float* table)
+{
+    table[threadIdx.x] = (float)threadIdx.x / 255.0f;
+    __syncthreads();
+}
+
 __device__ __forceinline__ RasterSetup loadSetup(const RasterSetup* setups, uint32_t t)
 {
     RasterSetup s;
@@ -210,8 +218,11 @@ __device__ __forceinline__ RasterSetup loadSetup(const RasterSetup* setups, uint
     return s;
 }
 
-__global__ void __launch_bounds__(256) k_raster_small(RasterDev r, const uint32_t* __restrict__ smallList, const uint32_t* __restrict__ counters)
+template<int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, const uint32_t* __restrict__ smallList, const uint32_t* __restrict__ counters)
 {
+    __shared__ float unorm[256];
+    fillUnormTable(unorm);
     const uint32_t count = counters[0];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
@@ -223,7 +234,7 @@ __global__ void __launch_bounds__(256) k_raster_small(RasterDev r, const uint32_
         const uint32_t bw = x1 - x0 + 1u, n = bw * (y1 - y0 + 1u);
         for (uint32_t i = lane; i < n; i += 32u)
         {
-            rasterPixel(s, tri, r.textures, r.mips, r.width, x0 + i % bw, y0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey());
+            rasterPixel(s, tri, r.textures, r.mips, r.width, x0 + i % bw, y0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
         }
     }
 }
@@ -248,9 +259,12 @@ __device__ __forceinline__ bool tileOutside(const RasterSetup& s, uint32_t tx0, 
     return false;
 }
 
-__global__ void __launch_bounds__(256)
+template<int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS)
 k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32_t* __restrict__ largeBase, const uint32_t* __restrict__ counters)
 {
+    __shared__ float unorm[256];
+    fillUnormTable(unorm);
     const uint32_t triCount = counters[1], items = counters[2];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
@@ -284,7 +298,7 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
         const uint32_t bw = px1 - px0 + 1u, n = bw * (py1 - py0 + 1u);
         for (uint32_t i = lane; i < n; i += 32u)
         {
-            rasterPixel(s, tri, r.textures, r.mips, r.width, px0 + i % bw, py0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey());
+            rasterPixel(s, tri, r.textures, r.mips, r.width, px0 + i % bw, py0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
         }
     }
 }
@@ -292,13 +306,14 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
 __global__ void __launch_bounds__(256)
 k_raster_resolve(RasterDev r, uint32_t* __restrict__ bgra8, uint32_t* __restrict__ triangleId)
 {
+    __shared__ float unorm[256];
+    fillUnormTable(unorm);
     const uint32_t total = r.width * r.height;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
     {
-        // 8x8-pixel blocks per 64 consecutive threads keep a warp's texture fetches close together
         const uint32_t px = i % r.width, py = i / r.width;
         uint32_t first;
-        bgra8[i] = rasterResolve(r.setups, r.textures, r.mips, r.width, px, py, reinterpret_cast<const uint64_t*>(r.visibility), first);
+        bgra8[i] = rasterResolve(r.setups, r.textures, r.mips, r.width, px, py, reinterpret_cast<const uint64_t*>(r.visibility), first, unorm);
         if (triangleId)
         {
             triangleId[i] = first;
@@ -334,9 +349,11 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     VKRT_CUDA_TRY(ctx, b.largeList.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.largeTiles.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.counters.reserve(64));
-    // Large triangles are rasterised nearest first, so that later ones are mostly rejected by the keys already in place
-    // (fewer atomics and fragment evaluations); the image does not depend on the order.  VKRT_RASTER_SORT=0 turns it off.
-    static const bool sortLarge = !(getenv("VKRT_RASTER_SORT") && atoi(getenv("VKRT_RASTER_SORT")) == 0);
+    // Optional (VKRT_RASTER_SORT=1): large triangles rasterised nearest first, so that later ones are mostly rejected by
+    // the keys already in place.  The image does not depend on the order.  Measured on B200, Sponza stand-in at 4K:
+    // 4.90 ms sorted against 4.68 ms unsorted - the kernel is bound by latency at low occupancy, not by its atomics -
+    // so the default is off.
+    static const bool sortLarge = getenv("VKRT_RASTER_SORT") && atoi(getenv("VKRT_RASTER_SORT")) != 0;
     if (sortLarge && n > 0)
     {
         VKRT_CUDA_TRY(ctx, b.sortKeys.reserve((size_t)n * 4));
@@ -383,8 +400,21 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
             ctx->launches += 1;
         }
         k_raster_scan<<<1, 1024, 0, s>>>(b.largeTiles.as<uint32_t>(), counters);
-        k_raster_small<<<grid, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
-        k_raster_large<<<grid, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+        // resident blocks per SM of the two triangle kernels: 3 (80 registers) or 4 (64 registers, a few spilled words);
+        // both are latency-bound (ncu: long-scoreboard and wait stalls at 22 % of the warp slots with the first, 89-register build)
+        static const int minBlocks = getenv("VKRT_RASTER_BLOCKS") ? atoi(getenv("VKRT_RASTER_BLOCKS")) : 3;
+        if (minBlocks >= 4)
+        {
+            const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
+            k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
+            k_raster_large<4><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+        }
+        else
+        {
+            const uint32_t g3 = (uint32_t)ctx->smCount * 3u;
+            k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
+            k_raster_large<3><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+        }
         ctx->launches += 4;
     }
     if (int e = waitPresents(ctx, frame)) // the image is about to be overwritten

@@ -159,7 +159,8 @@ VKRT_HD bool rasterDepth(const RasterSetup& t, uint32_t px, uint32_t py, int s, 
 // shader.frag:15-21 for the fragment of pixel (px, py): attributes at the pixel centre (no sample shading, no centroid),
 // implicit level of detail from the analytic screen-space derivatives of uv = (U/S, V/S):
 // rho^2 = max(|d(uv*size)/dx|^2, |d(uv*size)/dy|^2).  Returns false when the fragment is discarded.
-VKRT_HD bool rasterFragment(const RasterSetup& t, const TextureRecord* textures, const TextureMips* mips, uint32_t px, uint32_t py, float rgba[4])
+VKRT_HD bool rasterFragment(const RasterSetup& t, const TextureRecord* textures, const TextureMips* mips, uint32_t px, uint32_t py, float rgba[4],
+                            const float* unorm = nullptr)
 {
     const float x = (float)px + 0.5f, y = (float)py + 0.5f;
     const float U = plane3(t.ua, t.ub, t.uc, x, y), V = plane3(t.va, t.vb, t.vc, x, y), S = plane3(t.sa, t.sb, t.sc, x, y);
@@ -171,7 +172,7 @@ VKRT_HD bool rasterFragment(const RasterSetup& t, const TextureRecord* textures,
     const float w = (float)tex.width, h = (float)tex.height;
     const float rx2 = (dudx * w) * (dudx * w) + (dvdx * h) * (dvdx * h);
     const float ry2 = (dudy * w) * (dudy * w) + (dvdy * h) * (dvdy * h);
-    sampleTrilinear(tex, mips[t.texture], u, v, fmaxf(rx2, ry2), rgba);
+    sampleTrilinear(tex, mips[t.texture], u, v, fmaxf(rx2, ry2), rgba, unorm);
     return !(rgba[3] < 0.1f);
 }
 
@@ -189,7 +190,7 @@ VKRT_HD uint32_t rasterQuantise(const float rgba[4]) // UNORM8 store of one samp
 // visibility keys of the surviving samples.  `Min` performs key = min(key, candidate) (atomicMin on the device).
 template<typename Min>
 VKRT_HD void rasterPixel(const RasterSetup& t, uint32_t tri, const TextureRecord* textures, const TextureMips* mips, uint32_t width,
-                         uint32_t px, uint32_t py, uint64_t* visibility, Min minKey)
+                         uint32_t px, uint32_t py, uint64_t* visibility, Min minKey, const float* unorm = nullptr)
 {
     const uint32_t coverage = rasterCoverage(t, px, py);
     if (!coverage)
@@ -197,16 +198,14 @@ VKRT_HD void rasterPixel(const RasterSetup& t, uint32_t tri, const TextureRecord
         return;
     }
     uint64_t* keys = visibility + ((size_t)py * width + px) * kRasterSamples;
-    uint64_t candidate[kRasterSamples];
     uint32_t alive = 0;
     for (int s = 0; s < kRasterSamples; ++s)
     {
         uint32_t depth24;
         if (((coverage >> s) & 1u) && rasterDepth(t, px, py, s, depth24))
         {
-            candidate[s] = ((uint64_t)depth24 << 32) | tri;
             // keys only ever decrease, so a sample that already holds a smaller key can never be won by this triangle
-            alive |= candidate[s] < keys[s] ? 1u << s : 0u;
+            alive |= ((((uint64_t)depth24) << 32) | tri) < keys[s] ? 1u << s : 0u;
         }
     }
     if (!alive)
@@ -214,15 +213,16 @@ VKRT_HD void rasterPixel(const RasterSetup& t, uint32_t tri, const TextureRecord
         return;
     }
     float rgba[4];
-    if (!rasterFragment(t, textures, mips, px, py, rgba))
+    if (!rasterFragment(t, textures, mips, px, py, rgba, unorm))
     {
         return; // discard: no depth write either
     }
     for (int s = 0; s < kRasterSamples; ++s)
     {
-        if ((alive >> s) & 1u)
+        uint32_t depth24; // evaluated again rather than kept: eight 64-bit candidates cost 16 registers per thread
+        if (((alive >> s) & 1u) && rasterDepth(t, px, py, s, depth24))
         {
-            minKey(&keys[s], candidate[s]);
+            minKey(&keys[s], (((uint64_t)depth24) << 32) | tri);
         }
     }
 }
@@ -231,7 +231,7 @@ VKRT_HD void rasterPixel(const RasterSetup& t, uint32_t tri, const TextureRecord
 // quantised to UNORM8 as the multisampled colour attachment stores it) or the clear colour; the 8 samples are averaged
 // (vkCmdResolveImage / resolve attachment) and stored as B8G8R8A8.  Returns B | G<<8 | R<<16 | A<<24.
 VKRT_HD uint32_t rasterResolve(const RasterSetup* setups, const TextureRecord* textures, const TextureMips* mips, uint32_t width, uint32_t px,
-                               uint32_t py, const uint64_t* visibility, uint32_t& firstTriangle)
+                               uint32_t py, const uint64_t* visibility, uint32_t& firstTriangle, const float* unorm = nullptr)
 {
     const uint64_t* keys = visibility + ((size_t)py * width + px) * kRasterSamples;
     uint32_t sum[4] = {0, 0, 0, 0};
@@ -251,7 +251,7 @@ VKRT_HD uint32_t rasterResolve(const RasterSetup* setups, const TextureRecord* t
             if (tri != lastTri)
             {
                 float rgba[4];
-                rasterFragment(setups[tri], textures, mips, px, py, rgba);
+                rasterFragment(setups[tri], textures, mips, px, py, rgba, unorm);
                 lastColour = rasterQuantise(rgba);
                 lastTri = tri;
             }

@@ -102,8 +102,9 @@ VKRT_HD uint32_t loadTexel(const uint8_t* texels, size_t index)
 }
 
 // Bilinear REPEAT sample of one RGBA8 image level (LINEAR mag/min, src/Raytracer.cpp:436-458,467); Vulkan texel
-// addressing u*W - 0.5.
-VKRT_HD void sampleLevel(const uint8_t* texels, uint32_t width, uint32_t height, float u, float v, float rgba[4])
+// addressing u*W - 0.5.  `unorm` (optional) is a 256-entry table of c / 255.0f: the identical IEEE quotients, looked up
+// (shared memory) instead of divided - the rasteriser kernels, which filter a texture per fragment, pass one.
+VKRT_HD void sampleLevel(const uint8_t* texels, uint32_t width, uint32_t height, float u, float v, float rgba[4], const float* unorm = nullptr)
 {
     float x = u * (float)width - 0.5f;
     float y = v * (float)height - 0.5f;
@@ -126,9 +127,18 @@ VKRT_HD void sampleLevel(const uint8_t* texels, uint32_t width, uint32_t height,
     const uint32_t p11 = loadTexel(texels, (size_t)y1 * width + x1);
     for (int ch = 0; ch < 4; ++ch)
     {
-        const float t00 = (float)((p00 >> (8 * ch)) & 0xFFu) / 255.0f, t10 = (float)((p10 >> (8 * ch)) & 0xFFu) / 255.0f;
-        const float t01 = (float)((p01 >> (8 * ch)) & 0xFFu) / 255.0f, t11 = (float)((p11 >> (8 * ch)) & 0xFFu) / 255.0f;
-        rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+        if (unorm)
+        {
+            const float t00 = unorm[(p00 >> (8 * ch)) & 0xFFu], t10 = unorm[(p10 >> (8 * ch)) & 0xFFu];
+            const float t01 = unorm[(p01 >> (8 * ch)) & 0xFFu], t11 = unorm[(p11 >> (8 * ch)) & 0xFFu];
+            rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+        }
+        else
+        {
+            const float t00 = (float)((p00 >> (8 * ch)) & 0xFFu) / 255.0f, t10 = (float)((p10 >> (8 * ch)) & 0xFFu) / 255.0f;
+            const float t01 = (float)((p01 >> (8 * ch)) & 0xFFu) / 255.0f, t11 = (float)((p11 >> (8 * ch)) & 0xFFu) / 255.0f;
+            rgba[ch] = ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
+        }
     }
 }
 
@@ -221,11 +231,12 @@ VKRT_HD float coneFootprint2(F3 p0, F3 p1, F3 p2, float u0, float v0, float u1, 
 // Trilinear sample (mip LINEAR, minLod 0, no maxLod: src/Raytracer.cpp:436-458, src/Rasterizer.cpp:484-498) for a squared
 // footprint of `texels2` level-0 texels: lambda = 0.5 * log2(texels2), clamped to the chain.  A footprint that is not
 // > 1 texel (magnification, degenerate triangles or uv, NaN, inf) samples level 0 exactly as sampleTexture does.
-VKRT_HD void sampleTrilinear(const TextureRecord& tex, const TextureMips& mips, float u, float v, float texels2, float rgba[4])
+VKRT_HD void sampleTrilinear(const TextureRecord& tex, const TextureMips& mips, float u, float v, float texels2, float rgba[4],
+                             const float* unorm = nullptr)
 {
     if (!(texels2 > 1.0f) || !finite1(texels2) || mips.levels <= 1u)
     {
-        sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba);
+        sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba, unorm);
         return;
     }
     float lambda = 0.5f * lodLog2(texels2);
@@ -245,12 +256,12 @@ VKRT_HD void sampleTrilinear(const TextureRecord& tex, const TextureMips& mips, 
     }
     const uint8_t* base0 = l0 == 0 ? tex.texels : mips.texels + offset;
     const uint32_t w0 = mipExtent(tex.width, l0), h0 = mipExtent(tex.height, l0);
-    sampleLevel(base0, w0, h0, u, v, rgba);
+    sampleLevel(base0, w0, h0, u, v, rgba, unorm);
     if (frac > 0.0f) // l0 < levels - 1 here, because lambda <= levels - 1
     {
         const uint8_t* base1 = l0 == 0 ? mips.texels : base0 + (size_t)w0 * h0 * 4;
         float hi[4];
-        sampleLevel(base1, mipExtent(tex.width, l0 + 1), mipExtent(tex.height, l0 + 1), u, v, hi);
+        sampleLevel(base1, mipExtent(tex.width, l0 + 1), mipExtent(tex.height, l0 + 1), u, v, hi, unorm);
         for (int ch = 0; ch < 4; ++ch)
         {
             rgba[ch] = rgba[ch] * (1.0f - frac) + hi[ch] * frac;

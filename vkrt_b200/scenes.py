@@ -332,6 +332,10 @@ def sponza_standin_submeshes(layout: Optional[Dict] = None) -> List[Dict]:
         verts = np.concatenate(verts_list, axis=0)
         idx = np.concatenate(idx_list, axis=0)
         assert idx.size == 3 * T, (pi, idx.size, T)
+        # glTF front faces are counter-clockwise seen from the side the normal points to, and so are the real Sponza's;
+        # _element emits the opposite order.  The ray tracer does not care (no culling, src/Raytracer.cpp:1176), the
+        # rasteriser culls back faces (src/Rasterizer.cpp:803-804) and would show the insides of the elements.
+        idx = idx.reshape(-1, 3)[:, [0, 2, 1]].reshape(-1)
         assert verts.shape[0] <= V, (pi, verts.shape[0], V)
         if verts.shape[0] < V:  # pad with unreferenced copies of vertex 0 to the accessor's count
             verts = np.concatenate([verts, np.repeat(verts[:1], V - verts.shape[0], axis=0)], axis=0)
