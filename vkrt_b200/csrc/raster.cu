@@ -400,9 +400,10 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
             ctx->launches += 1;
         }
         k_raster_scan<<<1, 1024, 0, s>>>(b.largeTiles.as<uint32_t>(), counters);
-        // resident blocks per SM of the two triangle kernels: 3 (80 registers) or 4 (64 registers, a few spilled words);
-        // both are latency-bound (ncu: long-scoreboard and wait stalls at 22 % of the warp slots with the first, 89-register build)
-        static const int minBlocks = getenv("VKRT_RASTER_BLOCKS") ? atoi(getenv("VKRT_RASTER_BLOCKS")) : 3;
+        // resident blocks per SM of the two triangle kernels: 4 (64 registers, 17 spilled words; default) or 3 (80 registers).
+        // They are latency-bound (ncu on the first, 89-register build: long-scoreboard and wait stalls with 22 % of the warp
+        // slots filled); Sponza stand-in at 4K on B200: 4.68 ms per frame at 2 blocks, 4.12 ms at 3, 3.87 ms at 4.
+        static const int minBlocks = getenv("VKRT_RASTER_BLOCKS") ? atoi(getenv("VKRT_RASTER_BLOCKS")) : 4;
         if (minBlocks >= 4)
         {
             const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
