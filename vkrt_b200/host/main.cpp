@@ -1,6 +1,8 @@
-// main.cpp — headless counterpart of the reference's src/main.cpp:5-18: build a Context and a Raytracer, loop
-// render() until it returns false; optionally dump frames and print per-run statistics as one JSON line.
+// main.cpp — headless counterpart of the reference's src/main.cpp:5-18: build a Context and a Raytracer (or, with
+// --renderer raster, the Rasterizer the reference keeps commented out at src/main.cpp:8), loop render() until it returns
+// false; optionally dump frames and print per-run statistics as one JSON line.
 #include "Context.hpp"
+#include "Rasterizer.hpp"
 #include "Raytracer.hpp"
 
 #include <chrono>
@@ -15,6 +17,7 @@ int main(int argc, char** argv)
     options.width = 1280, options.height = 720; // BASELINE.json config 1
     uint32_t spp = 1;
     int textureLod = VKRT_TEXTURE_LOD_ZERO;
+    bool rasterizer = false;
     std::string out;
     for (int i = 1; i < argc; ++i)
     {
@@ -29,11 +32,12 @@ int main(int argc, char** argv)
         else if (a == "--models") Model::setModelsFolder(next());
         else if (a == "--out") out = next();
         else if (a == "--comm-file") options.commFile = next();
+        else if (a == "--renderer") rasterizer = std::string(next()) == "raster";
         else if (a == "--texture-lod") textureLod = std::string(next()) == "cones" ? VKRT_TEXTURE_LOD_RAY_CONES : VKRT_TEXTURE_LOD_ZERO;
         else
         {
             printf("usage: %s [--width W] [--height H] [--frames N] [--spp S] [--device D] [--script W:150,Z:150] [--models DIR] "
-                   "[--out frame_prefix] [--comm-file PATH] [--texture-lod zero|cones]\n", argv[0]);
+                   "[--out frame_prefix] [--comm-file PATH] [--texture-lod zero|cones] [--renderer raytrace|raster]\n", argv[0]);
             return a == "--help" ? 0 : 2;
         }
     }
@@ -43,6 +47,28 @@ int main(int argc, char** argv)
     if (options.worldSize > 1 && options.commFile.empty()) options.commFile = "/tmp/vkrt_comm_id";
 
     Context context(options);
+    if (rasterizer)
+    {
+        Rasterizer graphicsApp(context); // src/main.cpp:8
+        const auto t0 = std::chrono::steady_clock::now();
+        uint64_t frames = 0;
+        while (graphicsApp.render())
+        {
+            ++frames;
+            if (!out.empty())
+            {
+                char name[512];
+                snprintf(name, sizeof(name), "%s%04llu.ppm", out.c_str(), static_cast<unsigned long long>(frames - 1));
+                graphicsApp.saveFrame(name);
+            }
+        }
+        vkrt_context_synchronize(context.getDevice());
+        const double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        printf("{\"renderer\": \"raster\", \"frames\": %llu, \"seconds\": %.6f, \"triangles\": %llu, \"kernel_launches\": %llu}\n",
+               static_cast<unsigned long long>(frames), seconds, static_cast<unsigned long long>(graphicsApp.getBlasInfo().triangleCount),
+               static_cast<unsigned long long>(graphicsApp.getStats().kernelLaunches));
+        return 0;
+    }
     Raytracer graphicsApp(context);
     graphicsApp.setSamplesPerPixel(spp);
     graphicsApp.setTextureLod(textureLod);
