@@ -28,6 +28,9 @@ static void dump(const Camera& cam, const char* label, bool last)
 {
     const glm::mat4 view = cam.getViewMatrix(), proj = cam.getProjectionMatrix();
     const glm::mat4 viewInverse = glm::inverse(view), projInverse = glm::inverse(proj);
+    // Rasterizer::update, /root/reference/src/Rasterizer.cpp:189-190 (glm::scale(v) of gtx/transform.hpp is scale(mat4(1), v))
+    const glm::mat4 scaleMatrix = glm::scale(glm::mat4(1.0f), glm::vec3(0.01f, 0.01f, 0.01f));
+    const glm::mat4 wvpMatrix = proj * view * scaleMatrix;
     const glm::vec3 f = cam.getForward(), l = cam.getLeft(), u = cam.getUp(), p = cam.getPosition();
     printf("  {\n    \"label\": \"%s\",\n", label);
     printBits("position", &p.x, 3);
@@ -37,7 +40,8 @@ static void dump(const Camera& cam, const char* label, bool last)
     printBits("view", &view[0][0], 16);
     printBits("proj", &proj[0][0], 16);
     printBits("viewInverse", &viewInverse[0][0], 16);
-    printBits("projInverse", &projInverse[0][0], 16, true);
+    printBits("projInverse", &projInverse[0][0], 16);
+    printBits("wvp", &wvpMatrix[0][0], 16, true);
     printf("  }%s\n", last ? "" : ",");
 }
 
@@ -66,6 +70,12 @@ int main()
             cam.rotate(c_up, rotationAmount);
         }
         dump(cam, "after_150_W_150_Z", false);
+    }
+    {
+        Camera cam; // Rasterizer::setupCamera, src/Rasterizer.cpp:207-211
+        cam.setPosition({-4.0f, 2.0f, -0.2f});
+        cam.setRotation({0.0f, 1.51f, 0.0f});
+        dump(cam, "rasterizer_default", false);
     }
     {
         Camera cam;

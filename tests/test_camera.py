@@ -21,6 +21,7 @@ def _check(cam, ref):
     assert bits(cam.getUp()) == ref["up"]
     assert bits(cam.getViewMatrix()) == ref["view"]
     assert bits(cam.getProjectionMatrix()) == ref["proj"]
+    assert bits(cam.wvp(0.01)) == ref["wvp"]  # proj * view * scale(0.01) as glm multiplies it (src/Rasterizer.cpp:189-190)
     u = camera.uniforms_to_array(cam.uniforms())
     assert bits(u[0:16]) == ref["viewInverse"]
     assert bits(u[16:32]) == ref["projInverse"]
@@ -44,6 +45,10 @@ def test_camera_bit_exact_against_reference():
     for _ in range(150):
         cam.rotate((0, 1, 0), ra)
     _check(cam, g["after_150_W_150_Z"])
+    cam = camera.Camera()
+    cam.setPosition((-4.0, 2.0, -0.2))
+    cam.setRotation((0.0, 1.51, 0.0))
+    _check(cam, g["rasterizer_default"])
     cam = camera.Camera()
     cam.setPosition((-25.0, 45.0, -20.0))
     cam.setRotation((-0.6, -2.1, 0.1))
