@@ -31,7 +31,10 @@ WORKLOADS = {
     "config3": (3840, 2160, 8, "Sponza 3840x2160 8 spp jittered (Halton 2,3), 64x64 interleaved tiles over ranks"),
     "config4": (3840, 2160, 1, "4x4 instanced Sponza grid (16 instances) 3840x2160 1 spp"),
     "config5": (3840, 2160, 1, "procedural triangle soup, full BVH rebuild every frame, 3840x2160 1 spp"),
+    # SURVEY 8 f4 (not one of BASELINE.json's configs): the reference's Rasterizer path, single GPU
+    "raster": (3840, 2160, 1, "Sponza 3840x2160 through the rasteriser path (shader.vert/.frag, 8x MSAA, depth test, alpha test)"),
 }
+RASTER_METRIC = "Sponza 4K rasteriser Mpixel/s (8x MSAA)"
 
 
 def read_traffic(workload):
@@ -171,6 +174,123 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def raster_cpu_baseline(model, W, Hh, repeats=1):
+    """The oracle's z-buffer restatement of the reference's Rasterizer on all host cores; a bounded frame size."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
+    from vkrt_b200 import camera, scenes
+    from vkrt_b200.raytracer import flatten_model
+
+    o = H.OracleScene(flatten_model(model), scenes.REFERENCE_INSTANCE)
+    o.generate_mips()
+    cam = camera.Camera(np.float32(W) / np.float32(Hh))
+    cam.setPosition((-4.0, 2.0, -0.2))  # Rasterizer::setupCamera, src/Rasterizer.cpp:207-211
+    cam.setRotation((0.0, 1.51, 0.0))
+    wvp = cam.wvp(0.01)
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        o.rasterize(wvp, W, Hh, threads=cores)
+    dt = (time.perf_counter() - t0) / repeats
+    return {"value": W * Hh / dt / 1e6, "unit": "Mpixel/s", "cores": cores, "kind": "port",
+            "sample": f"one {W}x{Hh} frame of the same scene and pose ({dt:.2f} s per frame; every band of rows walks all 262,267 triangles)"}
+
+
+def run_raster(args):
+    """--workload raster: one step = one vkrt_rasterize frame.  Single GPU (the rasteriser does not split frames over ranks)."""
+    from vkrt_b200 import scenes
+
+    W, Hh, _, desc = WORKLOADS["raster"]
+    model = scenes.sponza_standin()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        cw, ch = 1280, 720
+        steps = max(args.steps, 1)
+        c = raster_cpu_baseline(model, cw, ch, repeats=steps)
+        print(json.dumps({"impl": "reference", "metric": RASTER_METRIC, "value": c["value"], "unit": "Mpixel/s", "n_gpus": args.gpus,
+                          "steps": steps, "warmup": 0, "ms_per_step": cw * ch / c["value"] / 1e3, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                          "config": {"workload": f"raster: {desc}", "scene": model["provenance"],
+                                     "note": "the reference's Vulkan rasteriser is unavailable on this box; CPU oracle (z-buffer restatement) timed"},
+                          "cpu_baseline": c, "e2e": {"value": c["value"], "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}),
+              flush=True)
+        return
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        raise SystemExit("bench.py --workload raster runs on one GPU (replicas only: the rasteriser does not partition a frame)")
+    import torch
+
+    from vkrt_b200 import binding as B
+    from vkrt_b200.raytracer import Rasterizer
+
+    torch.cuda.set_device(0)
+    rz = Rasterizer(model, W, Hh, device=0)
+    stream = torch.cuda.ExternalStream(rz.ctx.stream, device=0)
+    for _ in range(args.warmup):
+        rz.render(B.TRACE_NO_AOV)
+    rz.ctx.synchronize()
+    launches0 = int(rz.ctx.stats().kernelLaunches)
+    sampler = ClockSampler(0)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        rz.render(B.TRACE_NO_AOV)
+    e1.record(stream)
+    rz.ctx.synchronize()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = int(rz.ctx.stats().kernelLaunches) - launches0
+    # end to end: the 64-byte matrix goes in with every call, the resolved frame comes back through the presentation ring
+    ring = [rz.ctx.host_array((Hh, W, 4)) for _ in range(3)]
+    tickets = [None, None, None]
+
+    def e2e_step(k):
+        if tickets[k % 3] is not None:
+            rz.frame.present_wait(tickets[k % 3])
+        rz.render(B.TRACE_NO_AOV)
+        tickets[k % 3] = rz.frame.present(ring[k % 3])
+
+    def drain():
+        for i, t in enumerate(tickets):
+            if t is not None:
+                rz.frame.present_wait(t)
+                tickets[i] = None
+        rz.ctx.synchronize()
+
+    for k in range(3):
+        e2e_step(k)
+    drain()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        e2e_step(k)
+    drain()
+    e2e_s = time.perf_counter() - t0
+    tris = int(rz.blas.info().triangleCount)
+    px = W * Hh
+    peak, peak_src = read_peaks()
+    algo = px * (64 + 64 + 4) + tris * (76 + 96)  # keys cleared + keys resolved + image; set-up read + write (DESIGN 5.4)
+    line = {
+        "metric": RASTER_METRIC, "value": px * args.steps / (ms * 1e-3) / 1e6, "unit": "Mpixel/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"raster: {desc}", "scene": model["provenance"], "width": W, "height": Hh, "msaa": 8, "triangles": tris,
+                   "l2": "the 531 MB visibility-key buffer of a 4K frame exceeds the 126 MB L2; no explicit flush"},
+        "mtri_s": tris * args.steps / (ms * 1e-3) / 1e6,
+        "e2e": {"value": px * args.steps / e2e_s / 1e6, "unit": "Mpixel/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": px * 4},
+        "gpu_launches": launches, "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": algo * args.steps / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": algo * args.steps / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "note": "whole frame, algorithmic bytes 132 B/pixel + 172 B/triangle; ncu (profiles/r01_ncu_raster_kernels_v1.txt) shows the "
+                             "dominant kernel k_raster_large latency-bound at low occupancy, DRAM at 14 % of peak"},
+    }
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = raster_cpu_baseline(model, 1280, 720)
+    print(json.dumps(line), flush=True)
+    rz.close()
+
+
 def main():
     # stdout carries exactly one JSON line: this image exports NCCL_DEBUG=VERSION, which makes NCCL printf its version banner
     # to stdout; other NCCL_DEBUG levels (a user asking for INFO) are left alone but sent to stderr
@@ -193,6 +313,9 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
+    if args.workload == "raster":
+        run_raster(args)
+        return
     if args.impl == "reference":
         run_reference(args)
         return
