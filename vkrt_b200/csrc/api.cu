@@ -46,7 +46,7 @@ extern "C" {
 
 int vkrt_version(void)
 {
-    return 100; // 0.1.0
+    return 200; // 0.2.0: + mip chain, texture level of detail, rasteriser
 }
 
 int vkrt_context_create(int deviceOrdinal, VkrtContext** out)
