@@ -340,8 +340,8 @@ void emu_scene_generate_mips(EmuScene* s)
     }
 }
 
-// Sequential form of rasterizeFrame (raster.cu): set-up of every triangle, rasterPixel over its bounding box (the
-// small/large split and the tile rejection of the kernels only skip pixels that rasterPixel would reject), resolve.
+// Sequential form of rasterizeFrame (raster.cu): set-up of every triangle, the small / large split of k_raster_setup,
+// whole bounding boxes for small triangles, 16x16 tiles with the conservative edge rejection for large ones, resolve.
 void emu_rasterize(const EmuScene* s, const float* wvp, uint32_t width, uint32_t height, uint8_t* bgra8, uint32_t* triangleId)
 {
     const EmuBlas* b = s->blas;
@@ -371,11 +371,35 @@ void emu_rasterize(const EmuScene* s, const float* wvp, uint32_t width, uint32_t
             continue;
         }
         const uint32_t x0 = rs.bboxX & 0xFFFFu, x1 = rs.bboxX >> 16, y0 = rs.bboxY & 0xFFFFu, y1 = rs.bboxY >> 16;
-        for (uint32_t py = y0; py <= y1; ++py)
+        if (x1 - x0 < 32u && y1 - y0 < 32u) // k_raster_small: the whole bounding box
         {
-            for (uint32_t px = x0; px <= x1; ++px)
+            for (uint32_t py = y0; py <= y1; ++py)
             {
-                rasterPixel(rs, t, s->textures.data(), s->mips.data(), width, px, py, visibility.data(), minKey);
+                for (uint32_t px = x0; px <= x1; ++px)
+                {
+                    rasterPixel(rs, t, s->textures.data(), s->mips.data(), width, px, py, visibility.data(), minKey);
+                }
+            }
+            continue;
+        }
+        // k_raster_large: 16x16-pixel tiles of the bounding box, each rejected conservatively against the three edges
+        for (uint32_t ty = y0 / kRasterTile; ty <= y1 / kRasterTile; ++ty)
+        {
+            for (uint32_t tx = x0 / kRasterTile; tx <= x1 / kRasterTile; ++tx)
+            {
+                const uint32_t px0 = std::max(tx * kRasterTile, x0), px1 = std::min(tx * kRasterTile + kRasterTile - 1u, x1);
+                const uint32_t py0 = std::max(ty * kRasterTile, y0), py1 = std::min(ty * kRasterTile + kRasterTile - 1u, y1);
+                if (rasterTileOutside(rs, px0, py0, px1, py1))
+                {
+                    continue;
+                }
+                for (uint32_t py = py0; py <= py1; ++py)
+                {
+                    for (uint32_t px = px0; px <= px1; ++px)
+                    {
+                        rasterPixel(rs, t, s->textures.data(), s->mips.data(), width, px, py, visibility.data(), minKey);
+                    }
+                }
             }
         }
     }

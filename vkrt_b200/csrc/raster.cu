@@ -239,26 +239,6 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, c
     }
 }
 
-// true when the tile [tx0, tx1] x [ty0, ty1] (pixel indices, inclusive) lies entirely outside one edge
-__device__ __forceinline__ bool tileOutside(const RasterSetup& s, uint32_t tx0, uint32_t ty0, uint32_t tx1, uint32_t ty1)
-{
-    // samples lie strictly inside (px, px + 1): the extreme sample coordinates are bounded by the tile's outer corners;
-    // the small pad keeps the test conservative against the rounding of the plane evaluation
-    const float lx = (float)tx0, hx = (float)(tx1 + 1u), ly = (float)ty0, hy = (float)(ty1 + 1u);
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-    {
-        const float a = s.ea[i], b = s.eb[i], c = s.ec[i];
-        const float best = (a * (a > 0.0f ? hx : lx) + b * (b > 0.0f ? hy : ly)) + c;
-        const float pad = (fabsf(a) * hx + fabsf(b) * hy + fabsf(c)) * 1e-5f;
-        if (best < -pad)
-        {
-            return true;
-        }
-    }
-    return false;
-}
-
 template<int MIN_BLOCKS>
 __global__ void __launch_bounds__(256, MIN_BLOCKS)
 k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32_t* __restrict__ largeBase, const uint32_t* __restrict__ counters)
@@ -291,7 +271,7 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
         const uint32_t tx = x0 / kRasterTile + local % tilesX, ty = y0 / kRasterTile + local / tilesX;
         const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
         const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
-        if (tileOutside(s, px0, py0, px1, py1))
+        if (rasterTileOutside(s, px0, py0, px1, py1))
         {
             continue;
         }

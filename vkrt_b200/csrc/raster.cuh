@@ -227,6 +227,25 @@ VKRT_HD void rasterPixel(const RasterSetup& t, uint32_t tri, const TextureRecord
     }
 }
 
+// true when the tile [tx0, tx1] x [ty0, ty1] (pixel indices, inclusive) lies entirely outside one edge
+VKRT_HD bool rasterTileOutside(const RasterSetup& s, uint32_t tx0, uint32_t ty0, uint32_t tx1, uint32_t ty1)
+{
+    // samples lie strictly inside (px, px + 1): the extreme sample coordinates are bounded by the tile's outer corners;
+    // the small pad keeps the test conservative against the rounding of the plane evaluation
+    const float lx = (float)tx0, hx = (float)(tx1 + 1u), ly = (float)ty0, hy = (float)(ty1 + 1u);
+    for (int i = 0; i < 3; ++i)
+    {
+        const float a = s.ea[i], b = s.eb[i], c = s.ec[i];
+        const float best = (a * (a > 0.0f ? hx : lx) + b * (b > 0.0f ? hy : ly)) + c;
+        const float pad = (fabsf(a) * hx + fabsf(b) * hy + fabsf(c)) * 1e-5f;
+        if (best < -pad)
+        {
+            return true;
+        }
+    }
+    return false;
+}
+
 // Resolve of pixel (px, py): every sample takes the colour of the triangle that won it (shaded at the pixel centre,
 // quantised to UNORM8 as the multisampled colour attachment stores it) or the clear colour; the 8 samples are averaged
 // (vkCmdResolveImage / resolve attachment) and stored as B8G8R8A8.  Returns B | G<<8 | R<<16 | A<<24.
