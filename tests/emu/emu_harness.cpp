@@ -142,7 +142,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     bvh.nodes = binNodes.data(), bvh.flags = flags.data();
     bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
     bvh.count = n, bvh.root = &root;
-    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
+    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f, bvh.maxLeaf = kMaxLeafTris;
     if (n > 1)
     {
         for (uint32_t i = 0; i < n; ++i)

@@ -103,6 +103,7 @@ struct Bvh2
     uint32_t* dpChoice; // per binary node: split decisions
     int* dpParent;      // [0, count): parent of sorted leaf i; [count, 2*count-1): parent of binary node i - count
     float dpPrimCost;   // cost of one triangle test relative to one node test
+    uint32_t maxLeaf;   // primitives per leaf slot: kMaxLeafTris for a BLAS, 1 for a TLAS (one instance per slot)
 };
 
 VKRT_HD uint64_t lbvhDelta(const Bvh2& b, uint32_t j) // distance between sorted leaves j and j+1
@@ -351,7 +352,7 @@ VKRT_HD void dpSolve(const Bvh2& b, int ref)
     const float area = halfArea(f3(lo.x, lo.y, lo.z), f3(hi.x, hi.y, hi.z));
     const uint32_t count = floatAsUint(lo.w);
     float c[8];
-    c[1] = count <= kMaxLeafTris ? area * (float)count * b.dpPrimCost : area + dist[8];
+    c[1] = count <= b.maxLeaf ? area * (float)count * b.dpPrimCost : area + dist[8];
     for (int i = 2; i < 8; ++i)
     {
         if (dist[i] < c[i - 1])
@@ -493,7 +494,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
 
     CollapseChild c[8];
     int n = 0;
-    if (rootRef < 0 || self.count <= kMaxLeafTris)
+    if (rootRef < 0 || self.count <= b.maxLeaf)
     {
         // whole BLAS has <= 3 triangles: the root holds one leaf child
         c[0] = self;
@@ -522,7 +523,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             float bestArea = -1.0f;
             for (int k = 0; k < n; ++k)
             {
-                if (c[k].count > kMaxLeafTris)
+                if (c[k].count > b.maxLeaf)
                 {
                     const float ar = halfArea(c[k].lo, c[k].hi);
                     if (ar > bestArea)
@@ -548,7 +549,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             float bestArea = -1.0f;
             for (int k = 0; k < n; ++k)
             {
-                if (c[k].count > 1 && c[k].count <= kMaxLeafTris)
+                if (c[k].count > 1 && c[k].count <= b.maxLeaf)
                 {
                     const float ar = halfArea(c[k].lo, c[k].hi);
                     if (ar > bestArea)
@@ -622,7 +623,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     uint32_t innerCount = 0, primCount = 0;
     for (int k = 0; k < n; ++k)
     {
-        if (c[k].count > kMaxLeafTris)
+        if (c[k].count > b.maxLeaf)
         {
             ++innerCount;
         }
@@ -667,7 +668,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
         node.qhix[s] = (uint8_t)quantHi(c[k].hi.x, self.lo.x, sx);
         node.qhiy[s] = (uint8_t)quantHi(c[k].hi.y, self.lo.y, sy);
         node.qhiz[s] = (uint8_t)quantHi(c[k].hi.z, self.lo.z, sz);
-        if (c[k].count > kMaxLeafTris)
+        if (c[k].count > b.maxLeaf)
         {
             node.imask |= (uint8_t)(1u << s);
             a.taskRef[childBase + innerSeen] = c[k].ref;

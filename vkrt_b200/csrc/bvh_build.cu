@@ -5,6 +5,7 @@
 // all per-triangle streams are coalesced 4/16-byte accesses, the sort stages tiles through shared memory.
 #include "builder.cuh"
 #include "context.hpp"
+#include "traverse.cuh"
 
 #include <algorithm>
 #include <cfloat>
@@ -803,7 +804,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
     uint32_t n = 0;
     if (valid)
     {
-        if (rootRef < 0 || self.count <= kMaxLeafTris)
+        if (rootRef < 0 || self.count <= b.maxLeaf)
         {
             n = 1;
             if (l8 == 0)
@@ -857,7 +858,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
 #pragma unroll 1
     for (int iter = 0; iter < 6; ++iter)
     {
-        const uint32_t cat = (l8 < n && opening) ? (c.count > kMaxLeafTris ? innerCat : (c.count > 1u ? 1u : 0u)) : 0u;
+        const uint32_t cat = (l8 < n && opening) ? (c.count > b.maxLeaf ? innerCat : (c.count > 1u ? 1u : 0u)) : 0u;
         float area = cat ? halfArea(c.lo, c.hi) : -1.0f;
         uint32_t bestCat = cat, bestIdx = l8;
 #pragma unroll
@@ -974,7 +975,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
     d.hi.x = __shfl_sync(full, c.hi.x, from), d.hi.y = __shfl_sync(full, c.hi.y, from), d.hi.z = __shfl_sync(full, c.hi.z, from);
     d.count = __shfl_sync(full, c.count, from);
     const bool present = src >= 0;
-    const bool inner = present && d.count > kMaxLeafTris;
+    const bool inner = present && d.count > b.maxLeaf;
     const bool leaf = present && !inner;
 
     const uint32_t innerMask = (__ballot_sync(full, inner) >> base) & 0xFFu;
@@ -1298,6 +1299,265 @@ int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t coun
     return r;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Top-level input: world boxes of the instances (replaces the instance-buffer read of the TLAS build,
+// src/Raytracer.cpp:1179-1215).  Same outputs as k_tri_bounds: one box per primitive + scene / centroid bounds.
+// ------------------------------------------------------------------------------------------------
+namespace
+{
+__global__ void __launch_bounds__(kThreads)
+k_instance_bounds(const InstanceRecord* __restrict__ instances, uint32_t count, float4* __restrict__ triBox, uint32_t* sceneBounds)
+{
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        float l[3], h[3];
+        instanceWorldBounds(instances[i], l, h);
+        triBox[2 * (size_t)i] = make_float4(l[0], l[1], l[2], 0.0f);
+        triBox[2 * (size_t)i + 1] = make_float4(h[0], h[1], h[2], 0.0f);
+        for (int k = 0; k < 3; ++k)
+        {
+            const float c = 0.5f * (l[k] + h[k]);
+            lo[k] = fminf(lo[k], l[k]), hi[k] = fmaxf(hi[k], h[k]);
+            clo[k] = fminf(clo[k], c), chi[k] = fmaxf(chi[k], c);
+        }
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        const float a = warpMin(lo[k]), b = warpMax(hi[k]), c = warpMin(clo[k]), d = warpMax(chi[k]);
+        if ((threadIdx.x & 31) == 0)
+        {
+            atomicMin(&sceneBounds[k], orderedFromFloat(a));
+            atomicMax(&sceneBounds[3 + k], orderedFromFloat(b));
+            atomicMin(&sceneBounds[6 + k], orderedFromFloat(c));
+            atomicMax(&sceneBounds[9 + k], orderedFromFloat(d));
+        }
+    }
+}
+
+// Top-level leaves: Node8::reserved = mask of leaf slots (one instance each), see traverse.cuh.
+__global__ void __launch_bounds__(kThreads) k_tlas_finalize(Node8* nodes, uint32_t count)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count)
+    {
+        const uint32_t bits = nodes[i].leafBits;
+        uint32_t m = 0;
+        for (int sl = 0; sl < 8; ++sl)
+        {
+            m |= ((bits >> (3 * sl)) & 1u) << sl;
+        }
+        nodes[i].reserved = (uint8_t)m;
+    }
+}
+
+struct HierarchyResult
+{
+    uint32_t nodeCount = 0;
+    uint32_t levels = 0; // wide levels = longest root-to-leaf node path
+    float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
+    float sahCost = 0.0f;
+};
+
+int reserveBuildScratch(Context* ctx, uint32_t n, uint32_t nodeCapacity, bool packed)
+{
+    BuildScratch& sc = ctx->buildScratch;
+    const size_t n1 = std::max<size_t>(n, 1);
+    VKRT_CUDA_TRY(ctx, sc.triBox.reserve(n1 * 2 * sizeof(float4)));
+    if (packed)
+    {
+        VKRT_CUDA_TRY(ctx, sc.packedBuild.reserve(n1 * sizeof(PackedTri)));
+    }
+    VKRT_CUDA_TRY(ctx, sc.keysA.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.keysB.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.valsA.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.valsB.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(sortStateBytes(n)));
+    VKRT_CUDA_TRY(ctx, sc.binNodes.reserve(n1 * sizeof(BinNode)));
+    VKRT_CUDA_TRY(ctx, sc.flags.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.taskRef.reserve((size_t)nodeCapacity * 4));
+    VKRT_CUDA_TRY(ctx, sc.primSource.reserve(n1 * 4));
+    VKRT_CUDA_TRY(ctx, sc.small.reserve(256));
+    return VKRT_SUCCESS;
+}
+
+// The part of the builder that only sees boxes: Morton codes -> onesweep sort -> PLOC / LBVH -> (cost-optimal)
+// collapse into `nodes`.  On entry buildScratch.triBox holds the n boxes and `small` the reduced scene bounds
+// (k_tri_bounds / k_instance_bounds, stream-ordered).  On return buildScratch.primSource[0..n) is the primitive order
+// the leaves refer to, and everything is complete on the host side (the function synchronises).
+int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8* nodes, uint32_t nodeCapacity, HierarchyResult& out)
+{
+    cudaStream_t s = ctx->stream;
+    const int sm = ctx->smCount;
+    BuildScratch& sc = ctx->buildScratch;
+    const size_t n1 = std::max<size_t>(n, 1);
+    uint32_t* sceneBounds = sc.small.as<uint32_t>();           // 12 uints
+    uint32_t* counters = sc.small.as<uint32_t>() + 16;         // [0] nodes, [1] prims, [2] overflow
+    float* sahAccum = reinterpret_cast<float*>(sc.small.as<uint32_t>() + 32);
+    int* root = reinterpret_cast<int*>(sc.small.as<uint32_t>() + 40);
+
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(sc.tileHist.ptr, 0, sortStateBytes(n), s));
+    k_morton_hist<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triBox.as<float4>(), sceneBounds, n,
+                                                                   sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(),
+                                                                   sc.tileHist.as<uint32_t>());
+    ctx->launches += 1;
+    int r = radixSort(ctx, sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(), sc.keysB.as<uint32_t>(),
+                      sc.valsB.as<uint32_t>(), sc.tileHist.as<uint32_t>(), n);
+    if (r != VKRT_SUCCESS)
+    {
+        return r;
+    }
+
+    Bvh2 bvh;
+    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
+    bvh.maxLeaf = maxLeaf;
+    bvh.nodes = sc.binNodes.as<BinNode>();
+    bvh.flags = sc.flags.as<int>();
+    bvh.keys = sc.keysA.as<uint32_t>();
+    bvh.vals = sc.valsA.as<uint32_t>();
+    bvh.triBox = sc.triBox.as<float4>();
+    bvh.count = n;
+    bvh.root = root;
+    if (n > 1 && fast)
+    {
+        VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0xFF, (size_t)(n - 1) * 4, s)); // -1
+        k_lbvh<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+        ctx->launches += 1;
+    }
+    else if (n > 1)
+    {
+        const uint32_t statusCount = (n + kPlocTile - 1) / kPlocTile;
+        VKRT_CUDA_TRY(ctx, sc.plocLoA.reserve(n1 * sizeof(float4)));
+        VKRT_CUDA_TRY(ctx, sc.plocHiA.reserve(n1 * sizeof(float4)));
+        VKRT_CUDA_TRY(ctx, sc.plocLoB.reserve(n1 * sizeof(float4)));
+        VKRT_CUDA_TRY(ctx, sc.plocHiB.reserve(n1 * sizeof(float4)));
+        VKRT_CUDA_TRY(ctx, sc.plocStatus.reserve((size_t)statusCount * 4 + 64));
+        PlocClusters cl[2];
+        cl[0].id = sc.flags.as<int>(), cl[0].lo = sc.plocLoA.as<float4>(), cl[0].hi = sc.plocHiA.as<float4>();
+        cl[1].id = reinterpret_cast<int*>(sc.keysB.as<uint32_t>()), cl[1].lo = sc.plocLoB.as<float4>(), cl[1].hi = sc.plocHiB.as<float4>();
+        uint32_t* state = sc.plocStatus.as<uint32_t>(); // 16 words of state, then the look-back words
+        uint32_t* status = state + 16;
+        k_ploc_init<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(bvh, cl[0], state, status, statusCount);
+        ctx->launches += 1;
+        int round = 0;
+        int batch = 8;
+        for (uint32_t m = n; m > (uint32_t)kPlocTile; m >>= 1)
+        {
+            batch += 4; // measured: a round leaves ~84 % of the clusters; the last <= 1024 take one launch
+        }
+        for (;;)
+        {
+            for (int k = 0; k < batch; ++k, ++round)
+            {
+                k_ploc_round<<<(uint32_t)sm * 4u, kPlocThreads, 0, s>>>(cl[round & 1], cl[(round + 1) & 1], bvh, state, status, round & 1);
+            }
+            k_ploc_finish<<<1, 1, 0, s>>>(cl[round & 1], bvh, state, round & 1, state + 8);
+            ctx->launches += batch + 1;
+            uint32_t remaining = 0;
+            VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(&remaining, state + 8, 4, cudaMemcpyDeviceToHost, s));
+            VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+            if (remaining == 1)
+            {
+                break;
+            }
+            if (round > 4096)
+            {
+                return ctx->fail(VKRT_ERROR_CUDA, "PLOC: did not converge");
+            }
+            batch = 16;
+        }
+    }
+
+    // cost-optimal collapse (default; the fast-build path keeps the greedy one): parents, then a bottom-up climb
+    float dpPrimCost = fast ? 0.0f : kDpPrimCost;
+    if (const char* e = getenv("VKRT_BUILD_DP_PRIM_COST"))
+    {
+        dpPrimCost = (float)atof(e);
+    }
+    if (n > maxLeaf && n > 1 && dpPrimCost > 0.0f)
+    {
+        VKRT_CUDA_TRY(ctx, sc.dp.reserve((size_t)n * 12));
+        bvh.dpChoice = sc.dp.as<uint32_t>();
+        bvh.dpParent = reinterpret_cast<int*>(sc.dp.as<uint32_t>() + n);
+        bvh.dpPrimCost = dpPrimCost;
+        VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0, (size_t)(n - 1) * 4, s));
+        k_dp_parents<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+        k_dp_climb<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+        ctx->launches += 2;
+    }
+
+    CollapseArgs ca;
+    ca.bvh2 = bvh;
+    ca.nodes = nodes;
+    ca.taskRef = sc.taskRef.as<int>();
+    ca.primSource = sc.primSource.as<uint32_t>();
+    ca.nodeCounter = counters + 0;
+    ca.primCounter = counters + 1;
+    ca.overflow = counters + 2;
+    ca.sahAccum = sahAccum;
+    ca.nodeCapacity = nodeCapacity;
+    uint32_t* range = counters + 4; // {first, last, ticket, levels}
+    k_collapse_seed<<<1, 1, 0, s>>>(ca, range);
+    ctx->launches += 1;
+    uint32_t last = 0;
+    for (int batch = 0;; ++batch)
+    {
+        // one narrow sweep, then (wide, narrow) pairs: enough for 8 wide levels per batch
+        k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+        ctx->launches += 1;
+        if (n > kNarrowLevel) // with fewer primitives than one narrow level no level can be wide
+        {
+            for (int k = 0; k < 8; ++k)
+            {
+                k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range);
+                k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+            }
+            ctx->launches += 16;
+        }
+        uint32_t hostCounters[8];
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+        if (hostCounters[2])
+        {
+            return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "BVH collapse: wide node capacity exceeded");
+        }
+        if (hostCounters[4] == hostCounters[5]) // first == last: no wide node left to fill
+        {
+            last = hostCounters[0];
+            out.levels = hostCounters[7];
+            if (hostCounters[1] != n)
+            {
+                return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: packed " + std::to_string(hostCounters[1]) + " of " +
+                                                      std::to_string(n) + " primitives");
+            }
+            break;
+        }
+        if (batch > 64)
+        {
+            return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: did not terminate");
+        }
+    }
+    out.nodeCount = last;
+
+    uint32_t hb[12];
+    float hs[2];
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hb, sceneBounds, sizeof(hb), cudaMemcpyDeviceToHost, s));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hs, sahAccum, sizeof(hs), cudaMemcpyDeviceToHost, s));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    for (int k = 0; k < 3; ++k)
+    {
+        out.boundsMin[k] = floatFromOrdered(hb[k]);
+        out.boundsMax[k] = floatFromOrdered(hb[3 + k]);
+    }
+    const float dx = out.boundsMax[0] - out.boundsMin[0], dy = out.boundsMax[1] - out.boundsMin[1],
+                dz = out.boundsMax[2] - out.boundsMin[2];
+    const float rootArea = dx * dy + dy * dz + dz * dx;
+    out.sahCost = rootArea > 0.0f ? (hs[0] + hs[1]) / rootArea : 0.0f;
+    return VKRT_SUCCESS;
+}
+} // namespace
+
 // Runs the whole builder over the BLAS's device geometry copy.
 int buildBlasOnDevice(Context* ctx, Blas* blas)
 {
@@ -1314,43 +1574,24 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     const uint32_t nodeCapacity = kMaxLeafTris >= 3 ? std::max(1u, n / 2u + 8u) : n + 8u;
     VKRT_CUDA_TRY(ctx, blas->nodes.reserve((size_t)nodeCapacity * sizeof(Node8)));
     VKRT_CUDA_TRY(ctx, blas->tris.reserve(std::max<size_t>(1, n) * sizeof(PackedTri)));
-
-    // scratch layout
+    if (int r = reserveBuildScratch(ctx, n, nodeCapacity, true))
+    {
+        return r;
+    }
     BuildScratch& sc = ctx->buildScratch;
-    const size_t n1 = std::max<size_t>(n, 1);
-    VKRT_CUDA_TRY(ctx, sc.triBox.reserve(n1 * 2 * sizeof(float4)));
-    VKRT_CUDA_TRY(ctx, sc.packedBuild.reserve(n1 * sizeof(PackedTri)));
-    VKRT_CUDA_TRY(ctx, sc.keysA.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.keysB.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.valsA.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.valsB.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.tileHist.reserve(sortStateBytes(n)));
-    VKRT_CUDA_TRY(ctx, sc.binNodes.reserve(n1 * sizeof(BinNode)));
-    VKRT_CUDA_TRY(ctx, sc.flags.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.taskRef.reserve((size_t)nodeCapacity * 4));
-    VKRT_CUDA_TRY(ctx, sc.primSource.reserve(n1 * 4));
-    VKRT_CUDA_TRY(ctx, sc.small.reserve(256));
-
-    uint32_t* sceneBounds = sc.small.as<uint32_t>();           // 12 uints
-    uint32_t* counters = sc.small.as<uint32_t>() + 16;         // [0] nodes, [1] prims, [2] overflow
+    uint32_t* sceneBounds = sc.small.as<uint32_t>();
+    uint32_t* counters = sc.small.as<uint32_t>() + 16;
     float* sahAccum = reinterpret_cast<float*>(sc.small.as<uint32_t>() + 32);
     int* root = reinterpret_cast<int*>(sc.small.as<uint32_t>() + 40);
-
     k_init_build<<<1, 32, 0, s>>>(sceneBounds, counters, sahAccum, root);
     ctx->launches += 1;
-
-    GeometryTable geo;
-    geo.firstTri = blas->geomFirstTri.as<uint32_t>();
-    geo.indexBase = blas->geomIndexBase.as<uint64_t>();
-    geo.geometryCount = blas->geometryCount;
-    const uint8_t* vertices = blas->vertices.as<uint8_t>();
-    const uint32_t* indices = blas->indices.as<uint32_t>();
 
     if (n == 0)
     {
         k_empty_root<<<1, 1, 0, s>>>(blas->nodes.as<Node8>());
         ctx->launches += 1;
         blas->nodeCount = 1;
+        blas->levels = 1;
         for (int k = 0; k < 3; ++k)
         {
             blas->boundsMin[k] = 0.0f;
@@ -1360,163 +1601,37 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     }
     else
     {
-        k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, vertices, blas->vertexStride, indices, n,
-                                                                      sc.triBox.as<float4>(), sc.packedBuild.as<float4>(), sceneBounds);
-        VKRT_CUDA_TRY(ctx, cudaMemsetAsync(sc.tileHist.ptr, 0, sortStateBytes(n), s));
-        k_morton_hist<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.triBox.as<float4>(), sceneBounds, n,
-                                                                       sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(),
-                                                                       sc.tileHist.as<uint32_t>());
-        ctx->launches += 2;
-        int r = radixSort(ctx, sc.keysA.as<uint32_t>(), sc.valsA.as<uint32_t>(), sc.keysB.as<uint32_t>(),
-                          sc.valsB.as<uint32_t>(), sc.tileHist.as<uint32_t>(), n);
-        if (r != VKRT_SUCCESS)
+        GeometryTable geo;
+        geo.firstTri = blas->geomFirstTri.as<uint32_t>();
+        geo.indexBase = blas->geomIndexBase.as<uint64_t>();
+        geo.geometryCount = blas->geometryCount;
+        k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, blas->vertices.as<uint8_t>(), blas->vertexStride,
+                                                                      blas->indices.as<uint32_t>(), n, sc.triBox.as<float4>(),
+                                                                      sc.packedBuild.as<float4>(), sceneBounds);
+        ctx->launches += 1;
+        HierarchyResult h;
+        const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
+        if (int r = buildHierarchy(ctx, n, kMaxLeafTris, fast, blas->nodes.as<Node8>(), nodeCapacity, h))
         {
             return r;
         }
-
-        Bvh2 bvh;
-        bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
-        bvh.nodes = sc.binNodes.as<BinNode>();
-        bvh.flags = sc.flags.as<int>();
-        bvh.keys = sc.keysA.as<uint32_t>();
-        bvh.vals = sc.valsA.as<uint32_t>();
-        bvh.triBox = sc.triBox.as<float4>();
-        bvh.count = n;
-        bvh.root = root;
-        const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
-        if (n > 1 && fast)
+        if ((int)h.levels > kMaxBlasLevels)
         {
-            VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0xFF, (size_t)(n - 1) * 4, s)); // -1
-            k_lbvh<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
-            ctx->launches += 1;
+            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_build: hierarchy has " + std::to_string(h.levels) +
+                                                              " levels, more than the traversal stack holds (" +
+                                                              std::to_string(kMaxBlasLevels) + ")");
         }
-        else if (n > 1)
-        {
-            const uint32_t statusCount = (n + kPlocTile - 1) / kPlocTile;
-            VKRT_CUDA_TRY(ctx, sc.plocLoA.reserve(n1 * sizeof(float4)));
-            VKRT_CUDA_TRY(ctx, sc.plocHiA.reserve(n1 * sizeof(float4)));
-            VKRT_CUDA_TRY(ctx, sc.plocLoB.reserve(n1 * sizeof(float4)));
-            VKRT_CUDA_TRY(ctx, sc.plocHiB.reserve(n1 * sizeof(float4)));
-            VKRT_CUDA_TRY(ctx, sc.plocStatus.reserve((size_t)statusCount * 4 + 64));
-            PlocClusters cl[2];
-            cl[0].id = sc.flags.as<int>(), cl[0].lo = sc.plocLoA.as<float4>(), cl[0].hi = sc.plocHiA.as<float4>();
-            cl[1].id = reinterpret_cast<int*>(sc.keysB.as<uint32_t>()), cl[1].lo = sc.plocLoB.as<float4>(), cl[1].hi = sc.plocHiB.as<float4>();
-            uint32_t* state = sc.plocStatus.as<uint32_t>(); // 16 words of state, then the look-back words
-            uint32_t* status = state + 16;
-            k_ploc_init<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(bvh, cl[0], state, status, statusCount);
-            ctx->launches += 1;
-            int round = 0;
-            int batch = 8;
-            for (uint32_t m = n; m > (uint32_t)kPlocTile; m >>= 1)
-            {
-                batch += 4; // measured: a round leaves ~84 % of the clusters; the last <= 1024 take one launch
-            }
-            for (;;)
-            {
-                for (int k = 0; k < batch; ++k, ++round)
-                {
-                    k_ploc_round<<<(uint32_t)sm * 4u, kPlocThreads, 0, s>>>(cl[round & 1], cl[(round + 1) & 1], bvh, state, status, round & 1);
-                }
-                k_ploc_finish<<<1, 1, 0, s>>>(cl[round & 1], bvh, state, round & 1, state + 8);
-                ctx->launches += batch + 1;
-                uint32_t remaining = 0;
-                VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(&remaining, state + 8, 4, cudaMemcpyDeviceToHost, s));
-                VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
-                if (remaining == 1)
-                {
-                    break;
-                }
-                if (round > 4096)
-                {
-                    return ctx->fail(VKRT_ERROR_CUDA, "PLOC: did not converge");
-                }
-                batch = 16;
-            }
-        }
-
-        // cost-optimal collapse (default; the fast-build path keeps the greedy one): parents, then a bottom-up climb
-        float dpPrimCost = fast ? 0.0f : kDpPrimCost;
-        if (const char* e = getenv("VKRT_BUILD_DP_PRIM_COST"))
-        {
-            dpPrimCost = (float)atof(e);
-        }
-        if (n > kMaxLeafTris && dpPrimCost > 0.0f)
-        {
-            VKRT_CUDA_TRY(ctx, sc.dp.reserve((size_t)n * 12));
-            bvh.dpChoice = sc.dp.as<uint32_t>();
-            bvh.dpParent = reinterpret_cast<int*>(sc.dp.as<uint32_t>() + n);
-            bvh.dpPrimCost = dpPrimCost;
-            VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0, (size_t)(n - 1) * 4, s));
-            k_dp_parents<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
-            k_dp_climb<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
-            ctx->launches += 2;
-        }
-
-        CollapseArgs ca;
-        ca.bvh2 = bvh;
-        ca.nodes = blas->nodes.as<Node8>();
-        ca.taskRef = sc.taskRef.as<int>();
-        ca.primSource = sc.primSource.as<uint32_t>();
-        ca.nodeCounter = counters + 0;
-        ca.primCounter = counters + 1;
-        ca.overflow = counters + 2;
-        ca.sahAccum = sahAccum;
-        ca.nodeCapacity = nodeCapacity;
-        uint32_t* range = counters + 4; // {first, last, ticket, levels}
-        k_collapse_seed<<<1, 1, 0, s>>>(ca, range);
-        ctx->launches += 1;
-        uint32_t last = 0;
-        for (int batch = 0;; ++batch)
-        {
-            // one narrow sweep, then (wide, narrow) pairs: enough for 8 wide levels per batch
-            k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
-            for (int k = 0; k < 8; ++k)
-            {
-                k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range);
-                k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
-            }
-            ctx->launches += 17;
-            uint32_t hostCounters[8];
-            VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
-            VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
-            if (hostCounters[2])
-            {
-                return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "BVH collapse: wide node capacity exceeded");
-            }
-            if (hostCounters[4] == hostCounters[5]) // first == last: no wide node left to fill
-            {
-                last = hostCounters[0];
-                if (hostCounters[1] != n)
-                {
-                    return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: packed " + std::to_string(hostCounters[1]) + " of " +
-                                                          std::to_string(n) + " triangles");
-                }
-                break;
-            }
-            if (batch > 64)
-            {
-                return ctx->fail(VKRT_ERROR_CUDA, "BVH collapse: did not terminate");
-            }
-        }
-        blas->nodeCount = last;
+        blas->nodeCount = h.nodeCount;
+        blas->levels = h.levels;
         k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
                                                                      blas->tris.as<PackedTri>());
         ctx->launches += 1;
-
-        uint32_t hb[12];
-        float hs[2];
-        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hb, sceneBounds, sizeof(hb), cudaMemcpyDeviceToHost, s));
-        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hs, sahAccum, sizeof(hs), cudaMemcpyDeviceToHost, s));
-        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
         for (int k = 0; k < 3; ++k)
         {
-            blas->boundsMin[k] = floatFromOrdered(hb[k]);
-            blas->boundsMax[k] = floatFromOrdered(hb[3 + k]);
+            blas->boundsMin[k] = h.boundsMin[k];
+            blas->boundsMax[k] = h.boundsMax[k];
         }
-        const float dx = blas->boundsMax[0] - blas->boundsMin[0], dy = blas->boundsMax[1] - blas->boundsMin[1],
-                    dz = blas->boundsMax[2] - blas->boundsMin[2];
-        const float rootArea = dx * dy + dy * dz + dz * dx;
-        blas->sahCost = rootArea > 0.0f ? (hs[0] + hs[1]) / rootArea : 0.0f;
+        blas->sahCost = h.sahCost;
     }
 
     VKRT_CUDA_TRY(ctx, cudaEventRecord(ev1, s));
@@ -1524,8 +1639,66 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, ev0, ev1);
     blas->buildMs = ms;
+    blas->generation += 1;
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    VKRT_CUDA_TRY(ctx, cudaGetLastError());
+    return VKRT_SUCCESS;
+}
+
+// Top level: instance world boxes (k_instance_bounds) -> the same hierarchy builder with one instance per leaf slot.
+// tlas->instances must hold the uploaded records.  A single instance needs no top level (tlas->nodeCount = 0).
+int buildTlasOnDevice(Context* ctx, Tlas* tlas)
+{
+    const uint32_t n = tlas->instanceCount;
+    cudaStream_t s = ctx->stream;
+    tlas->nodeCount = 0;
+    tlas->levels = 0;
+    if (n <= 1)
+    {
+        return VKRT_SUCCESS;
+    }
+    cudaEvent_t ev0, ev1;
+    VKRT_CUDA_TRY(ctx, cudaEventCreate(&ev0));
+    VKRT_CUDA_TRY(ctx, cudaEventCreate(&ev1));
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(ev0, s));
+    const uint32_t nodeCapacity = n + 8u;
+    VKRT_CUDA_TRY(ctx, tlas->nodes.reserve((size_t)nodeCapacity * sizeof(Node8)));
+    VKRT_CUDA_TRY(ctx, tlas->leafInstance.reserve((size_t)n * 4));
+    if (int r = reserveBuildScratch(ctx, n, nodeCapacity, false))
+    {
+        return r;
+    }
+    BuildScratch& sc = ctx->buildScratch;
+    uint32_t* sceneBounds = sc.small.as<uint32_t>();
+    k_init_build<<<1, 32, 0, s>>>(sceneBounds, sc.small.as<uint32_t>() + 16, reinterpret_cast<float*>(sc.small.as<uint32_t>() + 32),
+                                  reinterpret_cast<int*>(sc.small.as<uint32_t>() + 40));
+    k_instance_bounds<<<gridFor(n, kThreads, ctx->smCount), kThreads, 0, s>>>(tlas->instances.as<InstanceRecord>(), n,
+                                                                              sc.triBox.as<float4>(), sceneBounds);
+    ctx->launches += 2;
+    HierarchyResult h;
+    if (int r = buildHierarchy(ctx, n, 1u, false, tlas->nodes.as<Node8>(), nodeCapacity, h))
+    {
+        return r;
+    }
+    k_tlas_finalize<<<(h.nodeCount + kThreads - 1) / kThreads, kThreads, 0, s>>>(tlas->nodes.as<Node8>(), h.nodeCount);
+    ctx->launches += 1;
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(tlas->leafInstance.ptr, sc.primSource.ptr, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(ev1, s));
+    VKRT_CUDA_TRY(ctx, cudaEventSynchronize(ev1));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    tlas->nodeCount = h.nodeCount;
+    tlas->levels = h.levels;
+    tlas->buildMs = ms;
+    tlas->sahCost = h.sahCost;
+    for (int k = 0; k < 3; ++k)
+    {
+        tlas->boundsMin[k] = h.boundsMin[k];
+        tlas->boundsMax[k] = h.boundsMax[k];
+    }
     VKRT_CUDA_TRY(ctx, cudaGetLastError());
     return VKRT_SUCCESS;
 }

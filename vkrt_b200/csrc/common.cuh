@@ -31,7 +31,7 @@ struct alignas(16) Node8
                           // primBase + popcount(leafBits below that bit): leaves are stored in slot order
     uint16_t sz;          // as sx, sy
     uint8_t imask;        // bit s set: slot s holds an internal child
-    uint8_t reserved;     // 0
+    uint8_t reserved;     // BLAS nodes: 0.  TLAS nodes: bit s set: slot s is a leaf holding one instance (k_tlas_finalize)
     uint8_t qlox[8], qloy[8], qloz[8];
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };
@@ -51,7 +51,8 @@ struct alignas(16) PackedTri
 };
 static_assert(sizeof(PackedTri) == 48, "PackedTri must be 48 bytes");
 
-// Per-instance record used by traversal (w2o) and shading (o2w, geometry pointers).
+// Per-instance record used by traversal (w2o) and shading (o2w, geometry pointers).  Built on the host from the 64-byte
+// VkAccelerationStructureInstanceKHR (src/Raytracer.cpp:1165-1177); the world box comes from k_instance_bounds.
 struct alignas(16) InstanceRecord
 {
     float w2o[12];
@@ -61,8 +62,13 @@ struct alignas(16) InstanceRecord
     const uint8_t* vertices; // device copy of the vertex buffer (stride bytes per vertex)
     const uint32_t* indices; // device copy of the (global) index buffer
     uint32_t vertexStride;
-    uint32_t pad[3];
+    uint32_t mask;           // VkAccelerationStructureInstanceKHR::mask (8 bits): visible to a ray iff mask & cullMask
+    uint32_t customIndex;    // instanceCustomIndex (24 bits); the reference's shaders never read gl_InstanceCustomIndexEXT
+    uint32_t flags;          // VkGeometryInstanceFlagsKHR; no ray of this pipeline culls, so TRIANGLE_FACING_CULL_DISABLE changes nothing
+    float blasLo[3], blasHi[3]; // object-space bounds of the BLAS at TLAS build time
+    uint32_t pad[2];
 };
+static_assert(sizeof(InstanceRecord) == 176, "InstanceRecord layout");
 
 struct TextureRecord
 {
@@ -88,6 +94,7 @@ struct HitRecord
 };
 
 constexpr uint32_t kInvalid = 0xFFFFFFFFu;
+constexpr uint32_t kMaxInstances = 1u << 24; // as many as instanceCustomIndex can name; the AOV triangle id keeps the low 8 bits
 constexpr float kRayTMin = 0.001f;    // shaders/shader.rgen:58, shader.rchit:139
 constexpr float kRayTMax = 1000.0f;   // shaders/shader.rgen:60
 constexpr int kTile = VKRT_TILE_SIZE; // multi-GPU image tile edge in pixels

@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 #include <memory>
+#include <utility>
 
 struct VkrtContext
 {
@@ -82,6 +83,7 @@ struct RasterBuffers
 };
 
 struct NcclApi; // dlopen'ed NCCL entry points (comm.cpp)
+struct Blas;
 
 struct Context : VkrtContext
 {
@@ -93,8 +95,10 @@ struct Context : VkrtContext
     uint64_t launches = 0;
 
     // shading resources
-    DeviceBuffer materials; // VkrtSubmeshInfo[]
+    DeviceBuffer materials; // VkrtSubmeshInfo[], texture indices made safe (syncMaterials, api.cu)
     uint32_t materialCount = 0;
+    std::vector<VkrtSubmeshInfo> materialsHost; // the table as the caller gave it
+    bool materialsDirty = false;
     DeviceBuffer textureRecords; // TextureRecord[]
     std::vector<void*> textureAllocs;
     uint32_t textureCount = 0;
@@ -122,6 +126,8 @@ struct Context : VkrtContext
     int stageEventCount = 0;
 
     // multi-GPU
+    std::vector<const Blas*> liveBlas; // handles handed out by vkrt_blas_build and not yet destroyed
+    DeviceBuffer errorFlags;           // u32[4] device-side: [0] traversal stack overflow
     int rank = 0, size = 1;
     void* ncclComm = nullptr;
     DeviceBuffer gatherStaging;
@@ -147,13 +153,23 @@ struct Blas : VkrtBlas
     float sahCost = 0.0f;
     float buildMs = 0.0f;
     uint32_t flags = 0;
+    uint32_t levels = 0;        // wide levels of the hierarchy (bounds the traversal stack)
+    uint64_t generation = 0;    // bumped by every (re)build: a TLAS remembers the generation it saw
+    bool shadingLayout = false; // vertices are the 64-byte Model::Vertex (stride % 16 == 0, >= 64): vkrt_trace / vkrt_rasterize can shade it
 };
 
 struct Tlas : VkrtTlas
 {
-    DeviceBuffer instances; // InstanceRecord[]
-    DeviceBuffer bounds;    // InstanceBounds[]
+    DeviceBuffer instances;    // InstanceRecord[]
+    DeviceBuffer nodes;        // Node8[]: hierarchy over the instances' world boxes (instanceCount > 1)
+    DeviceBuffer leafInstance; // u32[instanceCount]: instance index per top-level leaf
     uint32_t instanceCount = 0;
+    uint32_t nodeCount = 0, levels = 0;
+    uint32_t maxGeometryCount = 0; // largest geometry count among the referenced BLASes (material table check)
+    bool shadingLayout = true;     // every referenced BLAS can be shaded
+    float buildMs = 0.0f, sahCost = 0.0f;
+    float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
+    std::vector<std::pair<const Blas*, uint64_t>> blasRefs; // (BLAS, generation at build) per distinct BLAS
 };
 
 struct Frame : VkrtFrame
@@ -181,6 +197,11 @@ struct Frame : VkrtFrame
 int waitPresents(Context* ctx, Frame* frame);
 
 int buildBlasOnDevice(Context* ctx, Blas* blas);
+int buildTlasOnDevice(Context* ctx, Tlas* tlas);
+int syncMaterials(Context* ctx);
+int checkTlasCurrent(Context* ctx, const Tlas* tlas, const char* who);
+int checkSceneForShading(Context* ctx, const Tlas* tlas, const char* who); // stale TLAS, vertex layout, material rows
+int checkDeviceErrors(Context* ctx, const char* who); // device-side error flags, read at synchronisation points
 int sortPairsForTest(Context* ctx, uint32_t* keys, uint32_t* vals, uint32_t count);
 size_t sortPairsStateBytes(uint32_t count);
 int sortPairsDevice(Context* ctx, uint32_t* keysA, uint32_t* valsA, uint32_t* keysB, uint32_t* valsB, uint32_t* state, uint32_t count);

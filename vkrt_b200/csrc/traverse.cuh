@@ -13,7 +13,9 @@
 namespace vkrt
 {
 
-constexpr int kStackSize = 48; // node-group entries; deeper trees set TraceCounters::overflow
+constexpr int kStackSize = 48; // group entries.  A BLAS pushes at most one per level, the top level one per level plus two
+                               // when it enters an instance: the builders refuse hierarchies that could exceed this
+constexpr int kMaxBlasLevels = kStackSize;
 
 struct TraceCounters
 {
@@ -269,7 +271,7 @@ __device__ __forceinline__ void initSlotTables()
 // and the far planes pushed out by 2^-7 step (bn/bf below): the test stays conservative, and flat boxes (qlo == qhi)
 // keep tn < tf.  NaN planes (0*inf for axis-parallel rays) are dropped by fmaxf/fminf, i.e. that axis never culls.
 // Empty slots carry a zero box that a ray may well hit: they drop out because neither imask nor leafBits names them.
-VKRT_HD uint2 intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
+VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
     // n0.w = sx | sy << 16, n1.w = sz | imask << 16: upper halves of the floats 2^15 * scale
     const uint32_t e = floatAsUint(w.n0.w);
@@ -303,11 +305,27 @@ VKRT_HD uint2 intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, 
         testChild<6>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
         testChild<7>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminP, tmaxP, one, hitSlots);
     }
+    return hitSlots;
+}
+
+// Internal children among `hitSlots` (8 bits) in traversal priority order (nearest octant-order child in the highest
+// bit).  Only the low 8 bits of `imask` matter.
+VKRT_HD uint32_t orderInnerSlots(uint32_t hitSlots, uint32_t imask, uint32_t octant)
+{
 #if defined(__CUDA_ARCH__)
-    const uint32_t inner = sPermuteSlots[((7u - octant) << 8) | (hitSlots & (w.n1.w >> 16))];
-    return make_uint2(inner, sSpreadSlots[hitSlots] & w.n1.z);
+    return sPermuteSlots[((7u - octant) << 8) | (hitSlots & imask)];
 #else
-    return make_uint2(permuteSlots(hitSlots & (w.n1.w >> 16), 7u - octant), spreadSlots(hitSlots) & w.n1.z);
+    return permuteSlots(hitSlots & imask, 7u - octant);
+#endif
+}
+
+VKRT_HD uint2 intersectNode(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
+{
+    const uint32_t hitSlots = intersectNodeSlots(w, o, idir, octant, tminP, tmaxP, one);
+#if defined(__CUDA_ARCH__)
+    return make_uint2(orderInnerSlots(hitSlots, w.n1.w >> 16, octant), sSpreadSlots[hitSlots] & w.n1.z);
+#else
+    return make_uint2(orderInnerSlots(hitSlots, w.n1.w >> 16, octant), spreadSlots(hitSlots) & w.n1.z);
 #endif
 }
 
@@ -369,9 +387,12 @@ constexpr int kStepHit = 4;   // flag: at least one triangle was accepted during
 
 // One traversal step: pops the nearest pending internal child (if any), tests its 8 child boxes, then tests the
 // triangles the node references.  Returns 0 to continue, or kStepDone / kStepFound, optionally ORed with kStepHit.
+// `spFloor` is the stack height at which this BLAS was entered (0 unless a top-level traversal is suspended below);
+// `overflowFlag` (may be null) is set when a group had to be dropped because the stack is full: the builders refuse
+// hierarchies deeper than the stack (kStackSize), so this is a defensive signal that vkrt surfaces as an error.
 template<bool ANY>
 VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const PackedTri* tris, uint32_t instance, BestHit& best,
-                          TraceCounters* counters, uint32_t one)
+                          TraceCounters* counters, uint32_t one, int spFloor = 0, uint32_t* overflowFlag = nullptr)
 {
     int result = 0;
     uint32_t leafBits = 0;
@@ -387,9 +408,16 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
             {
                 stack[c.sp++] = c.ngroup;
             }
-            else if (counters)
+            else
             {
-                counters->overflow = 1;
+                if (counters)
+                {
+                    counters->overflow = 1;
+                }
+                if (overflowFlag)
+                {
+                    *overflowFlag = 1u;
+                }
             }
         }
         const uint32_t slot = (bit ^ octinv) & 7u; // bit is 24..31
@@ -445,7 +473,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
 
     if (c.ngroup.y <= 0x00FFFFFFu)
     {
-        if (c.sp == 0)
+        if (c.sp <= spFloor)
         {
             return result | kStepDone;
         }
@@ -474,85 +502,166 @@ VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d,
     }
 }
 
-// World AABB of one instance for the top-level pass.
-struct InstanceBounds
-{
-    float lo[3], hi[3];
-};
-
-// Conservative ray/AABB entry distance; returns false when the padded slab interval is empty.
-VKRT_HD bool intersectBounds(const InstanceBounds& b, F3 o, F3 idir, float tmin, float tmax, float& tnear)
-{
-    const float pad = 3.8146973e-06f;
-    float t0x = (b.lo[0] - o.x) * idir.x, t1x = (b.hi[0] - o.x) * idir.x;
-    float t0y = (b.lo[1] - o.y) * idir.y, t1y = (b.hi[1] - o.y) * idir.y;
-    float t0z = (b.lo[2] - o.z) * idir.z, t1z = (b.hi[2] - o.z) * idir.z;
-    float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
-    float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
-    tn = tn - fabsf(tn) * pad;
-    tf = tf + fabsf(tf) * pad;
-    tnear = tn;
-    return tn <= tf;
-}
-
-// Top-level pass: instances are visited front to back by the entry distance of their world bounds, ties by index.
-// The cursor remembers the last visited (distance, index); selectNextInstance returns the next one whose bounds the
-// ray still enters before `tmax`, or kInvalid.
-struct InstanceCursor
-{
-    float lastT;
-    uint32_t lastIdx;
-};
-VKRT_HD void resetCursor(InstanceCursor& cur)
-{
-    cur.lastT = -INFINITY;
-    cur.lastIdx = kInvalid; // "nothing visited yet"
-}
-VKRT_HD uint32_t selectNextInstance(const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 idir, float tmin, float tmax,
-                                    InstanceCursor& cur)
-{
-    float bestT = INFINITY;
-    uint32_t bestIdx = kInvalid;
-    const bool first = cur.lastIdx == kInvalid;
-    for (uint32_t i = 0; i < instanceCount; ++i)
-    {
-        float tn;
-        if (!intersectBounds(bounds[i], o, idir, tmin, tmax, tn))
-        {
-            continue;
-        }
-        // strict (t, index) ordering after the last visited instance
-        const bool after = first || tn > cur.lastT || (tn == cur.lastT && i > cur.lastIdx);
-        if (after && (tn < bestT || (tn == bestT && i < bestIdx)))
-        {
-            bestT = tn;
-            bestIdx = i;
-        }
-    }
-    if (bestIdx != kInvalid)
-    {
-        cur.lastT = bestT;
-        cur.lastIdx = bestIdx;
-    }
-    return bestIdx;
-}
-
 VKRT_HD bool validRay(F3 o, F3 d) { return finite3(o) && finite3(d) && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f); }
 
-// traceRayEXT over the whole scene: all instances (mask 0xFF, cull disabled — src/Raytracer.cpp:1172-1177).
-// Returns true on any accepted hit.  `best.t` must be initialised to the ray's tmax and best.tri to kInvalid.
+// ------------------------------------------------------------------------------------------------------------
+// Top level (replaces the TLAS the driver builds in Raytracer::createTLAS, src/Raytracer.cpp:1159-1283).
+// The TLAS is a Node8 hierarchy over the instances' world boxes, built on the device by the same builder as a BLAS
+// (k_instance_bounds feeds it boxes instead of k_tri_bounds), with exactly one instance per leaf slot:
+// Node8::reserved holds the mask of leaf slots, and the instance of leaf slot s is
+//     leafInstance[primBase + popcount(reserved & ((1 << s) - 1))].
+// One stack serves both levels.  While a ray is inside a BLAS the suspended top-level work lies below `spFloor`:
+//   node group      {childBase, hits << 24 | imask}                        (x < 2^31)
+//   instance group  {primBase | 2^31, hit leaf slots << 8 | leaf slots}    (x >= 2^31)
+// A ray enters an instance only if VkAccelerationStructureInstanceKHR::mask & cullMask != 0 (traceRayEXT's cullMask,
+// 0xFF in shaders/shader.rgen:52 and shader.rchit:133; the reference's instance has mask 0xFF, Raytracer.cpp:1174).
+// ------------------------------------------------------------------------------------------------------------
+struct TlasRefs
+{
+    const Node8* nodes;            // top-level nodes (null: a single instance, no top level)
+    const uint32_t* leafInstance;  // instance index per top-level leaf, in node order
+    const InstanceRecord* instances;
+    uint32_t instanceCount;
+    uint32_t cullMask;
+};
+
+constexpr uint32_t kTopInstanceGroup = 0x80000000u;
+constexpr int kTopDone = 1;  // no instance left to enter
+constexpr int kTopEnter = 2; // `instanceOut` names the next instance whose box the ray enters
+
+// World-space box-traversal state (no watertight constants: the top level tests boxes only).
+VKRT_HD void beginTop(RayCtx& c, F3 o, F3 d, float tmin, int sp)
+{
+    c.o = o;
+    c.idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    c.tmin = tmin;
+    c.tminP = padDown(tmin);
+    c.ngroup = make_uint2(0u, 0u);
+    c.tgroup = make_uint2(0u, 0u); // holds the pending instance group at the top level
+    c.sp = sp;
+}
+
+VKRT_HD void pushGroup(RayCtx& c, uint2* stack, uint2 g, TraceCounters* counters, uint32_t* overflowFlag)
+{
+    if (c.sp < kStackSize)
+    {
+        stack[c.sp++] = g;
+    }
+    else
+    {
+        if (counters)
+        {
+            counters->overflow = 1;
+        }
+        if (overflowFlag)
+        {
+            *overflowFlag = 1u;
+        }
+    }
+}
+
+// Advances the top-level traversal until the ray is about to enter an instance (kTopEnter) or nothing is left
+// (kTopDone).  `tmax` is the current hit distance.  c.ngroup / c.tgroup hold the pending node and instance groups.
+VKRT_HD int topStep(RayCtx& c, uint2* stack, const TlasRefs& top, float tmax, TraceCounters* counters, uint32_t one,
+                    uint32_t* overflowFlag, uint32_t& instanceOut)
+{
+    for (;;)
+    {
+        if (c.tgroup.y & 0xFF00u)
+        {
+            const uint32_t slot = highestBit(c.tgroup.y) - 8u;
+            c.tgroup.y &= ~(0x100u << slot);
+            const uint32_t idx = top.leafInstance[(c.tgroup.x & ~kTopInstanceGroup) + popCount(c.tgroup.y & 0xFFu & ((1u << slot) - 1u))];
+            if (top.instances[idx].mask & top.cullMask)
+            {
+                instanceOut = idx;
+                return kTopEnter;
+            }
+            continue;
+        }
+        if (c.ngroup.y > 0x00FFFFFFu)
+        {
+            const uint32_t octinv = 7u - c.octant;
+            const uint32_t bit = highestBit(c.ngroup.y);
+            const uint32_t base = c.ngroup.x;
+            c.ngroup.y &= ~(1u << bit);
+            if (c.ngroup.y > 0x00FFFFFFu)
+            {
+                pushGroup(c, stack, c.ngroup, counters, overflowFlag);
+            }
+            const uint32_t slot = (bit ^ octinv) & 7u;
+            const uint32_t rel = popCount(c.ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
+            const NodeWords w = loadNode(top.nodes, base + rel);
+            if (counters)
+            {
+                ++counters->nodes;
+            }
+            const uint32_t hitSlots = intersectNodeSlots(w, c.o, c.idir, c.octant, c.tminP, padUp(tmax), one);
+            const uint32_t imask = (w.n1.w >> 16) & 0xFFu, leafSlots = w.n1.w >> 24;
+            c.ngroup = make_uint2(w.n1.x, (orderInnerSlots(hitSlots, imask, c.octant) << 24) | imask);
+            c.tgroup = make_uint2(w.n1.y | kTopInstanceGroup, ((hitSlots & leafSlots) << 8) | leafSlots);
+            continue;
+        }
+        if (c.sp == 0)
+        {
+            return kTopDone;
+        }
+        const uint2 g = stack[--c.sp];
+        if (g.x & kTopInstanceGroup)
+        {
+            c.tgroup = g;
+        }
+        else
+        {
+            c.ngroup = g;
+        }
+    }
+}
+
+// Suspends the top level (pending groups go onto the stack) and moves the ray into `inst`.  Returns false when
+// the object-space ray is not traceable (non-finite or zero direction after the transform): the top level then
+// simply continues.  On success c is the object-space state and `spFloor` the stack height to return at.
+VKRT_HD bool enterInstanceTop(RayCtx& c, uint2* stack, const InstanceRecord& inst, F3 o, F3 d, float tmin, TraceCounters* counters,
+                              uint32_t* overflowFlag, int& spFloor)
+{
+    const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
+    if (!validRay(oo, dd))
+    {
+        return false;
+    }
+    if (c.ngroup.y > 0x00FFFFFFu)
+    {
+        pushGroup(c, stack, c.ngroup, counters, overflowFlag);
+    }
+    if (c.tgroup.y & 0xFF00u)
+    {
+        pushGroup(c, stack, c.tgroup, counters, overflowFlag);
+    }
+    const int sp = c.sp;
+    beginTraversal(c, oo, dd, tmin);
+    c.sp = sp;
+    spFloor = sp;
+    return true;
+}
+
+// traceRayEXT over the whole scene.  Returns true on any accepted hit.  `best.t` must be initialised to the ray's
+// tmax and best.tri to kInvalid.  (Sequential form, used by the host emulation; the kernels in wavefront.cu run the same
+// steps with the loop turned inside out so that a warp can re-converge between them.)
 template<bool ANY>
-VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* bounds, uint32_t instanceCount, F3 o, F3 d,
-                        float tmin, BestHit& best, TraceCounters* counters, uint32_t one = 0x3F800000u)
+VKRT_HD bool traceScene(const TlasRefs& top, F3 o, F3 d, float tmin, BestHit& best, TraceCounters* counters, uint32_t one = 0x3F800000u)
 {
     if (!validRay(o, d) || !(best.t > tmin))
     {
         return false;
     }
-    bool found = false;
-    if (instanceCount == 1)
+    if (!top.nodes)
     {
-        const InstanceRecord& inst = instances[0];
+        const InstanceRecord& inst = top.instances[0];
+        if (!(inst.mask & top.cullMask))
+        {
+            return false;
+        }
         const F3 oo = affinePoint(inst.w2o, o);
         const F3 dd = affineDir(inst.w2o, d);
         if (!validRay(oo, dd))
@@ -561,33 +670,63 @@ VKRT_HD bool traceScene(const InstanceRecord* instances, const InstanceBounds* b
         }
         return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one);
     }
-    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    InstanceCursor cur;
-    resetCursor(cur);
+    RayCtx c;
+    uint2 stack[kStackSize];
+    beginTop(c, o, d, tmin, 0);
+    c.ngroup = make_uint2(0u, 0x80000000u); // the top-level root
+    bool found = false;
     for (;;)
     {
-        const uint32_t idx = selectNextInstance(bounds, instanceCount, o, idir, tmin, best.t, cur);
-        if (idx == kInvalid)
+        uint32_t idx = 0;
+        if (topStep(c, stack, top, best.t, counters, one, nullptr, idx) == kTopDone)
         {
-            break;
+            return found;
         }
-        const InstanceRecord& inst = instances[idx];
-        const F3 oo = affinePoint(inst.w2o, o);
-        const F3 dd = affineDir(inst.w2o, d);
-        if (!validRay(oo, dd))
+        const InstanceRecord& inst = top.instances[idx];
+        int spFloor = 0;
+        if (!enterInstanceTop(c, stack, inst, o, d, tmin, counters, nullptr, spFloor))
         {
             continue;
         }
-        if (traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, idx, best, counters, one))
+        for (;;)
         {
-            found = true;
-            if (ANY)
+            const int r = traversalStep<ANY>(c, stack, inst.nodes, inst.tris, idx, best, counters, one, spFloor);
+            found = found || (r & kStepHit);
+            if (ANY && (r & kStepFound))
             {
                 return true;
             }
+            if (r & kStepDone)
+            {
+                break;
+            }
         }
+        beginTop(c, o, d, tmin, spFloor);
     }
-    return found;
+}
+
+// World box of an instance: the 8 corners of the BLAS box through object->world, padded by a few ulps (the top level
+// must never cull a ray that the object-space traversal, with its own roundings, would accept).
+VKRT_HD void instanceWorldBounds(const InstanceRecord& r, float lo[3], float hi[3])
+{
+    for (int k = 0; k < 3; ++k)
+    {
+        lo[k] = INFINITY;
+        hi[k] = -INFINITY;
+    }
+    for (int corner = 0; corner < 8; ++corner)
+    {
+        const F3 p = f3((corner & 1) ? r.blasHi[0] : r.blasLo[0], (corner & 2) ? r.blasHi[1] : r.blasLo[1], (corner & 4) ? r.blasHi[2] : r.blasLo[2]);
+        const F3 q = affinePoint(r.o2w, p);
+        lo[0] = fminf(lo[0], q.x), lo[1] = fminf(lo[1], q.y), lo[2] = fminf(lo[2], q.z);
+        hi[0] = fmaxf(hi[0], q.x), hi[1] = fmaxf(hi[1], q.y), hi[2] = fmaxf(hi[2], q.z);
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        const float padAbs = (fabsf(lo[k]) + fabsf(hi[k])) * 1e-5f + 1e-30f;
+        lo[k] -= padAbs;
+        hi[k] += padAbs;
+    }
 }
 
 } // namespace vkrt
