@@ -44,7 +44,10 @@ typedef enum VkrtResult
     VKRT_ERROR_CUDA = 3,
     VKRT_ERROR_OUT_OF_MEMORY = 4,
     VKRT_ERROR_NCCL = 5,
-    VKRT_ERROR_NOT_READY = 6
+    VKRT_ERROR_NOT_READY = 6,
+    VKRT_ERROR_TRAVERSAL_OVERFLOW = 7 /* a ray needed more traversal-stack entries than the library keeps (48); reported by the
+                                         next synchronising call (vkrt_frame_read, vkrt_context_synchronize, vkrt_trace_rays).  The
+                                         builders refuse hierarchies deep enough to cause it, so this signals a library defect. */
 } VkrtResult;
 
 /* ------------------------------------------------------------------------------------------------
@@ -94,6 +97,10 @@ typedef struct VkrtBuildSizes
 VKRT_API int vkrt_blas_sizes(VkrtContext* ctx, const VkrtGeometryRange* ranges, uint32_t geometryCount,
                              uint64_t vertexBytes, uint64_t indexCount, VkrtBuildSizes* out);
 
+/* `vertexStride` >= 12 and a multiple of 4 is enough to build and to trace rays (vkrt_trace_rays).  Shading (vkrt_trace)
+ * and vkrt_rasterize read the reference's 64-byte Model::Vertex (position, normal, uv, tangent as 4 x vec4,
+ * src/Model.hpp:13-19) with 16-byte loads: they need vertexStride >= 64 and a multiple of 16 and fail with
+ * VKRT_ERROR_INVALID_ARGUMENT otherwise.  The build fails if the hierarchy comes out deeper than the traversal stack (48 levels). */
 VKRT_API int vkrt_blas_build(VkrtContext* ctx, const void* vertices, size_t vertexBytes, uint32_t vertexStride,
                              const uint32_t* indices, size_t indexCount, const VkrtGeometryRange* ranges,
                              uint32_t geometryCount, uint32_t flags, VkrtBlas** out);
@@ -137,8 +144,32 @@ typedef struct VkrtInstance
     uint64_t accelerationStructureReference; /* vkrt_blas_reference() */
 } VkrtInstance;
 
+/* Builds the top level on the device: world boxes of the instances (k_instance_bounds), then the same builder as for a
+ * BLAS over those boxes, one instance per leaf of an 8-wide hierarchy; 1 .. 2^24 instances.  Traversal switches to an
+ * instance's BLAS with the ray transformed by the inverse of `transform` (origin and direction, t shared) and enters an
+ * instance only when `mask & 0xFF` (the cullMask of every traceRayEXT in the reference's shaders) is non-zero.  `flags`
+ * and `instanceCustomIndex` are recorded; nothing in this pipeline culls by facing or reads the custom index.
+ * A TLAS is tied to the BLAS builds it saw: after vkrt_blas_rebuild / vkrt_blas_destroy of a referenced BLAS, tracing
+ * it returns VKRT_ERROR_NOT_READY until the TLAS is built again (the reference rebuilds both in Raytracer's constructor). */
 VKRT_API int vkrt_tlas_build(VkrtContext* ctx, const VkrtInstance* instances, uint32_t instanceCount, VkrtTlas** out);
 VKRT_API void vkrt_tlas_destroy(VkrtContext* ctx, VkrtTlas* tlas);
+
+typedef struct VkrtTlasInfo
+{
+    uint32_t instanceCount;
+    uint32_t nodeCount; /* 80-byte top-level nodes; 0 for a single instance (no top level is needed) */
+    uint32_t levels;    /* depth of the top-level hierarchy */
+    uint32_t reserved;
+    float boundsMin[3];
+    float boundsMax[3];
+    float sahCost;
+    float buildMilliseconds; /* device time of the top-level build, CUDA events */
+} VkrtTlasInfo;
+VKRT_API int vkrt_tlas_info(VkrtContext* ctx, const VkrtTlas* tlas, VkrtTlasInfo* out);
+/* Debug/readback for invariant tests: `nodes` receives nodeCount*80 bytes (Node8::reserved = mask of leaf slots, leaf slot s
+ * of a node holds instance leafInstances[primBase + popcount(reserved & ((1<<s)-1))]), `leafInstances` instanceCount u32. */
+VKRT_API int vkrt_tlas_read(VkrtContext* ctx, const VkrtTlas* tlas, void* nodes, size_t nodeBytes, uint32_t* leafInstances,
+                            size_t leafBytes);
 
 /* ------------------------------------------------------------------------------------------------
  * Shading resources
@@ -296,7 +327,7 @@ typedef struct VkrtStats
     uint64_t kernelLaunches;                /* kernels launched by this library */
     float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* first wave of the last vkrt_trace, if timing enabled */
     uint32_t samplesPerWave; /* samples per pixel that went through the pipeline together in the last vkrt_trace */
-    uint32_t reserved;
+    uint32_t traversalOverflows; /* times VKRT_ERROR_TRAVERSAL_OVERFLOW was raised since the last reset */
 } VkrtStats;
 VKRT_API int vkrt_stats_enable(VkrtContext* ctx, int countTraversal, int timeStages);
 VKRT_API int vkrt_stats_reset(VkrtContext* ctx);

@@ -45,6 +45,19 @@ class BlasInfo(C.Structure):
     ]
 
 
+class TlasInfo(C.Structure):
+    _fields_ = [
+        ("instanceCount", C.c_uint32),
+        ("nodeCount", C.c_uint32),
+        ("levels", C.c_uint32),
+        ("reserved", C.c_uint32),
+        ("boundsMin", C.c_float * 3),
+        ("boundsMax", C.c_float * 3),
+        ("sahCost", C.c_float),
+        ("buildMilliseconds", C.c_float),
+    ]
+
+
 class Instance(C.Structure):
     _fields_ = [
         ("transform", C.c_float * 12),
@@ -98,7 +111,7 @@ class Stats(C.Structure):
         ("msResolve", C.c_float),
         ("msTotal", C.c_float),
         ("samplesPerWave", C.c_uint32),
-        ("reserved", C.c_uint32),
+        ("traversalOverflows", C.c_uint32),
     ]
 
 
@@ -149,6 +162,8 @@ EXPORTS = [
     "vkrt_blas_read",
     "vkrt_tlas_build",
     "vkrt_tlas_destroy",
+    "vkrt_tlas_info",
+    "vkrt_tlas_read",
     "vkrt_materials_set",
     "vkrt_textures_set",
     "vkrt_frame_create",
@@ -203,6 +218,8 @@ def load_library(path: Optional[str] = None):
         "vkrt_blas_read": (i32, [vp, vp, vp, sz, vp, sz]),
         "vkrt_tlas_build": (i32, [vp, C.POINTER(Instance), u32, C.POINTER(vp)]),
         "vkrt_tlas_destroy": (None, [vp, vp]),
+        "vkrt_tlas_info": (i32, [vp, vp, C.POINTER(TlasInfo)]),
+        "vkrt_tlas_read": (i32, [vp, vp, vp, sz, vp, sz]),
         "vkrt_materials_set": (i32, [vp, C.POINTER(SubmeshInfo), u32]),
         "vkrt_textures_set": (i32, [vp, C.POINTER(Image), u32]),
         "vkrt_textures_generate_mips": (i32, [vp]),
@@ -425,26 +442,45 @@ class Blas:
             pass
 
 
+INSTANCE_DTYPE = np.dtype([("transform", "<f4", 12), ("index_mask", "<u4"), ("sbt_flags", "<u4"), ("reference", "<u8")])
+assert INSTANCE_DTYPE.itemsize == 64
+
+
 class Tlas:
-    def __init__(self, ctx: Context, blases: Sequence[Blas], transforms: np.ndarray):
-        """transforms: (N,12) row-major 3x4; blases: one Blas per instance (or a single one, shared)."""
+    def __init__(self, ctx: Context, blases: Sequence[Blas], transforms: np.ndarray, masks: Optional[np.ndarray] = None):
+        """transforms: (N,12) row-major 3x4; blases: one Blas per instance (or a single one, shared); masks: (N,) 8-bit
+        VkAccelerationStructureInstanceKHR::mask values (default 0xFF, src/Raytracer.cpp:1174)."""
         self.ctx = ctx
         t = np.ascontiguousarray(transforms, dtype=np.float32).reshape(-1, 12)
         n = t.shape[0]
-        inst = (Instance * n)()
-        for i in range(n):
-            b = blases[i] if len(blases) > 1 else blases[0]
-            for k in range(12):
-                inst[i].transform[k] = float(t[i, k])
-            inst[i].instanceCustomIndex = 0
-            inst[i].mask = 0xFF
-            inst[i].sbtOffset = 0
-            inst[i].flags = 0x1  # VK_GEOMETRY_INSTANCE_TRIANGLE_FACING_CULL_DISABLE_BIT_KHR
-            inst[i].accelerationStructureReference = b.reference
+        # the 64-byte VkAccelerationStructureInstanceKHR records, filled as arrays (thousands of instances)
+        inst = np.zeros(n, dtype=INSTANCE_DTYPE)
+        inst["transform"] = t
+        m = np.full(n, 0xFF, dtype=np.uint32) if masks is None else np.asarray(masks, dtype=np.uint32) & 0xFF
+        inst["index_mask"] = m << 24  # instanceCustomIndex 0 : 24, mask : 8
+        inst["sbt_flags"] = np.uint32(0x1 << 24)  # sbtOffset 0, VK_GEOMETRY_INSTANCE_TRIANGLE_FACING_CULL_DISABLE_BIT_KHR
+        if len(blases) > 1:
+            inst["reference"] = np.array([b.reference for b in blases], dtype=np.uint64)
+        else:
+            inst["reference"] = np.uint64(blases[0].reference)
         h = C.c_void_p()
-        ctx.check(ctx.lib.vkrt_tlas_build(ctx.handle, inst, n, C.byref(h)))
+        ctx.check(ctx.lib.vkrt_tlas_build(ctx.handle, inst.ctypes.data_as(C.POINTER(Instance)), n, C.byref(h)))
         self.handle = h
         self._blases = list(blases)
+
+    def info(self) -> "TlasInfo":
+        out = TlasInfo()
+        self.ctx.check(self.ctx.lib.vkrt_tlas_info(self.ctx.handle, self.handle, C.byref(out)))
+        return out
+
+    def read(self):
+        """(top-level nodes, instance index per top-level leaf); both empty for a single instance."""
+        info = self.info()
+        nodes = np.zeros(int(info.nodeCount), dtype=NODE_DTYPE)
+        leaves = np.zeros(int(info.instanceCount) if info.nodeCount else 0, dtype=np.uint32)
+        self.ctx.check(self.ctx.lib.vkrt_tlas_read(self.ctx.handle, self.handle, _ptr(nodes) if nodes.size else None, nodes.nbytes,
+                                                   _ptr(leaves) if leaves.size else None, leaves.nbytes))
+        return nodes, leaves
 
     def trace_rays(self, rays: np.ndarray, any_hit: bool = False) -> np.ndarray:
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)

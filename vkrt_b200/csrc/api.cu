@@ -42,11 +42,102 @@ int uploadGeometry(Context* ctx, Blas* blas, const void* vertices, size_t vertex
 }
 } // namespace
 
+namespace vkrt
+{
+// The device copy of the material table with every texture index made safe to dereference.  The reference clamps only
+// the normal and metallic-roughness indices (src/Raytracer.cpp:1424-1426) and binds the base colour unchecked
+// (-1 = "material has no base-colour texture" would index textures[-1] in shader.rchit:157, undefined in Vulkan).
+// Here indices < 0 or >= the image count sample image 0, the rule the rasteriser path (raster.cu) and the oracle follow.
+int syncMaterials(Context* ctx)
+{
+    if (!ctx->materialsDirty || ctx->materialCount == 0)
+    {
+        return VKRT_SUCCESS;
+    }
+    std::vector<VkrtSubmeshInfo> safe = ctx->materialsHost;
+    if (ctx->textureCount)
+    {
+        auto fix = [&](int32_t& index) {
+            if (index < 0 || (uint32_t)index >= ctx->textureCount)
+            {
+                index = 0;
+            }
+        };
+        for (VkrtSubmeshInfo& r : safe)
+        {
+            fix(r.baseColorTextureIndex), fix(r.metallicRoughnessTextureIndex), fix(r.normalTextureIndex);
+        }
+    }
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaMemcpy(ctx->materials.ptr, safe.data(), safe.size() * sizeof(VkrtSubmeshInfo), cudaMemcpyHostToDevice));
+    ctx->materialsDirty = ctx->textureCount == 0; // checked again once textures exist
+    return VKRT_SUCCESS;
+}
+
+// A TLAS holds device pointers into its BLASes and their bounds: it is stale once one of them has been rebuilt
+// (vkrt_blas_rebuild moves the bounds and may move the node storage) or destroyed.
+int checkTlasCurrent(Context* ctx, const Tlas* tlas, const char* who)
+{
+    for (const auto& ref : tlas->blasRefs)
+    {
+        if (std::find(ctx->liveBlas.begin(), ctx->liveBlas.end(), ref.first) == ctx->liveBlas.end())
+        {
+            return ctx->fail(VKRT_ERROR_NOT_READY, std::string(who) + ": the TLAS references a destroyed BLAS");
+        }
+        if (ref.first->generation != ref.second)
+        {
+            return ctx->fail(VKRT_ERROR_NOT_READY, std::string(who) + ": a BLAS was rebuilt after this TLAS was built; build the TLAS again");
+        }
+    }
+    return VKRT_SUCCESS;
+}
+
+int checkSceneForShading(Context* ctx, const Tlas* tlas, const char* who)
+{
+    if (int r = checkTlasCurrent(ctx, tlas, who))
+    {
+        return r;
+    }
+    if (ctx->materialCount == 0 || ctx->textureCount == 0)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, std::string(who) + ": materials and textures must be set first");
+    }
+    if (!tlas->shadingLayout)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, std::string(who) + ": shading reads the 64-byte Model::Vertex (position, normal, uv, tangent "
+                                                                          "as 4 x vec4): every BLAS needs vertexStride >= 64 and a multiple of 16");
+    }
+    if (ctx->materialCount < tlas->maxGeometryCount)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, std::string(who) + ": the material table has " + std::to_string(ctx->materialCount) +
+                                                          " rows but a BLAS has " + std::to_string(tlas->maxGeometryCount) + " geometries");
+    }
+    return syncMaterials(ctx);
+}
+
+// Device-side error flags ([0] = a traversal stack overflowed and a subtree was dropped).  Read where the host already
+// waits for the stream; a set flag is cleared and reported once.
+int checkDeviceErrors(Context* ctx, const char* who)
+{
+    uint32_t flags[4] = {0, 0, 0, 0};
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(flags, ctx->errorFlags.ptr, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (flags[0])
+    {
+        cudaMemsetAsync(ctx->errorFlags.ptr, 0, sizeof(flags), ctx->stream);
+        ctx->stats.traversalOverflows += 1;
+        return ctx->fail(VKRT_ERROR_TRAVERSAL_OVERFLOW, std::string(who) + ": a ray needed more than " + std::to_string(kStackSize) +
+                                                             " traversal stack entries; the frame is incomplete");
+    }
+    return VKRT_SUCCESS;
+}
+} // namespace vkrt
+
 extern "C" {
 
 int vkrt_version(void)
 {
-    return 200; // 0.2.0: + mip chain, texture level of detail, rasteriser
+    return 300; // 0.3.0: + device-built TLAS hierarchy, instance masks, vkrt_tlas_info / _read, error surfacing
 }
 
 int vkrt_context_create(int deviceOrdinal, VkrtContext** out)
@@ -96,6 +187,14 @@ int vkrt_context_create(int deviceOrdinal, VkrtContext** out)
     {
         e = cudaMemsetAsync(ctx->statCounters.ptr, 0, 64, ctx->stream);
     }
+    if (e == cudaSuccess)
+    {
+        e = ctx->errorFlags.reserve(16);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemsetAsync(ctx->errorFlags.ptr, 0, 16, ctx->stream);
+    }
     if (e != cudaSuccess)
     {
         g_createError = std::string("vkrt_context_create: ") + cudaGetErrorString(e);
@@ -129,6 +228,7 @@ void vkrt_context_destroy(VkrtContext* c)
     ctx->wave.release();
     ctx->raster.release();
     ctx->statCounters.release();
+    ctx->errorFlags.release();
     ctx->gatherStaging.release();
     if (ctx->eventsCreated)
     {
@@ -154,8 +254,8 @@ const char* vkrt_last_error(const VkrtContext* c)
 int vkrt_context_synchronize(VkrtContext* c)
 {
     Context* ctx = C(c);
-    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    return VKRT_SUCCESS;
+    cudaSetDevice(ctx->device);
+    return checkDeviceErrors(ctx, "vkrt_context_synchronize");
 }
 
 void* vkrt_context_stream(VkrtContext* c)
@@ -249,6 +349,7 @@ int vkrt_blas_build(VkrtContext* c, const void* vertices, size_t vertexBytes, ui
         return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_blas_build: host allocation failed");
     }
     blas->vertexStride = vertexStride;
+    blas->shadingLayout = vertexStride >= 64 && (vertexStride & 15u) == 0; // shading reads 4 x float4 per vertex (Model::Vertex)
     blas->vertexBytes = vertexBytes;
     blas->indexCount = indexCount;
     blas->geometryCount = geometryCount;
@@ -289,6 +390,7 @@ int vkrt_blas_build(VkrtContext* c, const void* vertices, size_t vertexBytes, ui
     {
         return cleanup(r);
     }
+    ctx->liveBlas.push_back(blas);
     *out = blas;
     return VKRT_SUCCESS;
 }
@@ -326,6 +428,8 @@ void vkrt_blas_destroy(VkrtContext* c, VkrtBlas* b)
     {
         cudaSetDevice(C(c)->device);
         cudaStreamSynchronize(C(c)->stream);
+        auto& live = C(c)->liveBlas;
+        live.erase(std::remove(live.begin(), live.end(), (const Blas*)blas), live.end());
     }
     blas->vertices.release(), blas->indices.release();
     blas->geomFirstTri.release(), blas->geomIndexBase.release();
@@ -391,19 +495,46 @@ int vkrt_tlas_build(VkrtContext* c, const VkrtInstance* instances, uint32_t inst
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: NULL argument");
     }
     *out = nullptr;
-    if (instanceCount == 0 || instanceCount > 256)
+    if (instanceCount == 0 || instanceCount > kMaxInstances)
     {
-        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: instanceCount must be in 1..256");
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: instanceCount must be in 1.." + std::to_string(kMaxInstances));
     }
     cudaSetDevice(ctx->device);
+    Tlas* tlas = new (std::nothrow) Tlas();
+    if (!tlas)
+    {
+        return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_tlas_build: host allocation failed");
+    }
+    auto cleanup = [&](int code) {
+        vkrt_tlas_destroy(c, tlas);
+        return code;
+    };
     std::vector<InstanceRecord> recs(instanceCount);
-    std::vector<InstanceBounds> bounds(instanceCount);
+    uint32_t deepest = 0;
+    const Blas* lastSeen = nullptr;
     for (uint32_t i = 0; i < instanceCount; ++i)
     {
         const Blas* blas = reinterpret_cast<const Blas*>((uintptr_t)instances[i].accelerationStructureReference);
-        if (!blas)
+        if (blas != lastSeen) // thousands of instances usually share a few BLASes
         {
-            return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: instance " + std::to_string(i) + " has no BLAS reference");
+            if (!blas || std::find(ctx->liveBlas.begin(), ctx->liveBlas.end(), blas) == ctx->liveBlas.end())
+            {
+                return cleanup(ctx->fail(VKRT_ERROR_INVALID_ARGUMENT,
+                                         "vkrt_tlas_build: instance " + std::to_string(i) + " does not reference a live BLAS of this context"));
+            }
+            bool seen = false;
+            for (const auto& ref : tlas->blasRefs)
+            {
+                seen = seen || ref.first == blas;
+            }
+            if (!seen)
+            {
+                tlas->blasRefs.emplace_back(blas, blas->generation);
+            }
+            deepest = std::max(deepest, blas->levels);
+            tlas->maxGeometryCount = std::max(tlas->maxGeometryCount, blas->geometryCount);
+            tlas->shadingLayout = tlas->shadingLayout && blas->shadingLayout;
+            lastSeen = blas;
         }
         InstanceRecord& r = recs[i];
         std::memset(&r, 0, sizeof(r));
@@ -414,55 +545,38 @@ int vkrt_tlas_build(VkrtContext* c, const VkrtInstance* instances, uint32_t inst
         r.vertices = blas->vertices.as<uint8_t>();
         r.indices = blas->indices.as<uint32_t>();
         r.vertexStride = blas->vertexStride;
-        // world bounds: the 8 corners of the BLAS box through object->world, padded by a few ulps
-        InstanceBounds& wb = bounds[i];
+        r.mask = instances[i].mask;
+        r.customIndex = instances[i].instanceCustomIndex;
+        r.flags = instances[i].flags;
         for (int k = 0; k < 3; ++k)
         {
-            wb.lo[k] = INFINITY;
-            wb.hi[k] = -INFINITY;
+            r.blasLo[k] = blas->boundsMin[k];
+            r.blasHi[k] = blas->boundsMax[k];
         }
-        for (int corner = 0; corner < 8; ++corner)
-        {
-            const F3 p = f3((corner & 1) ? blas->boundsMax[0] : blas->boundsMin[0], (corner & 2) ? blas->boundsMax[1] : blas->boundsMin[1],
-                            (corner & 4) ? blas->boundsMax[2] : blas->boundsMin[2]);
-            const F3 q = affinePoint(r.o2w, p);
-            wb.lo[0] = std::min(wb.lo[0], q.x), wb.lo[1] = std::min(wb.lo[1], q.y), wb.lo[2] = std::min(wb.lo[2], q.z);
-            wb.hi[0] = std::max(wb.hi[0], q.x), wb.hi[1] = std::max(wb.hi[1], q.y), wb.hi[2] = std::max(wb.hi[2], q.z);
-        }
-        for (int k = 0; k < 3; ++k)
-        {
-            const float padAbs = (std::fabs(wb.lo[k]) + std::fabs(wb.hi[k])) * 1e-5f + 1e-30f;
-            wb.lo[k] -= padAbs;
-            wb.hi[k] += padAbs;
-        }
-    }
-    Tlas* tlas = new (std::nothrow) Tlas();
-    if (!tlas)
-    {
-        return ctx->fail(VKRT_ERROR_OUT_OF_MEMORY, "vkrt_tlas_build: host allocation failed");
     }
     tlas->instanceCount = instanceCount;
     cudaError_t e = tlas->instances.reserve(recs.size() * sizeof(InstanceRecord));
-    if (e == cudaSuccess)
-    {
-        e = tlas->bounds.reserve(bounds.size() * sizeof(InstanceBounds));
-    }
     if (e == cudaSuccess)
     {
         e = cudaMemcpyAsync(tlas->instances.ptr, recs.data(), recs.size() * sizeof(InstanceRecord), cudaMemcpyHostToDevice, ctx->stream);
     }
     if (e == cudaSuccess)
     {
-        e = cudaMemcpyAsync(tlas->bounds.ptr, bounds.data(), bounds.size() * sizeof(InstanceBounds), cudaMemcpyHostToDevice, ctx->stream);
-    }
-    if (e == cudaSuccess)
-    {
-        e = cudaStreamSynchronize(ctx->stream);
+        e = cudaStreamSynchronize(ctx->stream); // `recs` goes out of scope
     }
     if (e != cudaSuccess)
     {
-        vkrt_tlas_destroy(c, tlas);
-        return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_tlas_build: ") + cudaGetErrorString(e));
+        return cleanup(ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_tlas_build: ") + cudaGetErrorString(e)));
+    }
+    if (int r = buildTlasOnDevice(ctx, tlas))
+    {
+        return cleanup(r);
+    }
+    // one stack serves both levels (traverse.cuh): top-level path + the two groups parked on entering an instance + BLAS path
+    if (tlas->nodeCount && tlas->levels + 2u + deepest > (uint32_t)kStackSize)
+    {
+        return cleanup(ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_build: " + std::to_string(tlas->levels) + " top levels + " +
+                                                                  std::to_string(deepest) + " bottom levels exceed the traversal stack"));
     }
     *out = tlas;
     return VKRT_SUCCESS;
@@ -481,8 +595,54 @@ void vkrt_tlas_destroy(VkrtContext* c, VkrtTlas* t)
     }
     Tlas* tlas = T(t);
     tlas->instances.release();
-    tlas->bounds.release();
+    tlas->nodes.release();
+    tlas->leafInstance.release();
     delete tlas;
+}
+
+int vkrt_tlas_info(VkrtContext* c, const VkrtTlas* t, VkrtTlasInfo* out)
+{
+    Context* ctx = C(c);
+    if (!t || !out)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_info: NULL argument");
+    }
+    const Tlas* tlas = T(t);
+    out->instanceCount = tlas->instanceCount;
+    out->nodeCount = tlas->nodeCount;
+    out->levels = tlas->levels;
+    out->reserved = 0;
+    for (int k = 0; k < 3; ++k)
+    {
+        out->boundsMin[k] = tlas->boundsMin[k];
+        out->boundsMax[k] = tlas->boundsMax[k];
+    }
+    out->sahCost = tlas->sahCost;
+    out->buildMilliseconds = tlas->buildMs;
+    return VKRT_SUCCESS;
+}
+
+int vkrt_tlas_read(VkrtContext* c, const VkrtTlas* t, void* nodes, size_t nodeBytes, uint32_t* leafInstances, size_t leafBytes)
+{
+    Context* ctx = C(c);
+    const Tlas* tlas = T(t);
+    if (!tlas)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tlas_read: NULL tlas");
+    }
+    cudaSetDevice(ctx->device);
+    if (nodes && tlas->nodeCount)
+    {
+        const size_t bytes = std::min<size_t>(nodeBytes, (size_t)tlas->nodeCount * sizeof(Node8));
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(nodes, tlas->nodes.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (leafInstances && tlas->nodeCount)
+    {
+        const size_t bytes = std::min<size_t>(leafBytes, (size_t)tlas->instanceCount * 4);
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(leafInstances, tlas->leafInstance.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return VKRT_SUCCESS;
 }
 
 int vkrt_materials_set(VkrtContext* c, const VkrtSubmeshInfo* rows, uint32_t count)
@@ -495,10 +655,10 @@ int vkrt_materials_set(VkrtContext* c, const VkrtSubmeshInfo* rows, uint32_t cou
     cudaSetDevice(ctx->device);
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     VKRT_CUDA_TRY(ctx, ctx->materials.reserve((size_t)count * sizeof(VkrtSubmeshInfo)));
-    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->materials.ptr, rows, (size_t)count * sizeof(VkrtSubmeshInfo), cudaMemcpyHostToDevice, ctx->stream));
-    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->materialsHost.assign(rows, rows + count);
     ctx->materialCount = count;
-    return VKRT_SUCCESS;
+    ctx->materialsDirty = true;
+    return syncMaterials(ctx);
 }
 
 int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
@@ -551,6 +711,7 @@ int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->textureCount = count;
     ctx->textureHost = recs;
+    ctx->materialsDirty = true; // texture indices of the material rows are checked against the new image count
     return VKRT_SUCCESS;
 }
 
@@ -774,8 +935,7 @@ int vkrt_frame_read(VkrtContext* c, VkrtFrame* fr, int aov, void* dst, size_t pi
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_frame_read: pitch smaller than a row");
     }
     VKRT_CUDA_TRY(ctx, cudaMemcpy2DAsync(dst, pitch, src, row, row, f->height, cudaMemcpyDeviceToHost, ctx->stream));
-    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    return VKRT_SUCCESS;
+    return checkDeviceErrors(ctx, "vkrt_frame_read");
 }
 
 int vkrt_frame_present(VkrtContext* c, VkrtFrame* fr, void* dst, size_t pitch, uint64_t* ticket)

@@ -308,6 +308,15 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     {
         return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_rasterize: materials (one row per geometry) and textures must be set first");
     }
+    if (!blas->shadingLayout)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_rasterize: the vertex stage reads the 64-byte Model::Vertex (position and uv as vec4 "
+                                                      "at offsets 0 and 32): the geometry needs vertexStride >= 64 and a multiple of 16");
+    }
+    if (int r = syncMaterials(ctx))
+    {
+        return r;
+    }
     if (!ctx->mipsReady)
     {
         return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_rasterize: the fragment shader samples the mip chain; call vkrt_textures_generate_mips first");

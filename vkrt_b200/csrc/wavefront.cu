@@ -27,8 +27,11 @@ constexpr int kShadeThreads = 128;
 struct SceneDev
 {
     const InstanceRecord* instances;
-    const InstanceBounds* bounds;
+    const Node8* topNodes;        // top-level hierarchy over the instances (null when there is a single instance)
+    const uint32_t* leafInstance; // instance per top-level leaf
     uint32_t instanceCount;
+    uint32_t cullMask;            // traceRayEXT's cullMask: 0xFF in shader.rgen:52 and shader.rchit:133
+    uint32_t* errorFlags;         // [0] traversal stack overflow
     const VkrtSubmeshInfo* rows;
     const TextureRecord* textures;
     uint32_t one; // 0x3F800000, see byteToUnitFloat (traverse.cuh)
@@ -242,43 +245,8 @@ struct BlasBinding
     const Node8* nodes;
     const PackedTri* tris;
     uint32_t instance;
-    InstanceCursor cursor;
+    int spFloor; // MULTI: stack height at which the current BLAS was entered, -1 while the ray is at the top level
 };
-
-// Moves the ray into the next instance it enters (MULTI) or into instance 0; false when there is none.
-template<bool MULTI>
-__device__ __forceinline__ bool enterInstance(const SceneDev& scene, F3 o, F3 d, float tmin, float tmax, BlasBinding<MULTI>& bind, RayCtx& c)
-{
-    if (!MULTI)
-    {
-        const InstanceRecord& inst = scene.instances[0];
-        const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
-        if (!validRay(oo, dd))
-        {
-            return false;
-        }
-        beginTraversal(c, oo, dd, tmin);
-        return true;
-    }
-    const F3 idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    for (;;)
-    {
-        const uint32_t idx = selectNextInstance(scene.bounds, scene.instanceCount, o, idir, tmin, tmax, bind.cursor);
-        if (idx == kInvalid)
-        {
-            return false;
-        }
-        const InstanceRecord& inst = scene.instances[idx];
-        const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
-        if (!validRay(oo, dd))
-        {
-            continue;
-        }
-        bind.instance = idx, bind.nodes = inst.nodes, bind.tris = inst.tris;
-        beginTraversal(c, oo, dd, tmin);
-        return true;
-    }
-}
 
 template<bool ANY, bool MULTI, bool STATS, bool REFILL, typename Source>
 __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Source& src, uint32_t total, uint32_t* cursor, uint32_t refill,
@@ -296,7 +264,11 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
     RayCtx c;
     BestHit best;
     BlasBinding<MULTI> bind;
-    bind.nodes = scene.instances[0].nodes, bind.tris = scene.instances[0].tris, bind.instance = 0u;
+    bind.nodes = scene.instances[0].nodes, bind.tris = scene.instances[0].tris, bind.instance = 0u, bind.spFloor = 0;
+    TlasRefs top;
+    top.nodes = scene.topNodes, top.leafInstance = scene.leafInstance, top.instances = scene.instances;
+    top.instanceCount = scene.instanceCount, top.cullMask = scene.cullMask;
+    TraceCounters* const counters = STATS ? &tc : nullptr;
     uint32_t handle = 0;
     bool active = false;
 
@@ -339,9 +311,20 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                 {
                     if (MULTI)
                     {
-                        resetCursor(bind.cursor);
+                        beginTop(c, o, d, tmin, 0);
+                        c.ngroup = make_uint2(0u, 0x80000000u); // the top-level root
+                        bind.spFloor = -1;
                     }
-                    ok = enterInstance<MULTI>(scene, o, d, tmin, tmax, bind, c);
+                    else
+                    {
+                        const InstanceRecord& inst = scene.instances[0];
+                        const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
+                        ok = validRay(oo, dd) && (inst.mask & scene.cullMask) != 0u;
+                        if (ok)
+                        {
+                            beginTraversal(c, oo, dd, tmin);
+                        }
+                    }
                 }
                 if (ok)
                 {
@@ -365,7 +348,29 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
         {
             for (;;)
             {
-                const int r = traversalStep<ANY>(c, stack, bind.nodes, bind.tris, bind.instance, best, STATS ? &tc : nullptr, scene.one);
+                if (MULTI && bind.spFloor < 0)
+                {
+                    // top level: on to the next instance whose box the ray enters
+                    uint32_t idx = 0;
+                    if (topStep(c, stack, top, best.t, counters, scene.one, scene.errorFlags, idx) == kTopDone)
+                    {
+                        src.commit(handle, best, best.tri != kInvalid);
+                        active = false;
+                        break;
+                    }
+                    F3 o, d;
+                    float tmin, tmax;
+                    src.load(handle, o, d, tmin, tmax);
+                    const InstanceRecord& inst = scene.instances[idx];
+                    int floor = 0;
+                    if (enterInstanceTop(c, stack, inst, o, d, tmin, counters, scene.errorFlags, floor))
+                    {
+                        bind.instance = idx, bind.nodes = inst.nodes, bind.tris = inst.tris, bind.spFloor = floor;
+                    }
+                    continue;
+                }
+                const int r = traversalStep<ANY>(c, stack, bind.nodes, bind.tris, bind.instance, best, counters, scene.one,
+                                                 MULTI ? bind.spFloor : 0, scene.errorFlags);
                 if (r & kStepFound)
                 {
                     src.commit(handle, best, true);
@@ -376,13 +381,14 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                 {
                     if (MULTI)
                     {
+                        // back to the top level: the world-space box state is recomputed from the ray, the suspended
+                        // groups are on the stack below spFloor
                         F3 o, d;
                         float tmin, tmax;
                         src.load(handle, o, d, tmin, tmax);
-                        if (enterInstance<MULTI>(scene, o, d, tmin, best.t, bind, c))
-                        {
-                            continue;
-                        }
+                        beginTop(c, o, d, tmin, bind.spFloor);
+                        bind.spFloor = -1;
+                        continue;
                     }
                     src.commit(handle, best, best.tri != kInvalid);
                     active = false;
@@ -768,7 +774,7 @@ void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
                    uint32_t countImm, float4* hitA, uint32_t* hitInst, int statSlot, uint32_t* cursor)
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
-    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const bool st = ctx->countTraversal, multi = scene.topNodes != nullptr;
     cudaStream_t s = ctx->stream;
     const uint32_t rf = ctx->refillLanes;
 #define VKRT_LAUNCH(S, M) k_trace_closest<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, countPtr, countImm, hitA, hitInst, stat, statSlot, cursor, rf)
@@ -790,7 +796,7 @@ void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
 void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev& w, uint32_t* cursor)
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
-    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const bool st = ctx->countTraversal, multi = scene.topNodes != nullptr;
     cudaStream_t s = ctx->stream;
     const uint32_t rf = ctx->refillLanes;
 #define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf)
@@ -813,7 +819,7 @@ void launchAnyList(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
                    uint32_t* cursor)
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
-    const bool st = ctx->countTraversal, multi = scene.instanceCount > 1;
+    const bool st = ctx->countTraversal, multi = scene.topNodes != nullptr;
     cudaStream_t s = ctx->stream;
 #define VKRT_LAUNCH(S, M) k_trace_any_list<S, M><<<grid, kTraceThreads, 0, s>>>(scene, o, d, n, out, stat, cursor)
     if (st)
@@ -846,9 +852,9 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     {
         spp = 1;
     }
-    if (ctx->materialCount == 0 || ctx->textureCount == 0)
+    if (int rc = checkSceneForShading(ctx, tlas, "vkrt_trace"))
     {
-        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_trace: materials and textures must be set first");
+        return rc;
     }
     const uint32_t paths = frame->paths;
     // Samples per wave: all samples of a pixel that fit the queue budget go through the pipeline together, so a frame
@@ -893,8 +899,11 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
 
     SceneDev scene;
     scene.instances = tlas->instances.as<InstanceRecord>();
-    scene.bounds = tlas->bounds.as<InstanceBounds>();
+    scene.topNodes = tlas->nodeCount ? tlas->nodes.as<Node8>() : nullptr;
+    scene.leafInstance = tlas->leafInstance.as<uint32_t>();
     scene.instanceCount = tlas->instanceCount;
+    scene.cullMask = 0xFFu;
+    scene.errorFlags = ctx->errorFlags.as<uint32_t>();
     scene.rows = ctx->materials.as<VkrtSubmeshInfo>();
     scene.textures = ctx->textureRecords.as<TextureRecord>();
     scene.one = 0x3F800000u;
@@ -1068,6 +1077,10 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays: at most 2^31-1 rays per call");
     }
     const uint32_t n = (uint32_t)count;
+    if (int rc = checkTlasCurrent(ctx, tlas, "vkrt_trace_rays"))
+    {
+        return rc;
+    }
     int r = reserveWave(ctx, n);
     if (r != VKRT_SUCCESS)
     {
@@ -1088,8 +1101,11 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(w.rayD, d.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
     SceneDev scene;
     scene.instances = tlas->instances.as<InstanceRecord>();
-    scene.bounds = tlas->bounds.as<InstanceBounds>();
+    scene.topNodes = tlas->nodeCount ? tlas->nodes.as<Node8>() : nullptr;
+    scene.leafInstance = tlas->leafInstance.as<uint32_t>();
     scene.instanceCount = tlas->instanceCount;
+    scene.cullMask = 0xFFu;
+    scene.errorFlags = ctx->errorFlags.as<uint32_t>();
     scene.rows = nullptr;
     scene.textures = nullptr;
     scene.one = 0x3F800000u;
@@ -1118,7 +1134,7 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     {
         return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_trace_rays: ") + cudaGetErrorString(e));
     }
-    return VKRT_SUCCESS;
+    return checkDeviceErrors(ctx, "vkrt_trace_rays");
 }
 
 } // namespace vkrt
