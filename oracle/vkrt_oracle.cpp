@@ -155,6 +155,7 @@ struct Instance
 {
     float o2w[12];
     float w2o[12];
+    uint32_t mask = 0xFFu; /* VkAccelerationStructureInstanceKHR::mask, 0xFF in the reference (Raytracer.cpp:1174) */
 };
 
 /* Watertight per-ray precomputation (Woop et al. 2013, section 3). */
@@ -609,6 +610,11 @@ Hit OrcScene::trace(V3 o, V3 d, float tmin, float tmax, bool anyHit, int mode, C
     }
     for (uint32_t i = 0; i < instances.size(); ++i)
     {
+        /* instance mask against the cullMask of traceRayEXT, 0xFF at both call sites (shader.rgen:52, shader.rchit:133) */
+        if ((instances[i].mask & 0xFFu) == 0u)
+        {
+            continue;
+        }
         /* object-space ray: origin and direction through world->object, t shared (Vulkan spec) */
         const V3 oo = affinePoint(instances[i].w2o, o);
         const V3 dd = affineDir(instances[i].w2o, d);
@@ -868,6 +874,12 @@ uint8_t closestHit(const OrcScene& s, const OrcUniforms& u, const Hit& hit, V3 w
         footprint2 = (uvArea2 / worldArea2) * (wn * wn);
     }
     auto fetch = [&](int32_t textureIndex, float out[4]) {
+        /* textures[-1] (a material without that texture, which the reference does not clamp for base colour,
+         * Raytracer.cpp:1424-1426) or an index past the array is undefined in Vulkan; both sample image 0 here. */
+        if (textureIndex < 0 || (size_t)textureIndex >= s.images.size())
+        {
+            textureIndex = 0;
+        }
         if (lod)
         {
             s.sampleLod((uint32_t)textureIndex, uvx, uvy, footprint2, out);
@@ -975,6 +987,14 @@ OrcScene* orc_scene_create(const float* vertices, uint64_t vertexCount, const ui
     s->buildTriangles();
     s->buildBvh();
     return s;
+}
+
+void orc_scene_set_instance_masks(OrcScene* scene, const uint8_t* masks, uint32_t count)
+{
+    for (uint32_t i = 0; i < count && i < scene->instances.size(); ++i)
+    {
+        scene->instances[i].mask = masks[i];
+    }
 }
 
 void orc_scene_destroy(OrcScene* scene)

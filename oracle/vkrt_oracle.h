@@ -104,6 +104,9 @@ OrcScene* orc_scene_create(const float* vertices, uint64_t vertexCount, const ui
                            const OrcImage* images, uint32_t imageCount, const float* instances,
                            uint32_t instanceCount);
 void orc_scene_destroy(OrcScene* scene);
+/* 8-bit VkAccelerationStructureInstanceKHR::mask per instance (default 0xFF, Raytracer.cpp:1174); an instance whose
+ * mask & 0xFF (the cullMask of every traceRayEXT in the shaders) is zero is invisible to all rays. */
+void orc_scene_set_instance_masks(OrcScene* scene, const uint8_t* masks, uint32_t count);
 
 /* Replace vertex positions/attributes in place (config 5 rebuild) and rebuild the BVH. */
 void orc_scene_update_vertices(OrcScene* scene, const float* vertices, uint64_t vertexCount);

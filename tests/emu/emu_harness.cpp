@@ -38,7 +38,18 @@ struct EmuScene
 {
     EmuBlas* blas = nullptr;
     std::vector<InstanceRecord> instances;
-    std::vector<InstanceBounds> bounds;
+    std::vector<Node8> topNodes;        // as vkrt_tlas_build makes them (instanceCount > 1)
+    std::vector<uint32_t> leafInstance;
+    TlasRefs refs() const
+    {
+        TlasRefs t;
+        t.nodes = topNodes.empty() ? nullptr : topNodes.data();
+        t.leafInstance = leafInstance.data();
+        t.instances = instances.data();
+        t.instanceCount = (uint32_t)instances.size();
+        t.cullMask = 0xFFu;
+        return t;
+    }
     std::vector<VkrtSubmeshInfo> rows;
     std::vector<std::vector<uint8_t>> texels;
     std::vector<TextureRecord> textures;
@@ -46,6 +57,105 @@ struct EmuScene
     std::vector<TextureMips> mips;
     bool lod = false;
 };
+
+// The box-only part of the builder (bvh_build.cu::buildHierarchy), sequentially: Morton codes -> stable sort -> LBVH ->
+// optional cost-optimal collapse decisions -> collapse into wide nodes.  Returns the node count, 0 on failure.
+static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n, uint32_t maxLeaf, float dpPrimCost, const float clo[3],
+                                  const float chi[3], std::vector<Node8>& nodesOut, uint32_t nodeCapacity, std::vector<uint32_t>& primSource,
+                                  float sah[2])
+{
+    std::vector<uint32_t> keys(n), vals(n);
+    const F3 clo3 = f3(clo[0], clo[1], clo[2]);
+    const F3 inv = f3(chi[0] > clo[0] ? 1.0f / (chi[0] - clo[0]) : 0.f, chi[1] > clo[1] ? 1.0f / (chi[1] - clo[1]) : 0.f,
+                      chi[2] > clo[2] ? 1.0f / (chi[2] - clo[2]) : 0.f);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        const float4 l = triBox[2 * (size_t)i], h = triBox[2 * (size_t)i + 1];
+        keys[i] = morton30(f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)), clo3, inv);
+        vals[i] = i;
+    }
+    // radix sort stand-in (stable, like the GPU LSD sort)
+    std::vector<uint32_t> perm(n);
+    std::iota(perm.begin(), perm.end(), 0u);
+    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t c) { return keys[a] < keys[c]; });
+    std::vector<uint32_t> sk(n), sv(n);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        sk[i] = keys[perm[i]], sv[i] = vals[perm[i]];
+    }
+    // k_lbvh
+    std::vector<BinNode> binNodes(std::max(1u, n));
+    std::vector<int> flags(std::max(1u, n), -1);
+    int root = 0;
+    Bvh2 bvh;
+    bvh.nodes = binNodes.data(), bvh.flags = flags.data();
+    bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
+    bvh.count = n, bvh.root = &root;
+    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f, bvh.maxLeaf = maxLeaf;
+    if (n > 1)
+    {
+        for (uint32_t i = 0; i < n; ++i)
+        {
+            lbvhClimb(bvh, i);
+        }
+    }
+    // cost-optimal collapse: children before parents (the GPU climbs from the leaves with arrival counters)
+    std::vector<uint32_t> dpChoice;
+    if (n > 1 && n > maxLeaf && dpPrimCost > 0.0f)
+    {
+        dpChoice.assign(n, 0u);
+        bvh.dpChoice = dpChoice.data(), bvh.dpPrimCost = dpPrimCost;
+        std::vector<std::pair<int, int>> work; // (node, state)
+        work.emplace_back(root, 0);
+        while (!work.empty())
+        {
+            auto [node, state] = work.back();
+            if (state == 0)
+            {
+                work.back().second = 1;
+                const int2 ch = binNodes[node].children;
+                if (ch.x >= 0)
+                {
+                    work.emplace_back(ch.x, 0);
+                }
+                if (ch.y >= 0)
+                {
+                    work.emplace_back(ch.y, 0);
+                }
+            }
+            else
+            {
+                dpSolve(bvh, node);
+                work.pop_back();
+            }
+        }
+    }
+    // collapse
+    std::vector<int> taskRef(nodeCapacity);
+    primSource.assign(n, 0u);
+    uint32_t nodeCounter = 1, primCounter = 0, overflow = 0;
+    CollapseArgs ca;
+    ca.bvh2 = bvh, ca.nodes = nodesOut.data(), ca.taskRef = taskRef.data(), ca.primSource = primSource.data();
+    ca.nodeCounter = &nodeCounter, ca.primCounter = &primCounter, ca.sahAccum = sah, ca.nodeCapacity = nodeCapacity;
+    ca.overflow = &overflow;
+    taskRef[0] = n > 1 ? root : ~0;
+    uint32_t first = 0, last = 1;
+    while (first < last)
+    {
+        for (uint32_t i = first; i < last; ++i)
+        {
+            collapseNode(ca, i);
+        }
+        first = last;
+        last = nodeCounter;
+    }
+    if (overflow || primCounter != n)
+    {
+        fprintf(stderr, "emuBuildHierarchy: collapse failed (overflow=%u packed=%u of %u)\n", overflow, primCounter, n);
+        return 0;
+    }
+    return last;
+}
 
 extern "C" {
 
@@ -114,98 +224,13 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     {
         b->boundsMin[k] = lo[k], b->boundsMax[k] = hi[k];
     }
-    // k_morton
-    std::vector<uint32_t> keys(n), vals(n);
-    const F3 clo3 = f3(clo[0], clo[1], clo[2]);
-    const F3 inv = f3(chi[0] > clo[0] ? 1.0f / (chi[0] - clo[0]) : 0.f, chi[1] > clo[1] ? 1.0f / (chi[1] - clo[1]) : 0.f,
-                      chi[2] > clo[2] ? 1.0f / (chi[2] - clo[2]) : 0.f);
-    for (uint32_t i = 0; i < n; ++i)
-    {
-        const float4 l = triBox[2 * (size_t)i], h = triBox[2 * (size_t)i + 1];
-        keys[i] = morton30(f3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)), clo3, inv);
-        vals[i] = i;
-    }
-    // radix sort stand-in (stable, like the GPU LSD sort)
-    std::vector<uint32_t> perm(n);
-    std::iota(perm.begin(), perm.end(), 0u);
-    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t c) { return keys[a] < keys[c]; });
-    std::vector<uint32_t> sk(n), sv(n);
-    for (uint32_t i = 0; i < n; ++i)
-    {
-        sk[i] = keys[perm[i]], sv[i] = vals[perm[i]];
-    }
-    // k_lbvh
-    std::vector<BinNode> binNodes(std::max(1u, n));
-    std::vector<int> flags(std::max(1u, n), -1);
-    int root = 0;
-    Bvh2 bvh;
-    bvh.nodes = binNodes.data(), bvh.flags = flags.data();
-    bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
-    bvh.count = n, bvh.root = &root;
-    bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f, bvh.maxLeaf = kMaxLeafTris;
-    if (n > 1)
-    {
-        for (uint32_t i = 0; i < n; ++i)
-        {
-            lbvhClimb(bvh, i);
-        }
-    }
-    // cost-optimal collapse: children before parents (the GPU climbs from the leaves with arrival counters)
-    std::vector<uint32_t> dpChoice;
     const char* dpEnv = getenv("VKRT_EMU_DP_PRIM_COST");
     const float dpPrimCost = dpEnv ? (float)atof(dpEnv) : 0.5f;
-    if (n > 1 && dpPrimCost > 0.0f)
-    {
-        dpChoice.assign(n, 0u);
-        bvh.dpChoice = dpChoice.data(), bvh.dpPrimCost = dpPrimCost;
-        std::vector<std::pair<int, int>> work; // (node, state)
-        work.emplace_back(root, 0);
-        while (!work.empty())
-        {
-            auto [node, state] = work.back();
-            if (state == 0)
-            {
-                work.back().second = 1;
-                const int2 ch = binNodes[node].children;
-                if (ch.x >= 0)
-                {
-                    work.emplace_back(ch.x, 0);
-                }
-                if (ch.y >= 0)
-                {
-                    work.emplace_back(ch.y, 0);
-                }
-            }
-            else
-            {
-                dpSolve(bvh, node);
-                work.pop_back();
-            }
-        }
-    }
-    // collapse
-    std::vector<int> taskRef(nodeCapacity);
-    std::vector<uint32_t> primSource(n);
-    uint32_t nodeCounter = 1, primCounter = 0, overflow = 0;
+    std::vector<uint32_t> primSource;
     float sah[2] = {0.f, 0.f};
-    CollapseArgs ca;
-    ca.bvh2 = bvh, ca.nodes = b->nodes.data(), ca.taskRef = taskRef.data(), ca.primSource = primSource.data();
-    ca.nodeCounter = &nodeCounter, ca.primCounter = &primCounter, ca.sahAccum = sah, ca.nodeCapacity = nodeCapacity;
-    ca.overflow = &overflow;
-    taskRef[0] = n > 1 ? root : ~0;
-    uint32_t first = 0, last = 1;
-    while (first < last)
+    const uint32_t last = emuBuildHierarchy(triBox, n, kMaxLeafTris, dpPrimCost, clo, chi, b->nodes, nodeCapacity, primSource, sah);
+    if (last == 0)
     {
-        for (uint32_t i = first; i < last; ++i)
-        {
-            collapseNode(ca, i);
-        }
-        first = last;
-        last = nodeCounter;
-    }
-    if (overflow || primCounter != n)
-    {
-        fprintf(stderr, "emu_blas_build: collapse failed (overflow=%u packed=%u of %u)\n", overflow, primCounter, n);
         delete b;
         return nullptr;
     }
@@ -257,7 +282,6 @@ EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t insta
     EmuScene* s = new EmuScene();
     s->blas = blas;
     s->instances.resize(instanceCount);
-    s->bounds.resize(instanceCount);
     for (uint32_t i = 0; i < instanceCount; ++i)
     {
         InstanceRecord& r = s->instances[i];
@@ -267,23 +291,41 @@ EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t insta
         r.nodes = blas->nodes.data(), r.tris = blas->tris.data();
         r.vertices = blas->vertices.data(), r.indices = blas->indices.data();
         r.vertexStride = blas->stride;
-        InstanceBounds& wb = s->bounds[i];
+        r.mask = 0xFFu;
         for (int k = 0; k < 3; ++k)
         {
-            wb.lo[k] = INFINITY, wb.hi[k] = -INFINITY;
+            r.blasLo[k] = blas->boundsMin[k], r.blasHi[k] = blas->boundsMax[k];
         }
-        for (int corner = 0; corner < 8; ++corner)
+    }
+    if (instanceCount > 1)
+    {
+        // buildTlasOnDevice: k_instance_bounds, the box-only builder with one instance per leaf slot, k_tlas_finalize
+        const uint32_t n = instanceCount;
+        std::vector<float4> box(2 * (size_t)n);
+        float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (uint32_t i = 0; i < n; ++i)
         {
-            const F3 p = f3((corner & 1) ? blas->boundsMax[0] : blas->boundsMin[0], (corner & 2) ? blas->boundsMax[1] : blas->boundsMin[1],
-                            (corner & 4) ? blas->boundsMax[2] : blas->boundsMin[2]);
-            const F3 q = affinePoint(r.o2w, p);
-            wb.lo[0] = std::min(wb.lo[0], q.x), wb.lo[1] = std::min(wb.lo[1], q.y), wb.lo[2] = std::min(wb.lo[2], q.z);
-            wb.hi[0] = std::max(wb.hi[0], q.x), wb.hi[1] = std::max(wb.hi[1], q.y), wb.hi[2] = std::max(wb.hi[2], q.z);
+            float l[3], h[3];
+            instanceWorldBounds(s->instances[i], l, h);
+            box[2 * (size_t)i] = make_float4(l[0], l[1], l[2], 0.f), box[2 * (size_t)i + 1] = make_float4(h[0], h[1], h[2], 0.f);
+            for (int k = 0; k < 3; ++k)
+            {
+                const float c = 0.5f * (l[k] + h[k]);
+                clo[k] = fminf(clo[k], c), chi[k] = fmaxf(chi[k], c);
+            }
         }
-        for (int k = 0; k < 3; ++k)
+        s->topNodes.assign(n + 8u, Node8{});
+        float sah[2] = {0.f, 0.f};
+        const uint32_t last = emuBuildHierarchy(box, n, 1u, 0.5f, clo, chi, s->topNodes, n + 8u, s->leafInstance, sah);
+        s->topNodes.resize(last);
+        for (Node8& node : s->topNodes)
         {
-            const float padAbs = (std::fabs(wb.lo[k]) + std::fabs(wb.hi[k])) * 1e-5f + 1e-30f;
-            wb.lo[k] -= padAbs, wb.hi[k] += padAbs;
+            uint32_t m = 0;
+            for (int sl = 0; sl < 8; ++sl)
+            {
+                m |= ((node.leafBits >> (3 * sl)) & 1u) << sl;
+            }
+            node.reserved = (uint8_t)m;
         }
     }
     if (rows)
@@ -458,11 +500,11 @@ void emu_trace_rays(const EmuScene* s, const VkrtRay* rays, uint64_t count, int 
         bool found;
         if (anyHit)
         {
-            found = traceScene<true>(s->instances.data(), s->bounds.data(), (uint32_t)s->instances.size(), o, d, rays[i].tmin, best, &tc);
+            found = traceScene<true>(s->refs(), o, d, rays[i].tmin, best, &tc);
         }
         else
         {
-            found = traceScene<false>(s->instances.data(), s->bounds.data(), (uint32_t)s->instances.size(), o, d, rays[i].tmin, best, &tc);
+            found = traceScene<false>(s->refs(), o, d, rays[i].tmin, best, &tc);
         }
         nodes += tc.nodes, tris += tc.tris;
         VkrtHit& h = hits[i];
@@ -499,8 +541,7 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                 uint8_t* shadowMask)
 {
     const InstanceRecord* inst = s->instances.data();
-    const InstanceBounds* bnd = s->bounds.data();
-    const uint32_t ic = (uint32_t)s->instances.size();
+    const TlasRefs top = s->refs();
     spp = std::max(spp, 1u);
     for (uint32_t y = y0; y < std::min(y1, height); y += std::max(strideY, 1u))
     {
@@ -523,7 +564,7 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                     BestHit best;
                     best.t = kRayTMax, best.b1 = best.b2 = 0.f;
                     best.tri = kInvalid, best.instance = kInvalid, best.buildIndex = kInvalid;
-                    traceScene<false>(inst, bnd, ic, o, d, kRayTMin, best, nullptr);
+                    traceScene<false>(top, o, d, kRayTMin, best, nullptr);
                     if (best.tri == kInvalid)
                     {
                         acc.x += 0.8f, acc.y += 0.8f, acc.z += 1.0f;
@@ -555,7 +596,7 @@ void emu_render(const EmuScene* s, const VkrtUniforms* u, uint32_t width, uint32
                             BestHit sh;
                             sh.t = lt.distance, sh.b1 = sh.b2 = 0.f;
                             sh.tri = kInvalid, sh.instance = kInvalid, sh.buildIndex = kInvalid;
-                            if (traceScene<true>(inst, bnd, ic, sp.worldPos, lt.dir, kRayTMin, sh, nullptr))
+                            if (traceScene<true>(top, sp.worldPos, lt.dir, kRayTMin, sh, nullptr))
                             {
                                 bits |= 1u << i;
                             }

@@ -55,6 +55,7 @@ def oracle_lib():
         lib.orc_scene_create.restype = vp
         lib.orc_scene_create.argtypes = [vp, u64, vp, u64, C.POINTER(OrcGeometryRange), vp, u32, C.POINTER(OrcImage), u32, vp, u32]
         lib.orc_scene_destroy.argtypes = [vp]
+        lib.orc_scene_set_instance_masks.argtypes = [vp, vp, u32]
         lib.orc_scene_update_vertices.argtypes = [vp, vp, u64]
         lib.orc_scene_build_seconds.restype = C.c_double
         lib.orc_scene_build_seconds.argtypes = [vp]
@@ -107,6 +108,10 @@ class OracleScene:
                 self.h = None
         except Exception:
             pass
+
+    def set_instance_masks(self, masks):
+        m = np.ascontiguousarray(masks, dtype=np.uint8)
+        self.lib.orc_scene_set_instance_masks(self.h, _p(m), m.size)
 
     def build_seconds(self):
         return self.lib.orc_scene_build_seconds(self.h)
