@@ -328,6 +328,10 @@ typedef struct VkrtStats
     float msRaygen, msTraceClosest, msShade, msTraceAny, msResolve, msTotal; /* first wave of the last vkrt_trace, if timing enabled */
     uint32_t samplesPerWave; /* samples per pixel that went through the pipeline together in the last vkrt_trace */
     uint32_t traversalOverflows; /* times VKRT_ERROR_TRAVERSAL_OVERFLOW was raised since the last reset */
+    /* the ten stages of the first wave one by one (same events as the sums above): raygen, closest (primary), surface,
+     * any (shadow), resolve, closest (reflection), surface, any, resolve, sample resolve */
+    float msStage[10];
+    uint32_t reserved2[2];
 } VkrtStats;
 VKRT_API int vkrt_stats_enable(VkrtContext* ctx, int countTraversal, int timeStages);
 VKRT_API int vkrt_stats_reset(VkrtContext* ctx);
@@ -345,6 +349,9 @@ VKRT_API int vkrt_comm_init(VkrtContext* ctx, const uint8_t id[VKRT_UNIQUE_ID_BY
 /* Tile partition without NCCL (tests, emulation): subsequent frames own tiles with index % size == rank. */
 VKRT_API int vkrt_comm_emulate(VkrtContext* ctx, int rank, int size);
 VKRT_API int vkrt_comm_destroy(VkrtContext* ctx);
+/* FNV-1a (64-bit) of a host buffer: the frame checksum bench.py prints, so that runs on 1, 2, 4 and 8 GPUs can be seen to
+ * produce the same image.  Plain host code. */
+VKRT_API uint64_t vkrt_hash_fnv1a64(const void* data, size_t bytes);
 /* Owner rank of the tile containing pixel (x,y) for a frame of this width. */
 VKRT_API int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size);
 /* Gathers the BGRA8 tiles of all ranks into root's frame (stream-ordered; NCCL send/recv group). */

@@ -76,3 +76,58 @@ def check_bvh8(nodes, tris, expected_triangles):
             node_hi[ni] = np.maximum(node_hi[ni], chi)
         assert (node["p"] <= node_lo[ni]).all() or not np.isfinite(node_lo[ni]).all()
     return max_depth, int(seen_slot.sum()), len(nodes)
+
+
+def instance_world_boxes(blas_lo, blas_hi, transforms):
+    """Exact (float64) world boxes of instances: the 8 corners of the BLAS box through each row-major 3x4 transform."""
+    t = np.asarray(transforms, dtype=np.float64).reshape(-1, 3, 4)
+    corners = np.array([[(blas_hi if (c >> k) & 1 else blas_lo)[k] for k in range(3)] for c in range(8)], dtype=np.float64)
+    w = np.einsum("nij,cj->nci", t[:, :, :3], corners) + t[:, None, :, 3]
+    return w.min(axis=1), w.max(axis=1)
+
+
+def check_tlas(nodes, leaf_instance, inst_lo, inst_hi):
+    """Top-level hierarchy (vkrt_tlas_read): every instance sits in exactly one leaf slot (Node8.reserved = mask of leaf
+    slots, one instance each), internal children are contiguous, quantised child boxes contain the instances' world
+    boxes below them.  Returns the depth."""
+    n = len(leaf_instance)
+    assert np.array_equal(np.sort(leaf_instance), np.arange(n, dtype=np.uint32)), "every instance exactly once"
+    seen_node = np.zeros(len(nodes), dtype=np.int32)
+    seen_leaf = np.zeros(n, dtype=np.int32)
+    node_lo = np.full((len(nodes), 3), np.inf)
+    node_hi = np.full((len(nodes), 3), -np.inf)
+    order, stack, depth_max = [], [(0, 1)], 0
+    while stack:
+        ni, depth = stack.pop()
+        seen_node[ni] += 1
+        order.append(ni)
+        depth_max = max(depth_max, depth)
+        node = nodes[ni]
+        imask, leaves, bits = int(node["imask"]), int(node["reserved"]), int(node["leafBits"])
+        assert imask & leaves == 0
+        assert bits == sum(1 << (3 * s) for s in range(8) if (leaves >> s) & 1), "one instance per leaf slot"
+        for s in range(8):
+            if (imask >> s) & 1:
+                child = int(node["childBase"]) + bin(imask & ((1 << s) - 1)).count("1")
+                assert 0 < child < len(nodes)
+                stack.append((child, depth + 1))
+            elif (leaves >> s) & 1:
+                seen_leaf[int(node["primBase"]) + bin(leaves & ((1 << s) - 1)).count("1")] += 1
+    assert (seen_node == 1).all() and (seen_leaf == 1).all()
+    for ni in reversed(order):
+        node = nodes[ni]
+        lo, hi = decode_child_boxes(node)
+        imask, leaves = int(node["imask"]), int(node["reserved"])
+        for s in range(8):
+            if (imask >> s) & 1:
+                child = int(node["childBase"]) + bin(imask & ((1 << s) - 1)).count("1")
+                clo, chi = node_lo[child], node_hi[child]
+            elif (leaves >> s) & 1:
+                i = int(leaf_instance[int(node["primBase"]) + bin(leaves & ((1 << s) - 1)).count("1")])
+                clo, chi = inst_lo[i], inst_hi[i]
+            else:
+                continue
+            assert (lo[s] <= clo).all() and (hi[s] >= chi).all(), (ni, s)
+            node_lo[ni] = np.minimum(node_lo[ni], clo)
+            node_hi[ni] = np.maximum(node_hi[ni], chi)
+    return depth_max

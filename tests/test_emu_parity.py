@@ -155,6 +155,23 @@ def test_ray_parity_shared_edges_and_duplicates():
     assert (ho["primitive"][ho["instance"] != 0xFFFFFFFF] < 2 * n * n).all()  # ties go to the first copy
 
 
+def test_ray_parity_top_level_many_instances():
+    """Two-level traversal over a built top level: 300 rotated, scaled, overlapping instances of one small
+    BLAS; closest and any hit equal to the oracle, which simply loops over every instance."""
+    flat = flatten_model(scenes.random_soup(400, seed=9))
+    inst = scenes.random_instance_transforms(300, seed=2, extent=(80.0, 30.0, 80.0), scale=(0.3, 1.5))
+    o, e = H.OracleScene(flat, inst), H.EmuScene(flat, inst)
+    rays = H.random_rays(12000, 5, (-45, -20, -45), (45, 20, 45))
+    rays["tmax"][::5] = 12.0
+    ho, _ = o.trace_rays(rays)
+    he, nodes, tris = e.trace_rays(rays)
+    assert np.array_equal(ho, he)
+    assert len(np.unique(ho["instance"][ho["instance"] != 0xFFFFFFFF])) > 100
+    ao, _ = o.trace_rays(rays, any_hit=True)
+    ae, _, _ = e.trace_rays(rays, any_hit=True)
+    assert np.array_equal(ao["instance"] != 0xFFFFFFFF, ae["instance"] != 0xFFFFFFFF)
+
+
 def test_frame_parity_analytic_and_instances():
     flat = flatten_model(scenes.analytic_scene(metallic_floor=True))
     inst = np.stack([scenes.identity_instance(1.0), scenes.identity_instance(0.5, (10, 0, -4)), scenes.identity_instance(1.0, (-18, 1, 2))])

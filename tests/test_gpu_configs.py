@@ -1,0 +1,177 @@
+"""GPU tier: BASELINE.json's configs at their STATED sizes against the CPU oracle ("next" item 1).
+The oracle renders a strided pixel subset of the same frame (OracleScene.render(stride=...)); the CUDA path renders the
+whole frame through the C ABI.  Bars: BASELINE.json north_star (>= 99.9 % primitive id and shadow mask, RGB within 1/255);
+bit equality is asserted on top because it is what the design promises against this oracle (parity unpinned against the
+reference's Vulkan output, which is unavailable on this box)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import helpers as H
+from vkrt_b200 import binding as B
+from vkrt_b200 import scenes
+from vkrt_b200.raytracer import Raytracer
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def gpu_frame(rt):
+    return {"rgb": rt.readback(B.AOV_RGB32F), "bgra": rt.readback(B.AOV_BGRA8), "tri": rt.readback(B.AOV_TRIANGLE_ID),
+            "mask": rt.readback(B.AOV_SHADOW_MASK)}
+
+
+def assert_contract(c):
+    assert c["tri_agree"] >= 0.999 and c["mask_agree"] >= 0.999, c
+    assert c["bgra_max_diff"] <= 1 and c["rgb_max_diff"] <= 1.0 / 255.0 + 1e-6, c
+    assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"], c
+
+
+def strided(h, w, sy, sx):
+    sel = np.zeros((h, w), dtype=bool)
+    sel[::sy, ::sx] = True
+    return sel
+
+
+@pytest.fixture(scope="module")
+def sponza_model():
+    return scenes.sponza_standin()
+
+
+def test_config3_full_size_4k_8spp(sponza_model, sponza_flat):
+    """Config 3 (the metric config): 3840 x 2160, 8 spp Halton jitter, ragged 64-pixel tiles (2160 = 33.75 tiles), the
+    8-sample waves of the bench; every 8th pixel in x and y against the oracle.  Also the lane-refill kernels (MODE 2,
+    the config-5 scheduling) on the same frame: results must not depend on the scheduling knob."""
+    W, Hh = 3840, 2160
+    rt = Raytracer(sponza_model, W, Hh)
+    rt.render(spp=8)
+    g = gpu_frame(rt)
+    assert rt.ctx.stats().samplesPerWave == 8
+    o = H.OracleScene(sponza_flat, scenes.REFERENCE_INSTANCE)
+    a = o.render(rt.camera.uniforms(), W, Hh, spp=8, stride=(8, 8))
+    c = H.compare_frames(a, g, strided(Hh, W, 8, 8))
+    print("config3 4K 8spp parity:", c)
+    assert c["pixels"] == 480 * 270
+    assert_contract(c)
+    rt.ctx.set_lane_refill(20)
+    rt.render(spp=8)
+    g2 = gpu_frame(rt)
+    rt.ctx.set_lane_refill(0)
+    for plane in ("bgra", "tri", "mask"):
+        assert np.array_equal(g[plane], g2[plane]), plane
+    assert np.array_equal(g["rgb"], g2["rgb"], equal_nan=True)
+    rt.close()
+
+
+def test_config2_scripted_path_frames(sponza_model, sponza_flat):
+    """Config 2: 1920 x 1080, the reference's own input path (src/Raytracer.cpp:288-323, dt = 1/60): W held for frames
+    0..149, Z for 150..299.  Frames 0, 149, 150 and 299 against the oracle (every 2nd pixel)."""
+    W, Hh = 1920, 1080
+    rt = Raytracer(sponza_model, W, Hh)
+    o = H.OracleScene(sponza_flat, scenes.REFERENCE_INSTANCE)
+    dt = np.float32(1.0 / 60.0)
+    sel = strided(Hh, W, 2, 2)
+    for f in range(300):
+        if f == 0:
+            rt.camera.setPosition((6.3, 4.5, -0.7))
+            rt.camera.setRotation((0.0, 1.57, 0.0))
+        elif f < 150:
+            rt.camera.translate(rt.camera.getForward() * (np.float32(5.0) * dt))
+        else:
+            rt.camera.rotate((0, 1, 0), np.float32(1.5) * dt)
+        if f in (0, 149, 150, 299):
+            rt.render()
+            c = H.compare_frames(o.render(rt.camera.uniforms(), W, Hh, stride=(2, 2)), gpu_frame(rt), sel)
+            print(f"config2 frame {f}:", c)
+            assert_contract(c)
+    rt.close()
+
+
+def test_config4_full_size_4k_16_instances(sponza_model):
+    """Config 4 at its stated size: 16 instances of the Sponza BLAS through the built top level, 3840 x 2160, full-size
+    textures; every 8th pixel against the oracle."""
+    W, Hh = 3840, 2160
+    inst = scenes.instanced_grid_transforms()
+    rt = Raytracer(sponza_model, W, Hh, instances=inst)
+    info = rt.tlas.info()
+    assert info.instanceCount == 16 and info.nodeCount >= 1 and info.levels >= 1
+    rt.camera.setPosition((-25.0, 45.0, -20.0))
+    rt.camera.setRotation((-0.55, -2.16, 0.0))
+    rt.render()
+    g = gpu_frame(rt)
+    o = H.OracleScene(rt.flat, inst)
+    a = o.render(rt.camera.uniforms(), W, Hh, stride=(8, 8))
+    c = H.compare_frames(a, g, strided(Hh, W, 8, 8))
+    print("config4 4K parity:", c)
+    assert_contract(c)
+    seen = np.unique(g["tri"][g["tri"] != 0xFFFFFFFF] >> 24)
+    assert len(seen) >= 8
+    rt.close()
+
+
+def test_config5_ten_million_triangles_fast_build_lane_refill():
+    """Config 5's code path at 10 M triangles: device-generated soup, VKRT_BUILD_PREFER_FAST_BUILD (LBVH + greedy
+    collapse), rebuild in place after the per-frame motion, vkrt_trace_set_lane_refill(20) — the MODE 2 trace kernels.
+    20 k random rays (closest and any hit) against the oracle on the same vertices."""
+    import torch
+
+    from vkrt_b200.scenes_device import SoupDevice
+
+    n = 10_000_000
+    soup = SoupDevice(n, 0)
+    inst = scenes.identity_instance(1.0)
+    ctx = B.Context(0)
+    ctx.set_lane_refill(20)
+    blas = B.Blas(ctx, soup.vertices, soup.indices, soup.ranges(), flags=B.BUILD_PREFER_FAST_BUILD)
+    verts = soup.set_frame(3)
+    blas.rebuild(verts, B.BUILD_PREFER_FAST_BUILD)
+    info = blas.info()
+    assert info.triangleCount == n and info.nodeCount > n // 16
+    tlas = B.Tlas(ctx, [blas], inst)
+    rays = H.random_rays(20000, 17, (-20, 0, -12), (20, 15, 12))
+    rays["tmax"][::3] = 2.0
+    hg = tlas.trace_rays(rays)
+    ag = tlas.trace_rays(rays, any_hit=True)
+    host = {"vertices": verts.cpu().numpy(), "indices": soup.indices.cpu().numpy().astype(np.uint32), "ranges": soup.ranges(),
+            "rows": np.zeros((1, 4), dtype=np.int32), "images": soup.model_stub()["images"]}
+    o = H.OracleScene(host, inst)
+    ho, _ = o.trace_rays(rays)
+    ao, _ = o.trace_rays(rays, any_hit=True)
+    assert np.array_equal(ho, hg)
+    assert np.array_equal(ao["instance"] != 0xFFFFFFFF, ag["instance"] != 0xFFFFFFFF)
+    assert (hg["instance"] != 0xFFFFFFFF).mean() > 0.3
+    # a frame through the same kernels (refill on): 640 x 360, every pixel
+    ctx.set_materials(host["rows"])
+    ctx.set_textures(host["images"])
+    frame = B.Frame(ctx, 640, 360)
+    from vkrt_b200 import camera
+
+    u = camera.make_uniforms(640, 360)
+    frame.trace(tlas, u)
+    g = {"rgb": frame.read(B.AOV_RGB32F), "bgra": frame.read(B.AOV_BGRA8), "tri": frame.read(B.AOV_TRIANGLE_ID), "mask": frame.read(B.AOV_SHADOW_MASK)}
+    a = o.render(u, 640, 360)
+    assert_contract(H.compare_frames(a, g))
+    frame.close(), tlas.close(), blas.close(), ctx.close()
+    del soup, verts
+    torch.cuda.empty_cache()
+
+
+def test_multi_gpu_gathered_frame_equals_single_gpu():
+    """interleaved tiles over N ranks + NCCL gather + presentation ring == the single-GPU frame, byte for
+    byte (tests/multigpu_check.py under torchrun).  Needs at least 2 GPUs on the box."""
+    import torch
+
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n = 2 if n < 4 else 4
+    env = dict(os.environ)
+    env.pop("RANK", None), env.pop("WORLD_SIZE", None)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+                        "--master-port", "29631", os.path.join(ROOT, "tests", "multigpu_check.py")], capture_output=True, text=True,
+                       timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("single-GPU: True") == 2, r.stdout

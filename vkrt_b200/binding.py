@@ -112,6 +112,8 @@ class Stats(C.Structure):
         ("msTotal", C.c_float),
         ("samplesPerWave", C.c_uint32),
         ("traversalOverflows", C.c_uint32),
+        ("msStage", C.c_float * 10),
+        ("reserved2", C.c_uint32 * 2),
     ]
 
 
@@ -184,6 +186,7 @@ EXPORTS = [
     "vkrt_comm_emulate",
     "vkrt_comm_destroy",
     "vkrt_tile_owner",
+    "vkrt_hash_fnv1a64",
     "vkrt_tiles_gather",
 ]
 
@@ -245,6 +248,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_comm_emulate": (i32, [vp, i32, i32]),
         "vkrt_comm_destroy": (i32, [vp]),
         "vkrt_tile_owner": (i32, [u32, u32, u32, i32]),
+        "vkrt_hash_fnv1a64": (u64, [vp, sz]),
         "vkrt_tiles_gather": (i32, [vp, vp, i32]),
     }
     for name, (res, args) in sig.items():

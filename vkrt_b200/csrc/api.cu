@@ -7,10 +7,20 @@
 #include <cstring>
 #include <new>
 
+#include <nvtx3/nvToolsExt.h>
+
 using namespace vkrt;
 
 namespace
 {
+// NVTX ranges named after the reference's debug labels (DebugMarker::beginLabel, src/DebugMarker.cpp; "Render" at
+// src/Raytracer.cpp:151).  Header-only NVTX v3: a no-op unless a profiler is attached.
+struct NvtxRange
+{
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
 std::string g_createError;
 
 Context* C(VkrtContext* c) { return static_cast<Context*>(c); }
@@ -359,6 +369,7 @@ int vkrt_blas_build(VkrtContext* c, const void* vertices, size_t vertexBytes, ui
         vkrt_blas_destroy(c, blas);
         return code;
     };
+    NvtxRange range("createBLAS"); // src/Raytracer.cpp:1027
     int r = uploadGeometry(ctx, blas, vertices, vertexBytes, indices, indexCount, onDevice);
     if (r != VKRT_SUCCESS)
     {
@@ -408,6 +419,7 @@ int vkrt_blas_rebuild(VkrtContext* c, VkrtBlas* b, const void* vertices, size_t 
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_blas_rebuild: vertex data size differs from the original build");
     }
     cudaSetDevice(ctx->device);
+    NvtxRange range("createBLAS (rebuild)");
     blas->flags = flags; // PLOC (default) or LBVH (VKRT_BUILD_PREFER_FAST_BUILD) may change between rebuilds
     int r = uploadGeometry(ctx, blas, vertices, vertexBytes, nullptr, 0, (flags & VKRT_BUILD_INPUT_ON_DEVICE) != 0);
     if (r != VKRT_SUCCESS)
@@ -509,6 +521,7 @@ int vkrt_tlas_build(VkrtContext* c, const VkrtInstance* instances, uint32_t inst
         vkrt_tlas_destroy(c, tlas);
         return code;
     };
+    NvtxRange range("createTLAS"); // src/Raytracer.cpp:1159
     std::vector<InstanceRecord> recs(instanceCount);
     uint32_t deepest = 0;
     const Blas* lastSeen = nullptr;
@@ -890,6 +903,7 @@ int vkrt_trace(VkrtContext* c, const VkrtTlas* tlas, const VkrtUniforms* uniform
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace: NULL argument");
     }
     cudaSetDevice(ctx->device);
+    NvtxRange range("Render"); // DebugMarker::beginLabel(cb, "Render"), src/Raytracer.cpp:151
     return traceFrame(ctx, T(tlas), uniforms, spp, frameIndex, flags, F(frame));
 }
 
@@ -1052,6 +1066,7 @@ int vkrt_rasterize(VkrtContext* c, const VkrtBlas* b, const float* wvp, uint32_t
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_rasterize: NULL argument");
     }
     cudaSetDevice(ctx->device);
+    NvtxRange range("Render"); // DebugMarker::beginLabel(cb, "Render"), src/Rasterizer.cpp:117
     return rasterizeFrame(ctx, static_cast<const Blas*>(b), wvp, flags, F(fr));
 }
 
@@ -1130,6 +1145,10 @@ int vkrt_stats_get(VkrtContext* c, VkrtStats* out)
         ctx->stats.msTraceAny = ms(3, 4) + ms(7, 8);
         ctx->stats.msResolve = ms(9, 10);
         ctx->stats.msTotal = ms(0, 10);
+        for (int k = 0; k < 10; ++k)
+        {
+            ctx->stats.msStage[k] = ms(k, k + 1);
+        }
     }
     *out = ctx->stats;
     return VKRT_SUCCESS;
@@ -1182,6 +1201,17 @@ int vkrt_comm_destroy(VkrtContext* c)
     return commDestroy(C(c));
 }
 
+uint64_t vkrt_hash_fnv1a64(const void* data, size_t bytes)
+{
+    const uint8_t* p = static_cast<const uint8_t*>(data);
+    uint64_t h = 0xCBF29CE484222325ull;
+    for (size_t i = 0; i < bytes; ++i)
+    {
+        h = (h ^ p[i]) * 0x100000001B3ull;
+    }
+    return h;
+}
+
 int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size)
 {
     const uint32_t tilesX = (width + kTile - 1) / kTile;
@@ -1197,6 +1227,7 @@ int vkrt_tiles_gather(VkrtContext* c, VkrtFrame* frame, int root)
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tiles_gather: bad argument");
     }
     cudaSetDevice(ctx->device);
+    NvtxRange range("Tile gather");
     return gatherTiles(ctx, F(frame), root);
 }
 

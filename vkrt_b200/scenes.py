@@ -455,6 +455,24 @@ def write_sponza_bin(path: str, gltf_path: str):
         f.write(bytes(buf))
 
 
+def random_instance_transforms(n: int, seed: int = 1, extent=(60.0, 20.0, 60.0), scale=(0.2, 1.0)) -> np.ndarray:
+    """n row-major 3x4 object->world matrices: random rotation, uniform scale in `scale`, translation inside +-extent/2
+    (top-level tests: overlapping, rotated instance boxes)."""
+    rng = np.random.default_rng(seed)
+    q = rng.normal(0, 1, (n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w, x, y, z = q.T
+    rot = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                    2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                    2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], axis=1).reshape(n, 3, 3)
+    sc = rng.uniform(scale[0], scale[1], n)
+    tr = (rng.random((n, 3)) - 0.5) * np.asarray(extent)
+    m = np.zeros((n, 3, 4), dtype=np.float32)
+    m[:, :, :3] = rot * sc[:, None, None]
+    m[:, :, 3] = tr
+    return m.reshape(n, 12)
+
+
 def instanced_grid_transforms(nx: int = 4, nz: int = 4) -> np.ndarray:
     """BASELINE.json config 4: scale 0.01 + translation (40 i, 0, 25 j)."""
     out = []
