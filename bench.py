@@ -37,14 +37,32 @@ WORKLOADS = {
 RASTER_METRIC = "Sponza 4K rasteriser Mpixel/s (8x MSAA)"
 
 
+def csrc_sha():
+    """Hash of the library sources this run was built from (the same function as tools/ncu_traffic.py)."""
+    import hashlib
+
+    d = os.path.join(ROOT, "vkrt_b200", "csrc")
+    h = hashlib.sha256()
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh", ".hpp")) or name == "Makefile":
+            h.update(name.encode())
+            h.update(open(os.path.join(d, name), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def read_traffic(workload):
-    """Measured DRAM bytes per launch of the dominant kernel for this workload (ncu capture summarised under profiles/)."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    """ncu counters per launch of the trace kernels (DRAM bytes, warp and thread instructions) from the capture summarised in
+    profiles/r02_traffic.json (tools/ncu_traffic.py) - only if it was taken on exactly the library sources this run uses."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
     try:
         e = json.load(open(p)).get(workload)
-        return (float(e["bytes_per_launch_avg"]), e["capture"]) if e else (None, None)
     except Exception:
-        return None, None
+        return None, "no capture (profiles/r02_traffic.json missing)"
+    if not e:
+        return None, f"no capture of {workload} in profiles/r02_traffic.json"
+    if e.get("csrc_sha") != csrc_sha():
+        return None, f"capture at commit {e.get('commit')} is of other library sources (csrc hash {e.get('csrc_sha')} != {csrc_sha()}): not used"
+    return e, f"profiles/r02_traffic.json, ncu capture at commit {e.get('commit')} of these sources"
 
 
 def read_peaks():
@@ -343,6 +361,7 @@ def main():
     if args.build_flags < 0:
         args.build_flags = 1 if args.workload == "config5" else 0
     soup = None
+    t_ingest0 = time.perf_counter()
     if args.workload == "config5":
         from vkrt_b200 import scenes
         from vkrt_b200.scenes_device import SoupDevice
@@ -356,12 +375,36 @@ def main():
                        build_flags=args.build_flags)
     else:
         model, instances = build_scene(args.workload)
+        t_ingest1 = time.perf_counter()
         rt = Raytracer(model, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id,
                        build_flags=args.build_flags)
+    rt.ctx.synchronize()
+    t_ingest2 = time.perf_counter()
+    if soup is not None:
+        t_ingest1 = t_ingest0
+    # ingest: host side (glTF / stand-in geometry + image decode), then upload + mip chain + first BLAS/TLAS build (cold)
+    ingest = {"host_s": t_ingest1 - t_ingest0, "device_s": t_ingest2 - t_ingest1}
     build_ms = []
     lane_refill = args.lane_refill if args.lane_refill >= 0 else (20 if args.workload == "config5" else 0)
     rt.ctx.set_lane_refill(lane_refill)
     rt.set_texture_lod(B.TEXTURE_LOD_RAY_CONES if args.texture_lod == "cones" else B.TEXTURE_LOD_ZERO)
+    info = rt.blas.info()
+    cold_build_ms = float(info.buildMilliseconds)
+    # warm BLAS build: median of 10 vkrt_blas_rebuild calls per hierarchy flavour (device time of the whole kernel chain,
+    # CUDA events inside the library; storage and scratch already allocated) - the number "BVH build Mtri/s" is quoted on
+    warm = {}
+    verts_in = soup.vertices if soup is not None else rt.flat["vertices"]
+    for name, fl in (("ploc_optimal", 0), ("lbvh_greedy", 1)):
+        if soup is not None and fl == 0 and args.triangles > 20_000_000:
+            continue  # config 5 at 50 M rebuilds with LBVH every frame; the PLOC scratch would not leave room for the 4K queues
+        times = []
+        for _ in range(10):
+            rt.blas.rebuild(verts_in, fl)
+            times.append(float(rt.blas.info().buildMilliseconds))
+        warm[name] = {"ms_median": float(np.median(times)), "ms_min": float(np.min(times)),
+                      "mtri_s": info.triangleCount / float(np.median(times)) / 1e3, "nodes": int(rt.blas.info().nodeCount),
+                      "sah_cost": float(rt.blas.info().sahCost)}
+    rt.rebuild(verts_in, flags=args.build_flags)  # back to the flavour the frames are traced on (+ a fresh TLAS)
     info = rt.blas.info()
     stream = torch.cuda.ExternalStream(rt.ctx.stream, device=local)
     flags = B.TRACE_NO_AOV
@@ -413,11 +456,18 @@ def main():
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     st = rt.ctx.stats()
+    # checksum of the last frame of the timed region (gathered on rank 0): equal at N = 1, 2, 4, 8 <=> same image
+    frame_fnv = None
+    if rank == 0:
+        last = rt.readback(B.AOV_BGRA8)
+        frame_fnv = f"{int(rt.ctx.lib.vkrt_hash_fnv1a64(last.ctypes.data, last.nbytes)):016x}"
     wave_samples = max(1, int(st.samplesPerWave))  # the stage times below cover the first wave = this many samples
     rays_local = np.array([st.raysPrimary, st.raysShadow, st.raysReflection], dtype=np.float64)
     launches = int(st.kernelLaunches)
     stage = {"raygen": st.msRaygen, "trace_closest": st.msTraceClosest, "shade": st.msShade, "trace_any": st.msTraceAny,
              "resolve": st.msResolve, "sample_total": st.msTotal}
+    stage_each = [float(v) for v in st.msStage]  # raygen, closest d0, surface, any d0, resolve, closest d1, surface, any d1, resolve, sample resolve
+    bounce_frac = st.raysShadowBounce / max(st.raysShadow, 1)
 
     # end to end through the reference-facing call: render + readback into pinned host memory every step
     ring = [rt.ctx.host_array((Hh, W, 4)) for _ in range(3)] if rank == 0 else []
@@ -472,20 +522,46 @@ def main():
         # 32 (ray) + 4 (result) + 80 * nodes visited + 48 * triangles tested.
         b_any = 32 + 4 + 80 * n_node_any + 48 * n_tri_any
         b_cl = 32 + 16 + 80 * n_node_cl + 48 * n_tri_cl
-        any_rays_per_wave = rs / max(args.steps * spp, 1) / world * wave_samples
-        any_rays_per_sample = any_rays_per_wave
-        any_ms = max(stage["trace_any"], 1e-9)
-        achieved = any_rays_per_wave * b_any / (any_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "k_trace_any (2 launches per wave of samples)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "frac_of_8tbs_nominal": achieved / 8000.0, "peak_source": peak_src,
-                    "traffic": read_traffic(args.workload)[0], "traffic_source": read_traffic(args.workload)[1],
-                    "algorithmic_bytes_per_launch": any_rays_per_sample * b_any / 2,
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        issue_peak = 148 * 4 * sm_mhz * 1e6  # warp instructions per second: 148 SMs x 4 schedulers x clock
+        per_wave = 1.0 / max(args.steps * spp, 1) / world * wave_samples  # whole-job ray totals -> one rank's first wave
+        rays_launch = {"closest_d0": rp * per_wave, "any_d0": rs * (1.0 - bounce_frac) * per_wave,
+                       "closest_d1": rr * per_wave, "any_d1": rs * bounce_frac * per_wave}
+        ms_launch = {"closest_d0": stage_each[1], "any_d0": stage_each[3], "closest_d1": stage_each[5], "any_d1": stage_each[7]}
+        capture, capture_note = read_traffic(args.workload)
+        launches_out = {}
+        for name in ("closest_d0", "any_d0", "closest_d1", "any_d1"):
+            ms_l = max(ms_launch[name], 1e-9)
+            algo = rays_launch[name] * (b_any if name.startswith("any") else b_cl)
+            e = {"rays": rays_launch[name], "ms": ms_launch[name], "algorithmic_bytes": algo,
+                 "frac_algorithmic": algo / (ms_l * 1e-3) / 1e9 / peak, "traffic": None, "dram_frac": None, "issue_frac": None,
+                 "thread_inst_per_ray": None}
+            c = (capture or {}).get("launches", {}).get(name) if world == 1 else None
+            if c:
+                e["traffic"] = c.get("dram_read_bytes", 0.0) + c.get("dram_write_bytes", 0.0)
+                e["dram_frac"] = e["traffic"] / (ms_l * 1e-3) / 1e9 / peak
+                e["issue_frac"] = c["warp_inst"] / (ms_l * 1e-3) / issue_peak
+                e["thread_inst_per_ray"] = c["thread_inst"] / max(rays_launch[name], 1.0)
+                e["warp_inst"] = c["warp_inst"]
+            launches_out[name] = e
+        dom = launches_out["any_d0"]
+        roofline = {"bound": "hbm", "kernel": "k_trace_any, depth-0 launch (shadow rays of the primary hits; one launch per wave of samples)",
+                    "achieved": dom["algorithmic_bytes"] / (max(dom["ms"], 1e-9) * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                    "frac": dom["frac_algorithmic"], "frac_algorithmic": dom["frac_algorithmic"],
+                    "frac_of_8tbs_nominal": dom["algorithmic_bytes"] / (max(dom["ms"], 1e-9) * 1e-3) / 1e9 / 8000.0,
+                    "peak_source": peak_src, "traffic": dom["traffic"], "traffic_source": capture_note,
+                    "dram_frac": dom["dram_frac"], "issue_frac": dom["issue_frac"], "thread_inst_per_shadow_ray": dom["thread_inst_per_ray"],
+                    "issue_peak_ginst_s": issue_peak / 1e9, "sm_mhz_used": sm_mhz,
+                    "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "launch_ms": dom["ms"],
                     "bytes_per_ray_any": b_any, "bytes_per_ray_closest": b_cl,
                     "n_node_any": n_node_any, "n_tri_any": n_tri_any, "n_node_closest": n_node_cl, "n_tri_closest": n_tri_cl,
-                    "launch_ms_avg": any_ms / 2, "samples_per_wave": wave_samples, "lane_refill": lane_refill, "stage_ms_sample0": stage,
-                    "note": "achieved = algorithmic bytes (32 ray + 4 result + 80/node + 48/triangle) / kernel time; it can exceed the HBM "
-                            "peak because the BVH is served from L1/L2 (see traffic = measured DRAM bytes per launch); ncu shows the kernel "
-                            "bound by instruction issue (profiles/r01_ncu_trace_kernels_v5.txt: issue slots 79 % busy, DRAM 2 %)"}
+                    "launches": launches_out, "samples_per_wave": wave_samples, "lane_refill": lane_refill,
+                    "stage_ms_sample0": stage, "stage_ms_each": stage_each,
+                    "note": "frac = frac_algorithmic = algorithmic bytes (32 ray + 4 result + 80/node + 48/triangle, nodes and triangles per ray from "
+                            "the counting pass, one mean for both depths) / live launch time / HBM peak; it exceeds 1 when the BVH is served from "
+                            "L1/L2.  dram_frac = ncu-measured DRAM bytes of the same launch / live time / peak; issue_frac = ncu warp instructions / "
+                            "live time / (148 SMs x 4 x SM clock): the roof that binds these kernels.  Both are null unless "
+                            "profiles/r02_traffic.json was captured on exactly these library sources (single GPU only)."}
         line = {
             "metric": "Sponza 4K Mrays/s (prim+shadow+refl)", "value": total_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
@@ -496,7 +572,12 @@ def main():
                        "l2": "per-frame ray/hit/shading queues (>2 GB at 4K) exceed the 126 MB L2; no explicit flush"},
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},
             "mrays_s_by_type": {"primary": rp / (ms * 1e-3) / 1e6, "shadow": rs / (ms * 1e-3) / 1e6, "reflection": rr / (ms * 1e-3) / 1e6},
-            "bvh_build": {"ms": info.buildMilliseconds, "mtri_s": info.triangleCount / max(info.buildMilliseconds, 1e-9) / 1e3,
+            "frame_fnv": frame_fnv, "ingest": ingest,
+            "bvh_build": {"warm": warm, "warm_ms": (warm.get("lbvh_greedy" if args.build_flags & 1 else "ploc_optimal") or {}).get("ms_median"),
+                          "warm_mtri_s": (warm.get("lbvh_greedy" if args.build_flags & 1 else "ploc_optimal") or {}).get("mtri_s"),
+                          "cold_first_build_ms": cold_build_ms, "tlas": {"instances": int(rt.tlas.info().instanceCount),
+                                                                          "nodes": int(rt.tlas.info().nodeCount), "ms": float(rt.tlas.info().buildMilliseconds)},
+                          "ms": info.buildMilliseconds, "mtri_s": info.triangleCount / max(info.buildMilliseconds, 1e-9) / 1e3,
                           "sah_cost": info.sahCost, "build_flags": args.build_flags, "rebuilds_in_timed_region": len(build_ms),
                           "rebuild_ms_median": float(np.median(build_ms)) if build_ms else None,
                           "rebuild_mtri_s": info.triangleCount / float(np.median(build_ms)) / 1e3 if build_ms else None},

@@ -331,7 +331,7 @@ typedef struct VkrtStats
     /* the ten stages of the first wave one by one (same events as the sums above): raygen, closest (primary), surface,
      * any (shadow), resolve, closest (reflection), surface, any, resolve, sample resolve */
     float msStage[10];
-    uint32_t reserved2[2];
+    uint64_t raysShadowBounce; /* the part of raysShadow cast from reflection hits (the second k_trace_any launch of a wave) */
 } VkrtStats;
 VKRT_API int vkrt_stats_enable(VkrtContext* ctx, int countTraversal, int timeStages);
 VKRT_API int vkrt_stats_reset(VkrtContext* ctx);

@@ -113,7 +113,7 @@ class Stats(C.Structure):
         ("samplesPerWave", C.c_uint32),
         ("traversalOverflows", C.c_uint32),
         ("msStage", C.c_float * 10),
-        ("reserved2", C.c_uint32 * 2),
+        ("raysShadowBounce", C.c_uint64),
     ]
 
 

@@ -191,11 +191,11 @@ int vkrt_context_create(int deviceOrdinal, VkrtContext** out)
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess)
     {
-        e = ctx->statCounters.reserve(64);
+        e = ctx->statCounters.reserve(128);
     }
     if (e == cudaSuccess)
     {
-        e = cudaMemsetAsync(ctx->statCounters.ptr, 0, 64, ctx->stream);
+        e = cudaMemsetAsync(ctx->statCounters.ptr, 0, 128, ctx->stream);
     }
     if (e == cudaSuccess)
     {
@@ -1110,7 +1110,7 @@ int vkrt_stats_reset(VkrtContext* c)
     cudaSetDevice(ctx->device);
     ctx->stats = VkrtStats{};
     ctx->launches = 0;
-    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(ctx->statCounters.ptr, 0, 64, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(ctx->statCounters.ptr, 0, 128, ctx->stream));
     return VKRT_SUCCESS;
 }
 
@@ -1122,11 +1122,12 @@ int vkrt_stats_get(VkrtContext* c, VkrtStats* out)
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_stats_get: NULL argument");
     }
     cudaSetDevice(ctx->device);
-    unsigned long long host[8] = {};
+    unsigned long long host[16] = {};
     VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(host, ctx->statCounters.ptr, sizeof(host), cudaMemcpyDeviceToHost, ctx->stream));
     VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->stats.raysShadow = host[1];
     ctx->stats.raysReflection = host[2];
+    ctx->stats.raysShadowBounce = host[8];
     ctx->stats.nodesVisited = host[3] + host[6];
     ctx->stats.trianglesTested = host[4] + host[7];
     ctx->stats.nodesVisitedAny = host[6];

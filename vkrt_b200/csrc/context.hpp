@@ -120,7 +120,7 @@ struct Context : VkrtContext
     bool countTraversal = false;
     bool timeStages = false;
     VkrtStats stats{};
-    DeviceBuffer statCounters; // u64[8] device-side: rays p/s/r, nodes, tris
+    DeviceBuffer statCounters; // u64[16] device-side: rays p/s/r, nodes, tris; [8] shadow rays of the bounce
     cudaEvent_t stageEvents[16] = {};
     bool eventsCreated = false;
     int stageEventCount = 0;

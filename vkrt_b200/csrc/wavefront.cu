@@ -551,7 +551,7 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
 // shader.rchit:130-143 + shader_shadow.rmiss: any-hit rays, tmin 0.001, tmax = light distance
 template<int MODE, bool MULTI>
 __global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
-k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor, uint32_t refill)
+k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_t* cursor, uint32_t refill, uint32_t bounce)
 {
     constexpr bool STATS = MODE == 1;
     const uint32_t c0 = w.counters[0], c1 = w.counters[1], c2 = w.counters[2], c3 = w.counters[3];
@@ -565,6 +565,10 @@ k_trace_any(SceneDev scene, WaveDev w, unsigned long long* statCounters, uint32_
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
         atomicAdd(&statCounters[1], (unsigned long long)total);
+        if (bounce)
+        {
+            atomicAdd(&statCounters[8], (unsigned long long)total); // shadow rays cast from reflection hits
+        }
     }
 }
 
@@ -738,7 +742,7 @@ int reserveWave(Context* ctx, uint32_t paths)
     VKRT_CUDA_TRY(ctx, w.pathAccum.reserve(p * 16));
     VKRT_CUDA_TRY(ctx, w.sampleSum.reserve(p * 16));
     VKRT_CUDA_TRY(ctx, w.counters.reserve(64));
-    VKRT_CUDA_TRY(ctx, ctx->statCounters.reserve(64));
+    VKRT_CUDA_TRY(ctx, ctx->statCounters.reserve(128));
     if (ctx->textureLod == VKRT_TEXTURE_LOD_RAY_CONES)
     {
         VKRT_CUDA_TRY(ctx, w.coneT.reserve(p * 4));
@@ -793,13 +797,13 @@ void launchClosest(Context* ctx, const SceneDev& scene, uint32_t grid, const flo
 #undef VKRT_LAUNCH
 }
 
-void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev& w, uint32_t* cursor)
+void launchAny(Context* ctx, const SceneDev& scene, uint32_t grid, const WaveDev& w, uint32_t* cursor, uint32_t bounce)
 {
     unsigned long long* stat = ctx->statCounters.as<unsigned long long>();
     const bool st = ctx->countTraversal, multi = scene.topNodes != nullptr;
     cudaStream_t s = ctx->stream;
     const uint32_t rf = ctx->refillLanes;
-#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf)
+#define VKRT_LAUNCH(S, M) k_trace_any<S, M><<<grid, kTraceThreads, 0, s>>>(scene, w, stat, cursor, rf, bounce)
     if (st)
     {
         multi ? VKRT_LAUNCH(1, true) : VKRT_LAUNCH(1, false);
@@ -995,7 +999,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 3
         }
-        launchAny(ctx, scene, gridTrace, w, w.counters + 9);
+        launchAny(ctx, scene, gridTrace, w, w.counters + 9, 0u);
         if (timed)
         {
             mark(); // 4
@@ -1031,7 +1035,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 7
         }
-        launchAny(ctx, scene, gridTrace, w, w.counters + 11);
+        launchAny(ctx, scene, gridTrace, w, w.counters + 11, 1u);
         if (timed)
         {
             mark(); // 8
