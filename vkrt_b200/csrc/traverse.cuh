@@ -10,6 +10,10 @@
 #include "common.cuh"
 #include "device_math.cuh"
 
+#if defined(__CUDACC__)
+#include <cuda_fp16.h>
+#endif
+
 namespace vkrt
 {
 
@@ -271,8 +275,97 @@ __device__ __forceinline__ void initSlotTables()
 // and the far planes pushed out by 2^-7 step (bn/bf below): the test stays conservative, and flat boxes (qlo == qhi)
 // keep tn < tf.  NaN planes (0*inf for axis-parallel rays) are dropped by fmaxf/fminf, i.e. that axis never culls.
 // Empty slots carry a zero box that a ray may well hit: they drop out because neither imask nor leafBits names them.
+#if defined(__CUDA_ARCH__) && !defined(VKRT_NODE_TEST_FP32)
+#define VKRT_NODE_TEST_HALF2 1
+// ------------------------------------------------------------------------------------------------------------
+// Packed-half node test (device only): two children per instruction.
+//   * dequantisation: one PRMT drops TWO plane bytes into the low mantissa bytes of the half pair (0x6400 | q) =
+//     (1024 + q0, 1024 + q1), exact;
+//   * plane distances: one HFMA2 per plane pair,  t' = (1024 + q) * a + b',  with every t measured from `tRef`, the
+//     distance at which the ray enters the node's own box (clamped to the ray interval): the values that decide a
+//     child's test then lie within the node's own extent along the ray (|t'| <= ~256 |a|), where a half's 11 bits
+//     resolve 1/8 of a quantisation step, and  b' = (p - o) * idir - 1024 a - tRef  is formed in FP32;
+//   * interval: VHMNMX (three-input packed max/min) + HMNMX2 with the clamp, one HSET2 for both children.
+// Rounding: a -> half costs <= 1279 * 2^-11 |a| = 0.63 step, b' -> half <= 0.75 step, the HFMA2 result <= 0.13 step for
+// planes inside the node; near planes are therefore pulled in and far planes pushed out by kHalfSlackSteps = 2 steps
+// (the FP32 test uses 2^-7 step), the clamps by 2^-10 relative.  Overflow gives +-inf with the sign of the exact value or
+// NaN, which the min/max drop (that axis does not cull).  Only nodes whose steps a_k all lie in [2^-14, 32] take this
+// path (no subnormals, no overflow of 1279 a); any other node - rays almost parallel to a box face, degenerate
+// scales - takes the FP32 test below.  Box tests are not on the parity path: a conservative test cannot change
+// which triangle is hit, only how many nodes are visited (measured: DESIGN.md section 5.2).
+// ------------------------------------------------------------------------------------------------------------
+constexpr float kHalfSlackSteps = 2.0f;
+
+__device__ __forceinline__ __half2 asHalf2(uint32_t u)
+{
+    return *reinterpret_cast<const __half2*>(&u);
+}
+__device__ __forceinline__ uint32_t asUint(__half2 h)
+{
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// children 2*PAIR and 2*PAIR+1: bytes (2*PAIR & 3) and (2*PAIR & 3) + 1 of their half's plane words
+template<int PAIR>
+__device__ __forceinline__ void testChildPair(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, __half2 ax,
+                                              __half2 ay, __half2 az, __half2 bnx, __half2 bny, __half2 bnz, __half2 bfx, __half2 bfy,
+                                              __half2 bfz, __half2 tminH, __half2 tmaxH, uint32_t magic, uint32_t& hitPairs)
+{
+    constexpr uint32_t sel = ((2 * PAIR) & 3) == 0 ? 0x4140u : 0x4342u; // {q_i, 0x64, q_i+1, 0x64}
+    const __half2 tnx = __hfma2(asHalf2(__byte_perm(nx, magic, sel)), ax, bnx), tfx = __hfma2(asHalf2(__byte_perm(fx, magic, sel)), ax, bfx);
+    const __half2 tny = __hfma2(asHalf2(__byte_perm(ny, magic, sel)), ay, bny), tfy = __hfma2(asHalf2(__byte_perm(fy, magic, sel)), ay, bfy);
+    const __half2 tnz = __hfma2(asHalf2(__byte_perm(nz, magic, sel)), az, bnz), tfz = __hfma2(asHalf2(__byte_perm(fz, magic, sel)), az, bfz);
+    const __half2 tn = __hmax2(__hmax2(__hmax2(tnx, tny), tnz), tminH);
+    const __half2 tf = __hmin2(__hmin2(__hmin2(tfx, tfy), tfz), tmaxH);
+    // child 2*PAIR -> bit 2*PAIR, child 2*PAIR+1 -> bit 16 + 2*PAIR + 1 (folded by the caller)
+    hitPairs |= __hle2_mask(tn, tf) & ((1u << (2 * PAIR)) | (0x20000u << (2 * PAIR)));
+}
+#endif
+
 VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
+#if defined(VKRT_NODE_TEST_HALF2)
+    {
+        const uint32_t eb = floatAsUint(w.n0.w);
+        // A = 2^15 a, a = scale * idir = the distance between neighbouring quantisation planes along the ray
+        const float Ax = uintAsFloat(eb << 16) * idir.x, Ay = uintAsFloat(eb & 0xFFFF0000u) * idir.y, Az = uintAsFloat(w.n1.w << 16) * idir.z;
+        const float amax = fmaxf(fmaxf(fabsf(Ax), fabsf(Ay)), fabsf(Az)), amin = fminf(fminf(fabsf(Ax), fabsf(Ay)), fabsf(Az));
+        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32]; false for inf / NaN
+        {
+            const float t0x = (w.n0.x - o.x) * idir.x, t0y = (w.n0.y - o.y) * idir.y, t0z = (w.n0.z - o.z) * idir.z;
+            // entry distance of the node's own box [p, p + 255 scale]: the near plane of axis k is p_k when a_k > 0
+            const float kFar = 255.0f / 32768.0f;
+            const float tRef = fminf(fmaxf(fmaxf(fmaxf(fmaExplicit(fminf(Ax, 0.0f), kFar, t0x), fmaExplicit(fminf(Ay, 0.0f), kFar, t0y)),
+                                                 fmaExplicit(fminf(Az, 0.0f), kFar, t0z)), tminP), tmaxP);
+            const float kOff = -1024.0f / 32768.0f, kSlack = kHalfSlackSteps / 32768.0f;
+            const float bx = fmaExplicit(Ax, kOff, t0x - tRef), by = fmaExplicit(Ay, kOff, t0y - tRef), bz = fmaExplicit(Az, kOff, t0z - tRef);
+            const __half2 ax = __float2half2_rn(Ax * (1.0f / 32768.0f)), ay = __float2half2_rn(Ay * (1.0f / 32768.0f)),
+                          az = __float2half2_rn(Az * (1.0f / 32768.0f));
+            const __half2 bnx = __float2half2_rn(fmaExplicit(-fabsf(Ax), kSlack, bx)), bfx = __float2half2_rn(fmaExplicit(fabsf(Ax), kSlack, bx));
+            const __half2 bny = __float2half2_rn(fmaExplicit(-fabsf(Ay), kSlack, by)), bfy = __float2half2_rn(fmaExplicit(fabsf(Ay), kSlack, by));
+            const __half2 bnz = __float2half2_rn(fmaExplicit(-fabsf(Az), kSlack, bz)), bfz = __float2half2_rn(fmaExplicit(fabsf(Az), kSlack, bz));
+            const float tlo = tminP - tRef, thi = tmaxP - tRef; // <= 0 and >= 0
+            const __half2 tminH = __float2half2_rn(fmaExplicit(tlo, 1.0009765625f, -1e-7f)), tmaxH = __float2half2_rn(fmaExplicit(thi, 1.0009765625f, 1e-7f));
+            uint32_t hitPairs = 0;
+            const uint32_t m64 = one ^ 0x5BE46464u; // 0x64646464, derived from the kernel parameter so that PRMT keeps an immediate selector
+            {
+                const uint32_t nx = (octant & 1u) ? w.n3.z : w.n2.x, fx = (octant & 1u) ? w.n2.x : w.n3.z;
+                const uint32_t ny = (octant & 2u) ? w.n4.x : w.n2.z, fy = (octant & 2u) ? w.n2.z : w.n4.x;
+                const uint32_t nz = (octant & 4u) ? w.n4.z : w.n3.x, fz = (octant & 4u) ? w.n3.x : w.n4.z;
+                testChildPair<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminH, tmaxH, m64, hitPairs);
+                testChildPair<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminH, tmaxH, m64, hitPairs);
+            }
+            {
+                const uint32_t nx = (octant & 1u) ? w.n3.w : w.n2.y, fx = (octant & 1u) ? w.n2.y : w.n3.w;
+                const uint32_t ny = (octant & 2u) ? w.n4.y : w.n2.w, fy = (octant & 2u) ? w.n2.w : w.n4.y;
+                const uint32_t nz = (octant & 4u) ? w.n4.w : w.n3.y, fz = (octant & 4u) ? w.n3.y : w.n4.w;
+                testChildPair<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminH, tmaxH, m64, hitPairs);
+                testChildPair<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, tminH, tmaxH, m64, hitPairs);
+            }
+            return (hitPairs | (hitPairs >> 16)) & 0xFFu;
+        }
+    }
+#endif
     // n0.w = sx | sy << 16, n1.w = sz | imask << 16: upper halves of the floats 2^15 * scale
     const uint32_t e = floatAsUint(w.n0.w);
     const float sx = uintAsFloat(e << 16), sy = uintAsFloat(e & 0xFFFF0000u), sz = uintAsFloat(w.n1.w << 16);
