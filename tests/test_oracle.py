@@ -153,3 +153,125 @@ def test_nan_tangent_path_is_defined(sponza_flat):
     rays["tmin"], rays["tmax"] = 0.001, 1000
     h, _ = o.trace_rays(rays)
     assert h["geometry"][0] == 50
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Closed-form check of whole frames (textured quad, two-quad occluder, mirror quad).  The analytic scene is
+# three axis-aligned quads, so every ray/quad intersection, every shadow test and the reflection bounce have closed
+# forms; _Quads64 evaluates shader.rgen / shader.rchit / shader.rmiss straight from the GLSL in float64, sharing no
+# code with the oracle (no BVH, no watertight test, no texture sampler: the textures are constant images).
+# ---------------------------------------------------------------------------------------------------------------
+class _Quads64:
+    # (origin, edge u, edge v, normal, tangent, metallic blue channel) of floor, occluder, wall - scenes.analytic_scene
+    def __init__(self, metallic_floor):
+        f8 = np.float64
+        self.quads = [
+            (np.array([-8, 0, -8], f8), np.array([16, 0, 0], f8), np.array([0, 0, 16], f8), np.array([0, 1, 0], f8), np.array([1, 0, 0], f8), 1.0 if metallic_floor else 0.0),
+            (np.array([-1, 2, -1], f8), np.array([2, 0, 0], f8), np.array([0, 0, 2], f8), np.array([0, 1, 0], f8), np.array([1, 0, 0], f8), 0.0),
+            (np.array([-8, 0, -8], f8), np.array([16, 0, 0], f8), np.array([0, 8, 0], f8), np.array([0, 0, 1], f8), np.array([1, 0, 0], f8), 0.0),
+        ]
+        self.lights = camera.LIGHT_POSITIONS[:, :3].astype(f8)
+
+    def hit(self, o, d, tmin, tmax):
+        """(t, quad, margin): nearest quad with tmin < t < tmax; margin = distance (in quad-parameter units) of the hit from
+        the nearest quad edge, over all candidate quads - tiny margins mean float32 may legitimately decide otherwise."""
+        best, margin = (np.inf, -1), np.inf
+        for k, (p0, pu, pv, n, _, _) in enumerate(self.quads):
+            dn = d @ n
+            if dn == 0:
+                continue
+            t = ((p0 - o) @ n) / dn
+            if not (tmin < t < tmax):
+                continue
+            q = o + t * d - p0
+            a, b = (q @ pu) / (pu @ pu), (q @ pv) / (pv @ pv)
+            margin = min(margin, abs(a), abs(1 - a), abs(b), abs(1 - b))
+            if 0 <= a <= 1 and 0 <= b <= 1 and t < best[0]:
+                best = (t, k)
+        return best[0], best[1], margin
+
+    def shade(self, o, d, attenuation):
+        """shader.rchit:86-171 / shader.rmiss:17 -> (hitValue, done, next origin, next direction, next attenuation, mask, margin)."""
+        t, k, margin = self.hit(o, d, 0.001, 1000.0)
+        if k < 0:
+            return np.array([0.8, 0.8, 1.0]), 1, None, None, attenuation, 0, margin
+        p0, pu, pv, n, tan, metallic = self.quads[k]
+        pos = o + t * d
+        n_map = np.array([128, 128, 255]) / 255.0 * 2 - 1
+        n_map /= np.linalg.norm(n_map)
+        bit = np.cross(tan, n)  # getTBN, rchit:78-84
+        nn = tan * n_map[0] + bit * n_map[1] + n * n_map[2]
+        nn /= np.linalg.norm(nn)
+        total, mask = 0.0, 0
+        for i, L in enumerate(self.lights):
+            lv = L - pos
+            dist = np.linalg.norm(lv)
+            ld = lv / dist
+            ndl = float(nn @ ld)
+            mult = 1.0
+            if ndl > 0:
+                mask |= 16 << i
+                ts, ks, ms = self.hit(pos, ld, 0.001, dist)
+                margin = min(margin, ms)
+                if ks >= 0:
+                    mult = 0.3
+                    mask |= 1 << i
+            total += min(max(ndl, 0.0), 1.0) * (10.0 / dist ** 2) * mult
+        base = np.ones(3)
+        value = base * total * attenuation + base * 0.1
+        if metallic > 0.1:
+            attenuation = attenuation * 0.5 * metallic
+            value = value * (1 - attenuation)
+            return value, 0, pos, d - 2 * (nn @ d) * nn, attenuation, mask, margin
+        return value, 1, None, None, attenuation, mask, margin
+
+    def pixel(self, u, W, Hh, x, y):
+        ua = camera.uniforms_to_array(u).astype(np.float64)
+        vi, pi = ua[:16].reshape(4, 4).T, ua[16:32].reshape(4, 4).T
+        uv = (np.array([x + 0.5, y + 0.5]) / np.array([W, Hh])) * 2 - 1
+        tgt = pi @ np.array([uv[0], uv[1], 1, 1])
+        d = (vi @ np.append(tgt[:3] / np.linalg.norm(tgt[:3]), 0))[:3]
+        o = (vi @ np.array([0, 0, 0, 1.0]))[:3]
+        final, att, margin, mask0 = np.zeros(3), 1.0, np.inf, 0
+        for depth in range(2):  # rgen:49-73
+            value, done, o2, d2, att, mask, m = self.shade(o, d, att)
+            final += value
+            margin = min(margin, m)
+            if depth == 0:
+                mask0 = mask
+                first = self.hit(o, d, 0.001, 1000.0)[1]
+            if done == 1:
+                break
+            o, d = o2, d2
+        return final, mask0, first, margin
+
+
+@pytest.mark.parametrize("metallic,pose", [(False, ((0, 3, 9), (-0.2, 0, 0))), (False, ((2.5, 6, 3), (-1.1, 0.3, 0))),
+                                           (True, ((0, 3, 9), (-0.35, 0, 0))), (True, ((-3, 2, 6), (-0.3, -0.4, 0)))])
+def test_frames_match_closed_form_float64(metallic, pose):
+    """Two-quad occluder (floor + quad above it + wall: hard shadows of the four lights) and mirror quad (metallic floor:
+    one reflection bounce into wall, occluder underside or sky): primary quad, shadow mask and RGB of EVERY pixel of a
+    48 x 36 frame against the closed-form float64 evaluation.  Pixels whose rays pass within 1e-4 of a quad edge are
+    skipped (there float32 and float64 may disagree legitimately); at least 95 % of the frame must remain."""
+    flat, o = _analytic(metallic)
+    W, Hh = 48, 36
+    u = camera.make_uniforms(W, Hh, position=pose[0], rotation=pose[1])
+    r = o.render(u, W, Hh, mode=H.MODE_BRUTE)
+    ref = _Quads64(metallic)
+    checked = shadowed = reflected = 0
+    for y in range(Hh):
+        for x in range(W):
+            final, mask, first, margin = ref.pixel(u, W, Hh, x, y)
+            if margin < 1e-4:
+                continue
+            checked += 1
+            tri = int(r["tri"][y, x])
+            assert (tri == 0xFFFFFFFF and first < 0) or (tri != 0xFFFFFFFF and tri // 2 == first), (x, y, tri, first)
+            assert int(r["mask"][y, x]) == mask, (x, y, int(r["mask"][y, x]), mask)
+            assert np.allclose(r["rgb"][y, x], final, rtol=5e-5, atol=5e-6), (x, y, r["rgb"][y, x], final)
+            want = np.floor(np.clip(final, 0, 1) * 255 + 0.5)
+            assert (np.abs(r["bgra"][y, x][2::-1].astype(np.float64) - want) <= 1).all()
+            shadowed += (mask & 15) != 0
+            reflected += metallic and first == 0
+    assert checked > 0.95 * W * Hh and shadowed > 20
+    assert reflected > 100 or not metallic
