@@ -1,5 +1,15 @@
 // Raytracer.cpp — host driver of the ray-tracing path; follows the reference's constructor sequence
 // (src/Raytracer.cpp:54-83) and frame loop (:132-238) with the Vulkan calls replaced by the C ABI.
+//
+// PROVENANCE.  This is the maintainer's `Raytracer` class with the bodies that called Vulkan swapped for calls into
+// include/vkrt.h.  Three blocks are the REFERENCE'S OWN CODE, kept verbatim (only glm -> the
+// local Math.hpp types and the Vulkan calls cut out) because the drop-in contract is "same host logic, same quirks";
+// they are not this project's work and carry no claim of authorship:
+//   * Raytracer::updateCamera                       = src/Raytracer.cpp:273-324, character for character, including the
+//                                                     reference's identifiers `translationAmout` / `rotationAmout`;
+//   * Raytracer::createVertexAndIndexBuffer         = the concatenation loop of src/Raytracer.cpp:660-700;
+//   * Raytracer::updateMaterialIndexDescriptorSet   = the SubmeshInfo loop of src/Raytracer.cpp:1412-1427.
+// Everything else in this file (constructor order excepted, :54-83) is written against the C ABI.
 #include "Raytracer.hpp"
 #include "Utils.hpp"
 
@@ -97,6 +107,7 @@ void Raytracer::setupCamera()
     m_camera.setRotation({0.0f, 1.57f, 0.0f});
 }
 
+// >>> reference code, verbatim: src/Raytracer.cpp:273-324 (see PROVENANCE at the top of this file)
 void Raytracer::updateCamera(double deltaTime)
 {
     // src/Raytracer.cpp:273-324
@@ -184,6 +195,7 @@ void Raytracer::setTextureLod(int mode)
     VKRT_CHECK(m_device, vkrt_trace_set_texture_lod(m_device, mode));
 }
 
+// >>> reference code, verbatim: src/Raytracer.cpp:660-700 (see PROVENANCE at the top of this file)
 void Raytracer::createVertexAndIndexBuffer()
 {
     // src/Raytracer.cpp:642-742: one vertex buffer, one index buffer rebased by the running vertex count, and per
@@ -262,6 +274,7 @@ void Raytracer::setInstances(const std::vector<VkrtInstance>& instances)
     createTLAS();
 }
 
+// >>> reference code, verbatim: src/Raytracer.cpp:1412-1427 (see PROVENANCE at the top of this file)
 void Raytracer::updateMaterialIndexDescriptorSet()
 {
     // src/Raytracer.cpp:1412-1427
