@@ -460,6 +460,22 @@ VKRT_HD uint32_t quantExponent(float lo, float hi)
     return (uint32_t)e;
 }
 
+// Scale exponents of the three axes of one node.  A flat (or nearly flat) axis would get a scale many orders of
+// magnitude below the others; its exponent is raised to at most 8 below the largest one.  A perfectly flat axis still
+// quantises exactly (q = 0 for both planes), a nearly flat one grows by less than 1/65536 of the node's largest extent,
+// and the traversal's packed-half node test (traverse.cuh) sees plane spacings of one node within a factor 256 of
+// each other instead of arbitrarily far apart.
+VKRT_HD void quantExponents(F3 lo, F3 hi, uint32_t& ex, uint32_t& ey, uint32_t& ez)
+{
+    ex = quantExponent(lo.x, hi.x), ey = quantExponent(lo.y, hi.y), ez = quantExponent(lo.z, hi.z);
+    uint32_t em = ex > ey ? ex : ey;
+    em = em > ez ? em : ez;
+    const uint32_t floorE = em > 9u ? em - 8u : 1u;
+    ex = ex < floorE ? floorE : ex;
+    ey = ey < floorE ? floorE : ey;
+    ez = ez < floorE ? floorE : ez;
+}
+
 VKRT_HD uint32_t quantLo(float v, float origin, float scale)
 {
     float q = floorf((v - origin) / scale);
@@ -642,8 +658,8 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
 
     Node8 node;
     node.px = self.lo.x, node.py = self.lo.y, node.pz = self.lo.z;
-    const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
-                   ez = quantExponent(self.lo.z, self.hi.z);
+    uint32_t ex, ey, ez;
+    quantExponents(self.lo, self.hi, ex, ey, ez);
     node.sx = packScaleExponent(ex), node.sy = packScaleExponent(ey), node.sz = packScaleExponent(ez);
     const float sx = uintAsFloat(ex << 23), sy = uintAsFloat(ey << 23), sz = uintAsFloat(ez << 23);
     node.imask = 0;

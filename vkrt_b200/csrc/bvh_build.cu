@@ -1031,8 +1031,8 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
 
     if (valid && !overflow)
     {
-        const uint32_t ex = quantExponent(self.lo.x, self.hi.x), ey = quantExponent(self.lo.y, self.hi.y),
-                       ez = quantExponent(self.lo.z, self.hi.z);
+        uint32_t ex, ey, ez;
+        quantExponents(self.lo, self.hi, ex, ey, ez);
         const float sx = __uint_as_float(ex << 23), sy = __uint_as_float(ey << 23), sz = __uint_as_float(ez << 23);
         uint8_t q[6] = {0, 0, 0, 0, 0, 0};
         if (present)

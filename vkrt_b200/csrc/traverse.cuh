@@ -286,15 +286,17 @@ __device__ __forceinline__ void initSlotTables()
 //     child's test then lie within the node's own extent along the ray (|t'| <= ~256 |a|), where a half's 11 bits
 //     resolve 1/8 of a quantisation step, and  b' = (p - o) * idir - 1024 a - tRef  is formed in FP32;
 //   * interval: VHMNMX (three-input packed max/min) + HMNMX2 with the clamp, one HSET2 for both children.
-// Rounding: a -> half costs <= 1279 * 2^-11 |a| = 0.63 step, b' -> half <= 0.75 step, the HFMA2 result <= 0.13 step for
-// planes inside the node; near planes are therefore pulled in and far planes pushed out by kHalfSlackSteps = 2 steps
-// (the FP32 test uses 2^-7 step), the clamps by 2^-10 relative.  Overflow gives +-inf with the sign of the exact value or
-// NaN, which the min/max drop (that axis does not cull).  Only nodes whose steps a_k all lie in [2^-14, 32] take this
-// path (no subnormals, no overflow of 1279 a); any other node - rays almost parallel to a box face, degenerate
-// scales - takes the FP32 test below.  Box tests are not on the parity path: a conservative test cannot change
-// which triangle is hit, only how many nodes are visited (measured: DESIGN.md section 5.2).
+// Rounding, in quantisation steps |a| of the axis: truncating a to a half's 11 bits moves plane q by q (a - a_r) <= 0.25;
+// b' -> half <= 2^-11 (1279 + slack) = 0.63; the HFMA2 result <= 0.13 for planes inside the node: 1.01 in total, so near
+// planes are pulled in and far planes pushed out by kHalfSlackSteps = 1.125 steps (the FP32 test uses 2^-7 step) and the
+// clamps by 2^-10 relative.  Overflow gives +-inf with the sign of the exact value or NaN, which the min/max drop (that
+// axis does not cull).  Only nodes whose steps a_k all lie in [2^-14, 32] take this path (the builder keeps the three
+// scales of a node within 2^8 of each other, builder.cuh::quantExponents); any other node - rays almost parallel to a box
+// face, scenes in very small units - takes the FP32 test below.
+// Box tests are not on the parity path: a conservative test cannot change which triangle is hit, only how many nodes
+// are visited (measured: DESIGN.md section 5.2).
 // ------------------------------------------------------------------------------------------------------------
-constexpr float kHalfSlackSteps = 2.0f;
+constexpr float kHalfSlackSteps = 1.125f;
 
 __device__ __forceinline__ __half2 asHalf2(uint32_t u)
 {
@@ -328,7 +330,11 @@ VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t 
     {
         const uint32_t eb = floatAsUint(w.n0.w);
         // A = 2^15 a, a = scale * idir = the distance between neighbouring quantisation planes along the ray
-        const float Ax = uintAsFloat(eb << 16) * idir.x, Ay = uintAsFloat(eb & 0xFFFF0000u) * idir.y, Az = uintAsFloat(w.n1.w << 16) * idir.z;
+        // truncated to 11 significant bits: the half conversion below is then exact, and b' is formed with the SAME a the
+        // HFMA2 multiplies by, so the 1024 a offset of the dequantisation cancels exactly (what remains is q (a - a_r))
+        const float Ax = uintAsFloat(floatAsUint(uintAsFloat(eb << 16) * idir.x) & 0xFFFFE000u),
+                    Ay = uintAsFloat(floatAsUint(uintAsFloat(eb & 0xFFFF0000u) * idir.y) & 0xFFFFE000u),
+                    Az = uintAsFloat(floatAsUint(uintAsFloat(w.n1.w << 16) * idir.z) & 0xFFFFE000u);
         const float amax = fmaxf(fmaxf(fabsf(Ax), fabsf(Ay)), fabsf(Az)), amin = fminf(fminf(fabsf(Ax), fabsf(Ay)), fabsf(Az));
         if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32]; false for inf / NaN
         {
