@@ -36,8 +36,10 @@ def check_bvh8(nodes, tris, expected_triangles):
         max_depth = max(max_depth, depth)
         node = nodes[ni]
         imask = int(node["imask"])
-        leaf_bits = int(node["leafBits"])
-        assert leaf_bits < (1 << 24)
+        leaf_bits = int(node["leafBits"]) & 0xFFFFFF  # the top byte carries the node's scale normalisation
+        half = [int(node["sx"]), int(node["sy"]), int(node["sz"])]
+        exps = [(h >> 7) - 15 for h in half]
+        assert int(node["leafBits"]) >> 24 == 254 - max(exps) and max(exps) - min(exps) <= 4, (ni, exps)
         for s in range(8):
             unary = (leaf_bits >> (3 * s)) & 7
             if (imask >> s) & 1:
@@ -59,7 +61,7 @@ def check_bvh8(nodes, tris, expected_triangles):
         node = nodes[ni]
         lo, hi = decode_child_boxes(node)
         imask = int(node["imask"])
-        leaf_bits = int(node["leafBits"])
+        leaf_bits = int(node["leafBits"]) & 0xFFFFFF
         for s in range(8):
             unary = (leaf_bits >> (3 * s)) & 7
             if (imask >> s) & 1:
@@ -103,7 +105,7 @@ def check_tlas(nodes, leaf_instance, inst_lo, inst_hi):
         order.append(ni)
         depth_max = max(depth_max, depth)
         node = nodes[ni]
-        imask, leaves, bits = int(node["imask"]), int(node["reserved"]), int(node["leafBits"])
+        imask, leaves, bits = int(node["imask"]), int(node["reserved"]), int(node["leafBits"]) & 0xFFFFFF
         assert imask & leaves == 0
         assert bits == sum(1 << (3 * s) for s in range(8) if (leaves >> s) & 1), "one instance per leaf slot"
         for s in range(8):

@@ -191,6 +191,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
         Node8 root;
         memset(&root, 0, sizeof(root));
         root.sx = root.sy = root.sz = packScaleExponent(1);
+        root.leafBits = nodeScaleBits(1);
         b->nodes[0] = root;
         b->nodes.resize(1);
         for (int k = 0; k < 3; ++k)

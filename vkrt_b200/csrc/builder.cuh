@@ -461,20 +461,23 @@ VKRT_HD uint32_t quantExponent(float lo, float hi)
 }
 
 // Scale exponents of the three axes of one node.  A flat (or nearly flat) axis would get a scale many orders of
-// magnitude below the others; its exponent is raised to at most 8 below the largest one.  A perfectly flat axis still
-// quantises exactly (q = 0 for both planes), a nearly flat one grows by less than 1/65536 of the node's largest extent,
-// and the traversal's packed-half node test (traverse.cuh) sees plane spacings of one node within a factor 256 of
-// each other instead of arbitrarily far apart.
-VKRT_HD void quantExponents(F3 lo, F3 hi, uint32_t& ex, uint32_t& ey, uint32_t& ez)
+// magnitude below the others; its exponent is raised to at most 4 below the largest one.  A perfectly flat axis still
+// quantises exactly (q = 0 for both planes), a nearly flat one grows by less than 1/4096 of the node's largest extent,
+// and the traversal's packed-half node test (traverse.cuh) sees plane spacings of one node within a factor 16 of
+// each other.  Returns the largest exponent; Node8::leafBits carries 254 - that in its top byte (kNodeScaleShift).
+VKRT_HD uint32_t quantExponents(F3 lo, F3 hi, uint32_t& ex, uint32_t& ey, uint32_t& ez)
 {
     ex = quantExponent(lo.x, hi.x), ey = quantExponent(lo.y, hi.y), ez = quantExponent(lo.z, hi.z);
     uint32_t em = ex > ey ? ex : ey;
     em = em > ez ? em : ez;
-    const uint32_t floorE = em > 9u ? em - 8u : 1u;
+    const uint32_t floorE = em > 5u ? em - 4u : 1u;
     ex = ex < floorE ? floorE : ex;
     ey = ey < floorE ? floorE : ey;
     ez = ez < floorE ? floorE : ez;
+    return em;
 }
+// Top byte of Node8::leafBits: the exponent field of 2^(127 - largest scale exponent), i.e. of 1 / (largest scale).
+VKRT_HD uint32_t nodeScaleBits(uint32_t largestExponent) { return (254u - largestExponent) << 24; }
 
 VKRT_HD uint32_t quantLo(float v, float origin, float scale)
 {
@@ -659,13 +662,13 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     Node8 node;
     node.px = self.lo.x, node.py = self.lo.y, node.pz = self.lo.z;
     uint32_t ex, ey, ez;
-    quantExponents(self.lo, self.hi, ex, ey, ez);
+    const uint32_t em = quantExponents(self.lo, self.hi, ex, ey, ez);
     node.sx = packScaleExponent(ex), node.sy = packScaleExponent(ey), node.sz = packScaleExponent(ez);
     const float sx = uintAsFloat(ex << 23), sy = uintAsFloat(ey << 23), sz = uintAsFloat(ez << 23);
     node.imask = 0;
     node.childBase = childBase;
     node.primBase = primBase;
-    node.leafBits = 0;
+    node.leafBits = nodeScaleBits(em);
     node.reserved = 0;
     uint32_t innerSeen = 0, primOffset = 0;
     float leafArea = 0.0f;

@@ -1032,7 +1032,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
     if (valid && !overflow)
     {
         uint32_t ex, ey, ez;
-        quantExponents(self.lo, self.hi, ex, ey, ez);
+        const uint32_t em = quantExponents(self.lo, self.hi, ex, ey, ez);
         const float sx = __uint_as_float(ex << 23), sy = __uint_as_float(ey << 23), sz = __uint_as_float(ez << 23);
         uint8_t q[6] = {0, 0, 0, 0, 0, 0};
         if (present)
@@ -1066,7 +1066,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             uint32_t* hu = reinterpret_cast<uint32_t*>(stage);
             hf[0] = self.lo.x, hf[1] = self.lo.y, hf[2] = self.lo.z;
             hu[3] = (uint32_t)packScaleExponent(ex) | ((uint32_t)packScaleExponent(ey) << 16);
-            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits;
+            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits | nodeScaleBits(em);
             hu[7] = (uint32_t)packScaleExponent(ez) | (innerMask << 16);
             sahLocal[0] += halfArea(self.lo, self.hi);
         }
@@ -1194,6 +1194,7 @@ __global__ void k_empty_root(Node8* nodes)
     Node8 n;
     memset(&n, 0, sizeof(n));
     n.sx = n.sy = n.sz = packScaleExponent(1);
+    n.leafBits = nodeScaleBits(1);
     nodes[0] = n;
 }
 

@@ -29,6 +29,7 @@ struct alignas(16) Node8
     uint32_t primBase;    // index of the first primitive (packed triangle or instance) of this node
     uint32_t leafBits;    // bit 3*s+j set: slot s is a leaf holding a j-th triangle (j < 3); its packed triangle is
                           // primBase + popcount(leafBits below that bit): leaves are stored in slot order
+                          // bits 24..31: exponent field of 1 / (largest of the three scales) (builder.cuh::nodeScaleBits)
     uint16_t sz;          // as sx, sy
     uint8_t imask;        // bit s set: slot s holds an internal child
     uint8_t reserved;     // BLAS nodes: 0.  TLAS nodes: bit s set: slot s is a leaf holding one instance (k_tlas_finalize)

@@ -326,6 +326,17 @@ __device__ __forceinline__ void testChildPair(uint32_t nx, uint32_t ny, uint32_t
 
 VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
+    // Distances inside the test are measured in units of (largest scale of the node) x (1 / kappa of the ray): the caller
+    // passes idir, tminP, tmaxP already multiplied by the ray's power of two kappa (BoxRay below), the node contributes the
+    // power of two 1 / (largest scale) from the top byte of leafBits.  Scaling every distance by one positive power of two
+    // changes no comparison; it only moves the plane spacings a_k = scale_k * idir_k of every node of every scene to
+    // [1/16, 32) x (the ratio of the ray's direction components), where the packed-half arithmetic below is safe.
+    {
+        const float nodeK = uintAsFloat((w.n1.z >> 1) & 0x7F800000u);
+        idir = idir * nodeK;
+        tminP *= nodeK;
+        tmaxP *= nodeK;
+    }
 #if defined(VKRT_NODE_TEST_HALF2)
     {
         const uint32_t eb = floatAsUint(w.n0.w);
@@ -336,7 +347,7 @@ VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t 
                     Ay = uintAsFloat(floatAsUint(uintAsFloat(eb & 0xFFFF0000u) * idir.y) & 0xFFFFE000u),
                     Az = uintAsFloat(floatAsUint(uintAsFloat(w.n1.w << 16) * idir.z) & 0xFFFFE000u);
         const float amax = fmaxf(fmaxf(fabsf(Ax), fabsf(Ay)), fabsf(Az)), amin = fminf(fminf(fabsf(Ax), fabsf(Ay)), fabsf(Az));
-        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32]; false for inf / NaN
+        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32] (in practice >= 1/16, see above); false for inf / NaN
         {
             const float t0x = (w.n0.x - o.x) * idir.x, t0y = (w.n0.y - o.y) * idir.y, t0z = (w.n0.z - o.z) * idir.z;
             // entry distance of the node's own box [p, p + 255 scale]: the near plane of axis k is p_k when a_k > 0
@@ -458,23 +469,36 @@ struct BestHit
 // Per-ray traversal state inside one BLAS (object space).  Kept as plain scalars so it lives in registers.
 struct RayCtx
 {
-    F3 o, idir;
+    F3 o, idir;   // idir = (1 / d) * kappa
+    float kappa;  // power of two that brings the smallest |1 / d_k| of the ray to [1, 2) (see intersectNodeSlots)
     RayPre rp;
     uint32_t octant;
-    float tmin, tminP;
+    float tmin, tminP; // tminP = padDown(tmin) * kappa
     uint2 ngroup; // x = base index of the internal children, y = hit bits 24..31 | imask in bits 0..7
     uint2 tgroup; // x = first packed triangle of the node, y = hit bits 0..23
     int sp;
 };
 
+// Box-test constants of a ray: reciprocal direction, octant and clamp, all distances scaled by kappa.
+VKRT_HD void setBoxRay(RayCtx& c, F3 d, float tmin)
+{
+    const F3 id = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
+    const float m = fminf(fminf(fabsf(id.x), fabsf(id.y)), fabsf(id.z)); // finite for a valid ray (d != 0)
+    // 2^(127 - E) for m = 2^(E - 127) * [1, 2); exponent fields 0 (d overflowed 1/x) and 255 cannot arise from finite d != 0
+    // except through denormals, for which any power of two is as good as another: kappa = 1
+    const uint32_t e = floatAsUint(m) & 0x7F800000u;
+    c.kappa = (e == 0u || e == 0x7F800000u) ? 1.0f : uintAsFloat(0x7F000000u - e);
+    c.idir = id * c.kappa;
+    c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    c.tmin = tmin;
+    c.tminP = padDown(tmin) * c.kappa;
+}
+
 VKRT_HD void beginTraversal(RayCtx& c, F3 o, F3 d, float tmin)
 {
     c.o = o;
     c.rp = makeRayPre(d);
-    c.idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    c.tmin = tmin;
-    c.tminP = padDown(tmin);
+    setBoxRay(c, d, tmin);
     c.ngroup = make_uint2(0u, 0x80000000u);
     c.tgroup = make_uint2(0u, 0u);
     c.sp = 0;
@@ -526,7 +550,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
         {
             ++counters->nodes;
         }
-        const uint2 hits = intersectNode(w, c.o, c.idir, c.octant, c.tminP, padUp(best.t), one);
+        const uint2 hits = intersectNode(w, c.o, c.idir, c.octant, c.tminP, padUp(best.t) * c.kappa, one);
         const uint32_t imask = w.n1.w >> 16;
         c.ngroup = make_uint2(w.n1.x, (hits.x << 24) | imask);
         c.tgroup = make_uint2(w.n1.y, hits.y);
@@ -632,10 +656,7 @@ constexpr int kTopEnter = 2; // `instanceOut` names the next instance whose box 
 VKRT_HD void beginTop(RayCtx& c, F3 o, F3 d, float tmin, int sp)
 {
     c.o = o;
-    c.idir = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
-    c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    c.tmin = tmin;
-    c.tminP = padDown(tmin);
+    setBoxRay(c, d, tmin);
     c.ngroup = make_uint2(0u, 0u);
     c.tgroup = make_uint2(0u, 0u); // holds the pending instance group at the top level
     c.sp = sp;
@@ -696,7 +717,7 @@ VKRT_HD int topStep(RayCtx& c, uint2* stack, const TlasRefs& top, float tmax, Tr
             {
                 ++counters->nodes;
             }
-            const uint32_t hitSlots = intersectNodeSlots(w, c.o, c.idir, c.octant, c.tminP, padUp(tmax), one);
+            const uint32_t hitSlots = intersectNodeSlots(w, c.o, c.idir, c.octant, c.tminP, padUp(tmax) * c.kappa, one);
             const uint32_t imask = (w.n1.w >> 16) & 0xFFu, leafSlots = w.n1.w >> 24;
             c.ngroup = make_uint2(w.n1.x, (orderInnerSlots(hitSlots, imask, c.octant) << 24) | imask);
             c.tgroup = make_uint2(w.n1.y | kTopInstanceGroup, ((hitSlots & leafSlots) << 8) | leafSlots);
