@@ -330,7 +330,7 @@ VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t 
     // passes idir, tminP, tmaxP already multiplied by the ray's power of two kappa (BoxRay below), the node contributes the
     // power of two 1 / (largest scale) from the top byte of leafBits.  Scaling every distance by one positive power of two
     // changes no comparison; it only moves the plane spacings a_k = scale_k * idir_k of every node of every scene to
-    // [1/16, 32) x (the ratio of the ray's direction components), where the packed-half arithmetic below is safe.
+    // [2^-13, 2^-8) x (the ratio of the ray's direction components), inside the range of the packed-half arithmetic below.
     {
         const float nodeK = uintAsFloat((w.n1.z >> 1) & 0x7F800000u);
         idir = idir * nodeK;
@@ -347,7 +347,7 @@ VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t 
                     Ay = uintAsFloat(floatAsUint(uintAsFloat(eb & 0xFFFF0000u) * idir.y) & 0xFFFFE000u),
                     Az = uintAsFloat(floatAsUint(uintAsFloat(w.n1.w << 16) * idir.z) & 0xFFFFE000u);
         const float amax = fmaxf(fmaxf(fabsf(Ax), fabsf(Ay)), fabsf(Az)), amin = fminf(fminf(fabsf(Ax), fabsf(Ay)), fabsf(Az));
-        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32] (in practice >= 1/16, see above); false for inf / NaN
+        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32] (in practice >= 2^-13, see above); false for inf / NaN
         {
             const float t0x = (w.n0.x - o.x) * idir.x, t0y = (w.n0.y - o.y) * idir.y, t0z = (w.n0.z - o.z) * idir.z;
             // entry distance of the node's own box [p, p + 255 scale]: the near plane of axis k is p_k when a_k > 0
@@ -470,7 +470,7 @@ struct BestHit
 struct RayCtx
 {
     F3 o, idir;   // idir = (1 / d) * kappa
-    float kappa;  // power of two that brings the smallest |1 / d_k| of the ray to [1, 2) (see intersectNodeSlots)
+    float kappa;  // power of two that brings the smallest |1 / d_k| of the ray to [2^-9, 2^-8) (see setBoxRay, intersectNodeSlots)
     RayPre rp;
     uint32_t octant;
     float tmin, tminP; // tminP = padDown(tmin) * kappa
@@ -486,8 +486,10 @@ VKRT_HD void setBoxRay(RayCtx& c, F3 d, float tmin)
     const float m = fminf(fminf(fabsf(id.x), fabsf(id.y)), fabsf(id.z)); // finite for a valid ray (d != 0)
     // 2^(127 - E) for m = 2^(E - 127) * [1, 2); exponent fields 0 (d overflowed 1/x) and 255 cannot arise from finite d != 0
     // except through denormals, for which any power of two is as good as another: kappa = 1
+    // kappa = 2^(118 - E) for m = 2^(E - 127) * [1, 2): the smallest |1 / d_k| lands in [2^-9, 2^-8), which leaves the plane
+    // spacings 13 binades of head room for the other two axes and 4 below for a node's flatter axes (half: 2^-14 .. 2^15)
     const uint32_t e = floatAsUint(m) & 0x7F800000u;
-    c.kappa = (e == 0u || e == 0x7F800000u) ? 1.0f : uintAsFloat(0x7F000000u - e);
+    c.kappa = (e == 0u || e >= 0x7A000000u) ? 0.001953125f : uintAsFloat(0x7A800000u - e);
     c.idir = id * c.kappa;
     c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
     c.tmin = tmin;
