@@ -4,9 +4,9 @@ import numpy as np
 
 def decode_child_boxes(node):
     p = node["p"].astype(np.float32)
-    # sx, sy, sz hold the upper half of the float 2^15 * scale
+    # sx, sy, sz hold the upper half of the float `scale`
     half = np.array([node["sx"], node["sy"], node["sz"]], dtype=np.uint32)
-    scale = ((half << 16).view(np.float32) * np.float32(2.0 ** -15)).astype(np.float32)
+    scale = (half << 16).view(np.float32)
     lo = np.stack([p[0] + node["qlox"].astype(np.float32) * scale[0], p[1] + node["qloy"].astype(np.float32) * scale[1],
                    p[2] + node["qloz"].astype(np.float32) * scale[2]], axis=1)
     hi = np.stack([p[0] + node["qhix"].astype(np.float32) * scale[0], p[1] + node["qhiy"].astype(np.float32) * scale[1],
@@ -36,10 +36,11 @@ def check_bvh8(nodes, tris, expected_triangles):
         max_depth = max(max_depth, depth)
         node = nodes[ni]
         imask = int(node["imask"])
-        leaf_bits = int(node["leafBits"]) & 0xFFFFFF  # the top byte carries the node's scale normalisation
+        leaf_bits = int(node["leafBits"])
+        assert leaf_bits < (1 << 24)
         half = [int(node["sx"]), int(node["sy"]), int(node["sz"])]
-        exps = [(h >> 7) - 15 for h in half]
-        assert int(node["leafBits"]) >> 24 == 254 - max(exps) and max(exps) - min(exps) <= 4, (ni, exps)
+        exps = [h >> 7 for h in half]
+        assert max(exps) - min(exps) <= 4, (ni, exps)  # builder.cuh::quantExponents
         for s in range(8):
             unary = (leaf_bits >> (3 * s)) & 7
             if (imask >> s) & 1:

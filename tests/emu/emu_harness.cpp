@@ -32,6 +32,7 @@ struct EmuBlas
     std::vector<PackedTri> tris;
     float boundsMin[3], boundsMax[3];
     float sahCost = 0.f;
+    float boxScale = 1.f;
 };
 
 struct EmuScene
@@ -40,6 +41,7 @@ struct EmuScene
     std::vector<InstanceRecord> instances;
     std::vector<Node8> topNodes;        // as vkrt_tlas_build makes them (instanceCount > 1)
     std::vector<uint32_t> leafInstance;
+    float topBoxScale = 1.f;
     TlasRefs refs() const
     {
         TlasRefs t;
@@ -48,6 +50,7 @@ struct EmuScene
         t.instances = instances.data();
         t.instanceCount = (uint32_t)instances.size();
         t.cullMask = 0xFFu;
+        t.boxScale = topBoxScale;
         return t;
     }
     std::vector<VkrtSubmeshInfo> rows;
@@ -57,6 +60,20 @@ struct EmuScene
     std::vector<TextureMips> mips;
     bool lod = false;
 };
+
+// k_min_scale_exponent + boxScaleFromExponent
+static float emuBoxScale(const std::vector<Node8>& nodes)
+{
+    uint32_t e = 255u;
+    for (const Node8& n : nodes)
+    {
+        if (n.imask != 0 || (n.leafBits & 0xFFFFFFu) != 0u)
+        {
+            e = std::min(e, std::min(std::min((uint32_t)n.sx >> 7, (uint32_t)n.sy >> 7), (uint32_t)n.sz >> 7));
+        }
+    }
+    return boxScaleFromExponent(e == 255u ? 127u : e);
+}
 
 // The box-only part of the builder (bvh_build.cu::buildHierarchy), sequentially: Morton codes -> stable sort -> LBVH ->
 // optional cost-optimal collapse decisions -> collapse into wide nodes.  Returns the node count, 0 on failure.
@@ -191,7 +208,6 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
         Node8 root;
         memset(&root, 0, sizeof(root));
         root.sx = root.sy = root.sz = packScaleExponent(1);
-        root.leafBits = nodeScaleBits(1);
         b->nodes[0] = root;
         b->nodes.resize(1);
         for (int k = 0; k < 3; ++k)
@@ -236,6 +252,7 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
         return nullptr;
     }
     b->nodes.resize(last);
+    b->boxScale = emuBoxScale(b->nodes);
     for (uint32_t i = 0; i < n; ++i)
     {
         b->tris[i] = packTriangle(geo, b->vertices.data(), stride, b->indices.data(), primSource[i]);
@@ -293,6 +310,7 @@ EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t insta
         r.vertices = blas->vertices.data(), r.indices = blas->indices.data();
         r.vertexStride = blas->stride;
         r.mask = 0xFFu;
+        r.boxScale = blas->boxScale;
         for (int k = 0; k < 3; ++k)
         {
             r.blasLo[k] = blas->boundsMin[k], r.blasHi[k] = blas->boundsMax[k];
@@ -319,6 +337,7 @@ EmuScene* emu_scene_create(EmuBlas* blas, const float* instances, uint32_t insta
         float sah[2] = {0.f, 0.f};
         const uint32_t last = emuBuildHierarchy(box, n, 1u, 0.5f, clo, chi, s->topNodes, n + 8u, s->leafInstance, sah);
         s->topNodes.resize(last);
+        s->topBoxScale = emuBoxScale(s->topNodes);
         for (Node8& node : s->topNodes)
         {
             uint32_t m = 0;

@@ -561,6 +561,7 @@ int vkrt_tlas_build(VkrtContext* c, const VkrtInstance* instances, uint32_t inst
         r.mask = instances[i].mask;
         r.customIndex = instances[i].instanceCustomIndex;
         r.flags = instances[i].flags;
+        r.boxScale = blas->boxScale;
         for (int k = 0; k < 3; ++k)
         {
             r.blasLo[k] = blas->boundsMin[k];

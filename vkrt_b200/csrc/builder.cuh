@@ -464,7 +464,7 @@ VKRT_HD uint32_t quantExponent(float lo, float hi)
 // magnitude below the others; its exponent is raised to at most 4 below the largest one.  A perfectly flat axis still
 // quantises exactly (q = 0 for both planes), a nearly flat one grows by less than 1/4096 of the node's largest extent,
 // and the traversal's packed-half node test (traverse.cuh) sees plane spacings of one node within a factor 16 of
-// each other.  Returns the largest exponent; Node8::leafBits carries 254 - that in its top byte (kNodeScaleShift).
+// each other.  Returns the largest exponent.
 VKRT_HD uint32_t quantExponents(F3 lo, F3 hi, uint32_t& ex, uint32_t& ey, uint32_t& ez)
 {
     ex = quantExponent(lo.x, hi.x), ey = quantExponent(lo.y, hi.y), ez = quantExponent(lo.z, hi.z);
@@ -476,8 +476,13 @@ VKRT_HD uint32_t quantExponents(F3 lo, F3 hi, uint32_t& ex, uint32_t& ey, uint32
     ez = ez < floorE ? floorE : ez;
     return em;
 }
-// Top byte of Node8::leafBits: the exponent field of 2^(127 - largest scale exponent), i.e. of 1 / (largest scale).
-VKRT_HD uint32_t nodeScaleBits(uint32_t largestExponent) { return (254u - largestExponent) << 24; }
+// The power of two by which a hierarchy's box-test distances are scaled (traverse.cuh::setBoxRay), from the smallest scale
+// exponent of any of its nodes.
+VKRT_HD float boxScaleFromExponent(uint32_t smallestExponent)
+{
+    const uint32_t e = smallestExponent < 1u ? 1u : (smallestExponent > 240u ? 240u : smallestExponent);
+    return uintAsFloat((241u - e) << 23);
+}
 
 VKRT_HD uint32_t quantLo(float v, float origin, float scale)
 {
@@ -668,7 +673,8 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
     node.imask = 0;
     node.childBase = childBase;
     node.primBase = primBase;
-    node.leafBits = nodeScaleBits(em);
+    node.leafBits = 0;
+    (void)em;
     node.reserved = 0;
     uint32_t innerSeen = 0, primOffset = 0;
     float leafArea = 0.0f;

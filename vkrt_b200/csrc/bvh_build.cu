@@ -45,7 +45,7 @@ __global__ void k_init_build(uint32_t* sceneBounds, uint32_t* counters, float* s
     }
     if (i < 8)
     {
-        counters[i] = 0u;
+        counters[i] = i == 3 ? 255u : 0u; // [3]: running minimum of the nodes' scale exponents
     }
     if (i < 2)
     {
@@ -1066,7 +1066,8 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
             uint32_t* hu = reinterpret_cast<uint32_t*>(stage);
             hf[0] = self.lo.x, hf[1] = self.lo.y, hf[2] = self.lo.z;
             hu[3] = (uint32_t)packScaleExponent(ex) | ((uint32_t)packScaleExponent(ey) << 16);
-            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits | nodeScaleBits(em);
+            hu[4] = childBase, hu[5] = primBase, hu[6] = leafBits;
+            (void)em;
             hu[7] = (uint32_t)packScaleExponent(ez) | (innerMask << 16);
             sahLocal[0] += halfArea(self.lo, self.hi);
         }
@@ -1194,7 +1195,6 @@ __global__ void k_empty_root(Node8* nodes)
     Node8 n;
     memset(&n, 0, sizeof(n));
     n.sx = n.sy = n.sz = packScaleExponent(1);
-    n.leafBits = nodeScaleBits(1);
     nodes[0] = n;
 }
 
@@ -1353,9 +1353,32 @@ __global__ void __launch_bounds__(kThreads) k_tlas_finalize(Node8* nodes, uint32
     }
 }
 
+// smallest scale exponent over all nodes of a hierarchy (-> boxScaleFromExponent); counters[3], preset to 255 by k_init_build
+__global__ void __launch_bounds__(kThreads) k_min_scale_exponent(const Node8* __restrict__ nodes, uint32_t count, uint32_t* out)
+{
+    uint32_t e = 255u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const Node8& n = nodes[i];
+        if (n.imask != 0 || (n.leafBits & 0xFFFFFFu) != 0u)
+        {
+            e = min(e, min(min((uint32_t)n.sx >> 7, (uint32_t)n.sy >> 7), (uint32_t)n.sz >> 7));
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        e = min(e, __shfl_xor_sync(0xFFFFFFFFu, e, o));
+    }
+    if ((threadIdx.x & 31) == 0 && e < 255u)
+    {
+        atomicMin(out, e);
+    }
+}
+
 struct HierarchyResult
 {
     uint32_t nodeCount = 0;
+    uint32_t minExponent = 127; // smallest scale exponent of any node
     uint32_t levels = 0; // wide levels = longest root-to-leaf node path
     float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
     float sahCost = 0.0f;
@@ -1540,6 +1563,10 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8*
         }
     }
     out.nodeCount = last;
+    k_min_scale_exponent<<<gridFor(last, kThreads, sm), kThreads, 0, s>>>(nodes, last, counters + 3);
+    ctx->launches += 1;
+    uint32_t minExp = 255u;
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(&minExp, counters + 3, 4, cudaMemcpyDeviceToHost, s));
 
     uint32_t hb[12];
     float hs[2];
@@ -1555,6 +1582,7 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8*
                 dz = out.boundsMax[2] - out.boundsMin[2];
     const float rootArea = dx * dy + dy * dz + dz * dx;
     out.sahCost = rootArea > 0.0f ? (hs[0] + hs[1]) / rootArea : 0.0f;
+    out.minExponent = minExp == 255u ? 127u : minExp;
     return VKRT_SUCCESS;
 }
 } // namespace
@@ -1593,6 +1621,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         ctx->launches += 1;
         blas->nodeCount = 1;
         blas->levels = 1;
+        blas->boxScale = 1.0f;
         for (int k = 0; k < 3; ++k)
         {
             blas->boundsMin[k] = 0.0f;
@@ -1624,6 +1653,7 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         }
         blas->nodeCount = h.nodeCount;
         blas->levels = h.levels;
+        blas->boxScale = boxScaleFromExponent(h.minExponent);
         k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
                                                                      blas->tris.as<PackedTri>());
         ctx->launches += 1;
@@ -1693,6 +1723,7 @@ int buildTlasOnDevice(Context* ctx, Tlas* tlas)
     cudaEventDestroy(ev1);
     tlas->nodeCount = h.nodeCount;
     tlas->levels = h.levels;
+    tlas->boxScale = boxScaleFromExponent(h.minExponent);
     tlas->buildMs = ms;
     tlas->sahCost = h.sahCost;
     for (int k = 0; k < 3; ++k)

@@ -24,12 +24,11 @@ namespace vkrt
 struct alignas(16) Node8
 {
     float px, py, pz;     // quantisation origin (node box minimum)
-    uint16_t sx, sy;      // per-axis scale 2^(e-127) as the upper half of the float 2^(e-127+15): (e + 15) << 7
+    uint16_t sx, sy;      // per-axis scale 2^(e-127) as the upper half of that float: e << 7 (a shift or a mask makes the float)
     uint32_t childBase;   // index of the first internal child node
     uint32_t primBase;    // index of the first primitive (packed triangle or instance) of this node
     uint32_t leafBits;    // bit 3*s+j set: slot s is a leaf holding a j-th triangle (j < 3); its packed triangle is
                           // primBase + popcount(leafBits below that bit): leaves are stored in slot order
-                          // bits 24..31: exponent field of 1 / (largest of the three scales) (builder.cuh::nodeScaleBits)
     uint16_t sz;          // as sx, sy
     uint8_t imask;        // bit s set: slot s holds an internal child
     uint8_t reserved;     // BLAS nodes: 0.  TLAS nodes: bit s set: slot s is a leaf holding one instance (k_tlas_finalize)
@@ -37,7 +36,7 @@ struct alignas(16) Node8
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };
 // Packs a scale exponent byte the way Node8 stores it; the builder keeps e <= 239.
-inline __host__ __device__ uint16_t packScaleExponent(uint32_t e) { return (uint16_t)((e + 15u) << 7); }
+inline __host__ __device__ uint16_t packScaleExponent(uint32_t e) { return (uint16_t)(e << 7); }
 static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 
 // Packed triangle, 48 bytes: raw vertex positions (the watertight test needs all three) + Vulkan ids.
@@ -67,7 +66,8 @@ struct alignas(16) InstanceRecord
     uint32_t customIndex;    // instanceCustomIndex (24 bits); the reference's shaders never read gl_InstanceCustomIndexEXT
     uint32_t flags;          // VkGeometryInstanceFlagsKHR; no ray of this pipeline culls, so TRIANGLE_FACING_CULL_DISABLE changes nothing
     float blasLo[3], blasHi[3]; // object-space bounds of the BLAS at TLAS build time
-    uint32_t pad[2];
+    float boxScale;             // 2^(114 - smallest scale exponent of the BLAS's nodes), see traverse.cuh::setBoxRay
+    uint32_t pad[1];
 };
 static_assert(sizeof(InstanceRecord) == 176, "InstanceRecord layout");
 

@@ -154,6 +154,7 @@ struct Blas : VkrtBlas
     float buildMs = 0.0f;
     uint32_t flags = 0;
     uint32_t levels = 0;        // wide levels of the hierarchy (bounds the traversal stack)
+    float boxScale = 1.0f;      // power of two that normalises box-test distances in this hierarchy (traverse.cuh::setBoxRay)
     uint64_t generation = 0;    // bumped by every (re)build: a TLAS remembers the generation it saw
     bool shadingLayout = false; // vertices are the 64-byte Model::Vertex (stride % 16 == 0, >= 64): vkrt_trace / vkrt_rasterize can shade it
 };
@@ -165,6 +166,7 @@ struct Tlas : VkrtTlas
     DeviceBuffer leafInstance; // u32[instanceCount]: instance index per top-level leaf
     uint32_t instanceCount = 0;
     uint32_t nodeCount = 0, levels = 0;
+    float boxScale = 1.0f;         // as Blas::boxScale, for the top-level hierarchy
     uint32_t maxGeometryCount = 0; // largest geometry count among the referenced BLASes (material table check)
     bool shadingLayout = true;     // every referenced BLAS can be shaded
     float buildMs = 0.0f, sahCost = 0.0f;

@@ -326,43 +326,34 @@ __device__ __forceinline__ void testChildPair(uint32_t nx, uint32_t ny, uint32_t
 
 VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t octant, float tminP, float tmaxP, uint32_t one)
 {
-    // Distances inside the test are measured in units of (largest scale of the node) x (1 / kappa of the ray): the caller
-    // passes idir, tminP, tmaxP already multiplied by the ray's power of two kappa (BoxRay below), the node contributes the
-    // power of two 1 / (largest scale) from the top byte of leafBits.  Scaling every distance by one positive power of two
-    // changes no comparison; it only moves the plane spacings a_k = scale_k * idir_k of every node of every scene to
-    // [2^-13, 2^-8) x (the ratio of the ray's direction components), inside the range of the packed-half arithmetic below.
-    {
-        const float nodeK = uintAsFloat((w.n1.z >> 1) & 0x7F800000u);
-        idir = idir * nodeK;
-        tminP *= nodeK;
-        tmaxP *= nodeK;
-    }
+    // The caller passes idir, tminP, tmaxP multiplied by the ray's power of two kappa (setBoxRay): scaling every distance by
+    // one positive power of two changes no comparison, it only moves the plane spacings a_k = scale_k * idir_k of the
+    // scene's nodes into the range of the packed-half arithmetic below.
 #if defined(VKRT_NODE_TEST_HALF2)
     {
         const uint32_t eb = floatAsUint(w.n0.w);
-        // A = 2^15 a, a = scale * idir = the distance between neighbouring quantisation planes along the ray
-        // truncated to 11 significant bits: the half conversion below is then exact, and b' is formed with the SAME a the
-        // HFMA2 multiplies by, so the 1024 a offset of the dequantisation cancels exactly (what remains is q (a - a_r))
+        // a = scale * idir = the distance between neighbouring quantisation planes along the ray, truncated to 11 significant
+        // bits: the half conversion below is then exact, and b' is formed with the SAME a the HFMA2 multiplies by, so the
+        // 1024 a offset of the dequantisation cancels exactly (what remains is q (a - a_r))
         const float Ax = uintAsFloat(floatAsUint(uintAsFloat(eb << 16) * idir.x) & 0xFFFFE000u),
                     Ay = uintAsFloat(floatAsUint(uintAsFloat(eb & 0xFFFF0000u) * idir.y) & 0xFFFFE000u),
                     Az = uintAsFloat(floatAsUint(uintAsFloat(w.n1.w << 16) * idir.z) & 0xFFFFE000u);
         const float amax = fmaxf(fmaxf(fabsf(Ax), fabsf(Ay)), fabsf(Az)), amin = fminf(fminf(fabsf(Ax), fabsf(Ay)), fabsf(Az));
-        if (amax <= 1048576.0f && amin >= 2.0f) // a in [2^-14, 32] (in practice >= 2^-13, see above); false for inf / NaN
+        if (amax <= 32.0f && amin >= 6.103515625e-05f) // a in [2^-14, 32] (in practice >= 2^-13, see above); false for inf / NaN
         {
             const float t0x = (w.n0.x - o.x) * idir.x, t0y = (w.n0.y - o.y) * idir.y, t0z = (w.n0.z - o.z) * idir.z;
-            // entry distance of the node's own box [p, p + 255 scale]: the near plane of axis k is p_k when a_k > 0
-            const float kFar = 255.0f / 32768.0f;
-            const float tRef = fminf(fmaxf(fmaxf(fmaxf(fmaExplicit(fminf(Ax, 0.0f), kFar, t0x), fmaExplicit(fminf(Ay, 0.0f), kFar, t0y)),
-                                                 fmaExplicit(fminf(Az, 0.0f), kFar, t0z)), tminP), tmaxP);
-            const float kOff = -1024.0f / 32768.0f, kSlack = kHalfSlackSteps / 32768.0f;
-            const float bx = fmaExplicit(Ax, kOff, t0x - tRef), by = fmaExplicit(Ay, kOff, t0y - tRef), bz = fmaExplicit(Az, kOff, t0z - tRef);
-            const __half2 ax = __float2half2_rn(Ax * (1.0f / 32768.0f)), ay = __float2half2_rn(Ay * (1.0f / 32768.0f)),
-                          az = __float2half2_rn(Az * (1.0f / 32768.0f));
-            const __half2 bnx = __float2half2_rn(fmaExplicit(-fabsf(Ax), kSlack, bx)), bfx = __float2half2_rn(fmaExplicit(fabsf(Ax), kSlack, bx));
-            const __half2 bny = __float2half2_rn(fmaExplicit(-fabsf(Ay), kSlack, by)), bfy = __float2half2_rn(fmaExplicit(fabsf(Ay), kSlack, by));
-            const __half2 bnz = __float2half2_rn(fmaExplicit(-fabsf(Az), kSlack, bz)), bfz = __float2half2_rn(fmaExplicit(fabsf(Az), kSlack, bz));
-            const float tlo = tminP - tRef, thi = tmaxP - tRef; // <= 0 and >= 0
-            const __half2 tminH = __float2half2_rn(fmaExplicit(tlo, 1.0009765625f, -1e-7f)), tmaxH = __float2half2_rn(fmaExplicit(thi, 1.0009765625f, 1e-7f));
+            // entry distance of the node's own box [p, p + 255 scale] (the near plane of axis k is p_k when a_k > 0), not
+            // before the start of the ray: at tRef the ray is inside the box on every axis, so |t0_k - tRef| <= 255 |a_k|
+            const float tRef = fmaxf(fmaxf(fmaxf(fmaExplicit(fminf(Ax, 0.0f), 255.0f, t0x), fmaExplicit(fminf(Ay, 0.0f), 255.0f, t0y)),
+                                           fmaExplicit(fminf(Az, 0.0f), 255.0f, t0z)), tminP);
+            const float bx = fmaExplicit(Ax, -1024.0f, t0x - tRef), by = fmaExplicit(Ay, -1024.0f, t0y - tRef), bz = fmaExplicit(Az, -1024.0f, t0z - tRef);
+            const __half2 ax = __float2half2_rn(Ax), ay = __float2half2_rn(Ay), az = __float2half2_rn(Az);
+            const __half2 bnx = __float2half2_rn(fmaExplicit(-fabsf(Ax), kHalfSlackSteps, bx)), bfx = __float2half2_rn(fmaExplicit(fabsf(Ax), kHalfSlackSteps, bx));
+            const __half2 bny = __float2half2_rn(fmaExplicit(-fabsf(Ay), kHalfSlackSteps, by)), bfy = __float2half2_rn(fmaExplicit(fabsf(Ay), kHalfSlackSteps, by));
+            const __half2 bnz = __float2half2_rn(fmaExplicit(-fabsf(Az), kHalfSlackSteps, bz)), bfz = __float2half2_rn(fmaExplicit(fabsf(Az), kHalfSlackSteps, bz));
+            const float tlo = tminP - tRef, thi = tmaxP - tRef; // <= 0 and (for a node in reach) >= 0
+            const __half2 tminH = __float2half2_rn(fmaExplicit(-fabsf(tlo), 0.0009765625f, tlo) - 1e-7f),
+                          tmaxH = __float2half2_rn(fmaExplicit(fabsf(thi), 0.0009765625f, thi) + 1e-7f);
             uint32_t hitPairs = 0;
             const uint32_t m64 = one ^ 0x5BE46464u; // 0x64646464, derived from the kernel parameter so that PRMT keeps an immediate selector
             {
@@ -383,10 +374,11 @@ VKRT_HD uint32_t intersectNodeSlots(const NodeWords& w, F3 o, F3 idir, uint32_t 
         }
     }
 #endif
-    // n0.w = sx | sy << 16, n1.w = sz | imask << 16: upper halves of the floats 2^15 * scale
+    // n0.w = sx | sy << 16, n1.w = sz | imask << 16: upper halves of the scale floats; the byte-in-mantissa dequantisation
+    // (1 + q 2^-15, byteToUnitFloat) wants 2^15 * scale
     const uint32_t e = floatAsUint(w.n0.w);
     const float sx = uintAsFloat(e << 16), sy = uintAsFloat(e & 0xFFFF0000u), sz = uintAsFloat(w.n1.w << 16);
-    const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
+    const float ax = (sx * 32768.0f) * idir.x, ay = (sy * 32768.0f) * idir.y, az = (sz * 32768.0f) * idir.z;
     const float bx = fmaExplicit(w.n0.x - o.x, idir.x, -ax), by = fmaExplicit(w.n0.y - o.y, idir.y, -ay),
                 bz = fmaExplicit(w.n0.z - o.z, idir.z, -az);
     const float slack = 2.3841858e-07f; // 2^-22 of ax = 2^-7 quantisation step
@@ -470,7 +462,7 @@ struct BestHit
 struct RayCtx
 {
     F3 o, idir;   // idir = (1 / d) * kappa
-    float kappa;  // power of two that brings the smallest |1 / d_k| of the ray to [2^-9, 2^-8) (see setBoxRay, intersectNodeSlots)
+    float kappa;  // power of two that normalises the distances of the box tests (setBoxRay)
     RayPre rp;
     uint32_t octant;
     float tmin, tminP; // tminP = padDown(tmin) * kappa
@@ -480,27 +472,31 @@ struct RayCtx
 };
 
 // Box-test constants of a ray: reciprocal direction, octant and clamp, all distances scaled by kappa.
-VKRT_HD void setBoxRay(RayCtx& c, F3 d, float tmin)
+// `boxScale` is the hierarchy's power of two 2^(114 - e_lo), e_lo = the smallest scale exponent of any of its nodes
+// (Blas::boxScale / Tlas::boxScale): with the smallest |1 / d_k| of the ray normalised to [1, 2), the smallest plane
+// spacing a = scale * idir of the hierarchy lands at 2^-13, the bottom of the half range, and the spacings of larger
+// nodes and of the ray's other axes have 18 binades above it.
+VKRT_HD void setBoxRay(RayCtx& c, F3 d, float tmin, float boxScale)
 {
     const F3 id = f3(safeRcp(d.x), safeRcp(d.y), safeRcp(d.z));
     const float m = fminf(fminf(fabsf(id.x), fabsf(id.y)), fabsf(id.z)); // finite for a valid ray (d != 0)
     // 2^(127 - E) for m = 2^(E - 127) * [1, 2); exponent fields 0 (d overflowed 1/x) and 255 cannot arise from finite d != 0
     // except through denormals, for which any power of two is as good as another: kappa = 1
-    // kappa = 2^(118 - E) for m = 2^(E - 127) * [1, 2): the smallest |1 / d_k| lands in [2^-9, 2^-8), which leaves the plane
-    // spacings 13 binades of head room for the other two axes and 4 below for a node's flatter axes (half: 2^-14 .. 2^15)
+    // 2^(127 - E) for m = 2^(E - 127) * [1, 2); exponent fields 0 and 255 cannot arise from a finite d != 0 except through
+    // denormals, for which the normalisation does not matter (such nodes take the FP32 test)
     const uint32_t e = floatAsUint(m) & 0x7F800000u;
-    c.kappa = (e == 0u || e >= 0x7A000000u) ? 0.001953125f : uintAsFloat(0x7A800000u - e);
+    c.kappa = ((e == 0u || e == 0x7F800000u) ? 1.0f : uintAsFloat(0x7F000000u - e)) * boxScale;
     c.idir = id * c.kappa;
     c.octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
     c.tmin = tmin;
     c.tminP = padDown(tmin) * c.kappa;
 }
 
-VKRT_HD void beginTraversal(RayCtx& c, F3 o, F3 d, float tmin)
+VKRT_HD void beginTraversal(RayCtx& c, F3 o, F3 d, float tmin, float boxScale)
 {
     c.o = o;
     c.rp = makeRayPre(d);
-    setBoxRay(c, d, tmin);
+    setBoxRay(c, d, tmin, boxScale);
     c.ngroup = make_uint2(0u, 0x80000000u);
     c.tgroup = make_uint2(0u, 0u);
     c.sp = 0;
@@ -610,10 +606,10 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
 // Traverses one BLAS with an object-space ray.  ANY: return true at the first accepted triangle.
 template<bool ANY>
 VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d, float tmin, uint32_t instance,
-                          BestHit& best, TraceCounters* counters, uint32_t one)
+                          BestHit& best, TraceCounters* counters, uint32_t one, float boxScale)
 {
     RayCtx c;
-    beginTraversal(c, o, d, tmin);
+    beginTraversal(c, o, d, tmin, boxScale);
     uint2 stack[kStackSize];
     bool found = false;
     for (;;)
@@ -648,6 +644,7 @@ struct TlasRefs
     const InstanceRecord* instances;
     uint32_t instanceCount;
     uint32_t cullMask;
+    float boxScale; // of the top-level hierarchy (see setBoxRay)
 };
 
 constexpr uint32_t kTopInstanceGroup = 0x80000000u;
@@ -655,10 +652,10 @@ constexpr int kTopDone = 1;  // no instance left to enter
 constexpr int kTopEnter = 2; // `instanceOut` names the next instance whose box the ray enters
 
 // World-space box-traversal state (no watertight constants: the top level tests boxes only).
-VKRT_HD void beginTop(RayCtx& c, F3 o, F3 d, float tmin, int sp)
+VKRT_HD void beginTop(RayCtx& c, F3 o, F3 d, float tmin, int sp, float boxScale)
 {
     c.o = o;
-    setBoxRay(c, d, tmin);
+    setBoxRay(c, d, tmin, boxScale);
     c.ngroup = make_uint2(0u, 0u);
     c.tgroup = make_uint2(0u, 0u); // holds the pending instance group at the top level
     c.sp = sp;
@@ -761,7 +758,7 @@ VKRT_HD bool enterInstanceTop(RayCtx& c, uint2* stack, const InstanceRecord& ins
         pushGroup(c, stack, c.tgroup, counters, overflowFlag);
     }
     const int sp = c.sp;
-    beginTraversal(c, oo, dd, tmin);
+    beginTraversal(c, oo, dd, tmin, inst.boxScale);
     c.sp = sp;
     spFloor = sp;
     return true;
@@ -790,11 +787,11 @@ VKRT_HD bool traceScene(const TlasRefs& top, F3 o, F3 d, float tmin, BestHit& be
         {
             return false;
         }
-        return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one);
+        return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one, inst.boxScale);
     }
     RayCtx c;
     uint2 stack[kStackSize];
-    beginTop(c, o, d, tmin, 0);
+    beginTop(c, o, d, tmin, 0, top.boxScale);
     c.ngroup = make_uint2(0u, 0x80000000u); // the top-level root
     bool found = false;
     for (;;)
@@ -823,7 +820,7 @@ VKRT_HD bool traceScene(const TlasRefs& top, F3 o, F3 d, float tmin, BestHit& be
                 break;
             }
         }
-        beginTop(c, o, d, tmin, spFloor);
+        beginTop(c, o, d, tmin, spFloor, top.boxScale);
     }
 }
 

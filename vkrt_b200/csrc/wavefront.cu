@@ -32,6 +32,7 @@ struct SceneDev
     uint32_t instanceCount;
     uint32_t cullMask;            // traceRayEXT's cullMask: 0xFF in shader.rgen:52 and shader.rchit:133
     uint32_t* errorFlags;         // [0] traversal stack overflow
+    float topBoxScale;            // Tlas::boxScale
     const VkrtSubmeshInfo* rows;
     const TextureRecord* textures;
     uint32_t one; // 0x3F800000, see byteToUnitFloat (traverse.cuh)
@@ -267,7 +268,7 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
     bind.nodes = scene.instances[0].nodes, bind.tris = scene.instances[0].tris, bind.instance = 0u, bind.spFloor = 0;
     TlasRefs top;
     top.nodes = scene.topNodes, top.leafInstance = scene.leafInstance, top.instances = scene.instances;
-    top.instanceCount = scene.instanceCount, top.cullMask = scene.cullMask;
+    top.instanceCount = scene.instanceCount, top.cullMask = scene.cullMask, top.boxScale = scene.topBoxScale;
     TraceCounters* const counters = STATS ? &tc : nullptr;
     uint32_t handle = 0;
     bool active = false;
@@ -311,7 +312,7 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                 {
                     if (MULTI)
                     {
-                        beginTop(c, o, d, tmin, 0);
+                        beginTop(c, o, d, tmin, 0, scene.topBoxScale);
                         c.ngroup = make_uint2(0u, 0x80000000u); // the top-level root
                         bind.spFloor = -1;
                     }
@@ -322,7 +323,7 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                         ok = validRay(oo, dd) && (inst.mask & scene.cullMask) != 0u;
                         if (ok)
                         {
-                            beginTraversal(c, oo, dd, tmin);
+                            beginTraversal(c, oo, dd, tmin, inst.boxScale);
                         }
                     }
                 }
@@ -386,7 +387,7 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
                         F3 o, d;
                         float tmin, tmax;
                         src.load(handle, o, d, tmin, tmax);
-                        beginTop(c, o, d, tmin, bind.spFloor);
+                        beginTop(c, o, d, tmin, bind.spFloor, scene.topBoxScale);
                         bind.spFloor = -1;
                         continue;
                     }
@@ -908,6 +909,7 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
     scene.instanceCount = tlas->instanceCount;
     scene.cullMask = 0xFFu;
     scene.errorFlags = ctx->errorFlags.as<uint32_t>();
+    scene.topBoxScale = tlas->boxScale;
     scene.rows = ctx->materials.as<VkrtSubmeshInfo>();
     scene.textures = ctx->textureRecords.as<TextureRecord>();
     scene.one = 0x3F800000u;
@@ -1110,6 +1112,7 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     scene.instanceCount = tlas->instanceCount;
     scene.cullMask = 0xFFu;
     scene.errorFlags = ctx->errorFlags.as<uint32_t>();
+    scene.topBoxScale = tlas->boxScale;
     scene.rows = nullptr;
     scene.textures = nullptr;
     scene.one = 0x3F800000u;
