@@ -29,12 +29,19 @@ struct TraceCounters
 // Watertight per-ray constants.  The shear of Woop et al. 2013 is  A' = (A[kx] - Sx*A[kz], A[ky] - Sy*A[kz], Sz*A[kz]).
 // Instead of selecting vertex components by the runtime axis indices (two SEL per component on the saturated alu
 // pipe), each output is evaluated as a dot product with a per-ray vector whose entries are 1 at kx (ky), -Sx (-Sy) at
-// kz and 0 elsewhere: the products by 1 and 0 are exact, adding +-0 is exact, and -(S*a) == (-S)*a, so every result
-// is bit-identical to the selected form (finite vertices) while the work moves to the fma pipe.
+// kz and 0 elsewhere (shearDot below): the products by 1 and 0 are exact and adding +-0 is exact, so only the S*a term
+// rounds, and the work moves to the fma pipe.
 struct RayPre
 {
     F3 mx, my, mz;
 };
+
+// The shear of the watertight test as ONE fixed sequence of fused operations:  fma(a.x, m.x, fma(a.y, m.y, a.z * m.z)).
+// It is part of the numerical contract (the oracle evaluates exactly this expression): a function of the vertex and the
+// ray only, so the two triangles that share an edge still see identical sheared vertices, which is what the
+// watertightness argument of Woop et al. needs; the edge functions U, V, W stay unfused (a fused a*b - c*d is not
+// antisymmetric).  3 instructions instead of 5 per dot product, 20 fewer per triangle test.
+VKRT_HD float shearDot(F3 a, F3 m) { return fmaExplicit(a.x, m.x, fmaExplicit(a.y, m.y, a.z * m.z)); }
 
 VKRT_HD void setComp3(F3& v, int k, float value)
 {
@@ -92,9 +99,9 @@ VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, floa
                                float& b1, float& b2)
 {
     const F3 A = v0 - o, B = v1 - o, C = v2 - o;
-    const float Ax = dot3(A, rp.mx), Ay = dot3(A, rp.my);
-    const float Bx = dot3(B, rp.mx), By = dot3(B, rp.my);
-    const float Cx = dot3(C, rp.mx), Cy = dot3(C, rp.my);
+    const float Ax = shearDot(A, rp.mx), Ay = shearDot(A, rp.my);
+    const float Bx = shearDot(B, rp.mx), By = shearDot(B, rp.my);
+    const float Cx = shearDot(C, rp.mx), Cy = shearDot(C, rp.my);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -113,8 +120,8 @@ VKRT_HD bool intersectTriangle(F3 v0, F3 v1, F3 v2, F3 o, const RayPre& rp, floa
     {
         return false;
     }
-    const float Az = dot3(A, rp.mz), Bz = dot3(B, rp.mz), Cz = dot3(C, rp.mz);
-    const float T = (U * Az + V * Bz) + W * Cz;
+    const float Az = shearDot(A, rp.mz), Bz = shearDot(B, rp.mz), Cz = shearDot(C, rp.mz);
+    const float T = fmaExplicit(W, Cz, fmaExplicit(V, Bz, U * Az));
     const float rcp = 1.0f / det;
     const float t = T * rcp;
     if (!(t > tmin))
