@@ -27,7 +27,8 @@ def gpu_frame(rt):
 def assert_contract(c):
     assert c["tri_agree"] >= 0.999 and c["mask_agree"] >= 0.999, c
     assert c["bgra_max_diff"] <= 1 and c["rgb_max_diff"] <= 1.0 / 255.0 + 1e-6, c
-    assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"], c
+    if os.environ.get("VKRT_PARITY_EXACT", "1") != "0":  # 0: a build with other roundings (-fmad=true A/B), judged at the bars only
+        assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"], c
 
 
 def strided(h, w, sy, sx):

@@ -26,7 +26,7 @@ def assert_contract(c, exact=True):
     assert c["tri_agree"] >= 0.999, c
     assert c["mask_agree"] >= 0.999, c
     assert c["bgra_max_diff"] <= 1 and c["rgb_max_diff"] <= 1.0 / 255.0 + 1e-6, c
-    if exact:
+    if exact and os.environ.get("VKRT_PARITY_EXACT", "1") != "0":  # 0: a build with other roundings (-fmad=true A/B), judged at the bars only
         assert c["tri_agree"] == 1.0 and c["mask_agree"] == 1.0 and c["rgb_bit_equal"], c
 
 
