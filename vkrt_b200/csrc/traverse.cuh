@@ -21,6 +21,37 @@ constexpr int kStackSize = 48; // group entries.  A BLAS pushes at most one per 
                                // when it enters an instance: the builders refuse hierarchies that could exceed this
 constexpr int kMaxBlasLevels = kStackSize;
 
+// Traversal stack of one ray.  Default: kStackSize entries of per-thread local memory (they live in L1).  The A/B build
+// -DVKRT_SMEM_STACK keeps the kSmemStack entries nearest the top of the tree walk in shared memory (interleaved by thread, no
+// bank conflicts) and only deeper ones in local memory: the "short stack" variant, measured in DESIGN.md section 5.2.
+#if defined(__CUDA_ARCH__) && defined(VKRT_SMEM_STACK)
+constexpr int kSmemStack = 8;
+struct RayStack
+{
+    uint2* shared; // this thread's column: entry i at shared[i * blockDim.x]
+    uint2 deep[kStackSize - kSmemStack];
+    __device__ __forceinline__ void set(int i, uint2 v)
+    {
+        if (i < kSmemStack)
+        {
+            shared[i * blockDim.x] = v;
+        }
+        else
+        {
+            deep[i - kSmemStack] = v;
+        }
+    }
+    __device__ __forceinline__ uint2 get(int i) const { return i < kSmemStack ? shared[i * blockDim.x] : deep[i - kSmemStack]; }
+};
+#else
+struct RayStack
+{
+    uint2 e[kStackSize];
+    VKRT_HD void set(int i, uint2 v) { e[i] = v; }
+    VKRT_HD uint2 get(int i) const { return e[i]; }
+};
+#endif
+
 struct TraceCounters
 {
     uint32_t nodes = 0, tris = 0, overflow = 0;
@@ -519,7 +550,7 @@ constexpr int kStepHit = 4;   // flag: at least one triangle was accepted during
 // `overflowFlag` (may be null) is set when a group had to be dropped because the stack is full: the builders refuse
 // hierarchies deeper than the stack (kStackSize), so this is a defensive signal that vkrt surfaces as an error.
 template<bool ANY>
-VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const PackedTri* tris, uint32_t instance, BestHit& best,
+VKRT_HD int traversalStep(RayCtx& c, RayStack& stack, const Node8* nodes, const PackedTri* tris, uint32_t instance, BestHit& best,
                           TraceCounters* counters, uint32_t one, int spFloor = 0, uint32_t* overflowFlag = nullptr)
 {
     int result = 0;
@@ -534,7 +565,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
         {
             if (c.sp < kStackSize)
             {
-                stack[c.sp++] = c.ngroup;
+                stack.set(c.sp++, c.ngroup);
             }
             else
             {
@@ -605,7 +636,7 @@ VKRT_HD int traversalStep(RayCtx& c, uint2* stack, const Node8* nodes, const Pac
         {
             return result | kStepDone;
         }
-        c.ngroup = stack[--c.sp];
+        c.ngroup = stack.get(--c.sp);
     }
     return result;
 }
@@ -617,7 +648,7 @@ VKRT_HD bool traverseBlas(const Node8* nodes, const PackedTri* tris, F3 o, F3 d,
 {
     RayCtx c;
     beginTraversal(c, o, d, tmin, boxScale);
-    uint2 stack[kStackSize];
+    RayStack stack;
     bool found = false;
     for (;;)
     {
@@ -668,11 +699,11 @@ VKRT_HD void beginTop(RayCtx& c, F3 o, F3 d, float tmin, int sp, float boxScale)
     c.sp = sp;
 }
 
-VKRT_HD void pushGroup(RayCtx& c, uint2* stack, uint2 g, TraceCounters* counters, uint32_t* overflowFlag)
+VKRT_HD void pushGroup(RayCtx& c, RayStack& stack, uint2 g, TraceCounters* counters, uint32_t* overflowFlag)
 {
     if (c.sp < kStackSize)
     {
-        stack[c.sp++] = g;
+        stack.set(c.sp++, g);
     }
     else
     {
@@ -689,7 +720,7 @@ VKRT_HD void pushGroup(RayCtx& c, uint2* stack, uint2 g, TraceCounters* counters
 
 // Advances the top-level traversal until the ray is about to enter an instance (kTopEnter) or nothing is left
 // (kTopDone).  `tmax` is the current hit distance.  c.ngroup / c.tgroup hold the pending node and instance groups.
-VKRT_HD int topStep(RayCtx& c, uint2* stack, const TlasRefs& top, float tmax, TraceCounters* counters, uint32_t one,
+VKRT_HD int topStep(RayCtx& c, RayStack& stack, const TlasRefs& top, float tmax, TraceCounters* counters, uint32_t one,
                     uint32_t* overflowFlag, uint32_t& instanceOut)
 {
     for (;;)
@@ -733,7 +764,7 @@ VKRT_HD int topStep(RayCtx& c, uint2* stack, const TlasRefs& top, float tmax, Tr
         {
             return kTopDone;
         }
-        const uint2 g = stack[--c.sp];
+        const uint2 g = stack.get(--c.sp);
         if (g.x & kTopInstanceGroup)
         {
             c.tgroup = g;
@@ -748,7 +779,7 @@ VKRT_HD int topStep(RayCtx& c, uint2* stack, const TlasRefs& top, float tmax, Tr
 // Suspends the top level (pending groups go onto the stack) and moves the ray into `inst`.  Returns false when
 // the object-space ray is not traceable (non-finite or zero direction after the transform): the top level then
 // simply continues.  On success c is the object-space state and `spFloor` the stack height to return at.
-VKRT_HD bool enterInstanceTop(RayCtx& c, uint2* stack, const InstanceRecord& inst, F3 o, F3 d, float tmin, TraceCounters* counters,
+VKRT_HD bool enterInstanceTop(RayCtx& c, RayStack& stack, const InstanceRecord& inst, F3 o, F3 d, float tmin, TraceCounters* counters,
                               uint32_t* overflowFlag, int& spFloor)
 {
     const F3 oo = affinePoint(inst.w2o, o), dd = affineDir(inst.w2o, d);
@@ -797,7 +828,7 @@ VKRT_HD bool traceScene(const TlasRefs& top, F3 o, F3 d, float tmin, BestHit& be
         return traverseBlas<ANY>(inst.nodes, inst.tris, oo, dd, tmin, 0u, best, counters, one, inst.boxScale);
     }
     RayCtx c;
-    uint2 stack[kStackSize];
+    RayStack stack;
     beginTop(c, o, d, tmin, 0, top.boxScale);
     c.ngroup = make_uint2(0u, 0x80000000u); // the top-level root
     bool found = false;

@@ -261,7 +261,11 @@ __device__ __forceinline__ void tracePersistent(const SceneDev& scene, const Sou
     uint32_t poolNext = 0, poolEnd = 0; // warp-uniform
     bool exhausted = false;             // warp-uniform: the launch-wide cursor has passed `total`
 
-    uint2 stack[kStackSize];
+    RayStack stack;
+#if defined(VKRT_SMEM_STACK)
+    __shared__ uint2 sStack[kSmemStack * kTraceThreads];
+    stack.shared = sStack + threadIdx.x;
+#endif
     RayCtx c;
     BestHit best;
     BlasBinding<MULTI> bind;
