@@ -1,0 +1,9 @@
+#!/bin/bash
+O=gpurun_out; mkdir -p $O
+TAG=${1:-j}
+bash tools/gpu_r02_ab.sh ${TAG} main smemstack 2>&1 | grep -v "^ncu" 
+timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv --log-file $O/${TAG}_build50M_lbvh.csv \
+    python tools/build_bench.py --flags 1 --sizes 50000000 --repeat 1 --no-sponza > $O/${TAG}_build50M_lbvh.log 2>&1; echo "ncu build exit $?"
+python tools/ncu_launch_bytes.py $O/${TAG}_build50M_lbvh.csv 2 | head -30
+timeout 300 python tools/build_bench.py --flags 1 --sizes 2000000,10000000,50000000 2>&1 | tail -4
+timeout 300 python tools/build_bench.py --flags 0 --sizes 262144,10000000 2>&1 | tail -3

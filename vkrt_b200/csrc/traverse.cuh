@@ -24,24 +24,32 @@ constexpr int kMaxBlasLevels = kStackSize;
 // Traversal stack of one ray.  Default: kStackSize entries of per-thread local memory (they live in L1).  The A/B build
 // -DVKRT_SMEM_STACK keeps the kSmemStack entries nearest the top of the tree walk in shared memory (interleaved by thread, no
 // bank conflicts) and only deeper ones in local memory: the "short stack" variant, measured in DESIGN.md section 5.2.
-#if defined(__CUDA_ARCH__) && defined(VKRT_SMEM_STACK)
+#if defined(__CUDACC__) && defined(VKRT_SMEM_STACK)
 constexpr int kSmemStack = 8;
 struct RayStack
 {
     uint2* shared; // this thread's column: entry i at shared[i * blockDim.x]
     uint2 deep[kStackSize - kSmemStack];
-    __device__ __forceinline__ void set(int i, uint2 v)
+    VKRT_HD int stride() const
+    {
+#if defined(__CUDA_ARCH__)
+        return (int)blockDim.x;
+#else
+        return 1;
+#endif
+    }
+    VKRT_HD void set(int i, uint2 v)
     {
         if (i < kSmemStack)
         {
-            shared[i * blockDim.x] = v;
+            shared[i * stride()] = v;
         }
         else
         {
             deep[i - kSmemStack] = v;
         }
     }
-    __device__ __forceinline__ uint2 get(int i) const { return i < kSmemStack ? shared[i * blockDim.x] : deep[i - kSmemStack]; }
+    VKRT_HD uint2 get(int i) const { return i < kSmemStack ? shared[i * stride()] : deep[i - kSmemStack]; }
 };
 #else
 struct RayStack
