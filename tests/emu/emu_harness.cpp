@@ -105,6 +105,7 @@ static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n,
     std::vector<int> flags(std::max(1u, n), -1);
     int root = 0;
     Bvh2 bvh;
+    bvh.nodes32 = nullptr, bvh.sortedBox = nullptr;
     bvh.nodes = binNodes.data(), bvh.flags = flags.data();
     bvh.keys = sk.data(), bvh.vals = sv.data(), bvh.triBox = triBox.data();
     bvh.count = n, bvh.root = &root;

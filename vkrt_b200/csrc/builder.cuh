@@ -90,8 +90,24 @@ struct alignas(64) BinNode
 };
 static_assert(sizeof(BinNode) == 64, "BinNode must be 64 bytes");
 
+// Compact binary node of the fast-build (LBVH + greedy collapse) path: box and children in ONE 32-byte sector, so a
+// fetch costs one DRAM sector instead of two.  The leaf count of a subtree does not fit; what the collapse needs of it
+// (1, 2, 3 or "more than 3") travels in bits 29..30 of the REFERENCE to the node (kRefClass*): the LBVH climb knows the
+// count when it finishes a node and writes the tagged reference into the parent.  Hence at most 2^29 - 1 primitives.
+struct alignas(32) BinNode32
+{
+    float lo[3];
+    float hi[3];
+    int2 children;
+};
+static_assert(sizeof(BinNode32) == 32, "BinNode32 must be 32 bytes");
+constexpr int kRefIndexMask = 0x1FFFFFFF;
+constexpr uint32_t kCompactMaxPrims = 0x1FFFFFFFu;
+
 struct Bvh2
 {
+    BinNode32* nodes32;   // non-null: compact mode (nodes is unused); references carry the count class
+    float4* sortedBox;    // compact mode: the leaf boxes in sorted order, [2i] = min, [2i+1] = max (written by the climb)
     BinNode* nodes;
     int* flags;        // init -1; Apetrei range hand-off
     const uint32_t* keys;  // sorted Morton codes
@@ -105,6 +121,15 @@ struct Bvh2
     float dpPrimCost;   // cost of one triangle test relative to one node test
     uint32_t maxLeaf;   // primitives per leaf slot: kMaxLeafTris for a BLAS, 1 for a TLAS (one instance per slot)
 };
+
+// References to binary nodes: >= 0 internal (compact mode: index in bits 0..28, count class in bits 29..30: 0 = more than
+// 3 leaves, 2 = two, 3 = three), < 0 = ~sortedLeaf.
+VKRT_HD int refIndex(const Bvh2& b, int ref) { return b.nodes32 ? (ref & kRefIndexMask) : ref; }
+VKRT_HD int tagRef(int node, uint32_t count) { return node | (count <= 3u ? (int)(count << 29) : 0); }
+VKRT_HD int2 binChildren(const Bvh2& b, int ref)
+{
+    return b.nodes32 ? b.nodes32[ref & kRefIndexMask].children : b.nodes[ref].children;
+}
 
 VKRT_HD uint64_t lbvhDelta(const Bvh2& b, uint32_t j) // distance between sorted leaves j and j+1
 {
@@ -209,6 +234,84 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
     }
 }
 
+// The same climb over compact nodes.  Leaf boxes are copied into sorted order on the way (one coalesced 32-byte write per
+// leaf), so that the collapse reads a leaf's box with one fetch instead of two dependent ones (vals, then triBox).
+VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
+{
+    const uint32_t n = b.count;
+    uint32_t left = leaf, right = leaf;
+    int current = ~(int)leaf;
+    const uint32_t tri = b.vals[leaf];
+    float4 lo = b.triBox[2 * tri], hi = b.triBox[2 * tri + 1];
+    b.sortedBox[2 * (size_t)leaf] = lo;
+    b.sortedBox[2 * (size_t)leaf + 1] = hi;
+    for (;;)
+    {
+        uint32_t parent;
+        int prev;
+        bool isLeftChild;
+        if (left == 0 || (right != n - 1 && lbvhDelta(b, right) < lbvhDelta(b, left - 1)))
+        {
+            parent = right;
+            isLeftChild = true;
+            b.nodes32[parent].children.x = current;
+            VKRT_FENCE();
+            prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)left);
+            if (prev != -1)
+            {
+                right = (uint32_t)prev;
+            }
+        }
+        else
+        {
+            parent = left - 1;
+            isLeftChild = false;
+            b.nodes32[parent].children.y = current;
+            VKRT_FENCE();
+            prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)right);
+            if (prev != -1)
+            {
+                left = (uint32_t)prev;
+            }
+        }
+        if (prev == -1)
+        {
+            return; // first to arrive: the sibling's thread finishes this node
+        }
+        VKRT_FENCE();
+        // the sibling's box: its leaf box straight from the triangle boxes (its own copy in sortedBox may not be visible
+        // yet), or the finished node's box (written before its fence)
+        const volatile BinNode32* pn = b.nodes32 + parent;
+        const int sibling = isLeftChild ? pn->children.y : pn->children.x;
+        float slo[3], shi[3];
+        if (sibling < 0)
+        {
+            const uint32_t st = b.vals[~sibling];
+            const float4 l4 = b.triBox[2 * st], h4 = b.triBox[2 * st + 1];
+            slo[0] = l4.x, slo[1] = l4.y, slo[2] = l4.z, shi[0] = h4.x, shi[1] = h4.y, shi[2] = h4.z;
+        }
+        else
+        {
+            const float4* q = reinterpret_cast<const float4*>(b.nodes32 + (sibling & kRefIndexMask));
+            const float4 q0 = VKRT_LOAD_CG_F4(q), q1 = VKRT_LOAD_CG_F4(q + 1); // lo.xyz hi.x | hi.yz children
+            slo[0] = q0.x, slo[1] = q0.y, slo[2] = q0.z, shi[0] = q0.w, shi[1] = q1.x, shi[2] = q1.y;
+        }
+        lo.x = fminf(lo.x, slo[0]), lo.y = fminf(lo.y, slo[1]), lo.z = fminf(lo.z, slo[2]);
+        hi.x = fmaxf(hi.x, shi[0]), hi.y = fmaxf(hi.y, shi[1]), hi.z = fmaxf(hi.z, shi[2]);
+        // both children are in place: the whole 32-byte record goes out as two 16-byte stores
+        float4* out = reinterpret_cast<float4*>(b.nodes32 + parent);
+        const int cx = isLeftChild ? current : sibling, cy = isLeftChild ? sibling : current;
+        out[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
+        out[1] = make_float4(hi.y, hi.z, uintAsFloat((uint32_t)cx), uintAsFloat((uint32_t)cy));
+        current = tagRef((int)parent, right - left + 1u);
+        if (left == 0 && right == n - 1)
+        {
+            *b.root = current;
+            return;
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Collapse to 8-wide nodes
 // ------------------------------------------------------------------------------------------------
@@ -241,6 +344,25 @@ VKRT_HD CollapseChild collapseFetch(const Bvh2& b, int ref)
 {
     CollapseChild c;
     c.ref = ref;
+    if (b.nodes32)
+    {
+        if (ref < 0)
+        {
+            const uint32_t leaf = (uint32_t)~ref;
+            const float4 lo = b.sortedBox[2 * (size_t)leaf], hi = b.sortedBox[2 * (size_t)leaf + 1];
+            c.lo = f3(lo.x, lo.y, lo.z), c.hi = f3(hi.x, hi.y, hi.z);
+            c.count = 1;
+        }
+        else
+        {
+            const float4* q = reinterpret_cast<const float4*>(b.nodes32 + (ref & kRefIndexMask));
+            const float4 q0 = q[0], q1 = q[1];
+            c.lo = f3(q0.x, q0.y, q0.z), c.hi = f3(q0.w, q1.x, q1.y);
+            const uint32_t cls = ((uint32_t)ref >> 29) & 3u;
+            c.count = cls ? cls : 4u; // 4 stands for "more than 3": only ever compared with maxLeaf <= 3
+        }
+        return c;
+    }
     if (ref < 0)
     {
         const uint32_t leaf = (uint32_t)~ref;
@@ -268,7 +390,7 @@ VKRT_HD uint32_t collectLeaves(const Bvh2& b, int ref, uint32_t* out)
     }
     // at most 3 leaves: one child is a leaf, the other a leaf or a pair of leaves
     uint32_t n = 0;
-    const int2 ch = b.nodes[ref].children;
+    const int2 ch = binChildren(b, ref);
     const int side[2] = {ch.x, ch.y};
     for (int k = 0; k < 2; ++k)
     {
@@ -278,7 +400,7 @@ VKRT_HD uint32_t collectLeaves(const Bvh2& b, int ref, uint32_t* out)
         }
         else
         {
-            const int2 g = b.nodes[side[k]].children;
+            const int2 g = binChildren(b, side[k]);
             out[n++] = (uint32_t)~g.x; // grandchildren of a <= 3-leaf subtree are leaves
             out[n++] = (uint32_t)~g.y;
         }
@@ -537,8 +659,9 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
         }
         else
         {
-            c[0] = collapseFetch(b, b.nodes[rootRef].children.x);
-            c[1] = collapseFetch(b, b.nodes[rootRef].children.y);
+            const int2 rc = binChildren(b, rootRef);
+            c[0] = collapseFetch(b, rc.x);
+            c[1] = collapseFetch(b, rc.y);
             n = 2;
         }
         while (n < 8 && !b.dpChoice)
@@ -561,7 +684,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             {
                 break;
             }
-            const int2 ch = b.nodes[c[pick].ref].children;
+            const int2 ch = binChildren(b, c[pick].ref);
             c[pick] = collapseFetch(b, ch.x);
             c[n++] = collapseFetch(b, ch.y);
         }
@@ -587,7 +710,7 @@ VKRT_HD void collapseNode(const CollapseArgs& a, uint32_t wideIndex, float* sahL
             {
                 break;
             }
-            const int2 ch = b.nodes[c[pick].ref].children;
+            const int2 ch = binChildren(b, c[pick].ref);
             c[pick] = collapseFetch(b, ch.x);
             c[n++] = collapseFetch(b, ch.y);
         }

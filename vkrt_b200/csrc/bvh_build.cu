@@ -338,7 +338,14 @@ __global__ void __launch_bounds__(kThreads) k_lbvh(Bvh2 bvh)
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < bvh.count)
     {
-        lbvhClimb(bvh, i);
+        if (bvh.nodes32)
+        {
+            lbvhClimbCompact(bvh, i);
+        }
+        else
+        {
+            lbvhClimb(bvh, i);
+        }
     }
 }
 
@@ -815,7 +822,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         else if (!b.dpChoice)
         {
             n = 2;
-            const int2 ch = b.nodes[rootRef].children;
+            const int2 ch = binChildren(b, rootRef);
             if (l8 < 2)
             {
                 c = collapseFetch(b, l8 == 0 ? ch.x : ch.y);
@@ -880,7 +887,7 @@ __device__ __forceinline__ void collapseNodeCoop(const CollapseArgs& a, uint32_t
         const int pickRef = __shfl_sync(full, c.ref, base + bestIdx);
         if (opening && n < 8)
         {
-            const int2 ch = b.nodes[pickRef].children;
+            const int2 ch = binChildren(b, pickRef);
             if (l8 == bestIdx)
             {
                 c = collapseFetch(b, ch.x);
@@ -1433,9 +1440,25 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8*
         return r;
     }
 
+    // cost-optimal collapse (default; the fast-build path keeps the greedy one)
+    float dpPrimCost = fast ? 0.0f : kDpPrimCost;
+    if (const char* e = getenv("VKRT_BUILD_DP_PRIM_COST"))
+    {
+        dpPrimCost = (float)atof(e);
+    }
+    const bool useDp = n > maxLeaf && n > 1 && dpPrimCost > 0.0f;
+    // compact 32-byte binary nodes: LBVH + greedy collapse only (the cost-optimal collapse keeps its costs in the padding of
+    // the 64-byte record, PLOC its leaf counts in lo.w)
+    const bool compact = fast && !useDp && n > 1 && n <= kCompactMaxPrims && !getenv("VKRT_BUILD_NO_COMPACT");
+    if (compact)
+    {
+        VKRT_CUDA_TRY(ctx, sc.sortedBox.reserve(n1 * 2 * sizeof(float4)));
+    }
     Bvh2 bvh;
     bvh.dpChoice = nullptr, bvh.dpParent = nullptr, bvh.dpPrimCost = 0.0f;
     bvh.maxLeaf = maxLeaf;
+    bvh.nodes32 = compact ? sc.binNodes.as<BinNode32>() : nullptr;
+    bvh.sortedBox = compact ? sc.sortedBox.as<float4>() : nullptr;
     bvh.nodes = sc.binNodes.as<BinNode>();
     bvh.flags = sc.flags.as<int>();
     bvh.keys = sc.keysA.as<uint32_t>();
@@ -1493,13 +1516,8 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8*
         }
     }
 
-    // cost-optimal collapse (default; the fast-build path keeps the greedy one): parents, then a bottom-up climb
-    float dpPrimCost = fast ? 0.0f : kDpPrimCost;
-    if (const char* e = getenv("VKRT_BUILD_DP_PRIM_COST"))
-    {
-        dpPrimCost = (float)atof(e);
-    }
-    if (n > maxLeaf && n > 1 && dpPrimCost > 0.0f)
+    // cost-optimal collapse: parents, then a bottom-up climb
+    if (useDp)
     {
         VKRT_CUDA_TRY(ctx, sc.dp.reserve((size_t)n * 12));
         bvh.dpChoice = sc.dp.as<uint32_t>();

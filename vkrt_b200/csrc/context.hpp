@@ -24,13 +24,13 @@ namespace vkrt
 
 struct BuildScratch
 {
-    DeviceBuffer triBox, packedBuild, keysA, keysB, valsA, valsB, tileHist, binNodes, flags, taskRef, primSource, small;
+    DeviceBuffer triBox, packedBuild, keysA, keysB, valsA, valsB, tileHist, binNodes, flags, taskRef, primSource, small, sortedBox;
     DeviceBuffer plocLoA, plocHiA, plocLoB, plocHiB, plocStatus; // PLOC cluster boxes (ping-pong) and look-back words
     DeviceBuffer dp;                                              // cost-optimal collapse: decisions (n), parents (2n)
     void release()
     {
         DeviceBuffer* all[] = {&triBox, &packedBuild, &keysA, &keysB, &valsA, &valsB, &tileHist, &binNodes, &flags,
-                               &taskRef, &primSource, &small, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus, &dp};
+                               &taskRef, &primSource, &small, &sortedBox, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus, &dp};
         for (DeviceBuffer* b : all)
         {
             b->release();
