@@ -116,14 +116,15 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def build_scene(workload):
+def build_scene(workload, with_images=True):
+    """with_images=False: a rank that receives the texels from rank 0 (vkrt_textures_broadcast) skips the image decode."""
     from vkrt_b200 import scenes
 
     if workload == "config5":  # CPU arm only (the GPU arm generates the soup on the device): bounded triangle count
         model = scenes.procedural_soup(2_000_000)
         model["provenance"] = "procedural soup, 2,000,000 triangles (numpy generator; CPU arm is bounded to this size)"
         return model, scenes.identity_instance(1.0)
-    model = scenes.sponza_standin()
+    model = scenes.sponza_standin(with_images=with_images)
     instances = scenes.instanced_grid_transforms() if workload == "config4" else None
     return model, instances
 
@@ -374,10 +375,12 @@ def main():
         rt = Raytracer(None, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id, flat=flat,
                        build_flags=args.build_flags)
     else:
-        model, instances = build_scene(args.workload)
+        # scene ingest over N ranks: rank 0 decodes the 69 image files (thread pool) and uploads them; the other ranks build
+        # only the geometry and receive the texel pool over NVLink (vkrt_textures_broadcast)
+        model, instances = build_scene(args.workload, with_images=(rank == 0))
         t_ingest1 = time.perf_counter()
         rt = Raytracer(model, W, Hh, device=local, instances=instances, rank=rank, world_size=world, unique_id=unique_id,
-                       build_flags=args.build_flags)
+                       build_flags=args.build_flags, textures_from_root=0 if world > 1 else None)
     rt.ctx.synchronize()
     t_ingest2 = time.perf_counter()
     if soup is not None:

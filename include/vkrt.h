@@ -354,6 +354,12 @@ VKRT_API int vkrt_comm_destroy(VkrtContext* ctx);
 VKRT_API uint64_t vkrt_hash_fnv1a64(const void* data, size_t bytes);
 /* Owner rank of the tile containing pixel (x,y) for a frame of this width. */
 VKRT_API int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size);
+/* Scene ingest for several ranks (the reference decodes and uploads every image in Raytracer::createTextures,
+ * src/Raytracer.cpp:460-570, once per process): `root` has called vkrt_textures_set; every other rank calls this INSTEAD
+ * of vkrt_textures_set and receives the device-resident texel pool over NVLink (one ncclBroadcast), so the image files
+ * are decoded once per box, not once per GPU.  Collective: every rank of the communicator must call it.  Complete on
+ * return; the mip chain is not transferred (vkrt_textures_generate_mips rebuilds it in 0.2 ms). */
+VKRT_API int vkrt_textures_broadcast(VkrtContext* ctx, int root);
 /* Gathers the BGRA8 tiles of all ranks into root's frame (stream-ordered; NCCL send/recv group). */
 VKRT_API int vkrt_tiles_gather(VkrtContext* ctx, VkrtFrame* frame, int root);
 

@@ -20,12 +20,13 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    model = scenes.sponza_standin(max_texture_size=256)
+    # rank 0 decodes the textures; the other ranks receive them through vkrt_textures_broadcast (scene ingest over N ranks)
+    model = scenes.sponza_standin(max_texture_size=256, with_images=(rank == 0))
     ok = True
     for (w, h, spp) in ((1000, 600, 1), (640, 360, 4)):
         ids = [B.Context.comm_unique_id() if rank == 0 else None]  # one NCCL communicator per Raytracer
         dist.broadcast_object_list(ids, src=0)
-        rt = Raytracer(model, w, h, device=local, rank=rank, world_size=world, unique_id=ids[0])
+        rt = Raytracer(model, w, h, device=local, rank=rank, world_size=world, unique_id=ids[0], textures_from_root=0)
         rt.render(spp=spp)
         rt.ctx.synchronize()
         presented = None

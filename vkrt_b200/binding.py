@@ -188,6 +188,7 @@ EXPORTS = [
     "vkrt_tile_owner",
     "vkrt_hash_fnv1a64",
     "vkrt_tiles_gather",
+    "vkrt_textures_broadcast",
 ]
 
 _lib = None
@@ -250,6 +251,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_tile_owner": (i32, [u32, u32, u32, i32]),
         "vkrt_hash_fnv1a64": (u64, [vp, sz]),
         "vkrt_tiles_gather": (i32, [vp, vp, i32]),
+        "vkrt_textures_broadcast": (i32, [vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -315,6 +317,10 @@ class Context:
             keep.append(im)
             arr[i].width, arr[i].height, arr[i].rgba8 = im.shape[1], im.shape[0], im.ctypes.data
         self.check(self.lib.vkrt_textures_set(self.handle, arr, len(images)))
+
+    def textures_broadcast(self, root: int = 0):
+        """Collective over the communicator: ranks other than `root` receive root's uploaded textures (vkrt_textures_broadcast)."""
+        self.check(self.lib.vkrt_textures_broadcast(self.handle, root))
 
     def generate_mips(self):
         """Raytracer::createMipmaps (src/Raytracer.cpp:572-640) for every image, on the device."""

@@ -1221,6 +1221,18 @@ int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size)
     return size > 0 ? (int)(tile % (uint32_t)size) : 0;
 }
 
+int vkrt_textures_broadcast(VkrtContext* c, int root)
+{
+    Context* ctx = C(c);
+    if (!ctx || root < 0 || root >= ctx->size)
+    {
+        return ctx ? ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_textures_broadcast: bad root") : VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    cudaSetDevice(ctx->device);
+    NvtxRange range("createTextures (broadcast)");
+    return broadcastTextures(ctx, root);
+}
+
 int vkrt_tiles_gather(VkrtContext* c, VkrtFrame* frame, int root)
 {
     Context* ctx = C(c);

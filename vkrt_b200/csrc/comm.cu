@@ -34,6 +34,7 @@ struct NcclFns
     int (*commDestroy)(NcclComm) = nullptr;
     int (*send)(const void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*recv)(void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*broadcast)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*groupStart)() = nullptr;
     int (*groupEnd)() = nullptr;
     const char* (*getErrorString)(int) = nullptr;
@@ -72,6 +73,7 @@ NcclFns& nccl()
         fns.commDestroy = reinterpret_cast<int (*)(NcclComm)>(sym("ncclCommDestroy"));
         fns.send = reinterpret_cast<int (*)(const void*, size_t, int, int, NcclComm, cudaStream_t)>(sym("ncclSend"));
         fns.recv = reinterpret_cast<int (*)(void*, size_t, int, int, NcclComm, cudaStream_t)>(sym("ncclRecv"));
+        fns.broadcast = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t)>(sym("ncclBroadcast"));
         fns.groupStart = reinterpret_cast<int (*)()>(sym("ncclGroupStart"));
         fns.groupEnd = reinterpret_cast<int (*)()>(sym("ncclGroupEnd"));
         fns.getErrorString = reinterpret_cast<const char* (*)(int)>(sym("ncclGetErrorString"));
@@ -84,21 +86,34 @@ uint32_t ownedTilesOf(uint32_t tiles, int rank, int size)
     return tiles > (uint32_t)rank ? (tiles - (uint32_t)rank + (uint32_t)size - 1) / (uint32_t)size : 0;
 }
 
-// Scatter one peer's tile-major buffer into the linear image.
+// Scatters the staged tiles of all peers (rank after rank, the root left out; each rank's tiles in its own order) into
+// the linear image.  Rank r owns tiles r, r + size, ...: tiles / size of them, one more when r < tiles % size.
 __global__ void __launch_bounds__(256)
-k_untile(const uint32_t* __restrict__ tiles, uint32_t ownedTiles, uint32_t rank, uint32_t size, uint32_t tilesX, uint32_t width,
-         uint32_t height, uint32_t* __restrict__ image)
+k_untile_all(const uint32_t* __restrict__ staged, uint32_t stagedTiles, uint32_t tiles, uint32_t root, uint32_t size, uint32_t tilesX,
+             uint32_t width, uint32_t height, uint32_t* __restrict__ image)
 {
-    const uint32_t total = ownedTiles * (uint32_t)kTilePixels;
+    const uint32_t total = stagedTiles * (uint32_t)kTilePixels;
+    const uint32_t q = tiles / size, rem = tiles % size;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
     {
-        const uint32_t tl = i / (uint32_t)kTilePixels, pit = i % (uint32_t)kTilePixels;
+        uint32_t tl = i / (uint32_t)kTilePixels;
+        const uint32_t pit = i % (uint32_t)kTilePixels;
+        uint32_t rank = 0;
+        for (; rank < size; ++rank)
+        {
+            const uint32_t owned = rank == root ? 0u : q + (rank < rem ? 1u : 0u);
+            if (tl < owned)
+            {
+                break;
+            }
+            tl -= owned;
+        }
         const uint32_t tile = rank + tl * size;
         const uint32_t x = (tile % tilesX) * (uint32_t)kTile + (pit % (uint32_t)kTile);
         const uint32_t y = (tile / tilesX) * (uint32_t)kTile + (pit / (uint32_t)kTile);
-        if (x < width && y < height)
+        if (rank < size && x < width && y < height)
         {
-            image[(size_t)y * width + x] = tiles[i];
+            image[(size_t)y * width + x] = staged[i];
         }
     }
 }
@@ -159,6 +174,110 @@ int commDestroy(Context* ctx)
     return VKRT_SUCCESS;
 }
 
+// Scene ingest for N ranks: the root has decoded and uploaded the images once (vkrt_textures_set); every
+// other rank receives the device-resident texel pool over NVLink instead of decoding the same 69 files again.
+//   1. a fixed-size header (count, then width/height per image) so that the receivers can lay out their pool;
+//   2. the pool itself (all images, each 256-byte aligned - the layout vkrt_textures_set uses), one ncclBroadcast.
+int broadcastTextures(Context* ctx, int root)
+{
+    constexpr uint32_t kMaxImages = 4095;
+    if (ctx->size == 1)
+    {
+        return ctx->textureCount ? VKRT_SUCCESS : ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_textures_broadcast: no textures set");
+    }
+    if (!ctx->ncclComm)
+    {
+        return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_textures_broadcast: no communicator (vkrt_comm_init)");
+    }
+    NcclFns& n = nccl();
+    cudaStream_t s = ctx->stream;
+    const bool isRoot = ctx->rank == root;
+    if (isRoot && (ctx->textureCount == 0 || ctx->textureCount > kMaxImages))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_textures_broadcast: the root needs 1..4095 textures set");
+    }
+    std::vector<uint32_t> header(2 * (kMaxImages + 1), 0u);
+    if (isRoot)
+    {
+        header[0] = ctx->textureCount;
+        for (uint32_t i = 0; i < ctx->textureCount; ++i)
+        {
+            header[2 + 2 * i] = ctx->textureHost[i].width;
+            header[3 + 2 * i] = ctx->textureHost[i].height;
+        }
+    }
+    DeviceBuffer hb;
+    VKRT_CUDA_TRY(ctx, hb.reserve(header.size() * 4));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hb.ptr, header.data(), header.size() * 4, cudaMemcpyHostToDevice, s));
+    int rc = n.broadcast(hb.ptr, hb.ptr, header.size() * 4, kNcclUint8, root, ctx->ncclComm, s);
+    if (rc == 0)
+    {
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(header.data(), hb.ptr, header.size() * 4, cudaMemcpyDeviceToHost, s));
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    }
+    hb.release();
+    if (rc != 0)
+    {
+        return ctx->fail(VKRT_ERROR_NCCL, std::string("ncclBroadcast: ") + n.getErrorString(rc));
+    }
+    const uint32_t count = header[0];
+    if (count == 0 || count > kMaxImages)
+    {
+        return ctx->fail(VKRT_ERROR_NCCL, "vkrt_textures_broadcast: bad header from the root");
+    }
+    std::vector<size_t> offsets(count);
+    size_t total = 0;
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        offsets[i] = total;
+        total += (((size_t)header[2 + 2 * i] * header[3 + 2 * i] * 4) + 255) & ~(size_t)255;
+    }
+    void* pool = nullptr;
+    if (isRoot)
+    {
+        pool = ctx->textureAllocs.empty() ? nullptr : ctx->textureAllocs[0];
+    }
+    else
+    {
+        for (void* p : ctx->textureAllocs)
+        {
+            cudaFree(p);
+        }
+        ctx->textureAllocs.clear();
+        ctx->textureCount = 0;
+        VKRT_CUDA_TRY(ctx, cudaMalloc(&pool, total));
+        ctx->textureAllocs.push_back(pool);
+    }
+    rc = n.broadcast(pool, pool, total, kNcclUint8, root, ctx->ncclComm, s);
+    if (rc != 0)
+    {
+        return ctx->fail(VKRT_ERROR_NCCL, std::string("ncclBroadcast: ") + n.getErrorString(rc));
+    }
+    if (!isRoot)
+    {
+        std::vector<TextureRecord> recs(count);
+        for (uint32_t i = 0; i < count; ++i)
+        {
+            recs[i].texels = static_cast<const uint8_t*>(pool) + offsets[i];
+            recs[i].width = header[2 + 2 * i];
+            recs[i].height = header[3 + 2 * i];
+        }
+        VKRT_CUDA_TRY(ctx, ctx->textureRecords.reserve(recs.size() * sizeof(TextureRecord)));
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->textureRecords.ptr, recs.data(), recs.size() * sizeof(TextureRecord), cudaMemcpyHostToDevice, s));
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+        ctx->textureCount = count;
+        ctx->textureHost = recs;
+        ctx->mipsHost.clear();
+        ctx->mipsReady = false;
+        ctx->materialsDirty = true;
+    }
+    else
+    {
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    }
+    return VKRT_SUCCESS;
+}
+
 int gatherTiles(Context* ctx, Frame* frame, int root)
 {
     if (frame->size == 1)
@@ -202,18 +321,22 @@ int gatherTiles(Context* ctx, Frame* frame, int root)
         {
             return ctx->fail(VKRT_ERROR_NCCL, std::string("ncclRecv: ") + n.getErrorString(rc ? rc : rc2));
         }
-        for (int r = 0; r < ctx->size; ++r)
+        // one launch scatters the tiles of every peer: staged tile k of the concatenated peers maps back to its rank and
+        // its index among that rank's tiles (ranks before the root hold one tile more when the tile count does not divide)
         {
-            const uint32_t owned = ownedTilesOf(tiles, r, ctx->size);
-            if (r == root || owned == 0)
+            uint32_t stagedTiles = 0;
+            for (int r = 0; r < ctx->size; ++r)
             {
-                continue;
+                stagedTiles += r == root ? 0u : ownedTilesOf(tiles, r, ctx->size);
             }
-            const uint32_t total = owned * (uint32_t)kTilePixels;
-            const uint32_t grid = std::min<uint32_t>((total + 255) / 256, (uint32_t)ctx->smCount * 8u);
-            k_untile<<<grid, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(staging + offset[(size_t)r]), owned, (uint32_t)r,
-                                         (uint32_t)ctx->size, frame->tilesX, frame->width, frame->height, frame->bgra8.as<uint32_t>());
-            ctx->launches += 1;
+            if (stagedTiles)
+            {
+                const uint32_t total = stagedTiles * (uint32_t)kTilePixels;
+                const uint32_t grid = std::min<uint32_t>((total + 255) / 256, (uint32_t)ctx->smCount * 8u);
+                k_untile_all<<<grid, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(staging), stagedTiles, tiles, (uint32_t)root,
+                                                 (uint32_t)ctx->size, frame->tilesX, frame->width, frame->height, frame->bgra8.as<uint32_t>());
+                ctx->launches += 1;
+            }
         }
         VKRT_CUDA_TRY(ctx, cudaGetLastError());
         frame->gathered = true;

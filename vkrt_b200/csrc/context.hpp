@@ -213,6 +213,7 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
 int generateMips(Context* ctx); // textures.cu
 int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t flags, Frame* frame); // raster.cu
 int gatherTiles(Context* ctx, Frame* frame, int root);
+int broadcastTextures(Context* ctx, int root);
 int commInit(Context* ctx, const uint8_t* id, int rank, int size);
 int commDestroy(Context* ctx);
 int commUniqueId(uint8_t* id, std::string& err);

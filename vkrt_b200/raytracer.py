@@ -39,7 +39,7 @@ def flatten_model(model: Dict) -> Dict:
         index_counter_offset += s["vertices"].shape[0]
         index_byte_offset += 4 * idx.size
         index_buffer_offset += idx.size // 3
-    return {"vertices": vertices, "indices": indices, "ranges": ranges, "rows": rows, "images": model["images"]}
+    return {"vertices": vertices, "indices": indices, "ranges": ranges, "rows": rows, "images": model.get("images")}
 
 
 class Raytracer:
@@ -47,7 +47,7 @@ class Raytracer:
 
     def __init__(self, model: Dict, width: int, height: int, device: int = 0, instances: Optional[np.ndarray] = None,
                  build_flags: int = 0, rank: int = 0, world_size: int = 1, unique_id: Optional[bytes] = None,
-                 emulate_ranks: bool = False, flat: Optional[Dict] = None):
+                 emulate_ranks: bool = False, flat: Optional[Dict] = None, textures_from_root: Optional[int] = None):
         """`flat` (optional) is an already flattened scene whose vertices/indices may be CUDA tensors (config 5)."""
         self.width, self.height = width, height
         self.flat = flat if flat is not None else flatten_model(model)
@@ -62,7 +62,11 @@ class Raytracer:
         self.blas = B.Blas(self.ctx, self.flat["vertices"], self.flat["indices"], self.flat["ranges"], flags=build_flags)
         self.tlas = B.Tlas(self.ctx, [self.blas], self.instances)
         self.ctx.set_materials(self.flat["rows"])
-        self.ctx.set_textures(self.flat["images"])
+        if self.flat.get("images") is not None:
+            self.ctx.set_textures(self.flat["images"])
+        if world_size > 1 and not emulate_ranks and textures_from_root is not None:
+            # scene ingest for N ranks: only `textures_from_root` decoded the image files; the others get the texels over NVLink
+            self.ctx.textures_broadcast(textures_from_root)
         self.ctx.generate_mips()  # createTextures -> createMipmaps, src/Raytracer.cpp:562 (sampled only in the ray-cone mode)
         self.frame = B.Frame(self.ctx, width, height)
         self.camera = Camera(np.float32(width) / np.float32(height))

@@ -389,13 +389,20 @@ def load_sponza_images(layout: Optional[Dict] = None, max_size: Optional[int] = 
     if d is not None and all(os.path.isfile(os.path.join(d, im["uri"])) for im in layout["images"]):
         from .model import decode_image  # host C++ decoder: bit-identical to the reference's stb_image on these files
 
-        for im in layout["images"]:
+        def one(im):
             with open(os.path.join(d, im["uri"]), "rb") as f:
                 rgba = decode_image(f.read())
             if max_size and max(rgba.shape[:2]) > max_size:
                 step = max(rgba.shape[:2]) // max_size
                 rgba = np.ascontiguousarray(rgba[::step, ::step])
-            images.append(rgba)
+            return rgba
+
+        # the reference decodes the 69 images one after the other (stb_image inside tinygltf, src/Model.cpp:138-151); the
+        # decoder is called through ctypes, which releases the GIL, so a thread pool decodes them on all host cores
+        from concurrent.futures import ThreadPoolExecutor
+
+        with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as pool:
+            images = list(pool.map(one, layout["images"]))
         return images, "reference textures (host decoder, == stb_image)" + (f", subsampled to {max_size}" if max_size else "")
     # procedural fall-back: role-dependent content so normal maps stay normal-like and metallic maps binary-ish
     roles = {}
@@ -420,8 +427,14 @@ def load_sponza_images(layout: Optional[Dict] = None, max_size: Optional[int] = 
     return images, "procedural textures (reference texture files not staged)"
 
 
-def sponza_standin(max_texture_size: Optional[int] = None) -> Dict:
+def sponza_standin(max_texture_size: Optional[int] = None, with_images: bool = True) -> Dict:
+    """with_images=False: geometry and materials only (a rank that receives the textures from another rank,
+    Raytracer(textures_from_root=...))."""
     layout = load_layout()
+    if not with_images:
+        materials = [(m["baseColor"], m["metallicRoughness"], m["normal"]) for m in layout["materials"]]
+        return {"submeshes": sponza_standin_submeshes(layout), "materials": materials, "images": None,
+                "provenance": "stand-in geometry (Sponza.bin absent from the reference checkout) + textures received from the root rank"}
     images, provenance = load_sponza_images(layout, max_texture_size)
     materials = [(m["baseColor"], m["metallicRoughness"], m["normal"]) for m in layout["materials"]]
     return {"submeshes": sponza_standin_submeshes(layout), "materials": materials, "images": images,
