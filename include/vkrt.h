@@ -360,8 +360,14 @@ VKRT_API int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size);
  * are decoded once per box, not once per GPU.  Collective: every rank of the communicator must call it.  Complete on
  * return; the mip chain is not transferred (vkrt_textures_generate_mips rebuilds it in 0.2 ms). */
 VKRT_API int vkrt_textures_broadcast(VkrtContext* ctx, int root);
-/* Gathers the BGRA8 tiles of all ranks into root's frame (stream-ordered; NCCL send/recv group). */
+/* Gathers the BGRA8 tiles of all ranks into root's frame: a grouped NCCL send/recv exchange plus one scatter kernel on the
+ * library's communication stream, ordered after everything queued on the context so far.  Returns without waiting; the
+ * next vkrt_trace into the same frame may be queued at once (only its final image write waits for the gather, so the
+ * exchange overlaps the next frame's traversal).  vkrt_frame_read, vkrt_frame_present and vkrt_context_synchronize wait
+ * for it; vkrt_tiles_gather_wait makes the context stream wait for it explicitly (stream-ordered, for callers that time
+ * with events on vkrt_context_stream). */
 VKRT_API int vkrt_tiles_gather(VkrtContext* ctx, VkrtFrame* frame, int root);
+VKRT_API int vkrt_tiles_gather_wait(VkrtContext* ctx, VkrtFrame* frame);
 
 #ifdef __cplusplus
 }

@@ -189,6 +189,7 @@ EXPORTS = [
     "vkrt_hash_fnv1a64",
     "vkrt_tiles_gather",
     "vkrt_textures_broadcast",
+    "vkrt_tiles_gather_wait",
 ]
 
 _lib = None
@@ -252,6 +253,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_hash_fnv1a64": (u64, [vp, sz]),
         "vkrt_tiles_gather": (i32, [vp, vp, i32]),
         "vkrt_textures_broadcast": (i32, [vp, i32]),
+        "vkrt_tiles_gather_wait": (i32, [vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -527,6 +529,10 @@ class Frame:
 
     def gather(self, root: int = 0):
         self.ctx.check(self.ctx.lib.vkrt_tiles_gather(self.ctx.handle, self.handle, root))
+
+    def gather_wait(self):
+        """Stream-ordered: the context stream waits for the outstanding tile gather of this frame."""
+        self.ctx.check(self.ctx.lib.vkrt_tiles_gather_wait(self.ctx.handle, self.handle))
 
     def read(self, aov: int, out: Optional[np.ndarray] = None) -> np.ndarray:
         shape, dt = {

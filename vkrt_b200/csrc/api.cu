@@ -252,6 +252,12 @@ void vkrt_context_destroy(VkrtContext* c)
         cudaStreamSynchronize(ctx->copyStream);
         cudaStreamDestroy(ctx->copyStream);
     }
+    if (ctx->commStream)
+    {
+        cudaStreamSynchronize(ctx->commStream);
+        cudaStreamDestroy(ctx->commStream);
+        cudaEventDestroy(ctx->commReady);
+    }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -265,6 +271,10 @@ int vkrt_context_synchronize(VkrtContext* c)
 {
     Context* ctx = C(c);
     cudaSetDevice(ctx->device);
+    if (ctx->commStream)
+    {
+        VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->commStream));
+    }
     return checkDeviceErrors(ctx, "vkrt_context_synchronize");
 }
 
@@ -880,6 +890,14 @@ void vkrt_frame_destroy(VkrtContext* c, VkrtFrame* fr)
     {
         cudaStreamSynchronize(C(c)->copyStream);
     }
+    if (c && C(c)->commStream)
+    {
+        cudaStreamSynchronize(C(c)->commStream);
+    }
+    if (f->gatherDone)
+    {
+        cudaEventDestroy(f->gatherDone);
+    }
     if (f->presentReady)
     {
         cudaEventDestroy(f->presentReady);
@@ -940,6 +958,10 @@ int vkrt_frame_read(VkrtContext* c, VkrtFrame* fr, int aov, void* dst, size_t pi
     {
         return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_frame_read: this output was not rendered (VKRT_TRACE_NO_AOV?)");
     }
+    if (int r = joinGather(ctx, f))
+    {
+        return r;
+    }
     const size_t row = (size_t)f->width * bpp;
     if (pitch == 0)
     {
@@ -982,6 +1004,10 @@ int vkrt_frame_present(VkrtContext* c, VkrtFrame* fr, void* dst, size_t pitch, u
     if (!f->presentReady)
     {
         VKRT_CUDA_TRY(ctx, cudaEventCreateWithFlags(&f->presentReady, cudaEventDisableTiming));
+    }
+    if (int r = joinGather(ctx, f))
+    {
+        return r;
     }
     const uint64_t n = f->presentNext;
     cudaEvent_t& done = f->presentDone[n % Frame::kPresentRing];
@@ -1219,6 +1245,17 @@ int vkrt_tile_owner(uint32_t width, uint32_t x, uint32_t y, int size)
     const uint32_t tilesX = (width + kTile - 1) / kTile;
     const uint32_t tile = (y / kTile) * tilesX + (x / kTile);
     return size > 0 ? (int)(tile % (uint32_t)size) : 0;
+}
+
+int vkrt_tiles_gather_wait(VkrtContext* c, VkrtFrame* frame)
+{
+    Context* ctx = C(c);
+    if (!frame)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tiles_gather_wait: NULL frame");
+    }
+    cudaSetDevice(ctx->device);
+    return joinGather(ctx, F(frame));
 }
 
 int vkrt_textures_broadcast(VkrtContext* c, int root)

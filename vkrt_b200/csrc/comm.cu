@@ -294,7 +294,25 @@ int gatherTiles(Context* ctx, Frame* frame, int root)
         return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_tiles_gather: frame was created under a different communicator");
     }
     NcclFns& n = nccl();
-    cudaStream_t s = ctx->stream;
+    // The exchange runs on its own stream, ordered after everything queued on the context stream so far.  The caller may
+    // queue the next vkrt_trace at once: only its last kernel (k_resolve_sample, which rewrites the tile buffer and the
+    // image) waits for this gather (joinGather), so the NCCL transfer and the untile overlap the next frame's traversal.
+    if (!ctx->commStream)
+    {
+        VKRT_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->commStream, cudaStreamNonBlocking));
+        VKRT_CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->commReady, cudaEventDisableTiming));
+    }
+    if (!frame->gatherDone)
+    {
+        VKRT_CUDA_TRY(ctx, cudaEventCreateWithFlags(&frame->gatherDone, cudaEventDisableTiming));
+    }
+    if (int r = joinGather(ctx, frame)) // a second gather of the same frame without a trace in between
+    {
+        return r;
+    }
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(ctx->commReady, ctx->stream));
+    VKRT_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->commStream, ctx->commReady, 0));
+    cudaStream_t s = ctx->commStream;
     const uint32_t tiles = frame->tilesX * frame->tilesY;
     const size_t tileBytes = (size_t)kTilePixels * 4;
     if (ctx->rank == root)
@@ -354,6 +372,18 @@ int gatherTiles(Context* ctx, Frame* frame, int root)
         {
             return ctx->fail(VKRT_ERROR_NCCL, std::string("ncclSend: ") + n.getErrorString(rc ? rc : rc2));
         }
+    }
+    VKRT_CUDA_TRY(ctx, cudaEventRecord(frame->gatherDone, ctx->commStream));
+    frame->gatherPending = true;
+    return VKRT_SUCCESS;
+}
+
+int joinGather(Context* ctx, Frame* frame)
+{
+    if (frame->gatherPending)
+    {
+        VKRT_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, frame->gatherDone, 0));
+        frame->gatherPending = false;
     }
     return VKRT_SUCCESS;
 }

@@ -91,6 +91,8 @@ struct Context : VkrtContext
     int smCount = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copyStream = nullptr; // vkrt_frame_present copies (created on first use)
+    cudaStream_t commStream = nullptr; // vkrt_tiles_gather: NCCL exchange + untile, overlapping the next frame's traversal
+    cudaEvent_t commReady = nullptr;   // recorded on `stream` when a gather is queued
     std::string lastError;
     uint64_t launches = 0;
 
@@ -188,6 +190,8 @@ struct Frame : VkrtFrame
     DeviceBuffer shadowMask;  // width*height u8 (AOV)
     DeviceBuffer visibility;  // width*height*8 u64 (depth24 << 32 | triangle) keys of the rasteriser (raster.cu)
     bool gathered = false;
+    cudaEvent_t gatherDone = nullptr; // recorded on the comm stream after a gather of this frame
+    bool gatherPending = false;       // the context stream has not waited for gatherDone yet
     // presentation ring (vkrt_frame_present): copy n uses presentDone[n % kPresentRing]
     static constexpr int kPresentRing = 8;
     cudaEvent_t presentReady = nullptr;              // recorded on the context stream when a present is queued
@@ -197,6 +201,8 @@ struct Frame : VkrtFrame
 };
 // Makes the context stream wait for the outstanding presents of `frame` before its image is overwritten.
 int waitPresents(Context* ctx, Frame* frame);
+// Makes the context stream wait for an outstanding vkrt_tiles_gather of `frame` (before its buffers are read or rewritten).
+int joinGather(Context* ctx, Frame* frame);
 
 int buildBlasOnDevice(Context* ctx, Blas* blas);
 int buildTlasOnDevice(Context* ctx, Tlas* tlas);

@@ -407,6 +407,10 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         }
         ctx->launches += 4;
     }
+    if (int e = joinGather(ctx, frame))
+    {
+        return e;
+    }
     if (int e = waitPresents(ctx, frame)) // the image is about to be overwritten
     {
         return e;

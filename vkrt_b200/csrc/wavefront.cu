@@ -1064,6 +1064,10 @@ int traceFrame(Context* ctx, const Tlas* tlas, const VkrtUniforms* uniforms, uin
         {
             mark(); // 9
         }
+        if (int r = joinGather(ctx, frame)) // ... and an outstanding tile gather still reads the tile buffer / writes the image
+        {
+            return r;
+        }
         if (int r = waitPresents(ctx, frame)) // the image is about to be overwritten: outstanding vkrt_frame_present copies first
         {
             return r;
