@@ -143,9 +143,9 @@ VKRT_HD void sampleLevel(const uint8_t* texels, uint32_t width, uint32_t height,
 }
 
 // texture(sampler2D, uv) at LOD 0 (what the reference's ray-tracing shaders get: no derivatives).
-VKRT_HD void sampleTexture(const TextureRecord& tex, float u, float v, float rgba[4])
+VKRT_HD void sampleTexture(const TextureRecord& tex, float u, float v, float rgba[4], const float* unorm = nullptr)
 {
-    sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba);
+    sampleLevel(tex.texels, tex.width, tex.height, u, v, rgba, unorm);
 }
 
 // ---- Mip chain and ray-cone level of detail (off by default, the parity frames sample LOD 0) ----------
@@ -270,9 +270,10 @@ VKRT_HD void sampleTrilinear(const TextureRecord& tex, const TextureMips& mips, 
 }
 
 // Ray-cone level of detail: the squared uv footprint covers footprint2 * W * H texels of this texture.
-VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips, float u, float v, float footprint2, float rgba[4])
+VKRT_HD void sampleTextureLod(const TextureRecord& tex, const TextureMips& mips, float u, float v, float footprint2, float rgba[4],
+                              const float* unorm = nullptr)
 {
-    sampleTrilinear(tex, mips, u, v, (footprint2 * (float)tex.width) * (float)tex.height, rgba);
+    sampleTrilinear(tex, mips, u, v, (footprint2 * (float)tex.width) * (float)tex.height, rgba, unorm);
 }
 
 VKRT_HD float4 loadF4(const uint8_t* base, size_t byteOffset)
@@ -289,7 +290,8 @@ VKRT_HD float4 loadF4(const uint8_t* base, size_t byteOffset)
 // shader.rchit:88-108.  LOD = false is the reference's behaviour (every texture() call samples level 0).
 template<bool LOD = false>
 VKRT_HD SurfacePoint shadeSurface(const InstanceRecord& inst, const VkrtSubmeshInfo* rows, const TextureRecord* textures,
-                                  uint32_t geometry, uint32_t primitive, float b1, float b2, const LodInput* lod = nullptr)
+                                  uint32_t geometry, uint32_t primitive, float b1, float b2, const LodInput* lod = nullptr,
+                                  const float* unorm = nullptr)
 {
     SurfacePoint sp;
     sp.geometry = geometry;
@@ -330,11 +332,11 @@ VKRT_HD SurfacePoint shadeSurface(const InstanceRecord& inst, const VkrtSubmeshI
                                        affinePoint(inst.o2w, f3(p2.x, p2.y, p2.z)), uv0.x, uv0.y, uv1.x, uv1.y, uv2.x, uv2.y,
                                        lod->worldRayDir, lod->coneWidth);
         const uint32_t ti = (uint32_t)row.normalTextureIndex;
-        sampleTextureLod(textures[ti], lod->mips[ti], sp.u, sp.v, sp.footprint2, texel);
+        sampleTextureLod(textures[ti], lod->mips[ti], sp.u, sp.v, sp.footprint2, texel, unorm);
     }
     else
     {
-        sampleTexture(textures[(uint32_t)row.normalTextureIndex], sp.u, sp.v, texel); // rchit:106-107
+        sampleTexture(textures[(uint32_t)row.normalTextureIndex], sp.u, sp.v, texel, unorm); // rchit:106-107
     }
     const F3 mapN = f3(texel[0] * 2.0f - 1.0f, texel[1] * 2.0f - 1.0f, texel[2] * 2.0f - 1.0f);
     const F3 mn = normalize3(mapN);
@@ -377,7 +379,7 @@ struct ResolveOut
 template<bool LOD = false>
 VKRT_HD ResolveOut shadeResolve(const VkrtUniforms& u, const VkrtSubmeshInfo* rows, const TextureRecord* textures,
                                 const SurfacePoint& sp, uint32_t shadowBits, float attenuation, F3 worldRayDir,
-                                const TextureMips* mips = nullptr)
+                                const TextureMips* mips = nullptr, const float* unorm = nullptr)
 {
     ResolveOut out;
     float totalLightAmount = 0.0f;
@@ -393,22 +395,22 @@ VKRT_HD ResolveOut shadeResolve(const VkrtUniforms& u, const VkrtSubmeshInfo* ro
     if (LOD)
     {
         const uint32_t ti = (uint32_t)row.baseColorTextureIndex;
-        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel);
+        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel, unorm);
     }
     else
     {
-        sampleTexture(textures[(uint32_t)row.baseColorTextureIndex], sp.u, sp.v, texel); // rchit:156-157
+        sampleTexture(textures[(uint32_t)row.baseColorTextureIndex], sp.u, sp.v, texel, unorm); // rchit:156-157
     }
     const F3 baseColor = f3(texel[0], texel[1], texel[2]);
     out.hitValue = (baseColor * totalLightAmount) * attenuation + baseColor * ambient; // rchit:158
     if (LOD)
     {
         const uint32_t ti = (uint32_t)row.metallicRoughnessTextureIndex;
-        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel);
+        sampleTextureLod(textures[ti], mips[ti], sp.u, sp.v, sp.footprint2, texel, unorm);
     }
     else
     {
-        sampleTexture(textures[(uint32_t)row.metallicRoughnessTextureIndex], sp.u, sp.v, texel); // rchit:161-162
+        sampleTexture(textures[(uint32_t)row.metallicRoughnessTextureIndex], sp.u, sp.v, texel, unorm); // rchit:161-162
     }
     const float metallic = texel[2];
     out.attenuation = attenuation;

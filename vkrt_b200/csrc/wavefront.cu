@@ -456,6 +456,14 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                 const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
 {
     __shared__ AppendStage stage;
+    // c / 255.0f for every byte value: the bilinear filter converts 16 texel bytes per texture() call, each an IEEE division
+    // (~10 instructions); the table holds the identical quotients (bit-equal results, as in the rasteriser and the mip kernel)
+    __shared__ float unorm[256];
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x)
+    {
+        unorm[i] = (float)i / 255.0f;
+    }
+    __syncthreads();
     const uint32_t count = countPtr ? *countPtr : countImm;
     const uint32_t rounded = (count + blockDim.x - 1u) / blockDim.x * blockDim.x; // whole blocks stay in the loop (blockAppend4)
     int parity = 0;
@@ -515,12 +523,12 @@ k_shade_surface(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
                     LodInput lod;
                     lod.mips = scene.mips, lod.worldRayDir = f3(d4.x, d4.y, d4.z);
                     lod.coneWidth = pixelSpreadAngle(u, f.map.height) * travelled;
-                    sp = shadeSurface<true>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z, &lod);
+                    sp = shadeSurface<true>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z, &lod, unorm);
                     w.surfFoot[q] = sp.footprint2;
                 }
                 else
                 {
-                    sp = shadeSurface<false>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z);
+                    sp = shadeSurface<false>(inst, scene.rows, scene.textures, geometry, primitive, h.y, h.z, nullptr, unorm);
                 }
                 for (int i = 0; i < 4; ++i)
                 {
@@ -589,6 +597,12 @@ __global__ void __launch_bounds__(kShadeThreads)
 k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev w, FrameDev f, const float4* __restrict__ rayD,
                 const uint32_t* __restrict__ pathOf, const uint32_t* __restrict__ countPtr, uint32_t countImm, int depth, uint32_t aovSamples)
 {
+    __shared__ float unorm[256]; // see k_shade_surface
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x)
+    {
+        unorm[i] = (float)i / 255.0f;
+    }
+    __syncthreads();
     const uint32_t count = countPtr ? *countPtr : countImm;
     const uint32_t rounded = (count + 31u) & ~31u;
     for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < rounded; q += gridDim.x * blockDim.x)
@@ -614,7 +628,7 @@ k_shade_resolve(const __grid_constant__ VkrtUniforms u, SceneDev scene, WaveDev 
             const uint32_t bits = w.shadowBits[q];
             float4 acc = w.pathAccum[p];
             const float4 d4 = rayD[q];
-            const ResolveOut r = shadeResolve<LOD>(u, scene.rows, scene.textures, sp, bits & 0xFu, acc.w, f3(d4.x, d4.y, d4.z), scene.mips);
+            const ResolveOut r = shadeResolve<LOD>(u, scene.rows, scene.textures, sp, bits & 0xFu, acc.w, f3(d4.x, d4.y, d4.z), scene.mips, unorm);
             acc.x += r.hitValue.x, acc.y += r.hitValue.y, acc.z += r.hitValue.z; // rgen:63
             acc.w = r.attenuation;
             w.pathAccum[p] = acc;
