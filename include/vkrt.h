@@ -287,7 +287,9 @@ VKRT_API void* vkrt_frame_device_bgra8(VkrtFrame* frame);
  * :1054-1075); `wvp` is the column-major proj * view * world matrix of Rasterizer::update (:189-191).  Materials, textures
  * and the mip chain must have been set.  Stream-ordered like vkrt_trace; with AOVs, VKRT_AOV_TRIANGLE_ID_U32 holds the
  * triangle (cumulative index over the geometries) seen by sample 0 of every pixel, ~0 where the clear colour shows.
- * Single-GPU frames only.  The ImGui overlay (:149-159) is not drawn.
+ * With a communicator attached the frame is split like vkrt_trace's: each rank draws the pixels of the 64x64 tiles it owns
+ * (every rank runs the vertex stage over all triangles), and vkrt_tiles_gather assembles the image on the root.
+ * The ImGui overlay (:149-159) is not drawn.
  * ---------------------------------------------------------------------------------------------- */
 VKRT_API int vkrt_rasterize(VkrtContext* ctx, const VkrtBlas* geometry, const float* wvp, uint32_t flags, VkrtFrame* frame);
 

@@ -34,7 +34,14 @@ struct RasterDev
     const TextureMips* mips;
     unsigned long long* visibility;
     uint32_t width, height;
+    // multi-GPU: this rank draws the pixels of the 64x64 image tiles it owns (tile % size == rank), like vkrt_trace
+    uint32_t tilesX, rank, size, ownedTiles;
 };
+
+__device__ __forceinline__ bool ownsPixel(const RasterDev& r, uint32_t x, uint32_t y)
+{
+    return r.size == 1u || ((y / (uint32_t)kTile) * r.tilesX + x / (uint32_t)kTile) % r.size == r.rank;
+}
 
 struct Mat4
 {
@@ -49,11 +56,30 @@ struct AtomicMinKey
     }
 };
 
-__global__ void __launch_bounds__(256) k_raster_clear(ulonglong2* __restrict__ keys, size_t pairs, uint32_t* counters)
+__global__ void __launch_bounds__(256) k_raster_clear(ulonglong2* __restrict__ keys, size_t pairs, uint32_t* counters, RasterDev r)
 {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (size_t)gridDim.x * blockDim.x)
+    if (r.size == 1u)
     {
-        keys[i] = make_ulonglong2(~0ull, ~0ull);
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (size_t)gridDim.x * blockDim.x)
+        {
+            keys[i] = make_ulonglong2(~0ull, ~0ull);
+        }
+    }
+    else
+    {
+        // only the owned tiles: 4 key pairs (64 bytes) per pixel, rows of 64 pixels are contiguous
+        const size_t total = (size_t)r.ownedTiles * kTilePixels * (kRasterSamples / 2);
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+        {
+            const uint32_t pair = (uint32_t)(i % (kRasterSamples / 2));
+            const size_t p = i / (kRasterSamples / 2);
+            const uint32_t tile = r.rank + (uint32_t)(p / kTilePixels) * r.size, pit = (uint32_t)(p % kTilePixels);
+            const uint32_t x = (tile % r.tilesX) * (uint32_t)kTile + pit % (uint32_t)kTile, y = (tile / r.tilesX) * (uint32_t)kTile + pit / (uint32_t)kTile;
+            if (x < r.width && y < r.height)
+            {
+                keys[((size_t)y * r.width + x) * (kRasterSamples / 2) + pair] = make_ulonglong2(~0ull, ~0ull);
+            }
+        }
     }
     if (blockIdx.x == 0 && threadIdx.x < 4)
     {
@@ -234,7 +260,11 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, c
         const uint32_t bw = x1 - x0 + 1u, n = bw * (y1 - y0 + 1u);
         for (uint32_t i = lane; i < n; i += 32u)
         {
-            rasterPixel(s, tri, r.textures, r.mips, r.width, x0 + i % bw, y0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
+            const uint32_t px = x0 + i % bw, py = y0 + i / bw;
+            if (ownsPixel(r, px, py))
+            {
+                rasterPixel(s, tri, r.textures, r.mips, r.width, px, py, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
+            }
         }
     }
 }
@@ -271,7 +301,7 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
         const uint32_t tx = x0 / kRasterTile + local % tilesX, ty = y0 / kRasterTile + local / tilesX;
         const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
         const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
-        if (rasterTileOutside(s, px0, py0, px1, py1))
+        if (!ownsPixel(r, px0, py0) || rasterTileOutside(s, px0, py0, px1, py1)) // a 16x16 tile lies inside one 64x64 ownership tile
         {
             continue;
         }
@@ -284,20 +314,43 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
 }
 
 __global__ void __launch_bounds__(256)
-k_raster_resolve(RasterDev r, uint32_t* __restrict__ bgra8, uint32_t* __restrict__ triangleId)
+k_raster_resolve(RasterDev r, uint32_t* __restrict__ bgra8, uint32_t* __restrict__ tileBgra8, uint32_t* __restrict__ triangleId)
 {
     __shared__ float unorm[256];
     fillUnormTable(unorm);
-    const uint32_t total = r.width * r.height;
+    if (r.size == 1u)
+    {
+        const uint32_t total = r.width * r.height;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+        {
+            const uint32_t px = i % r.width, py = i / r.width;
+            uint32_t first;
+            bgra8[i] = rasterResolve(r.setups, r.textures, r.mips, r.width, px, py, reinterpret_cast<const uint64_t*>(r.visibility), first, unorm);
+            if (triangleId)
+            {
+                triangleId[i] = first;
+            }
+        }
+        return;
+    }
+    // owned tiles only; the tile-major copy is the NCCL send buffer of vkrt_tiles_gather (row-major inside a tile)
+    const uint32_t total = r.ownedTiles * (uint32_t)kTilePixels;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
     {
-        const uint32_t px = i % r.width, py = i / r.width;
-        uint32_t first;
-        bgra8[i] = rasterResolve(r.setups, r.textures, r.mips, r.width, px, py, reinterpret_cast<const uint64_t*>(r.visibility), first, unorm);
-        if (triangleId)
+        const uint32_t tile = r.rank + (i / (uint32_t)kTilePixels) * r.size, pit = i % (uint32_t)kTilePixels;
+        const uint32_t px = (tile % r.tilesX) * (uint32_t)kTile + pit % (uint32_t)kTile, py = (tile / r.tilesX) * (uint32_t)kTile + pit / (uint32_t)kTile;
+        uint32_t value = 0u;
+        if (px < r.width && py < r.height)
         {
-            triangleId[i] = first;
+            uint32_t first;
+            value = rasterResolve(r.setups, r.textures, r.mips, r.width, px, py, reinterpret_cast<const uint64_t*>(r.visibility), first, unorm);
+            bgra8[(size_t)py * r.width + px] = value;
+            if (triangleId)
+            {
+                triangleId[(size_t)py * r.width + px] = first;
+            }
         }
+        tileBgra8[i] = value;
     }
 }
 } // namespace
@@ -320,10 +373,6 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     if (!ctx->mipsReady)
     {
         return ctx->fail(VKRT_ERROR_NOT_READY, "vkrt_rasterize: the fragment shader samples the mip chain; call vkrt_textures_generate_mips first");
-    }
-    if (frame->size > 1)
-    {
-        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_rasterize: frames split over ranks are not supported by the rasteriser");
     }
     if (frame->width > 32768u || frame->height > 32768u)
     {
@@ -371,8 +420,9 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     r.mips = ctx->textureMips.as<TextureMips>();
     r.visibility = frame->visibility.as<unsigned long long>();
     r.width = W, r.height = H;
+    r.tilesX = frame->tilesX, r.rank = (uint32_t)frame->rank, r.size = (uint32_t)frame->size, r.ownedTiles = frame->ownedTiles;
 
-    k_raster_clear<<<grid, 256, 0, s>>>(frame->visibility.as<ulonglong2>(), samples / 2, counters);
+    k_raster_clear<<<grid, 256, 0, s>>>(frame->visibility.as<ulonglong2>(), samples / 2, counters, r);
     if (n > 0)
     {
         k_raster_setup<<<grid, 256, 0, s>>>(holder, geo, blas->vertices.as<uint8_t>(), blas->vertexStride, blas->indices.as<uint32_t>(),
@@ -415,7 +465,8 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     {
         return e;
     }
-    k_raster_resolve<<<grid, 256, 0, s>>>(r, frame->bgra8.as<uint32_t>(), aov ? frame->triangleId.as<uint32_t>() : nullptr);
+    k_raster_resolve<<<grid, 256, 0, s>>>(r, frame->bgra8.as<uint32_t>(), frame->size > 1 ? frame->tileBgra8.as<uint32_t>() : nullptr,
+                                          aov ? frame->triangleId.as<uint32_t>() : nullptr);
     ctx->launches += 2;
     frame->gathered = false;
     VKRT_CUDA_TRY(ctx, cudaGetLastError());

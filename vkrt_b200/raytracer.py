@@ -117,14 +117,25 @@ class Rasterizer:
     uploaded in the constructor, `render()` draws one frame with shader.vert / shader.frag semantics (base-colour texture
     through its mip chain, alpha test, 8x MSAA, depth test LESS) on the GPU via vkrt_rasterize."""
 
-    def __init__(self, model: Dict, width: int, height: int, device: int = 0, flat: Optional[Dict] = None):
+    def __init__(self, model: Dict, width: int, height: int, device: int = 0, flat: Optional[Dict] = None, rank: int = 0,
+                 world_size: int = 1, unique_id: Optional[bytes] = None, emulate_ranks: bool = False,
+                 textures_from_root: Optional[int] = None):
         self.width, self.height = width, height
         self.flat = flat if flat is not None else flatten_model(model)
         self.ctx = B.Context(device)
+        self.rank, self.world_size = rank, world_size
+        if world_size > 1:
+            if emulate_ranks:
+                self.ctx.comm_emulate(rank, world_size)
+            else:
+                self.ctx.comm_init(unique_id, rank, world_size)
         # vertex/index buffers (createVertexAndIndexBuffer, src/Rasterizer.cpp:1040-1085); the BLAS object holds the device copy
         self.blas = B.Blas(self.ctx, self.flat["vertices"], self.flat["indices"], self.flat["ranges"], flags=B.BUILD_PREFER_FAST_BUILD)
         self.ctx.set_materials(self.flat["rows"])
-        self.ctx.set_textures(self.flat["images"])
+        if self.flat.get("images") is not None:
+            self.ctx.set_textures(self.flat["images"])
+        if world_size > 1 and not emulate_ranks and textures_from_root is not None:
+            self.ctx.textures_broadcast(textures_from_root)
         self.ctx.generate_mips()  # createTextures -> createMipmaps, src/Rasterizer.cpp:560-700
         self.frame = B.Frame(self.ctx, width, height)
         self.camera = Camera(np.float32(width) / np.float32(height))
@@ -136,8 +147,10 @@ class Rasterizer:
     def wvp(self) -> np.ndarray:
         return self.camera.wvp(self.scale)
 
-    def render(self, flags: int = 0):
+    def render(self, flags: int = 0, gather: bool = True):
         self.frame.rasterize(self.blas, self.wvp(), flags)
+        if gather and self.world_size > 1:
+            self.frame.gather(0)
 
     def readback(self, aov: int = B.AOV_BGRA8, out: Optional[np.ndarray] = None) -> np.ndarray:
         return self.frame.read(aov, out)
