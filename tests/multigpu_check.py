@@ -13,7 +13,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vkrt_b200 import binding as B  # noqa: E402
 from vkrt_b200 import scenes  # noqa: E402
-from vkrt_b200.raytracer import Raytracer  # noqa: E402
+from vkrt_b200.raytracer import Rasterizer, Raytracer  # noqa: E402
 
 
 def main():
@@ -50,6 +50,23 @@ def main():
             print(f"multigpu_check {w}x{h} spp={spp} ranks={world}: gathered == presented == single-GPU: {same}", flush=True)
             ok = ok and same
         dist.barrier()
+    # the second renderer over the same tile split and gather
+    ids = [B.Context.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    w, h = 1000, 600
+    rz = Rasterizer(model, w, h, device=local, rank=rank, world_size=world, unique_id=ids[0], textures_from_root=0)
+    rz.render()
+    rz.ctx.synchronize()
+    got = rz.readback(B.AOV_BGRA8) if rank == 0 else None
+    rz.close()
+    if rank == 0:
+        single = Rasterizer(model, w, h, device=local)
+        single.render()
+        same = np.array_equal(got, single.readback(B.AOV_BGRA8))
+        single.close()
+        print(f"multigpu_check rasteriser {w}x{h} ranks={world}: gathered == single-GPU: {same}", flush=True)
+        ok = ok and same
+    dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
