@@ -736,6 +736,7 @@ int vkrt_textures_set(VkrtContext* c, const VkrtImage* images, uint32_t count)
     ctx->textureCount = count;
     ctx->textureHost = recs;
     ctx->materialsDirty = true; // texture indices of the material rows are checked against the new image count
+    ctx->textureGeneration += 1;
     return VKRT_SUCCESS;
 }
 

@@ -270,6 +270,7 @@ int broadcastTextures(Context* ctx, int root)
         ctx->mipsHost.clear();
         ctx->mipsReady = false;
         ctx->materialsDirty = true;
+        ctx->textureGeneration += 1;
     }
     else
     {

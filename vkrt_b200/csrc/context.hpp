@@ -72,9 +72,12 @@ struct RasterBuffers
     DeviceBuffer smallList, largeList, largeTiles; // u32[triangles] each
     DeviceBuffer sortKeys, sortKeysB, sortValsB, sortState; // front-to-back order of the large triangles
     DeviceBuffer counters;                        // u32[16]
+    DeviceBuffer tileZ;                           // u32 per 16x16 tile: hierarchical-Z bound (raster.cu)
+    DeviceBuffer minAlpha;                        // u32 per image: smallest alpha byte
+    uint64_t minAlphaGeneration = ~0ull;          // Context::textureGeneration the table was computed for
     void release()
     {
-        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &sortKeys, &sortKeysB, &sortValsB, &sortState, &counters};
+        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &sortKeys, &sortKeysB, &sortValsB, &sortState, &counters, &tileZ, &minAlpha};
         for (DeviceBuffer* b : all)
         {
             b->release();
@@ -104,6 +107,7 @@ struct Context : VkrtContext
     DeviceBuffer textureRecords; // TextureRecord[]
     std::vector<void*> textureAllocs;
     uint32_t textureCount = 0;
+    uint64_t textureGeneration = 0; // bumped whenever the texel pool changes (vkrt_textures_set / _broadcast)
     std::vector<TextureRecord> textureHost; // host copy of the records (device pointers), for vkrt_texture_info / _read
     DeviceBuffer textureMips;               // TextureMips[], parallel to textureRecords (vkrt_textures_generate_mips)
     std::vector<TextureMips> mipsHost;

@@ -36,6 +36,13 @@ struct RasterDev
     uint32_t width, height;
     // multi-GPU: this rank draws the pixels of the 64x64 image tiles it owns (tile % size == rank), like vkrt_trace
     uint32_t tilesX, rank, size, ownedTiles;
+    // hierarchical Z: per 16x16 tile the smallest "every sample of this tile is at most this deep" bound published so far by
+    // an opaque triangle that covers the whole tile; a triangle whose nearest depth in the tile lies behind it is skipped
+    // without touching the keys.  Keys only ever decrease and the final key is a minimum, so skipping a certain loser is
+    // independent of what has been written when.
+    uint32_t* tileZ;
+    uint32_t tilesX16, tilesY16;
+    const uint32_t* minAlpha; // per image: smallest alpha byte (an occluder must not discard, shader.frag:19)
 };
 
 __device__ __forceinline__ bool ownsPixel(const RasterDev& r, uint32_t x, uint32_t y)
@@ -81,9 +88,33 @@ __global__ void __launch_bounds__(256) k_raster_clear(ulonglong2* __restrict__ k
             }
         }
     }
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < r.tilesX16 * r.tilesY16; i += gridDim.x * blockDim.x)
+    {
+        r.tileZ[i] = 0xFFFFFFFFu;
+    }
     if (blockIdx.x == 0 && threadIdx.x < 4)
     {
         counters[threadIdx.x] = 0u; // [0] small triangles, [1] large triangles, [2] large work items
+    }
+}
+
+// smallest alpha byte of every image (level 0; the mip levels are rounded averages of it, so they stay within 1 of it)
+__global__ void __launch_bounds__(256) k_texture_min_alpha(const TextureRecord* __restrict__ textures, uint32_t* __restrict__ minAlpha)
+{
+    const TextureRecord t = textures[blockIdx.y];
+    const uint32_t n = t.width * t.height;
+    uint32_t m = 255u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        m = min(m, (uint32_t)t.texels[4 * (size_t)i + 3]);
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicMin(&minAlpha[blockIdx.y], m);
     }
 }
 
@@ -257,6 +288,25 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, c
         const uint32_t tri = smallList[w];
         const RasterSetup s = loadSetup(r.setups, tri);
         const uint32_t x0 = s.bboxX & 0xFFFFu, x1 = s.bboxX >> 16, y0 = s.bboxY & 0xFFFFu, y1 = s.bboxY >> 16;
+        {
+            // hierarchical Z: hidden when, in every 16x16 tile the bounding box touches (at most 3 x 3), the triangle's nearest
+            // depth lies behind the tile's published bound (the large triangles have been drawn before this kernel)
+            uint32_t zmin24, zmax24;
+            if (rasterDepthRange(s, x0, y0, x1, y1, zmin24, zmax24))
+            {
+                const uint32_t tx0 = x0 / kRasterTile, tx1 = x1 / kRasterTile, ty0 = y0 / kRasterTile, ty1 = y1 / kRasterTile;
+                const uint32_t tw = tx1 - tx0 + 1u, tn = tw * (ty1 - ty0 + 1u);
+                bool visible = false;
+                for (uint32_t k = lane; k < tn; k += 32u)
+                {
+                    visible = visible || !(zmin24 > r.tileZ[(ty0 + k / tw) * r.tilesX16 + tx0 + k % tw]);
+                }
+                if (!__any_sync(0xFFFFFFFFu, visible))
+                {
+                    continue;
+                }
+            }
+        }
         const uint32_t bw = x1 - x0 + 1u, n = bw * (y1 - y0 + 1u);
         for (uint32_t i = lane; i < n; i += 32u)
         {
@@ -278,20 +328,29 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
     const uint32_t triCount = counters[1], items = counters[2];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < items; w += warpsTotal)
+    // a warp takes runs of kRun consecutive work items: one binary search per run, then a walk along the scanned counts
+    // (consecutive items are neighbouring tiles of the same triangle; the search was 13 % of this kernel's stall samples)
+    constexpr uint32_t kRun = 8;
+    for (uint32_t base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * kRun; base < items; base += warpsTotal * kRun)
     {
-        uint32_t lo = 0, hi = triCount; // largeBase[lo] <= w < largeBase[hi]
-        while (hi - lo > 1u)
+      uint32_t lo = 0, hi = triCount; // largeBase[lo] <= base < largeBase[hi]
+      while (hi - lo > 1u)
+      {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (largeBase[mid] <= base)
+          {
+              lo = mid;
+          }
+          else
+          {
+              hi = mid;
+          }
+      }
+      for (uint32_t w = base; w < min(base + kRun, items); ++w)
+      {
+        while (lo + 1u < triCount && largeBase[lo + 1u] <= w)
         {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (largeBase[mid] <= w)
-            {
-                lo = mid;
-            }
-            else
-            {
-                hi = mid;
-            }
+            ++lo;
         }
         const uint32_t tri = largeList[lo];
         const RasterSetup s = loadSetup(r.setups, tri);
@@ -305,11 +364,34 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
         {
             continue;
         }
+        {
+            // hierarchical Z (see RasterDev::tileZ): skip when certainly hidden; publish a bound when this triangle is opaque
+            // and covers every sample of the whole tile
+            uint32_t* tz = r.tileZ + ty * r.tilesX16 + tx;
+            uint32_t zmin24, zmax24;
+            if (rasterDepthRange(s, px0, py0, px1, py1, zmin24, zmax24))
+            {
+                if (zmin24 > *reinterpret_cast<volatile uint32_t*>(tz))
+                {
+                    continue;
+                }
+                const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
+                if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
+                    r.minAlpha[s.texture] >= 28u && rasterTileInside(s, px0, py0, px1, py1))
+                {
+                    if (lane == 0)
+                    {
+                        atomicMin(tz, zmax24);
+                    }
+                }
+            }
+        }
         const uint32_t bw = px1 - px0 + 1u, n = bw * (py1 - py0 + 1u);
         for (uint32_t i = lane; i < n; i += 32u)
         {
             rasterPixel(s, tri, r.textures, r.mips, r.width, px0 + i % bw, py0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
         }
+      }
     }
 }
 
@@ -387,6 +469,9 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     VKRT_CUDA_TRY(ctx, b.largeList.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.largeTiles.reserve(std::max<size_t>(n, 1) * 4));
     VKRT_CUDA_TRY(ctx, b.counters.reserve(64));
+    const uint32_t tilesX16 = (W + kRasterTile - 1u) / kRasterTile, tilesY16 = (H + kRasterTile - 1u) / kRasterTile;
+    VKRT_CUDA_TRY(ctx, b.tileZ.reserve((size_t)tilesX16 * tilesY16 * 4));
+    VKRT_CUDA_TRY(ctx, b.minAlpha.reserve((size_t)ctx->textureCount * 4));
     // Optional (VKRT_RASTER_SORT=1): large triangles rasterised nearest first, so that later ones are mostly rejected by
     // the keys already in place.  The image does not depend on the order.  Measured on B200, Sponza stand-in at 4K:
     // 4.90 ms sorted against 4.68 ms unsorted - the kernel is bound by latency at low occupancy, not by its atomics -
@@ -421,6 +506,15 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     r.visibility = frame->visibility.as<unsigned long long>();
     r.width = W, r.height = H;
     r.tilesX = frame->tilesX, r.rank = (uint32_t)frame->rank, r.size = (uint32_t)frame->size, r.ownedTiles = frame->ownedTiles;
+    r.tileZ = b.tileZ.as<uint32_t>(), r.tilesX16 = tilesX16, r.tilesY16 = tilesY16;
+    r.minAlpha = b.minAlpha.as<uint32_t>();
+    if (b.minAlphaGeneration != ctx->textureGeneration)
+    {
+        VKRT_CUDA_TRY(ctx, cudaMemsetAsync(b.minAlpha.ptr, 0xFF, (size_t)ctx->textureCount * 4, s));
+        k_texture_min_alpha<<<dim3(32, ctx->textureCount), 256, 0, s>>>(r.textures, b.minAlpha.as<uint32_t>());
+        ctx->launches += 1;
+        b.minAlphaGeneration = ctx->textureGeneration;
+    }
 
     k_raster_clear<<<grid, 256, 0, s>>>(frame->visibility.as<ulonglong2>(), samples / 2, counters, r);
     if (n > 0)
@@ -446,14 +540,15 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         if (minBlocks >= 4)
         {
             const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
-            k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
+            // large triangles first: they publish the hierarchical-Z bounds that the small ones are tested against
             k_raster_large<4><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
         else
         {
             const uint32_t g3 = (uint32_t)ctx->smCount * 3u;
-            k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
             k_raster_large<3><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
         ctx->launches += 4;
     }

@@ -246,6 +246,44 @@ VKRT_HD bool rasterTileOutside(const RasterSetup& s, uint32_t tx0, uint32_t ty0,
     return false;
 }
 
+// Conservative 24-bit depth range of a triangle over the pixel rectangle [x0, x1] x [y0, y1] (inclusive; all sample
+// positions of those pixels): the depth plane is linear, so its extremes are at the corners; the pad covers the rounding
+// of the plane evaluation and of the quantisation.  Returns false when the plane leaves [0, 1] there (clipped samples).
+VKRT_HD bool rasterDepthRange(const RasterSetup& t, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t& zmin24, uint32_t& zmax24)
+{
+    const float lx = (float)x0, hx = (float)(x1 + 1u), ly = (float)y0, hy = (float)(y1 + 1u);
+    const float z00 = plane3(t.za, t.zb, t.zc, lx, ly), z10 = plane3(t.za, t.zb, t.zc, hx, ly);
+    const float z01 = plane3(t.za, t.zb, t.zc, lx, hy), z11 = plane3(t.za, t.zb, t.zc, hx, hy);
+    const float pad = (fabsf(t.za) * hx + fabsf(t.zb) * hy + fabsf(t.zc)) * 4e-7f + 1e-7f;
+    const float lo = fminf(fminf(z00, z10), fminf(z01, z11)) - pad, hi = fmaxf(fmaxf(z00, z10), fmaxf(z01, z11)) + pad;
+    if (!(lo >= 0.0f && hi <= 1.0f)) // also false for NaN
+    {
+        return false;
+    }
+    zmin24 = (uint32_t)(lo * 16777215.0f + 0.5f);
+    zmax24 = (uint32_t)(hi * 16777215.0f + 0.5f);
+    zmin24 = zmin24 > 0u ? zmin24 - 1u : 0u;
+    zmax24 += 1u;
+    return true;
+}
+
+// true when every sample of the pixel rectangle lies strictly inside all three edges (no tie rule involved)
+VKRT_HD bool rasterTileInside(const RasterSetup& s, uint32_t tx0, uint32_t ty0, uint32_t tx1, uint32_t ty1)
+{
+    const float lx = (float)tx0, hx = (float)(tx1 + 1u), ly = (float)ty0, hy = (float)(ty1 + 1u);
+    for (int i = 0; i < 3; ++i)
+    {
+        const float a = s.ea[i], b = s.eb[i], c = s.ec[i];
+        const float worst = (a * (a > 0.0f ? lx : hx) + b * (b > 0.0f ? ly : hy)) + c;
+        const float pad = (fabsf(a) * hx + fabsf(b) * hy + fabsf(c)) * 1e-5f;
+        if (!(worst > pad))
+        {
+            return false;
+        }
+    }
+    return true;
+}
+
 // Resolve of pixel (px, py): every sample takes the colour of the triangle that won it (shaded at the pixel centre,
 // quantised to UNORM8 as the multisampled colour attachment stores it) or the clear colour; the 8 samples are averaged
 // (vkCmdResolveImage / resolve attachment) and stored as B8G8R8A8.  Returns B | G<<8 | R<<16 | A<<24.
