@@ -319,7 +319,9 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, c
     }
 }
 
-template<int MIN_BLOCKS>
+// OCCLUDERS: the same walk over (large triangle, tile) items, but only the hierarchical-Z bounds are published - no pixel
+// is touched.  Run before the drawing pass, it makes the culling independent of the order in which items are drawn.
+template<int MIN_BLOCKS, bool OCCLUDERS>
 __global__ void __launch_bounds__(256, MIN_BLOCKS)
 k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32_t* __restrict__ largeBase, const uint32_t* __restrict__ counters)
 {
@@ -375,15 +377,22 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
                 {
                     continue;
                 }
-                const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
-                if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
-                    r.minAlpha[s.texture] >= 28u && rasterTileInside(s, px0, py0, px1, py1))
+                if (OCCLUDERS)
                 {
-                    if (lane == 0)
+                    const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
+                    if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
+                        r.minAlpha[s.texture] >= 28u && rasterTileInside(s, px0, py0, px1, py1))
                     {
-                        atomicMin(tz, zmax24);
+                        if (lane == 0)
+                        {
+                            atomicMin(tz, zmax24);
+                        }
                     }
                 }
+            }
+            if (OCCLUDERS)
+            {
+                continue;
             }
         }
         const uint32_t bw = px1 - px0 + 1u, n = bw * (py1 - py0 + 1u);
@@ -541,16 +550,18 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         {
             const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
             // large triangles first: they publish the hierarchical-Z bounds that the small ones are tested against
-            k_raster_large<4><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_large<4, true><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_large<4, false><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
         else
         {
             const uint32_t g3 = (uint32_t)ctx->smCount * 3u;
-            k_raster_large<3><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_large<3, true><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_large<3, false><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
-        ctx->launches += 4;
+        ctx->launches += 5;
     }
     if (int e = joinGather(ctx, frame))
     {
