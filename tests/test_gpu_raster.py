@@ -119,3 +119,33 @@ def test_raster_tile_partition_emulated_ranks():
         acc_tri[owner == r] = tri[owner == r]
         rz.close()
     assert np.array_equal(acc_img, ref_img) and np.array_equal(acc_tri, ref_tri)
+
+
+def test_raster_work_list_overflow_falls_back():
+    """The binned large-triangle path keeps an explicit (triangle, tile) list of fixed capacity; a frame that overflows it is
+    drawn by the implicit path instead.  VKRT_RASTER_ITEMS=64 forces that (read once per process, hence the subprocess):
+    same image, same triangle ids."""
+    import os
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "from vkrt_b200 import binding as B, scenes\n"
+        "from vkrt_b200.raytracer import Rasterizer\n"
+        "rz = Rasterizer(scenes.sponza_standin(max_texture_size=128), 640, 360)\n"
+        "rz.render()\n"
+        "img, tri = rz.readback(B.AOV_BGRA8), rz.readback(B.AOV_TRIANGLE_ID)\n"
+        "print(int(rz.ctx.lib.vkrt_hash_fnv1a64(img.ctypes.data, img.nbytes)), int(rz.ctx.lib.vkrt_hash_fnv1a64(tri.ctypes.data, tri.nbytes)))\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for cap in (None, "64"):
+        env = dict(os.environ)
+        env.pop("VKRT_RASTER_ITEMS", None)
+        if cap:
+            env["VKRT_RASTER_ITEMS"] = cap
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines()[-1])
+    assert outs[0] == outs[1], outs

@@ -74,10 +74,11 @@ struct RasterBuffers
     DeviceBuffer counters;                        // u32[16]
     DeviceBuffer tileZ;                           // u32 per 16x16 tile: hierarchical-Z bound (raster.cu)
     DeviceBuffer minAlpha;                        // u32 per image: smallest alpha byte
+    DeviceBuffer items;                           // uint2 (triangle, tile) work list of the binned large-triangle path
     uint64_t minAlphaGeneration = ~0ull;          // Context::textureGeneration the table was computed for
     void release()
     {
-        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &sortKeys, &sortKeysB, &sortValsB, &sortState, &counters, &tileZ, &minAlpha};
+        DeviceBuffer* all[] = {&setups, &smallList, &largeList, &largeTiles, &sortKeys, &sortKeysB, &sortValsB, &sortState, &counters, &tileZ, &minAlpha, &items};
         for (DeviceBuffer* b : all)
         {
             b->release();

@@ -26,6 +26,7 @@ namespace vkrt
 namespace
 {
 constexpr uint32_t kSmallExtent = 32; // bounding boxes up to 32x32 pixels are walked by one warp
+constexpr uint32_t kRasterItemCapacity = 4u << 20; // explicit (triangle, tile) work list of the binned large-triangle path, 8 bytes each
 
 struct RasterDev
 {
@@ -43,6 +44,7 @@ struct RasterDev
     uint32_t* tileZ;
     uint32_t tilesX16, tilesY16;
     const uint32_t* minAlpha; // per image: smallest alpha byte (an occluder must not discard, shader.frag:19)
+    uint32_t itemCapacity;    // entries of the explicit work list (kRasterItemCapacity; VKRT_RASTER_ITEMS overrides it for tests)
 };
 
 __device__ __forceinline__ bool ownsPixel(const RasterDev& r, uint32_t x, uint32_t y)
@@ -319,12 +321,16 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_raster_small(RasterDev r, c
     }
 }
 
-// OCCLUDERS: the same walk over (large triangle, tile) items, but only the hierarchical-Z bounds are published - no pixel
-// is touched.  Run before the drawing pass, it makes the culling independent of the order in which items are drawn.
-template<int MIN_BLOCKS, bool OCCLUDERS>
+// Implicit form: warp per bounding-box tile, found by binary search in the scanned tile counts.  Draws the frame only when
+// the explicit work list of the binned form overflowed.
+template<int MIN_BLOCKS>
 __global__ void __launch_bounds__(256, MIN_BLOCKS)
 k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32_t* __restrict__ largeBase, const uint32_t* __restrict__ counters)
 {
+    if (counters[3] <= r.itemCapacity)
+    {
+        return;
+    }
     __shared__ float unorm[256];
     fillUnormTable(unorm);
     const uint32_t triCount = counters[1], items = counters[2];
@@ -377,22 +383,6 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
                 {
                     continue;
                 }
-                if (OCCLUDERS)
-                {
-                    const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
-                    if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
-                        r.minAlpha[s.texture] >= 28u && rasterTileInside(s, px0, py0, px1, py1))
-                    {
-                        if (lane == 0)
-                        {
-                            atomicMin(tz, zmax24);
-                        }
-                    }
-                }
-            }
-            if (OCCLUDERS)
-            {
-                continue;
             }
         }
         const uint32_t bw = px1 - px0 + 1u, n = bw * (py1 - py0 + 1u);
@@ -401,6 +391,118 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
             rasterPixel(s, tri, r.textures, r.mips, r.width, px0 + i % bw, py0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
         }
       }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Large triangles, binned form (default).  Three launches over the large-triangle list:
+//   k_raster_tiles<true>   warp per triangle, LANES over the 16x16 tiles of its bounding box: opaque triangles that cover a
+//                          whole tile publish the hierarchical-Z bound (nothing else is touched);
+//   k_raster_tiles<false>  same walk: every tile that is owned, not outside an edge and not behind its tile's bound is
+//                          appended to an explicit work list (warp-aggregated append);
+//   k_raster_items         warp per listed (triangle, tile): lanes over the tile's pixels.
+// Against the implicit form (k_raster_large: warp per bounding-box tile, found by binary search) no warp is spent on a
+// tile that is rejected, and the bounds are complete before anything is drawn.  The list has a fixed capacity; a frame
+// that would overflow it (counters[3] > capacity) is drawn by k_raster_large instead - both draw kernels are launched,
+// one of them returns at once.
+// ------------------------------------------------------------------------------------------------------------
+
+template<bool PUBLISH>
+__global__ void __launch_bounds__(256)
+k_raster_tiles(RasterDev r, const uint32_t* __restrict__ largeList, uint32_t* __restrict__ counters, uint2* __restrict__ items)
+{
+    const uint32_t triCount = counters[1];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < triCount; i += warpsTotal)
+    {
+        const uint32_t tri = largeList[i];
+        const RasterSetup s = loadSetup(r.setups, tri);
+        const uint32_t x0 = s.bboxX & 0xFFFFu, x1 = s.bboxX >> 16, y0 = s.bboxY & 0xFFFFu, y1 = s.bboxY >> 16;
+        const uint32_t tx0 = x0 / kRasterTile, ty0 = y0 / kRasterTile;
+        const uint32_t tw = x1 / kRasterTile - tx0 + 1u, tn = tw * (y1 / kRasterTile - ty0 + 1u);
+        const bool opaque = PUBLISH && r.minAlpha[s.texture] >= 28u;
+        if (PUBLISH && !opaque)
+        {
+            continue;
+        }
+        for (uint32_t base = 0; base < tn; base += 32u)
+        {
+            const uint32_t local = base + lane;
+            bool keep = local < tn;
+            uint32_t tx = 0, ty = 0;
+            if (keep)
+            {
+                tx = tx0 + local % tw, ty = ty0 + local / tw;
+                const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
+                const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
+                keep = ownsPixel(r, px0, py0) && !rasterTileOutside(s, px0, py0, px1, py1);
+                uint32_t zmin24, zmax24;
+                if (keep && rasterDepthRange(s, px0, py0, px1, py1, zmin24, zmax24))
+                {
+                    uint32_t* tz = r.tileZ + ty * r.tilesX16 + tx;
+                    if (PUBLISH)
+                    {
+                        const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
+                        if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
+                            rasterTileInside(s, px0, py0, px1, py1))
+                        {
+                            atomicMin(tz, zmax24);
+                        }
+                    }
+                    else
+                    {
+                        keep = !(zmin24 > *tz);
+                    }
+                }
+            }
+            if (!PUBLISH)
+            {
+                const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
+                if (ballot)
+                {
+                    uint32_t slot = 0;
+                    if (lane == 0)
+                    {
+                        slot = atomicAdd(&counters[3], (uint32_t)__popc(ballot));
+                    }
+                    slot = __shfl_sync(0xFFFFFFFFu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
+                    if (keep && slot < r.itemCapacity)
+                    {
+                        items[slot] = make_uint2(tri, tx | (ty << 16));
+                    }
+                }
+            }
+        }
+    }
+}
+
+template<int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS)
+k_raster_items(RasterDev r, const uint2* __restrict__ items, const uint32_t* __restrict__ counters)
+{
+    __shared__ float unorm[256];
+    fillUnormTable(unorm);
+    const uint32_t count = counters[3];
+    if (count > r.itemCapacity)
+    {
+        return; // the work list overflowed: k_raster_large draws this frame
+    }
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < count; w += warpsTotal)
+    {
+        const uint2 item = __ldg(items + w);
+        const uint32_t tri = item.x, tx = item.y & 0xFFFFu, ty = item.y >> 16;
+        const RasterSetup s = loadSetup(r.setups, tri);
+        const uint32_t x0 = s.bboxX & 0xFFFFu, x1 = s.bboxX >> 16, y0 = s.bboxY & 0xFFFFu, y1 = s.bboxY >> 16;
+        const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
+        const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
+        const uint32_t bw = px1 - px0 + 1u, n = bw * (py1 - py0 + 1u);
+        for (uint32_t i = lane; i < n; i += 32u)
+        {
+            rasterPixel(s, tri, r.textures, r.mips, r.width, px0 + i % bw, py0 + i / bw, reinterpret_cast<uint64_t*>(r.visibility), AtomicMinKey(), unorm);
+        }
     }
 }
 
@@ -481,6 +583,7 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     const uint32_t tilesX16 = (W + kRasterTile - 1u) / kRasterTile, tilesY16 = (H + kRasterTile - 1u) / kRasterTile;
     VKRT_CUDA_TRY(ctx, b.tileZ.reserve((size_t)tilesX16 * tilesY16 * 4));
     VKRT_CUDA_TRY(ctx, b.minAlpha.reserve((size_t)ctx->textureCount * 4));
+    VKRT_CUDA_TRY(ctx, b.items.reserve((size_t)kRasterItemCapacity * sizeof(uint2)));
     // Optional (VKRT_RASTER_SORT=1): large triangles rasterised nearest first, so that later ones are mostly rejected by
     // the keys already in place.  The image does not depend on the order.  Measured on B200, Sponza stand-in at 4K:
     // 4.90 ms sorted against 4.68 ms unsorted - the kernel is bound by latency at low occupancy, not by its atomics -
@@ -517,6 +620,8 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
     r.tilesX = frame->tilesX, r.rank = (uint32_t)frame->rank, r.size = (uint32_t)frame->size, r.ownedTiles = frame->ownedTiles;
     r.tileZ = b.tileZ.as<uint32_t>(), r.tilesX16 = tilesX16, r.tilesY16 = tilesY16;
     r.minAlpha = b.minAlpha.as<uint32_t>();
+    static const uint32_t itemCapacity = getenv("VKRT_RASTER_ITEMS") ? (uint32_t)std::min<long>(std::max<long>(atol(getenv("VKRT_RASTER_ITEMS")), 1), (long)kRasterItemCapacity) : kRasterItemCapacity;
+    r.itemCapacity = itemCapacity;
     if (b.minAlphaGeneration != ctx->textureGeneration)
     {
         VKRT_CUDA_TRY(ctx, cudaMemsetAsync(b.minAlpha.ptr, 0xFF, (size_t)ctx->textureCount * 4, s));
@@ -550,18 +655,22 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         {
             const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
             // large triangles first: they publish the hierarchical-Z bounds that the small ones are tested against
-            k_raster_large<4, true><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
-            k_raster_large<4, false><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_tiles<true><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<false><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_items<4><<<g4, 256, 0, s>>>(r, b.items.as<uint2>(), counters);
+            k_raster_large<4><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
         else
         {
             const uint32_t g3 = (uint32_t)ctx->smCount * 3u;
-            k_raster_large<3, true><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
-            k_raster_large<3, false><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
+            k_raster_tiles<true><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<false><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_items<3><<<g3, 256, 0, s>>>(r, b.items.as<uint2>(), counters);
+            k_raster_large<3><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
         }
-        ctx->launches += 5;
+        ctx->launches += 7;
     }
     if (int e = joinGather(ctx, frame))
     {
