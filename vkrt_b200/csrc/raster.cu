@@ -396,8 +396,8 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
 
 // ------------------------------------------------------------------------------------------------------------
 // Large triangles, binned form (default).  Three launches over the large-triangle list:
-//   k_raster_tiles<true>   warp per triangle, LANES over the 16x16 tiles of its bounding box: opaque triangles that cover a
-//                          whole tile publish the hierarchical-Z bound (nothing else is touched);
+//   k_raster_tiles<true>   lanes over the (triangle, 16x16 bounding-box tile) pairs: opaque triangles that cover a whole
+//                          tile publish the hierarchical-Z bound (nothing else is touched);
 //   k_raster_tiles<false>  same walk: every tile that is owned, not outside an edge and not behind its tile's bound is
 //                          appended to an explicit work list (warp-aggregated append);
 //   k_raster_items         warp per listed (triangle, tile): lanes over the tile's pixels.
@@ -409,68 +409,81 @@ k_raster_large(RasterDev r, const uint32_t* __restrict__ largeList, const uint32
 
 template<bool PUBLISH>
 __global__ void __launch_bounds__(256)
-k_raster_tiles(RasterDev r, const uint32_t* __restrict__ largeList, uint32_t* __restrict__ counters, uint2* __restrict__ items)
+k_raster_tiles(RasterDev r, const uint32_t* __restrict__ largeList, const uint32_t* __restrict__ largeBase, uint32_t* __restrict__ counters,
+               uint2* __restrict__ items)
 {
-    const uint32_t triCount = counters[1];
+    // LANES over the implicit (triangle, bounding-box tile) pairs, 32 consecutive ones per warp iteration: balanced whatever
+    // the sizes of the triangles (a warp per triangle left the few screen-filling ones to single warps: 230 us per pass).
+    // One binary search in the scanned tile counts per warp iteration; each lane then walks forward to its own triangle.
+    const uint32_t triCount = counters[1], pairs = counters[2];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < triCount; i += warpsTotal)
+    for (uint32_t base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u; base < pairs; base += warpsTotal * 32u)
     {
-        const uint32_t tri = largeList[i];
-        const RasterSetup s = loadSetup(r.setups, tri);
-        const uint32_t x0 = s.bboxX & 0xFFFFu, x1 = s.bboxX >> 16, y0 = s.bboxY & 0xFFFFu, y1 = s.bboxY >> 16;
-        const uint32_t tx0 = x0 / kRasterTile, ty0 = y0 / kRasterTile;
-        const uint32_t tw = x1 / kRasterTile - tx0 + 1u, tn = tw * (y1 / kRasterTile - ty0 + 1u);
-        const bool opaque = PUBLISH && r.minAlpha[s.texture] >= 28u;
-        if (PUBLISH && !opaque)
+        uint32_t lo = 0, hi = triCount; // largeBase[lo] <= base < largeBase[hi]
+        while (hi - lo > 1u)
         {
-            continue;
-        }
-        for (uint32_t base = 0; base < tn; base += 32u)
-        {
-            const uint32_t local = base + lane;
-            bool keep = local < tn;
-            uint32_t tx = 0, ty = 0;
-            if (keep)
+            const uint32_t mid = (lo + hi) >> 1;
+            if (largeBase[mid] <= base)
             {
-                tx = tx0 + local % tw, ty = ty0 + local / tw;
-                const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
-                const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
-                keep = ownsPixel(r, px0, py0) && !rasterTileOutside(s, px0, py0, px1, py1);
-                uint32_t zmin24, zmax24;
-                if (keep && rasterDepthRange(s, px0, py0, px1, py1, zmin24, zmax24))
+                lo = mid;
+            }
+            else
+            {
+                hi = mid;
+            }
+        }
+        const uint32_t w = base + lane;
+        bool keep = w < pairs;
+        uint32_t tri = 0, tx = 0, ty = 0;
+        if (keep)
+        {
+            while (lo + 1u < triCount && largeBase[lo + 1u] <= w)
+            {
+                ++lo;
+            }
+            tri = largeList[lo];
+            const RasterSetup s = loadSetup(r.setups, tri);
+            const uint32_t x0 = s.bboxX & 0xFFFFu, x1 = s.bboxX >> 16, y0 = s.bboxY & 0xFFFFu, y1 = s.bboxY >> 16;
+            const uint32_t tw = x1 / kRasterTile - x0 / kRasterTile + 1u;
+            const uint32_t local = w - largeBase[lo];
+            tx = x0 / kRasterTile + local % tw, ty = y0 / kRasterTile + local / tw;
+            const uint32_t px0 = max(tx * kRasterTile, x0), px1 = min(tx * kRasterTile + kRasterTile - 1u, x1);
+            const uint32_t py0 = max(ty * kRasterTile, y0), py1 = min(ty * kRasterTile + kRasterTile - 1u, y1);
+            keep = ownsPixel(r, px0, py0) && !rasterTileOutside(s, px0, py0, px1, py1);
+            uint32_t zmin24, zmax24;
+            if (keep && rasterDepthRange(s, px0, py0, px1, py1, zmin24, zmax24))
+            {
+                uint32_t* tz = r.tileZ + ty * r.tilesX16 + tx;
+                if (PUBLISH)
                 {
-                    uint32_t* tz = r.tileZ + ty * r.tilesX16 + tx;
-                    if (PUBLISH)
+                    const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
+                    if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
+                        r.minAlpha[s.texture] >= 28u && rasterTileInside(s, px0, py0, px1, py1))
                     {
-                        const uint32_t fx1 = min(tx * kRasterTile + kRasterTile - 1u, r.width - 1u), fy1 = min(ty * kRasterTile + kRasterTile - 1u, r.height - 1u);
-                        if (px0 == tx * kRasterTile && py0 == ty * kRasterTile && px1 == fx1 && py1 == fy1 && zmax24 < 0xFFFFFFu &&
-                            rasterTileInside(s, px0, py0, px1, py1))
-                        {
-                            atomicMin(tz, zmax24);
-                        }
-                    }
-                    else
-                    {
-                        keep = !(zmin24 > *tz);
+                        atomicMin(tz, zmax24);
                     }
                 }
-            }
-            if (!PUBLISH)
-            {
-                const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
-                if (ballot)
+                else
                 {
-                    uint32_t slot = 0;
-                    if (lane == 0)
-                    {
-                        slot = atomicAdd(&counters[3], (uint32_t)__popc(ballot));
-                    }
-                    slot = __shfl_sync(0xFFFFFFFFu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
-                    if (keep && slot < r.itemCapacity)
-                    {
-                        items[slot] = make_uint2(tri, tx | (ty << 16));
-                    }
+                    keep = !(zmin24 > *tz);
+                }
+            }
+        }
+        if (!PUBLISH)
+        {
+            const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
+            if (ballot)
+            {
+                uint32_t slot = 0;
+                if (lane == 0)
+                {
+                    slot = atomicAdd(&counters[3], (uint32_t)__popc(ballot));
+                }
+                slot = __shfl_sync(0xFFFFFFFFu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
+                if (keep && slot < r.itemCapacity)
+                {
+                    items[slot] = make_uint2(tri, tx | (ty << 16));
                 }
             }
         }
@@ -655,8 +668,8 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         {
             const uint32_t g4 = (uint32_t)ctx->smCount * 4u;
             // large triangles first: they publish the hierarchical-Z bounds that the small ones are tested against
-            k_raster_tiles<true><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
-            k_raster_tiles<false><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<true><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<false><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters, b.items.as<uint2>());
             k_raster_items<4><<<g4, 256, 0, s>>>(r, b.items.as<uint2>(), counters);
             k_raster_large<4><<<g4, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<4><<<g4, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
@@ -664,8 +677,8 @@ int rasterizeFrame(Context* ctx, const Blas* blas, const float* wvp, uint32_t fl
         else
         {
             const uint32_t g3 = (uint32_t)ctx->smCount * 3u;
-            k_raster_tiles<true><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
-            k_raster_tiles<false><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<true><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters, b.items.as<uint2>());
+            k_raster_tiles<false><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters, b.items.as<uint2>());
             k_raster_items<3><<<g3, 256, 0, s>>>(r, b.items.as<uint2>(), counters);
             k_raster_large<3><<<g3, 256, 0, s>>>(r, b.largeList.as<uint32_t>(), b.largeTiles.as<uint32_t>(), counters);
             k_raster_small<3><<<g3, 256, 0, s>>>(r, b.smallList.as<uint32_t>(), counters);
