@@ -160,6 +160,55 @@ def test_config5_ten_million_triangles_fast_build_lane_refill():
     torch.cuda.empty_cache()
 
 
+def test_config5_full_size_fifty_million_triangles_properties():
+    """Config 5 at its STATED size (50 M triangles; the oracle cannot hold that in seconds), through size-independent
+    properties: (1) the closest hits of 200 k rays are identical under two different hierarchies of the same triangles -
+    LBVH + greedy collapse (the per-frame rebuild path, lane refill on) and PLOC + cost-optimal collapse - which the id
+    tie-break makes well defined; (2) any-hit == "closest hit found something" for every ray; (3) a rebuild over the
+    same vertices reproduces the same hits; (4) moved vertices change them."""
+    import torch
+
+    from vkrt_b200.scenes_device import SoupDevice
+
+    n = 50_000_000
+    free, _ = torch.cuda.mem_get_info(0)
+    if free < 70 << 30:
+        pytest.skip("needs ~60 GB of free device memory")
+    soup = SoupDevice(n, 0)
+    inst = scenes.identity_instance(1.0)
+    ctx = B.Context(0)
+    ctx.set_lane_refill(20)
+    verts = soup.set_frame(0)
+    blas = B.Blas(ctx, verts, soup.indices, soup.ranges(), flags=B.BUILD_PREFER_FAST_BUILD)
+    assert blas.info().triangleCount == n
+    rays = H.random_rays(200000, 23, (-20, 0, -12), (20, 15, 12))
+    rays["tmax"][::3] = 1.5
+    tl = B.Tlas(ctx, [blas], inst)
+    h_lbvh = tl.trace_rays(rays)
+    a_lbvh = tl.trace_rays(rays, any_hit=True)
+    assert np.array_equal(h_lbvh["instance"] != 0xFFFFFFFF, a_lbvh["instance"] != 0xFFFFFFFF)
+    assert 0.2 < (h_lbvh["instance"] != 0xFFFFFFFF).mean() < 1.0
+    tl.close()
+    blas.rebuild(verts, B.BUILD_PREFER_FAST_BUILD)
+    tl = B.Tlas(ctx, [blas], inst)
+    assert np.array_equal(tl.trace_rays(rays), h_lbvh)
+    tl.close()
+    ctx.set_lane_refill(0)
+    blas.rebuild(verts, B.BUILD_DEFAULT)  # PLOC + cost-optimal collapse: another tree over the same triangles
+    assert blas.info().nodeCount != 0
+    tl = B.Tlas(ctx, [blas], inst)
+    h_ploc = tl.trace_rays(rays)
+    assert np.array_equal(h_ploc, h_lbvh)
+    tl.close()
+    moved = soup.set_frame(9)
+    blas.rebuild(moved, B.BUILD_PREFER_FAST_BUILD)
+    tl = B.Tlas(ctx, [blas], inst)
+    assert not np.array_equal(tl.trace_rays(rays), h_lbvh)
+    tl.close(), blas.close(), ctx.close()
+    del soup, verts, moved
+    torch.cuda.empty_cache()
+
+
 def test_multi_gpu_gathered_frame_equals_single_gpu():
     """interleaved tiles over N ranks + NCCL gather + presentation ring == the single-GPU frame, byte for
     byte (tests/multigpu_check.py under torchrun).  Needs at least 2 GPUs on the box."""

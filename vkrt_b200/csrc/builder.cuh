@@ -278,7 +278,9 @@ VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
         {
             return; // first to arrive: the sibling's thread finishes this node
         }
+#if !defined(VKRT_LBVH_ONE_FENCE)
         VKRT_FENCE();
+#endif
         // the sibling's box: its leaf box straight from the triangle boxes (its own copy in sortedBox may not be visible
         // yet), or the finished node's box (written before its fence)
         const volatile BinNode32* pn = b.nodes32 + parent;
