@@ -1,7 +1,7 @@
 #!/bin/bash
 O=gpurun_out; mkdir -p $O
-timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -x -q -k "fifty_million or ten_million" --durations=3 > $O/q_tests.log 2>&1; echo "50M test exit $?"; tail -6 $O/q_tests.log
-for v in main onefence; do
+echo skip
+for v in main onefence acqrel; do
   if [ $v = main ]; then L=$PWD/vkrt_b200/csrc/libvkrt_b200.so; else L=$PWD/vkrt_b200/csrc/libvkrt_b200_$v.so; fi
   VKRT_B200_LIB=$L timeout 300 python tools/build_bench.py --flags 1 --sizes 10000000,50000000 2>&1 | tail -3 | cut -c1-200
   VKRT_B200_LIB=$L timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "builder or rebuild or device_input" 2>&1 | tail -1

@@ -138,6 +138,15 @@ VKRT_HD uint64_t lbvhDelta(const Bvh2& b, uint32_t j) // distance between sorted
 }
 
 #if defined(__CUDA_ARCH__)
+// exchange with release + acquire semantics at device scope: the writes before it are visible to whoever reads the old
+// value, and the reads after it see what the writer of the old value wrote before its own exchange
+__device__ __forceinline__ int atomicExchAcqRel(int* p, int v)
+{
+    int old;
+    asm volatile("atom.acq_rel.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+#define VKRT_ATOMIC_EXCH_ACQ_REL(ptr, v) atomicExchAcqRel((ptr), (v))
 #define VKRT_ATOMIC_EXCH(ptr, v) atomicExch((ptr), (v))
 #define VKRT_ATOMIC_ADD(ptr, v) atomicAdd((ptr), (v))
 #define VKRT_FENCE() __threadfence()
@@ -158,6 +167,7 @@ inline T hostAdd(T* p, T v)
     return o;
 }
 #define VKRT_ATOMIC_EXCH(ptr, v) hostExch((ptr), (v))
+#define VKRT_ATOMIC_EXCH_ACQ_REL(ptr, v) hostExch((ptr), (v))
 #define VKRT_ATOMIC_ADD(ptr, v) hostAdd((ptr), (v))
 #define VKRT_FENCE() ((void)0)
 #define VKRT_LOAD_CG_F4(ptr) (*(ptr))
@@ -255,8 +265,12 @@ VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
             parent = right;
             isLeftChild = true;
             b.nodes32[parent].children.x = current;
+#if defined(VKRT_LBVH_ACQ_REL)
+            prev = VKRT_ATOMIC_EXCH_ACQ_REL(&b.flags[parent], (int)left);
+#else
             VKRT_FENCE();
             prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)left);
+#endif
             if (prev != -1)
             {
                 right = (uint32_t)prev;
@@ -267,8 +281,12 @@ VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
             parent = left - 1;
             isLeftChild = false;
             b.nodes32[parent].children.y = current;
+#if defined(VKRT_LBVH_ACQ_REL)
+            prev = VKRT_ATOMIC_EXCH_ACQ_REL(&b.flags[parent], (int)right);
+#else
             VKRT_FENCE();
             prev = VKRT_ATOMIC_EXCH(&b.flags[parent], (int)right);
+#endif
             if (prev != -1)
             {
                 left = (uint32_t)prev;
@@ -278,7 +296,7 @@ VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
         {
             return; // first to arrive: the sibling's thread finishes this node
         }
-#if !defined(VKRT_LBVH_ONE_FENCE)
+#if !defined(VKRT_LBVH_ONE_FENCE) && !defined(VKRT_LBVH_ACQ_REL)
         VKRT_FENCE();
 #endif
         // the sibling's box: its leaf box straight from the triangle boxes (its own copy in sortedBox may not be visible
