@@ -246,6 +246,12 @@ VKRT_HD void lbvhClimb(const Bvh2& b, uint32_t leaf)
 
 // The same climb over compact nodes.  Leaf boxes are copied into sorted order on the way (one coalesced 32-byte write per
 // leaf), so that the collapse reads a leaf's box with one fetch instead of two dependent ones (vals, then triBox).
+// The hand-off at a node is one exchange with release + acquire semantics (18.48 ms against 19.40 ms with a fence on
+// either side of a relaxed exchange, 50 M triangles, profiles/r02_q_build_fence_ab.txt); -DVKRT_LBVH_TWO_FENCE and
+// -DVKRT_LBVH_ONE_FENCE keep the measured alternatives buildable.
+#if !defined(VKRT_LBVH_TWO_FENCE) && !defined(VKRT_LBVH_ONE_FENCE) && !defined(VKRT_LBVH_ACQ_REL)
+#define VKRT_LBVH_ACQ_REL 1
+#endif
 VKRT_HD void lbvhClimbCompact(const Bvh2& b, uint32_t leaf)
 {
     const uint32_t n = b.count;
