@@ -318,6 +318,22 @@ typedef struct VkrtHit
 VKRT_API int vkrt_trace_rays(VkrtContext* ctx, const VkrtTlas* tlas, const VkrtRay* rays, uint64_t count, int anyHit,
                              VkrtHit* hits);
 
+/* vkrt_trace_rays without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same records and results as vkrt_trace_rays, bit for bit.  The staged rays, the hits, the ray-pool
+ * cursor and the overflow flag live in ONE file-scope device array of the library (about 3.5 MiB: 256 bytes +
+ * VKRT_STATIC_MAX_RAYS x (32 + 24) bytes), which every GPU that loads the library holds until the process exits; the
+ * call makes no cudaMalloc / cudaFree / cudaMallocHost and no allocating library call.  `rays` and `hits` are the
+ * caller's buffers and may be host or device pointers (copied with cudaMemcpyDefault on the context's stream); the
+ * call returns after the stream has drained.  count > VKRT_STATIC_MAX_RAYS → VKRT_ERROR_INVALID_ARGUMENT ("... at most
+ * 65536 rays per call"), nothing is launched.  All calls on one GPU share the array and it keeps the last call's
+ * contents (the call clears the cursor and the flag itself): two calls that overlap on the same GPU - from two
+ * threads or two contexts - race; serialise them.  The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress); make that call outside stream capture. */
+#define VKRT_STATIC_MAX_RAYS 65536u
+VKRT_API int vkrt_trace_rays_static(VkrtContext* ctx, const VkrtTlas* tlas, const VkrtRay* rays, uint32_t count, int anyHit,
+                                    VkrtHit* hits);
+
 /* ------------------------------------------------------------------------------------------------
  * Statistics for the roofline: counted since the last vkrt_stats_reset.
  * ---------------------------------------------------------------------------------------------- */

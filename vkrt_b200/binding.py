@@ -178,6 +178,7 @@ EXPORTS = [
     "vkrt_host_free",
     "vkrt_frame_device_bgra8",
     "vkrt_trace_rays",
+    "vkrt_trace_rays_static",
     "vkrt_stats_enable",
     "vkrt_stats_reset",
     "vkrt_stats_get",
@@ -191,6 +192,8 @@ EXPORTS = [
     "vkrt_textures_broadcast",
     "vkrt_tiles_gather_wait",
 ]
+
+STATIC_MAX_RAYS = 65536  # VKRT_STATIC_MAX_RAYS
 
 _lib = None
 
@@ -242,6 +245,7 @@ def load_library(path: Optional[str] = None):
         "vkrt_host_free": (None, [vp, vp]),
         "vkrt_frame_device_bgra8": (vp, [vp]),
         "vkrt_trace_rays": (i32, [vp, vp, vp, u64, i32, vp]),
+        "vkrt_trace_rays_static": (i32, [vp, vp, vp, u32, i32, vp]),
         "vkrt_stats_enable": (i32, [vp, i32, i32]),
         "vkrt_stats_reset": (i32, [vp]),
         "vkrt_stats_get": (i32, [vp, C.POINTER(Stats)]),
@@ -498,6 +502,15 @@ class Tlas:
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
         hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
         self.ctx.check(self.ctx.lib.vkrt_trace_rays(self.ctx.handle, self.handle, _ptr(rays), rays.shape[0], int(any_hit), _ptr(hits)))
+        return hits
+
+    def trace_rays_static(self, rays: np.ndarray, any_hit: bool = False) -> np.ndarray:
+        """vkrt_trace_rays_static: the same batch through the library's file-scope scratch array, no allocation on the
+        device; at most STATIC_MAX_RAYS rays per call."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        self.ctx.check(self.ctx.lib.vkrt_trace_rays_static(self.ctx.handle, self.handle, _ptr(rays), rays.shape[0], int(any_hit),
+                                                           _ptr(hits)))
         return hits
 
     def close(self):

@@ -11,7 +11,10 @@
 #include "traverse.cuh"
 
 #include <algorithm>
+#include <cstddef>
 #include <cstdlib>
+#include <mutex>
+#include <string>
 
 namespace vkrt
 {
@@ -1172,4 +1175,185 @@ int traceRaysHost(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint64_t 
     return checkDeviceErrors(ctx, "vkrt_trace_rays");
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// vkrt_trace_rays_static: the ray-level entry without any allocation (include/vkrt.h).  No counterpart in the
+// reference; added for callers that cannot call cudaMalloc.  Everything the call
+// needs on the device besides the caller's scene lives in one file-scope array; the kernel is the persistent trace
+// kernel over a source that reads the 32-byte ray records and writes the 24-byte hit records in place.
+// ------------------------------------------------------------------------------------------------------------------
+namespace
+{
+struct StaticScratch
+{
+    uint32_t header[64];               // [0] ray-pool cursor, [4] traversal stack overflow flag; cleared by every call
+    VkrtRay rays[VKRT_STATIC_MAX_RAYS]; // staged input
+    VkrtHit hits[VKRT_STATIC_MAX_RAYS]; // staged output
+};
+static_assert(sizeof(VkrtRay) == 32 && sizeof(VkrtHit) == 24, "record sizes of include/vkrt.h");
+static_assert(offsetof(StaticScratch, rays) == 256 && offsetof(StaticScratch, hits) % 16 == 0, "scratch layout");
+
+// Held by every GPU that loads the library until the process exits.  In host code this name is only a handle for
+// cudaGetSymbolAddress - never pass it to a kernel.
+static __device__ __align__(256) unsigned char g_staticScratch[sizeof(StaticScratch)];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_staticMutex;
+StaticScratch* g_staticAddress[kStaticMaxDevices]; // device address of g_staticScratch per device ordinal, resolved once
+
+// The device of `ctx` is current.
+int staticScratchAddress(Context* ctx, StaticScratch** out)
+{
+    if (ctx->device < 0 || ctx->device >= kStaticMaxDevices)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays_static: device ordinal beyond 63");
+    }
+    std::lock_guard<std::mutex> lock(g_staticMutex);
+    if (!g_staticAddress[ctx->device])
+    {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_staticScratch);
+        if (e != cudaSuccess || !p)
+        {
+            return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_trace_rays_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        }
+        g_staticAddress[ctx->device] = static_cast<StaticScratch*>(p);
+    }
+    *out = g_staticAddress[ctx->device];
+    return VKRT_SUCCESS;
+}
+
+template<bool ANY>
+struct StaticRaySource
+{
+    const VkrtRay* rays;
+    VkrtHit* out;
+    const InstanceRecord* instances;
+    __device__ __forceinline__ uint32_t map(uint32_t i) const { return i; }
+    __device__ __forceinline__ void load(uint32_t h, F3& o, F3& d, float& tmin, float& tmax) const
+    {
+        const float4* r = reinterpret_cast<const float4*>(rays + h); // 32-byte records at a 256-byte aligned base
+        const float4 o4 = r[0], d4 = r[1];
+        o = f3(o4.x, o4.y, o4.z), d = f3(d4.x, d4.y, d4.z);
+        tmin = o4.w, tmax = d4.w;
+    }
+    __device__ __forceinline__ void commit(uint32_t h, const BestHit& best, bool found) const
+    {
+        VkrtHit o;
+        if (ANY)
+        {
+            // what ListAnySource::commit writes
+            o.t = found ? best.t : 0.f, o.b1 = 0.f, o.b2 = 0.f;
+            o.instance = found ? best.instance : kInvalid;
+            o.geometry = o.primitive = found ? 0u : kInvalid;
+        }
+        else if (best.tri == kInvalid)
+        {
+            o.t = 0.f, o.b1 = 0.f, o.b2 = 0.f;
+            o.instance = o.geometry = o.primitive = kInvalid;
+        }
+        else
+        {
+            // what ClosestSource::commit + k_hits_export write
+            const float4 tag = reinterpret_cast<const float4*>(instances[best.instance].tris + best.tri)[2];
+            o.t = best.t, o.b1 = best.b1, o.b2 = best.b2;
+            o.instance = best.instance;
+            o.geometry = __float_as_uint(tag.y);
+            o.primitive = __float_as_uint(tag.z);
+        }
+        out[h] = o;
+    }
+};
+
+template<bool ANY, bool MULTI>
+__global__ void __launch_bounds__(kTraceThreads, VKRT_TRACE_MIN_BLOCKS)
+k_trace_rays_static(SceneDev scene, StaticScratch* scratch, uint32_t count)
+{
+    TraceCounters tc;
+    StaticRaySource<ANY> src;
+    src.rays = scratch->rays, src.out = scratch->hits, src.instances = scene.instances;
+    tracePersistent<ANY, MULTI, false, false>(scene, src, count, &scratch->header[0], 0u, tc);
+}
+} // namespace
+
+int traceRaysStatic(Context* ctx, const Tlas* tlas, const VkrtRay* rays, uint32_t count, int anyHit, VkrtHit* hits)
+{
+    if (count > VKRT_STATIC_MAX_RAYS)
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays_static: at most 65536 rays per call (VKRT_STATIC_MAX_RAYS); "
+                                                      "split the batch or use vkrt_trace_rays");
+    }
+    if (count == 0)
+    {
+        return VKRT_SUCCESS;
+    }
+    if (int rc = checkTlasCurrent(ctx, tlas, "vkrt_trace_rays_static"))
+    {
+        return rc;
+    }
+    StaticScratch* scratch = nullptr;
+    if (int rc = staticScratchAddress(ctx, &scratch))
+    {
+        return rc;
+    }
+    cudaStream_t s = ctx->stream;
+    // the array keeps the last call's contents: the cursor and the overflow flag must start at zero
+    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(scratch->header, 0, sizeof(scratch->header), s));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(scratch->rays, rays, (size_t)count * sizeof(VkrtRay), cudaMemcpyDefault, s));
+    SceneDev scene;
+    scene.instances = tlas->instances.as<InstanceRecord>();
+    scene.topNodes = tlas->nodeCount ? tlas->nodes.as<Node8>() : nullptr;
+    scene.leafInstance = tlas->leafInstance.as<uint32_t>();
+    scene.instanceCount = tlas->instanceCount;
+    scene.cullMask = 0xFFu;
+    scene.errorFlags = scratch->header + 4;
+    scene.topBoxScale = tlas->boxScale;
+    scene.rows = nullptr;
+    scene.textures = nullptr;
+    scene.one = 0x3F800000u;
+    scene.mips = nullptr;
+    const uint32_t grid = persistentGrid(ctx, VKRT_TRACE_MIN_BLOCKS);
+    const bool multi = scene.topNodes != nullptr;
+    if (anyHit)
+    {
+        multi ? k_trace_rays_static<true, true><<<grid, kTraceThreads, 0, s>>>(scene, scratch, count)
+              : k_trace_rays_static<true, false><<<grid, kTraceThreads, 0, s>>>(scene, scratch, count);
+    }
+    else
+    {
+        multi ? k_trace_rays_static<false, true><<<grid, kTraceThreads, 0, s>>>(scene, scratch, count)
+              : k_trace_rays_static<false, false><<<grid, kTraceThreads, 0, s>>>(scene, scratch, count);
+    }
+    VKRT_CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches += 1;
+    uint32_t flags[4] = {0, 0, 0, 0};
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hits, scratch->hits, (size_t)count * sizeof(VkrtHit), cudaMemcpyDefault, s));
+    VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(flags, scratch->header + 4, sizeof(flags), cudaMemcpyDeviceToHost, s));
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    if (flags[0])
+    {
+        ctx->stats.traversalOverflows += 1;
+        return ctx->fail(VKRT_ERROR_TRAVERSAL_OVERFLOW, "vkrt_trace_rays_static: a ray ran out of traversal stack entries; the hits are incomplete");
+    }
+    return VKRT_SUCCESS;
+}
+
 } // namespace vkrt
+
+extern "C" int vkrt_trace_rays_static(VkrtContext* c, const VkrtTlas* tlas, const VkrtRay* rays, uint32_t count, int anyHit, VkrtHit* hits)
+{
+    vkrt::Context* ctx = static_cast<vkrt::Context*>(c);
+    if (!ctx)
+    {
+        return VKRT_ERROR_INVALID_ARGUMENT;
+    }
+    if (!tlas || (count && (!rays || !hits)))
+    {
+        return ctx->fail(VKRT_ERROR_INVALID_ARGUMENT, "vkrt_trace_rays_static: NULL argument");
+    }
+    const cudaError_t e = cudaSetDevice(ctx->device);
+    if (e != cudaSuccess)
+    {
+        return ctx->fail(VKRT_ERROR_CUDA, std::string("vkrt_trace_rays_static: cudaSetDevice: ") + cudaGetErrorString(e));
+    }
+    return vkrt::traceRaysStatic(ctx, static_cast<const vkrt::Tlas*>(tlas), rays, count, anyHit, hits);
+}
