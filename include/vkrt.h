@@ -83,7 +83,12 @@ typedef enum VkrtBuildFlags
     VKRT_BUILD_DEFAULT = 0,
     VKRT_BUILD_PREFER_FAST_BUILD = 1u << 0, /* LBVH + greedy collapse instead of PLOC + cost-optimal collapse: ~2x faster build, ~25 % slower rays */
     VKRT_BUILD_INPUT_ON_DEVICE = 1u << 1,   /* `vertices` and `indices` are CUDA device pointers */
-    VKRT_BUILD_KEEP_HOST_INPUT = 1u << 2    /* reserved */
+    VKRT_BUILD_KEEP_HOST_INPUT = 1u << 2,   /* reserved */
+    /* VK_BUILD_ACCELERATION_STRUCTURE_PREFER_FAST_TRACE_BIT_KHR: after PLOC, parallel reinsertion passes (Meister & Bittner 2018)
+     * move subtrees to where they cost the least surface area, large nodes first; several times the build time for
+     * fewer node visits per ray.  For hierarchies that are built once and traced many times.  Ignored together with
+     * VKRT_BUILD_PREFER_FAST_BUILD. */
+    VKRT_BUILD_PREFER_FAST_TRACE = 1u << 3
 } VkrtBuildFlags;
 
 typedef struct VkrtBuildSizes

@@ -8,13 +8,19 @@
  * by std::stable_sort and the wavefront queues by a per-pixel loop; both are covered by the `-m gpu` tests.
  */
 #include "../../vkrt_b200/csrc/builder.cuh"
+#include "../../vkrt_b200/csrc/reinsert.cuh"
 #include "../../vkrt_b200/csrc/shading.cuh"
 #include "../../vkrt_b200/csrc/raster.cuh"
 #include "../../vkrt_b200/csrc/traverse.cuh"
 
+#include "hierarchy_lab.hpp"
+
 #include <algorithm>
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
 #include <numeric>
 #include <vector>
 
@@ -79,7 +85,7 @@ static float emuBoxScale(const std::vector<Node8>& nodes)
 // optional cost-optimal collapse decisions -> collapse into wide nodes.  Returns the node count, 0 on failure.
 static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n, uint32_t maxLeaf, float dpPrimCost, const float clo[3],
                                   const float chi[3], std::vector<Node8>& nodesOut, uint32_t nodeCapacity, std::vector<uint32_t>& primSource,
-                                  float sah[2])
+                                  float sah[2], uint32_t reinsertPasses = 0)
 {
     std::vector<uint32_t> keys(n), vals(n);
     const F3 clo3 = f3(clo[0], clo[1], clo[2]);
@@ -116,6 +122,144 @@ static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n,
         {
             lbvhClimb(bvh, i);
         }
+    }
+    // experiments on the binary hierarchy (hierarchy_lab.hpp); the default leaves the LBVH as it is
+    const char* labMode = getenv("VKRT_EMU_BINARY");
+    const char* labReinsert = getenv("VKRT_EMU_REINSERT");
+    if (n > 2 && ((labMode && strcmp(labMode, "lbvh") != 0) || labReinsert || getenv("VKRT_LAB_TOP")))
+    {
+        std::vector<lab::Box> leaves(n);
+        for (uint32_t i = 0; i < n; ++i)
+        {
+            const float4 l = triBox[2 * (size_t)sv[i]], h = triBox[2 * (size_t)sv[i] + 1];
+            leaves[i] = lab::Box{{l.x, l.y, l.z}, {h.x, h.y, h.z}};
+        }
+        lab::Tree t;
+        t.init(n, leaves);
+        auto fromRef = [&](int ref) { return ref >= 0 ? ref : (int)(n - 1) + ~ref; };
+        if (labMode && strcmp(labMode, "ploc") == 0)
+        {
+            lab::buildPloc(t, 8);
+        }
+        else if (labMode && strcmp(labMode, "sah") == 0)
+        {
+            lab::buildSah(t);
+        }
+        else
+        {
+            for (uint32_t i = 0; i + 1 < n; ++i)
+            {
+                t.left[i] = fromRef(binNodes[i].children.x), t.right[i] = fromRef(binNodes[i].children.y);
+                t.parent[t.left[i]] = (int)i, t.parent[t.right[i]] = (int)i;
+                const float4 l = binNodes[i].lo, h = binNodes[i].hi;
+                t.box[i] = lab::Box{{l.x, l.y, l.z}, {h.x, h.y, h.z}};
+            }
+            t.root = root, t.parent[root] = -1;
+        }
+        fprintf(stderr, "lab: %s binary SAH %.3f\n", labMode ? labMode : "lbvh", t.sah());
+        if (getenv("VKRT_LAB_TOP"))
+        {
+            lab::rebuildTop(t, (uint32_t)atoi(getenv("VKRT_LAB_TOP")));
+            fprintf(stderr, "lab: top rebuilt over %s subtrees, binary SAH %.3f\n", getenv("VKRT_LAB_TOP"), t.sah());
+        }
+        if (labReinsert)
+        {
+            lab::reinsert(t, atoi(labReinsert));
+        }
+        // back to BinNode records: boxes and leaf counts bottom-up
+        std::vector<uint32_t> count(2 * (size_t)n - 1, 1u);
+        std::vector<std::pair<int, int>> work;
+        work.emplace_back(t.root, 0);
+        while (!work.empty())
+        {
+            auto [node, state] = work.back();
+            if (t.isLeaf(node))
+            {
+                work.pop_back();
+            }
+            else if (state == 0)
+            {
+                work.back().second = 1;
+                work.emplace_back(t.left[node], 0);
+                work.emplace_back(t.right[node], 0);
+            }
+            else
+            {
+                count[node] = count[t.left[node]] + count[t.right[node]];
+                const lab::Box b = lab::merge(t.box[t.left[node]], t.box[t.right[node]]);
+                auto toRef = [&](int id) { return t.isLeaf(id) ? ~(id - (int)(n - 1)) : id; };
+                binNodes[node].lo = make_float4(b.lo[0], b.lo[1], b.lo[2], uintAsFloat(count[node]));
+                binNodes[node].hi = make_float4(b.hi[0], b.hi[1], b.hi[2], 0.0f);
+                binNodes[node].children = make_int2(toRef(t.left[node]), toRef(t.right[node]));
+                t.box[node] = b;
+                work.pop_back();
+            }
+        }
+        root = t.root;
+    }
+    // the builder's reinsertion passes (reinsert.cuh), phase by phase like the kernels
+    const char* passesEnv = getenv("VKRT_EMU_FAST_TRACE");
+    const int passes = passesEnv ? atoi(passesEnv) : (int)reinsertPasses;
+    if (n > 3 && passes > 0)
+    {
+        std::vector<int> parent(2 * (size_t)n - 1, -1), target(2 * (size_t)n - 1);
+        std::vector<float> gain(2 * (size_t)n - 1);
+        std::vector<unsigned long long> lock(2 * (size_t)n - 1);
+        uint32_t moved = 0;
+        bvh.dpParent = parent.data();
+        for (uint32_t i = 0; i + 1 < n; ++i)
+        {
+            dpLinkParents(bvh, i);
+        }
+        parent[n + (uint32_t)root] = -1;
+        ReinsertArgs ra;
+        ra.bvh = bvh, ra.target = target.data(), ra.gain = gain.data(), ra.lock = lock.data(), ra.moved = &moved;
+        const uint32_t slots = 2 * n - 1;
+        const BinNode& rootNode = binNodes[root];
+        const float rootArea = halfArea(f3(rootNode.lo.x, rootNode.lo.y, rootNode.lo.z), f3(rootNode.hi.x, rootNode.hi.y, rootNode.hi.z));
+        const int bands = getenv("VKRT_EMU_BANDS") ? atoi(getenv("VKRT_EMU_BANDS")) : 1;
+        const float bandRatio = getenv("VKRT_EMU_BAND_RATIO") ? (float)atof(getenv("VKRT_EMU_BAND_RATIO")) : 4.0f;
+        for (int pass = 0; pass < passes; ++pass)
+        {
+            const int bandIters = getenv("VKRT_EMU_BAND_ITERS") ? atoi(getenv("VKRT_EMU_BAND_ITERS")) : 1;
+            const int band = (pass / bandIters) % bands;
+            ra.areaHi = band == 0 ? FLT_MAX : rootArea * powf(bandRatio, -(float)band);
+            ra.areaLo = band == bands - 1 ? 0.0f : rootArea * powf(bandRatio, -(float)(band + 1));
+            moved = 0;
+            for (uint32_t i = 0; i < slots; ++i)
+            {
+                reinsertSearch(ra, i);
+            }
+            for (uint32_t i = 0; i < slots; ++i)
+            {
+                reinsertLock(ra, i);
+            }
+            for (uint32_t i = 0; i < slots; ++i)
+            {
+                reinsertVerify(ra, i);
+            }
+            for (uint32_t i = 0; i < slots; ++i)
+            {
+                reinsertApply(ra, i);
+            }
+            std::fill(flags.begin(), flags.end(), 0);
+            for (uint32_t i = 0; i < n; ++i)
+            {
+                reinsertRefit(bvh, i);
+            }
+            if (getenv("VKRT_EMU_VERBOSE"))
+            {
+                double sum = 0;
+                for (uint32_t i = 0; i + 1 < n; ++i)
+                {
+                    sum += halfArea(f3(binNodes[i].lo.x, binNodes[i].lo.y, binNodes[i].lo.z), f3(binNodes[i].hi.x, binNodes[i].hi.y, binNodes[i].hi.z));
+                }
+                const BinNode& r = binNodes[root];
+                fprintf(stderr, "emu: reinsertion pass %d moved %u, binary SAH %.3f\n", pass, moved,
+                        sum / halfArea(f3(r.lo.x, r.lo.y, r.lo.z), f3(r.hi.x, r.hi.y, r.hi.z)));
+            }
+        }
+        bvh.dpParent = nullptr;
     }
     // cost-optimal collapse: children before parents (the GPU climbs from the leaves with arrival counters)
     std::vector<uint32_t> dpChoice;

@@ -5,6 +5,7 @@
 // all per-triangle streams are coalesced 4/16-byte accesses, the sort stages tiles through shared memory.
 #include "builder.cuh"
 #include "context.hpp"
+#include "reinsert.cuh"
 #include "traverse.cuh"
 
 #include <algorithm>
@@ -1105,6 +1106,65 @@ __global__ void __launch_bounds__(kThreads) k_dp_climb(Bvh2 bvh)
     }
 }
 
+// ---- reinsertion passes (reinsert.cuh), VKRT_BUILD_PREFER_FAST_TRACE ----
+// state[0] = surface area of the root box (float bits), state[1] = moves applied so far
+__global__ void k_reinsert_begin(Bvh2 bvh, uint32_t* state)
+{
+    const int root = *bvh.root;
+    bvh.dpParent[bvh.count + (uint32_t)root] = -1;
+    const float4 lo = bvh.nodes[root].lo, hi = bvh.nodes[root].hi;
+    state[0] = floatAsUint(halfArea(f3(lo.x, lo.y, lo.z), f3(hi.x, hi.y, hi.z)));
+    state[1] = 0u;
+}
+
+// Only nodes whose surface area lies in [loMul, hiMul) x the root's area are looked at in this pass: large nodes first.
+__global__ void __launch_bounds__(128) k_reinsert_search(ReinsertArgs a, const uint32_t* state, float hiMul, float loMul)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot < 2u * a.bvh.count - 1u)
+    {
+        const float rootArea = uintAsFloat(state[0]);
+        a.areaHi = hiMul * rootArea, a.areaLo = loMul * rootArea;
+        reinsertSearch(a, slot);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_reinsert_lock(ReinsertArgs a)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot < 2u * a.bvh.count - 1u)
+    {
+        reinsertLock(a, slot);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_reinsert_verify(ReinsertArgs a)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot < 2u * a.bvh.count - 1u)
+    {
+        reinsertVerify(a, slot);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_reinsert_apply(ReinsertArgs a)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot < 2u * a.bvh.count - 1u)
+    {
+        reinsertApply(a, slot);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_reinsert_refit(Bvh2 bvh)
+{
+    const uint32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf < bvh.count)
+    {
+        reinsertRefit(bvh, leaf);
+    }
+}
+
 __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
 {
     a.taskRef[0] = a.bvh2.count > 1 ? *a.bvh2.root : ~0;
@@ -1389,6 +1449,7 @@ struct HierarchyResult
     uint32_t levels = 0; // wide levels = longest root-to-leaf node path
     float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
     float sahCost = 0.0f;
+    uint32_t reinsertMoves = 0; // VKRT_BUILD_PREFER_FAST_TRACE: nodes moved by the reinsertion passes
 };
 
 int reserveBuildScratch(Context* ctx, uint32_t n, uint32_t nodeCapacity, bool packed)
@@ -1417,7 +1478,8 @@ int reserveBuildScratch(Context* ctx, uint32_t n, uint32_t nodeCapacity, bool pa
 // collapse into `nodes`.  On entry buildScratch.triBox holds the n boxes and `small` the reduced scene bounds
 // (k_tri_bounds / k_instance_bounds, stream-ordered).  On return buildScratch.primSource[0..n) is the primitive order
 // the leaves refer to, and everything is complete on the host side (the function synchronises).
-int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8* nodes, uint32_t nodeCapacity, HierarchyResult& out)
+int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, bool fastTrace, Node8* nodes, uint32_t nodeCapacity,
+                   HierarchyResult& out)
 {
     cudaStream_t s = ctx->stream;
     const int sm = ctx->smCount;
@@ -1514,6 +1576,54 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, Node8*
             }
             batch = 16;
         }
+    }
+
+    // quality passes on the binary hierarchy (VKRT_BUILD_PREFER_FAST_TRACE): parallel reinsertion, large nodes first
+    out.reinsertMoves = 0;
+    if (fastTrace && !compact && n > 3)
+    {
+        const uint32_t slots = 2u * n - 1u;
+        VKRT_CUDA_TRY(ctx, sc.dp.reserve((size_t)n * 12));
+        VKRT_CUDA_TRY(ctx, sc.reinsert.reserve((size_t)slots * 16 + 64));
+        bvh.dpParent = reinterpret_cast<int*>(sc.dp.as<uint32_t>() + n);
+        ReinsertArgs ra;
+        ra.bvh = bvh;
+        ra.lock = sc.reinsert.as<unsigned long long>();
+        ra.target = reinterpret_cast<int*>(ra.lock + slots);
+        ra.gain = reinterpret_cast<float*>(ra.target + slots);
+        uint32_t* state = reinterpret_cast<uint32_t*>(ra.gain + slots);
+        ra.moved = state + 1;
+        ra.areaLo = 0.0f, ra.areaHi = FLT_MAX;
+        k_dp_parents<<<(n + kThreads - 1) / kThreads, kThreads, 0, s>>>(bvh);
+        k_reinsert_begin<<<1, 1, 0, s>>>(bvh, state);
+        ctx->launches += 2;
+        int sweeps = kReinsertSweeps, bands = kReinsertBands, iters = kReinsertIterations;
+        float ratio = kReinsertBandRatio;
+        if (const char* e = getenv("VKRT_BUILD_REINSERT")) // experiments: "sweeps,bands,iterations,ratio"
+        {
+            sscanf(e, "%d,%d,%d,%f", &sweeps, &bands, &iters, &ratio);
+        }
+        const uint32_t gridSlots = (slots + kThreads - 1) / kThreads, gridLeaves = (n + kThreads - 1) / kThreads;
+        for (int sweep = 0; sweep < sweeps; ++sweep)
+        {
+            for (int band = 0; band < bands; ++band)
+            {
+                const float hiMul = band == 0 ? FLT_MAX : powf(ratio, -(float)band);
+                const float loMul = band == bands - 1 ? 0.0f : powf(ratio, -(float)(band + 1));
+                for (int it = 0; it < iters; ++it)
+                {
+                    k_reinsert_search<<<(slots + 127) / 128, 128, 0, s>>>(ra, state, hiMul, loMul);
+                    k_reinsert_lock<<<gridSlots, kThreads, 0, s>>>(ra);
+                    k_reinsert_verify<<<gridSlots, kThreads, 0, s>>>(ra);
+                    k_reinsert_apply<<<gridSlots, kThreads, 0, s>>>(ra);
+                    VKRT_CUDA_TRY(ctx, cudaMemsetAsync(bvh.flags, 0, (size_t)(n - 1) * 4, s));
+                    k_reinsert_refit<<<gridLeaves, kThreads, 0, s>>>(bvh);
+                    ctx->launches += 5;
+                }
+            }
+        }
+        VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(&out.reinsertMoves, ra.moved, 4, cudaMemcpyDeviceToHost, s));
+        bvh.dpParent = nullptr;
     }
 
     // cost-optimal collapse: parents, then a bottom-up climb
@@ -1659,7 +1769,8 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         ctx->launches += 1;
         HierarchyResult h;
         const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
-        if (int r = buildHierarchy(ctx, n, kMaxLeafTris, fast, blas->nodes.as<Node8>(), nodeCapacity, h))
+        const bool fastTrace = (blas->flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0 || getenv("VKRT_BUILD_FAST_TRACE") != nullptr;
+        if (int r = buildHierarchy(ctx, n, kMaxLeafTris, fast, fastTrace && !fast, blas->nodes.as<Node8>(), nodeCapacity, h))
         {
             return r;
         }
@@ -1726,7 +1837,7 @@ int buildTlasOnDevice(Context* ctx, Tlas* tlas)
                                                                               sc.triBox.as<float4>(), sceneBounds);
     ctx->launches += 2;
     HierarchyResult h;
-    if (int r = buildHierarchy(ctx, n, 1u, false, tlas->nodes.as<Node8>(), nodeCapacity, h))
+    if (int r = buildHierarchy(ctx, n, 1u, false, false, tlas->nodes.as<Node8>(), nodeCapacity, h))
     {
         return r;
     }

@@ -27,10 +27,11 @@ struct BuildScratch
     DeviceBuffer triBox, packedBuild, keysA, keysB, valsA, valsB, tileHist, binNodes, flags, taskRef, primSource, small, sortedBox;
     DeviceBuffer plocLoA, plocHiA, plocLoB, plocHiB, plocStatus; // PLOC cluster boxes (ping-pong) and look-back words
     DeviceBuffer dp;                                              // cost-optimal collapse: decisions (n), parents (2n)
+    DeviceBuffer reinsert;                                        // reinsertion passes: target, gain (4 B each) and lock (8 B) per node
     void release()
     {
         DeviceBuffer* all[] = {&triBox, &packedBuild, &keysA, &keysB, &valsA, &valsB, &tileHist, &binNodes, &flags,
-                               &taskRef, &primSource, &small, &sortedBox, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus, &dp};
+                               &taskRef, &primSource, &small, &sortedBox, &plocLoA, &plocHiA, &plocLoB, &plocHiB, &plocStatus, &dp, &reinsert};
         for (DeviceBuffer* b : all)
         {
             b->release();
