@@ -355,7 +355,7 @@ def main():
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--triangles", type=int, default=50_000_000, help="config5 only: triangles in the procedural soup")
-    ap.add_argument("--build-flags", type=int, default=-1, help="VkrtBuildFlags; default 0 (PLOC), config5 1 (LBVH: faster rebuild and, on the soup, fewer nodes per ray)")
+    ap.add_argument("--build-flags", type=int, default=-1, help="VkrtBuildFlags; default 8 (PLOC + reinsertion passes, for hierarchies built once), config5 1 (LBVH: faster rebuild and, on the soup, fewer nodes per ray)")
     ap.add_argument("--texture-lod", default="zero", choices=["zero", "cones"],
                     help="zero: every texture() samples level 0 as the reference's ray-tracing shaders do (default, the parity mode); "
                          "cones: ray-cone level of detail over the generated mip chain (SURVEY 8 f3)")
@@ -391,7 +391,9 @@ def main():
 
     W, Hh, spp, desc = WORKLOADS[args.workload]
     if args.build_flags < 0:
-        args.build_flags = 1 if args.workload == "config5" else 0
+        # config 5 rebuilds every frame (LBVH); the others build once and trace many frames, like the reference's constructor:
+        # VKRT_BUILD_PREFER_FAST_TRACE (reinsertion passes after PLOC, ~10x the build time, fewer node visits per ray)
+        args.build_flags = 1 if args.workload == "config5" else 8
     soup = None
     t_ingest0 = time.perf_counter()
     if args.workload == "config5":
@@ -428,8 +430,10 @@ def main():
     # CUDA events inside the library; storage and scratch already allocated) - the number "BVH build Mtri/s" is quoted on
     warm = {}
     verts_in = soup.vertices if soup is not None else rt.flat["vertices"]
-    for name, fl in (("ploc_optimal", 0), ("lbvh_greedy", 1)):
-        if soup is not None and fl == 0 and args.triangles > 20_000_000:
+    for name, fl in (("ploc_optimal", 0), ("lbvh_greedy", 1), ("ploc_reinsert_optimal", 8)):
+        if fl == 8 and not (args.build_flags & 8):
+            continue
+        if soup is not None and fl != 1 and args.triangles > 20_000_000:
             continue  # config 5 at 50 M rebuilds with LBVH every frame; the PLOC scratch would not leave room for the 4K queues
         times = []
         for _ in range(10):
@@ -438,6 +442,7 @@ def main():
         warm[name] = {"ms_median": float(np.median(times)), "ms_min": float(np.min(times)),
                       "mtri_s": info.triangleCount / float(np.median(times)) / 1e3, "nodes": int(rt.blas.info().nodeCount),
                       "sah_cost": float(rt.blas.info().sahCost)}
+    flavour = "lbvh_greedy" if args.build_flags & 1 else ("ploc_reinsert_optimal" if args.build_flags & 8 else "ploc_optimal")
     rt.rebuild(verts_in, flags=args.build_flags)  # back to the flavour the frames are traced on (+ a fresh TLAS)
     info = rt.blas.info()
     stream = torch.cuda.ExternalStream(rt.ctx.stream, device=local)
@@ -602,14 +607,14 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "scene": model["provenance"], "width": W, "height": Hh, "spp": spp,
-                       "texture_lod": args.texture_lod, "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "instances": 1 if instances is None else int(np.asarray(instances).size // 12),
+                       "texture_lod": args.texture_lod, "triangles": int(info.triangleCount), "bvh8_nodes": int(info.nodeCount), "bvh_build_flags": args.build_flags, "bvh_flavour": flavour, "instances": 1 if instances is None else int(np.asarray(instances).size // 12),
                        "parallelism": f"interleaved 64x64 tiles over {world} rank(s), scene replicated, NCCL send/recv gather to rank 0",
                        "l2": "per-frame ray/hit/shading queues (>2 GB at 4K) exceed the 126 MB L2; no explicit flush"},
             "rays_per_step": {"primary": rp / args.steps, "shadow": rs / args.steps, "reflection": rr / args.steps},
             "mrays_s_by_type": {"primary": rp / (ms * 1e-3) / 1e6, "shadow": rs / (ms * 1e-3) / 1e6, "reflection": rr / (ms * 1e-3) / 1e6},
             "frame_fnv": frame_fnv, "ingest": ingest,
-            "bvh_build": {"warm": warm, "warm_ms": (warm.get("lbvh_greedy" if args.build_flags & 1 else "ploc_optimal") or {}).get("ms_median"),
-                          "warm_mtri_s": (warm.get("lbvh_greedy" if args.build_flags & 1 else "ploc_optimal") or {}).get("mtri_s"),
+            "bvh_build": {"warm": warm, "warm_ms": (warm.get(flavour) or {}).get("ms_median"),
+                          "warm_mtri_s": (warm.get(flavour) or {}).get("mtri_s"), "flavour": flavour,
                           "cold_first_build_ms": cold_build_ms, "tlas": {"instances": int(rt.tlas.info().instanceCount),
                                                                           "nodes": int(rt.tlas.info().nodeCount), "ms": float(rt.tlas.info().buildMilliseconds)},
                           "ms": info.buildMilliseconds, "mtri_s": info.triangleCount / max(info.buildMilliseconds, 1e-9) / 1e3,

@@ -85,7 +85,7 @@ static float emuBoxScale(const std::vector<Node8>& nodes)
 // optional cost-optimal collapse decisions -> collapse into wide nodes.  Returns the node count, 0 on failure.
 static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n, uint32_t maxLeaf, float dpPrimCost, const float clo[3],
                                   const float chi[3], std::vector<Node8>& nodesOut, uint32_t nodeCapacity, std::vector<uint32_t>& primSource,
-                                  float sah[2], uint32_t reinsertPasses = 0)
+                                  float sah[2], bool fastTrace = false)
 {
     std::vector<uint32_t> keys(n), vals(n);
     const F3 clo3 = f3(clo[0], clo[1], clo[2]);
@@ -197,10 +197,9 @@ static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n,
         }
         root = t.root;
     }
-    // the builder's reinsertion passes (reinsert.cuh), phase by phase like the kernels
-    const char* passesEnv = getenv("VKRT_EMU_FAST_TRACE");
-    const int passes = passesEnv ? atoi(passesEnv) : (int)reinsertPasses;
-    if (n > 3 && passes > 0)
+    // the builder's reinsertion passes (reinsert.cuh), phase by phase like the kernels, on the schedule of
+    // bvh_build.cu::buildHierarchy (VKRT_BUILD_PREFER_FAST_TRACE); VKRT_EMU_FAST_TRACE=1 turns them on for experiments
+    if (n > 3 && (fastTrace || getenv("VKRT_EMU_FAST_TRACE")))
     {
         std::vector<int> parent(2 * (size_t)n - 1, -1), target(2 * (size_t)n - 1);
         std::vector<float> gain(2 * (size_t)n - 1);
@@ -217,47 +216,49 @@ static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n,
         const uint32_t slots = 2 * n - 1;
         const BinNode& rootNode = binNodes[root];
         const float rootArea = halfArea(f3(rootNode.lo.x, rootNode.lo.y, rootNode.lo.z), f3(rootNode.hi.x, rootNode.hi.y, rootNode.hi.z));
-        const int bands = getenv("VKRT_EMU_BANDS") ? atoi(getenv("VKRT_EMU_BANDS")) : 1;
-        const float bandRatio = getenv("VKRT_EMU_BAND_RATIO") ? (float)atof(getenv("VKRT_EMU_BAND_RATIO")) : 4.0f;
-        for (int pass = 0; pass < passes; ++pass)
+        int sweeps = kReinsertSweeps, bands = kReinsertBands, iters = kReinsertIterations;
+        float ratio = kReinsertBandRatio;
+        if (const char* e = getenv("VKRT_BUILD_REINSERT"))
         {
-            const int bandIters = getenv("VKRT_EMU_BAND_ITERS") ? atoi(getenv("VKRT_EMU_BAND_ITERS")) : 1;
-            const int band = (pass / bandIters) % bands;
-            ra.areaHi = band == 0 ? FLT_MAX : rootArea * powf(bandRatio, -(float)band);
-            ra.areaLo = band == bands - 1 ? 0.0f : rootArea * powf(bandRatio, -(float)(band + 1));
-            moved = 0;
-            for (uint32_t i = 0; i < slots; ++i)
+            sscanf(e, "%d,%d,%d,%f", &sweeps, &bands, &iters, &ratio);
+        }
+        for (int sweep = 0; sweep < sweeps; ++sweep)
+        {
+            for (int band = 0; band < bands; ++band)
             {
-                reinsertSearch(ra, i);
-            }
-            for (uint32_t i = 0; i < slots; ++i)
-            {
-                reinsertLock(ra, i);
-            }
-            for (uint32_t i = 0; i < slots; ++i)
-            {
-                reinsertVerify(ra, i);
-            }
-            for (uint32_t i = 0; i < slots; ++i)
-            {
-                reinsertApply(ra, i);
-            }
-            std::fill(flags.begin(), flags.end(), 0);
-            for (uint32_t i = 0; i < n; ++i)
-            {
-                reinsertRefit(bvh, i);
-            }
-            if (getenv("VKRT_EMU_VERBOSE"))
-            {
-                double sum = 0;
-                for (uint32_t i = 0; i + 1 < n; ++i)
+                // the same float expressions as the host loop and k_reinsert_search
+                const float hiMul = band == 0 ? FLT_MAX : powf(ratio, -(float)band);
+                const float loMul = band == bands - 1 ? 0.0f : powf(ratio, -(float)(band + 1));
+                ra.areaHi = hiMul * rootArea, ra.areaLo = loMul * rootArea;
+                for (int it = 0; it < iters; ++it)
                 {
-                    sum += halfArea(f3(binNodes[i].lo.x, binNodes[i].lo.y, binNodes[i].lo.z), f3(binNodes[i].hi.x, binNodes[i].hi.y, binNodes[i].hi.z));
+                    for (uint32_t i = 0; i < slots; ++i)
+                    {
+                        reinsertSearch(ra, i);
+                    }
+                    for (uint32_t i = 0; i < slots; ++i)
+                    {
+                        reinsertLock(ra, i);
+                    }
+                    for (uint32_t i = 0; i < slots; ++i)
+                    {
+                        reinsertVerify(ra, i);
+                    }
+                    for (uint32_t i = 0; i < slots; ++i)
+                    {
+                        reinsertApply(ra, i);
+                    }
+                    std::fill(flags.begin(), flags.end(), 0);
+                    for (uint32_t i = 0; i < n; ++i)
+                    {
+                        reinsertRefit(bvh, i);
+                    }
                 }
-                const BinNode& r = binNodes[root];
-                fprintf(stderr, "emu: reinsertion pass %d moved %u, binary SAH %.3f\n", pass, moved,
-                        sum / halfArea(f3(r.lo.x, r.lo.y, r.lo.z), f3(r.hi.x, r.hi.y, r.hi.z)));
             }
+        }
+        if (getenv("VKRT_EMU_VERBOSE"))
+        {
+            fprintf(stderr, "emu: reinsertion moved %u nodes in %d passes\n", moved, sweeps * bands * iters);
         }
         bvh.dpParent = nullptr;
     }
@@ -321,8 +322,18 @@ static uint32_t emuBuildHierarchy(const std::vector<float4>& triBox, uint32_t n,
 
 extern "C" {
 
+EmuBlas* emu_blas_build_flags(const void* vertices, size_t vertexBytes, uint32_t stride, const uint32_t* indices, size_t indexCount,
+                              const VkrtGeometryRange* ranges, uint32_t geometryCount, uint32_t flags);
+
 EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t stride, const uint32_t* indices, size_t indexCount,
                         const VkrtGeometryRange* ranges, uint32_t geometryCount)
+{
+    return emu_blas_build_flags(vertices, vertexBytes, stride, indices, indexCount, ranges, geometryCount, 0u);
+}
+
+// flags: VkrtBuildFlags; only VKRT_BUILD_PREFER_FAST_TRACE changes anything here (the binary hierarchy is always the LBVH)
+EmuBlas* emu_blas_build_flags(const void* vertices, size_t vertexBytes, uint32_t stride, const uint32_t* indices, size_t indexCount,
+                              const VkrtGeometryRange* ranges, uint32_t geometryCount, uint32_t flags)
 {
     EmuBlas* b = new EmuBlas();
     b->vertices.assign((const uint8_t*)vertices, (const uint8_t*)vertices + vertexBytes);
@@ -390,7 +401,8 @@ EmuBlas* emu_blas_build(const void* vertices, size_t vertexBytes, uint32_t strid
     const float dpPrimCost = dpEnv ? (float)atof(dpEnv) : 0.5f;
     std::vector<uint32_t> primSource;
     float sah[2] = {0.f, 0.f};
-    const uint32_t last = emuBuildHierarchy(triBox, n, kMaxLeafTris, dpPrimCost, clo, chi, b->nodes, nodeCapacity, primSource, sah);
+    const uint32_t last = emuBuildHierarchy(triBox, n, kMaxLeafTris, dpPrimCost, clo, chi, b->nodes, nodeCapacity, primSource, sah,
+                                            (flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0);
     if (last == 0)
     {
         delete b;

@@ -177,6 +177,8 @@ def emu_lib():
         vp, u32, u64, i32, sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
         lib.emu_blas_build.restype = vp
         lib.emu_blas_build.argtypes = [vp, sz, u32, vp, sz, C.POINTER(B.GeometryRange), u32]
+        lib.emu_blas_build_flags.restype = vp
+        lib.emu_blas_build_flags.argtypes = [vp, sz, u32, vp, sz, C.POINTER(B.GeometryRange), u32, u32]
         lib.emu_blas_destroy.argtypes = [vp]
         lib.emu_blas_node_count.restype = u32
         lib.emu_blas_node_count.argtypes = [vp]
@@ -206,7 +208,7 @@ def emu_lib():
 class EmuScene:
     """Host emulation of libvkrt_b200's kernel logic over the same flat scene."""
 
-    def __init__(self, flat, instances):
+    def __init__(self, flat, instances, flags=0):
         lib = emu_lib()
         self.lib = lib
         self.v = np.ascontiguousarray(flat["vertices"], dtype=np.float32)
@@ -214,7 +216,7 @@ class EmuScene:
         rng = (B.GeometryRange * len(flat["ranges"]))()
         for k, r in enumerate(flat["ranges"]):
             rng[k].primitiveCount, rng[k].maxVertex, rng[k].indexByteOffset = int(r[0]), int(r[1]), int(r[2])
-        self.blas = lib.emu_blas_build(_p(self.v), self.v.nbytes, 64, _p(self.i), self.i.size, rng, len(flat["ranges"]))
+        self.blas = lib.emu_blas_build_flags(_p(self.v), self.v.nbytes, 64, _p(self.i), self.i.size, rng, len(flat["ranges"]), flags)
         assert self.blas, "emu_blas_build failed"
         self.rows = np.ascontiguousarray(flat["rows"], dtype=np.int32)
         self.imgs = [np.ascontiguousarray(im, dtype=np.uint8) for im in flat["images"]]

@@ -35,6 +35,40 @@ def test_builder_invariants_soup_and_duplicates():
     check_bvh8(nodes, tris, 300)
 
 
+def test_reinsertion_passes_fast_trace():
+    """VKRT_BUILD_PREFER_FAST_TRACE (reinsert.cuh), the same search / lock / verify / apply / refit passes the kernels run:
+    the tree stays valid (every triangle once, boxes contain), costs less, answers every ray like the oracle, and
+    degenerate inputs (tiny counts, identical boxes: no strictly larger target, so nothing may move) survive."""
+    from vkrt_b200 import binding as B
+
+    flat = flatten_model(scenes.random_soup(4000, seed=21, geometries=3))
+    inst = scenes.identity_instance(1.0)
+    plain, fast = H.EmuScene(flat, inst), H.EmuScene(flat, inst, flags=B.BUILD_PREFER_FAST_TRACE)
+    nodes, tris = fast.read_blas()
+    depth, slots, inner = check_bvh8(nodes, tris, 4000)
+    assert depth < 40
+    assert fast.sah() < 0.97 * plain.sah()
+    rays = H.random_rays(20000, 5, (-12, -8, -10), (12, 8, 10))
+    rays["tmax"][::5] = 4.0
+    hp, np_, tp = plain.trace_rays(rays)
+    hf, nf, tf = fast.trace_rays(rays)
+    assert np.array_equal(hp, hf)
+    ho, _ = H.OracleScene(flat, inst).trace_rays(rays)
+    assert np.array_equal(ho, hf)
+    assert nf < np_  # fewer node visits for the same answers
+    ap, _, _ = plain.trace_rays(rays, any_hit=True)
+    af, _, _ = fast.trace_rays(rays, any_hit=True)
+    assert np.array_equal(ap["instance"] != 0xFFFFFFFF, af["instance"] != 0xFFFFFFFF)
+    for n in (1, 2, 3, 4, 5, 9, 33):
+        small = flatten_model(scenes.random_soup(n, seed=n + 40, geometries=1))
+        nodes, tris = H.EmuScene(small, inst, flags=B.BUILD_PREFER_FAST_TRACE).read_blas()
+        check_bvh8(nodes, tris, n)
+    m = scenes.random_soup(300, seed=9, geometries=1)
+    m["submeshes"][0]["vertices"][:, :3] = np.tile(m["submeshes"][0]["vertices"][:3, :3], (300, 1))
+    nodes, tris = H.EmuScene(flatten_model(m), inst, flags=B.BUILD_PREFER_FAST_TRACE).read_blas()
+    check_bvh8(nodes, tris, 300)
+
+
 def test_path_to_pixel_partition():
     """pathToPixel (shading.cuh): over the ranks every pixel of a ragged frame is produced exactly once, a warp of 32
     consecutive paths is one 8x4 block and 4 consecutive paths a 2x2 quad (the layout the pixel-major waves rely on)."""

@@ -67,7 +67,7 @@ def test_radix_sort_matches_numpy():
     ctx.close()
 
 
-@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD])  # PLOC / LBVH hierarchy
+@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD, B.BUILD_PREFER_FAST_TRACE])  # PLOC / LBVH / PLOC + reinsertion
 def test_builder_invariants(flags):
     ctx = B.Context(0)
     for n in (0, 1, 2, 3, 4, 5, 9, 33, 1023, 1025, 5000):
@@ -107,7 +107,7 @@ def test_collapse_modes(monkeypatch):
     assert res["optimal"][0] < res["greedy"][0]
 
 
-@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD])
+@pytest.mark.parametrize("flags", [B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_BUILD, B.BUILD_PREFER_FAST_TRACE])
 def test_builder_duplicates(flags):
     """Thousands of identical triangles (equal Morton codes, equal merge distances): the builder must still terminate
     with every triangle referenced once; PLOC pairs equal-distance clusters as buddies, LBVH splits ties by index."""
@@ -171,6 +171,42 @@ def test_builder_invariants_sponza(sponza_rt, sponza_flat):
     first = np.concatenate([[0], np.cumsum(sponza_flat["ranges"][:, 0].astype(np.int64))])
     assert np.array_equal(first[tris["geometry"]] + tris["primitive"], tris["buildIndex"])
     assert np.allclose(info.boundsMin, sponza_flat["vertices"][sponza_flat["indices"], :3].min(0))
+
+
+def test_fast_trace_build_same_answers_fewer_node_visits(sponza_flat):
+    """VKRT_BUILD_PREFER_FAST_TRACE on the Sponza stand-in: a valid hierarchy with a lower cost, the same hit for every ray
+    (closest and any), fewer node visits, the same tree again on a rebuild (the lock resolution does not depend on thread
+    order), and the default flavour back after a rebuild without the flag."""
+    ctx = B.Context(0)
+    inst = scenes.identity_instance(1.0)
+    plain = B.Blas(ctx, sponza_flat["vertices"], sponza_flat["indices"], sponza_flat["ranges"])
+    fast = B.Blas(ctx, sponza_flat["vertices"], sponza_flat["indices"], sponza_flat["ranges"], flags=B.BUILD_PREFER_FAST_TRACE)
+    nodes, tris = fast.read()
+    check_bvh8(nodes, tris, 262267)
+    sah_fast = fast.info().sahCost
+    assert sah_fast < 0.95 * plain.info().sahCost
+    tp, tf = B.Tlas(ctx, [plain], inst), B.Tlas(ctx, [fast], inst)
+    rays = H.random_rays(400000, 17, (-11, 0.2, -5), (11, 9, 5))
+    rays["tmax"][::6] = 5.0
+    visits = []
+    hits = []
+    for t in (tp, tf):
+        ctx.stats_enable(True, False)
+        ctx.stats_reset()
+        hits.append((t.trace_rays(rays), t.trace_rays(rays, any_hit=True)))
+        visits.append(ctx.stats().nodesVisited)
+        ctx.stats_enable(False, False)
+    assert np.array_equal(hits[0][0], hits[1][0])
+    assert np.array_equal(hits[0][1]["instance"] != 0xFFFFFFFF, hits[1][1]["instance"] != 0xFFFFFFFF)
+    assert visits[1] < 0.95 * visits[0], visits
+    fast.rebuild(sponza_flat["vertices"], B.BUILD_PREFER_FAST_TRACE)
+    # (the order of the wide nodes in memory depends on the collapse's allocation atomics; their number and cost do not)
+    assert fast.info().nodeCount == len(nodes) and abs(fast.info().sahCost - sah_fast) < 1e-3
+    fast.rebuild(sponza_flat["vertices"], B.BUILD_DEFAULT)
+    assert fast.info().nodeCount == plain.info().nodeCount and abs(fast.info().sahCost - plain.info().sahCost) < 1e-3
+    for o in (tp, tf, plain, fast):
+        o.close()
+    ctx.close()
 
 
 @pytest.mark.parametrize("seed", [3, 4])

@@ -95,14 +95,16 @@ def main():
         return run_one(a.one, a.width, a.height)
     for m in a.modes:
         env = dict(os.environ)
-        base, _, par = m.partition("*")  # "<mode>*<k>": k passes of the builder's own parallel reinsertion (reinsert.cuh)
+        base, _, par = m.partition("*")  # "<mode>*1": the builder's own parallel reinsertion (reinsert.cuh) on its default schedule, "<mode>*s,b,i,r": on another
         base, _, passes = base.partition("+")
         env["VKRT_EMU_BINARY"] = base
         env["VKRT_EMU_VERBOSE"] = "1"
         if passes:
             env["VKRT_EMU_REINSERT"] = passes
         if par:
-            env["VKRT_EMU_FAST_TRACE"] = par
+            env["VKRT_EMU_FAST_TRACE"] = "1"
+            if par != "1":
+                env["VKRT_BUILD_REINSERT"] = par  # "<sweeps>,<bands>,<iterations>,<ratio>"
         subprocess.run([sys.executable, __file__, "--one", m, "--width", str(a.width), "--height", str(a.height)], env=env, check=True)
 
 

@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("VKRT_B200_LIB") or os.path.join(os.path.dirname(os.pa
 
 AOV_BGRA8, AOV_RGB32F, AOV_TRIANGLE_ID, AOV_SHADOW_MASK = 0, 1, 2, 3
 BUILD_DEFAULT, BUILD_PREFER_FAST_BUILD, BUILD_INPUT_ON_DEVICE = 0, 1, 2
+BUILD_PREFER_FAST_TRACE = 8  # reinsertion passes after PLOC: slower build, fewer node visits per ray
 TRACE_DEFAULT, TRACE_NO_AOV = 0, 1
 TEXTURE_LOD_ZERO, TEXTURE_LOD_RAY_CONES = 0, 1
 TILE = 64
