@@ -356,7 +356,7 @@ EmuBlas* emu_blas_build_flags(const void* vertices, size_t vertexBytes, uint32_t
     geo.indexBase = b->indexBase.data();
     geo.geometryCount = geometryCount;
 
-    const uint32_t nodeCapacity = std::max(1u, n / 2u + 8u);
+    const uint32_t nodeCapacity = getenv("VKRT_EMU_MAX_LEAF") ? n + 8u : std::max(1u, n / 2u + 8u);
     b->nodes.assign(nodeCapacity, Node8{});
     b->tris.assign(std::max(1u, n), PackedTri{});
     if (n == 0)
@@ -401,7 +401,8 @@ EmuBlas* emu_blas_build_flags(const void* vertices, size_t vertexBytes, uint32_t
     const float dpPrimCost = dpEnv ? (float)atof(dpEnv) : 0.5f;
     std::vector<uint32_t> primSource;
     float sah[2] = {0.f, 0.f};
-    const uint32_t last = emuBuildHierarchy(triBox, n, kMaxLeafTris, dpPrimCost, clo, chi, b->nodes, nodeCapacity, primSource, sah,
+    const uint32_t maxLeaf = getenv("VKRT_EMU_MAX_LEAF") ? (uint32_t)atoi(getenv("VKRT_EMU_MAX_LEAF")) : kMaxLeafTris; // experiments
+    const uint32_t last = emuBuildHierarchy(triBox, n, maxLeaf, dpPrimCost, clo, chi, b->nodes, nodeCapacity, primSource, sah,
                                             (flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0);
     if (last == 0)
     {

@@ -31,5 +31,8 @@ timeout 600 ncu --set full --import-source on --clock-control none -k regex:'k_t
     python bench.py --workload config3 --steps 1 --warmup 3 --no-cpu-baseline > $O/${T}_trace_full.log 2>&1; echo "ncu full exit $?"
 timeout 300 python tools/build_bench.py --flags 0 --sizes 262144,2000000,10000000 > $O/${T}_build_ploc.jsonl 2>&1; echo "build ploc exit $?"
 timeout 300 python tools/build_bench.py --flags 1 > $O/${T}_build_lbvh.jsonl 2>&1; echo "build lbvh exit $?"
+timeout 300 python tools/build_bench.py --flags 8 --sizes 262144,2000000 > $O/${T}_build_fast_trace.jsonl 2>&1; echo "build fast trace exit $?"
+for size in 1 8; do timeout 300 python tools/rank_stage_times.py --size $size 2>&1 | tail -1; done > $O/${T}_rank_stage_times.txt; echo "rank stage times exit $?"
+timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $O/${T}_smoke.log 2>&1; echo "smoke exit $?"
 cp profiles/r02_traffic.json $O/${T}_r02_traffic.json
 ls $O | grep "^${T}_" | wc -l
