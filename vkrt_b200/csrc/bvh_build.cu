@@ -766,11 +766,13 @@ __global__ void k_ploc_finish(PlocClusters c, Bvh2 bvh, const uint32_t* state, i
 }
 
 // Level-synchronous collapse without host round trips.  `range` = {first, last, ticket, levels}: wide nodes
-// [first,last) were allocated by the previous level.  Narrow levels (<= kNarrowLevel nodes) are swept by ONE block that
+// [first,last) were allocated by the previous level.  Narrow levels (<= kNarrowMax nodes) are swept by ONE block that
 // loops over levels with __syncthreads(); wide levels take one multi-block launch each, whose last block publishes
 // the next range.  Each kernel is a no-op when the current level belongs to the other kind, so the host just
 // alternates them (see buildBlasOnDevice).
-constexpr uint32_t kNarrowLevel = 1024;
+constexpr uint32_t kNarrowLevel = 1024; // threads of the one-block sweep
+constexpr uint32_t kNarrowMax = 256;    // largest level the one-block sweep takes: above, a launch over all SMs is faster than one SM
+                                        // (Sponza 1.78 -> 1.54 ms default, 0.70 -> 0.61 ms fast build; profiles/r02_y_narrow_max.txt)
 
 __device__ __forceinline__ void flushSah(const CollapseArgs& a, const float* sah)
 {
@@ -1173,7 +1175,7 @@ __global__ void k_collapse_seed(CollapseArgs a, uint32_t* range)
     range[0] = 0u, range[1] = 1u, range[2] = 0u, range[3] = 0u;
 }
 
-__global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a, uint32_t* range)
+__global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a, uint32_t* range, uint32_t narrowMax)
 {
     __shared__ uint32_t sFirst, sLast;
     __shared__ __align__(16) uint8_t sStage[kNarrowLevel / 8][80];
@@ -1188,7 +1190,7 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
     for (;;)
     {
         const uint32_t first = sFirst, last = sLast;
-        if (first >= last || last - first > kNarrowLevel)
+        if (first >= last || last - first > narrowMax)
         {
             break;
         }
@@ -1214,10 +1216,10 @@ __global__ void __launch_bounds__(kNarrowLevel) k_collapse_narrow(CollapseArgs a
     }
 }
 
-__global__ void __launch_bounds__(128) k_collapse_wide(CollapseArgs a, uint32_t* range)
+__global__ void __launch_bounds__(128) k_collapse_wide(CollapseArgs a, uint32_t* range, uint32_t narrowMax)
 {
     const uint32_t first = range[0], last = range[1];
-    if (last - first <= kNarrowLevel) // also covers the finished state first == last
+    if (last - first <= narrowMax) // also covers the finished state first == last
     {
         return;
     }
@@ -1653,19 +1655,30 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, bool f
     k_collapse_seed<<<1, 1, 0, s>>>(ca, range);
     ctx->launches += 1;
     uint32_t last = 0;
+    // levels of at most narrowMax nodes are swept by one block without leaving the kernel; larger ones take a launch each
+    uint32_t narrowMax = kNarrowMax;
+    int widePairs = 8;
+    if (const char* e = getenv("VKRT_BUILD_NARROW_MAX")) // experiments
+    {
+        narrowMax = std::min<uint32_t>(std::max(atoi(e), 8), kNarrowLevel);
+    }
+    if (const char* e = getenv("VKRT_BUILD_WIDE_PAIRS")) // experiments
+    {
+        widePairs = std::min(std::max(atoi(e), 1), 32);
+    }
     for (int batch = 0;; ++batch)
     {
         // one narrow sweep, then (wide, narrow) pairs: enough for 8 wide levels per batch
-        k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+        k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range, narrowMax);
         ctx->launches += 1;
-        if (n > kNarrowLevel) // with fewer primitives than one narrow level no level can be wide
+        if (n > narrowMax) // with fewer primitives than one narrow level no level can be wide
         {
-            for (int k = 0; k < 8; ++k)
+            for (int k = 0; k < widePairs; ++k)
             {
-                k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range);
-                k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range);
+                k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range, narrowMax);
+                k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range, narrowMax);
             }
-            ctx->launches += 16;
+            ctx->launches += 2 * widePairs;
         }
         uint32_t hostCounters[8];
         VKRT_CUDA_TRY(ctx, cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
