@@ -87,7 +87,8 @@ typedef enum VkrtBuildFlags
     /* VK_BUILD_ACCELERATION_STRUCTURE_PREFER_FAST_TRACE_BIT_KHR: after PLOC, parallel reinsertion passes (Meister & Bittner 2018)
      * move subtrees to where they cost the least surface area, large nodes first; several times the build time for
      * fewer node visits per ray.  For hierarchies that are built once and traced many times.  Ignored together with
-     * VKRT_BUILD_PREFER_FAST_BUILD. */
+     * VKRT_BUILD_PREFER_FAST_BUILD; if the passes leave the hierarchy deeper than the traversal stack it is built again
+     * without them. */
     VKRT_BUILD_PREFER_FAST_TRACE = 1u << 3
 } VkrtBuildFlags;
 

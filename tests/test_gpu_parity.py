@@ -173,7 +173,7 @@ def test_builder_invariants_sponza(sponza_rt, sponza_flat):
     assert np.allclose(info.boundsMin, sponza_flat["vertices"][sponza_flat["indices"], :3].min(0))
 
 
-def test_fast_trace_build_same_answers_fewer_node_visits(sponza_flat):
+def test_fast_trace_build_same_answers_fewer_node_visits(sponza_flat, monkeypatch):
     """VKRT_BUILD_PREFER_FAST_TRACE on the Sponza stand-in: a valid hierarchy with a lower cost, the same hit for every ray
     (closest and any), fewer node visits, the same tree again on a rebuild (the lock resolution does not depend on thread
     order), and the default flavour back after a rebuild without the flag."""
@@ -203,6 +203,11 @@ def test_fast_trace_build_same_answers_fewer_node_visits(sponza_flat):
     # (the order of the wide nodes in memory depends on the collapse's allocation atomics; their number and cost do not)
     assert fast.info().nodeCount == len(nodes) and abs(fast.info().sahCost - sah_fast) < 1e-3
     fast.rebuild(sponza_flat["vertices"], B.BUILD_DEFAULT)
+    assert fast.info().nodeCount == plain.info().nodeCount and abs(fast.info().sahCost - plain.info().sahCost) < 1e-3
+    # a hierarchy the passes left deeper than the traversal stack is built again without them (forced here by the test hook)
+    monkeypatch.setenv("VKRT_BUILD_TEST_DEPTH_FALLBACK", "1")
+    fast.rebuild(sponza_flat["vertices"], B.BUILD_PREFER_FAST_TRACE)
+    monkeypatch.delenv("VKRT_BUILD_TEST_DEPTH_FALLBACK")
     assert fast.info().nodeCount == plain.info().nodeCount and abs(fast.info().sahCost - plain.info().sahCost) < 1e-3
     for o in (tp, tf, plain, fast):
         o.close()

@@ -1776,16 +1776,30 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         geo.firstTri = blas->geomFirstTri.as<uint32_t>();
         geo.indexBase = blas->geomIndexBase.as<uint64_t>();
         geo.geometryCount = blas->geometryCount;
-        k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, blas->vertices.as<uint8_t>(), blas->vertexStride,
-                                                                      blas->indices.as<uint32_t>(), n, sc.triBox.as<float4>(),
-                                                                      sc.packedBuild.as<float4>(), sceneBounds);
-        ctx->launches += 1;
         HierarchyResult h;
         const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
-        const bool fastTrace = (blas->flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0 || getenv("VKRT_BUILD_FAST_TRACE") != nullptr;
-        if (int r = buildHierarchy(ctx, n, kMaxLeafTris, fast, fastTrace && !fast, blas->nodes.as<Node8>(), nodeCapacity, h))
+        bool fastTrace = !fast && ((blas->flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0 || getenv("VKRT_BUILD_FAST_TRACE") != nullptr);
+        for (;;)
         {
-            return r;
+            k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, blas->vertices.as<uint8_t>(), blas->vertexStride,
+                                                                          blas->indices.as<uint32_t>(), n, sc.triBox.as<float4>(),
+                                                                          sc.packedBuild.as<float4>(), sceneBounds);
+            ctx->launches += 1;
+            h = HierarchyResult{};
+            if (int r = buildHierarchy(ctx, n, kMaxLeafTris, fast, fastTrace, blas->nodes.as<Node8>(), nodeCapacity, h))
+            {
+                return r;
+            }
+            const char* forced = getenv("VKRT_BUILD_TEST_DEPTH_FALLBACK"); // test hook: pretend the reinsertion made the tree too deep
+            if (fastTrace && ((int)h.levels > kMaxBlasLevels || forced))
+            {
+                // the reinsertion passes do not bound the depth: build again without them rather than refuse the scene
+                fastTrace = false;
+                k_init_build<<<1, 32, 0, s>>>(sceneBounds, counters, sahAccum, root);
+                ctx->launches += 1;
+                continue;
+            }
+            break;
         }
         if ((int)h.levels > kMaxBlasLevels)
         {
