@@ -34,6 +34,17 @@ def main():
     m = np.median(np.array(rows[2:]), axis=0)
     names = ["raygen", "closest0", "surface0", "any0", "resolve0", "closest1", "surface1", "any1", "resolve1", "sample", "total"]
     print(f"rank {a.rank}/{a.size}: " + "  ".join(f"{n} {v:.3f}" for n, v in zip(names, m)), flush=True)
+    # the same frames as a user runs them (no per-stage events: the bounce overlaps the depth-0 shadow rays), wall clock
+    import time
+    rt.ctx.stats_enable(False, False)
+    for _ in range(3):
+        rt.render(spp=a.spp, flags=B.TRACE_NO_AOV, gather=False)
+    rt.ctx.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(20):
+        rt.render(spp=a.spp, flags=B.TRACE_NO_AOV, gather=False)
+    rt.ctx.synchronize()
+    print(f"rank {a.rank}/{a.size}: untimed frame {(time.perf_counter() - t0) / 20 * 1e3:.3f} ms (stages serialised: {m[-1]:.3f})", flush=True)
 
 
 if __name__ == "__main__":
