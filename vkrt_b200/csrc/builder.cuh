@@ -147,6 +147,15 @@ __device__ __forceinline__ int atomicExchAcqRel(int* p, int v)
     return old;
 }
 #define VKRT_ATOMIC_EXCH_ACQ_REL(ptr, v) atomicExchAcqRel((ptr), (v))
+// arrival counter with the same semantics: what this thread wrote before is visible to the thread that arrives second, and
+// that thread sees it after its own increment - one instruction instead of a relaxed add between two fences
+__device__ __forceinline__ int atomicAddAcqRel(int* p, int v)
+{
+    int old;
+    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+#define VKRT_ATOMIC_ADD_ACQ_REL(ptr, v) atomicAddAcqRel((ptr), (v))
 #define VKRT_ATOMIC_EXCH(ptr, v) atomicExch((ptr), (v))
 #define VKRT_ATOMIC_ADD(ptr, v) atomicAdd((ptr), (v))
 #define VKRT_FENCE() __threadfence()
@@ -168,6 +177,7 @@ inline T hostAdd(T* p, T v)
 }
 #define VKRT_ATOMIC_EXCH(ptr, v) hostExch((ptr), (v))
 #define VKRT_ATOMIC_EXCH_ACQ_REL(ptr, v) hostExch((ptr), (v))
+#define VKRT_ATOMIC_ADD_ACQ_REL(ptr, v) hostAdd((ptr), (v))
 #define VKRT_ATOMIC_ADD(ptr, v) hostAdd((ptr), (v))
 #define VKRT_FENCE() ((void)0)
 #define VKRT_LOAD_CG_F4(ptr) (*(ptr))
@@ -535,12 +545,10 @@ VKRT_HD void dpClimb(const Bvh2& b, uint32_t leaf)
     int node = b.dpParent[leaf];
     for (;;)
     {
-        VKRT_FENCE();
-        if (VKRT_ATOMIC_ADD(&b.flags[node], 1) == 0)
+        if (VKRT_ATOMIC_ADD_ACQ_REL(&b.flags[node], 1) == 0)
         {
             return;
         }
-        VKRT_FENCE();
         dpSolve(b, node);
         if (node == root)
         {

@@ -75,12 +75,12 @@ VKRT_HD int reinsertSibling(const Bvh2& b, int parent, int ref)
 struct ReinsertBest
 {
     float gain;
-    int target, lca;
+    int target;
 };
 
 // Depth-first search of the subtree under `start` for the position that costs L the least.  `induced` = area already
-// added to the nodes between `start` and the common ancestor `lca`; `base` = area the removal of L has saved up to there.
-VKRT_HD void reinsertDescend(const Bvh2& b, int start, float induced, bool startIsCandidate, float base, int lca, F3 llo, F3 lhi,
+// added to the nodes between `start` and the common ancestor; `base` = area the removal of L has saved up to there.
+VKRT_HD void reinsertDescend(const Bvh2& b, int start, float induced, bool startIsCandidate, float base, F3 llo, F3 lhi,
                              float areaL, ReinsertBest& best)
 {
     int stackRef[kReinsertStack];
@@ -106,7 +106,7 @@ VKRT_HD void reinsertDescend(const Bvh2& b, int start, float induced, bool start
         const float areaY = halfArea(ylo, yhi);
         if (isCandidate && areaY > areaL && g > best.gain) // only next to a LARGER node (no cycles, see the header)
         {
-            best.gain = g, best.target = y, best.lca = lca;
+            best.gain = g, best.target = y;
         }
         if (y >= 0)
         {
@@ -151,16 +151,16 @@ VKRT_HD void reinsertSearch(const ReinsertArgs& a, uint32_t slot)
     const int S = reinsertSibling(b, P, L);
     reinsertBox(b, S, shrLo, shrHi);
     ReinsertBest best;
-    best.gain = 0.0f, best.target = kReinsertNoMove, best.lca = -1;
+    best.gain = 0.0f, best.target = kReinsertNoMove;
     // below the sibling (the sibling itself is where L is now)
     float base = areaP;
-    reinsertDescend(b, S, 0.0f, false, base, P, llo, lhi, areaL, best);
+    reinsertDescend(b, S, 0.0f, false, base, llo, lhi, areaL, best);
     // up the path: the sibling subtree of every ancestor, then the ancestor itself, shrunk by the removal
     int prev = P, A = G;
     while (A >= 0)
     {
         const int C = reinsertSibling(b, A, prev);
-        reinsertDescend(b, C, 0.0f, true, base, A, llo, lhi, areaL, best);
+        reinsertDescend(b, C, 0.0f, true, base, llo, lhi, areaL, best);
         F3 clo, chi, alo, ahi;
         reinsertBox(b, C, clo, chi);
         shrLo = f3(fminf(shrLo.x, clo.x), fminf(shrLo.y, clo.y), fminf(shrLo.z, clo.z));
@@ -173,7 +173,7 @@ VKRT_HD void reinsertSearch(const ReinsertArgs& a, uint32_t slot)
             const float g = base + dec - reinsertMergedArea(shrLo, shrHi, llo, lhi);
             if (halfArea(shrLo, shrHi) > areaL && g > best.gain)
             {
-                best.gain = g, best.target = A, best.lca = GA;
+                best.gain = g, best.target = A;
             }
         }
         base += dec;
@@ -283,12 +283,10 @@ VKRT_HD void reinsertRefit(const Bvh2& b, uint32_t leaf)
     int node = b.dpParent[leaf];
     while (node >= 0)
     {
-        VKRT_FENCE();
-        if (VKRT_ATOMIC_ADD(&b.flags[node], 1) == 0)
+        if (VKRT_ATOMIC_ADD_ACQ_REL(&b.flags[node], 1) == 0)
         {
             return; // the thread that arrives second finds both children finished
         }
-        VKRT_FENCE();
         const int2 ch = b.nodes[node].children;
         float4 lo[2], hi[2];
         uint32_t count = 0;
