@@ -214,6 +214,29 @@ def test_fast_trace_build_same_answers_fewer_node_visits(sponza_flat, monkeypatc
     ctx.close()
 
 
+def test_fast_trace_build_matches_host_emulation(monkeypatch):
+    """The reinsertion passes are deterministic (locks go to the larger (gain, node) key, whatever the thread order), so
+    the GPU must end at the tree that the host emulation reaches by running the same passes one node at a time: same
+    number of wide nodes, same cost, same node visits for the same rays.  (The emulation's sequential PLOC stands in for
+    k_ploc_round; without the passes both give the same tree too.)"""
+    flat = flatten_model(scenes.random_soup(20000, seed=31, geometries=5))
+    inst = scenes.identity_instance(1.0)
+    monkeypatch.setenv("VKRT_EMU_BINARY", "ploc")
+    rays = H.random_rays(50000, 9, (-12, -8, -10), (12, 8, 10))
+    ctx = B.Context(0)
+    for flags in (B.BUILD_DEFAULT, B.BUILD_PREFER_FAST_TRACE):
+        emu = H.EmuScene(flat, inst, flags=flags)
+        blas = B.Blas(ctx, flat["vertices"], flat["indices"], flat["ranges"], flags=flags)
+        tlas = B.Tlas(ctx, [blas], inst)
+        nodes_emu, _ = emu.read_blas()
+        assert blas.info().nodeCount == len(nodes_emu), flags
+        assert abs(blas.info().sahCost - emu.sah()) < 1e-3 * emu.sah(), flags
+        he, _, _ = emu.trace_rays(rays)
+        assert np.array_equal(he, tlas.trace_rays(rays))
+        tlas.close(), blas.close()
+    ctx.close()
+
+
 @pytest.mark.parametrize("seed", [3, 4])
 def test_ray_parity_soup(seed):
     flat = flatten_model(scenes.random_soup(6000, seed=seed))
