@@ -252,6 +252,11 @@ void vkrt_context_destroy(VkrtContext* c)
         cudaStreamSynchronize(ctx->copyStream);
         cudaStreamDestroy(ctx->copyStream);
     }
+    if (ctx->buildReadback)
+    {
+        cudaFreeHost(ctx->buildReadback);
+        ctx->buildReadback = nullptr;
+    }
     if (ctx->commStream)
     {
         cudaStreamSynchronize(ctx->commStream);
@@ -452,6 +457,11 @@ void vkrt_blas_destroy(VkrtContext* c, VkrtBlas* b)
         cudaStreamSynchronize(C(c)->stream);
         auto& live = C(c)->liveBlas;
         live.erase(std::remove(live.begin(), live.end(), (const Blas*)blas), live.end());
+    }
+    if (blas->buildGraph)
+    {
+        cudaGraphExecDestroy(blas->buildGraph);
+        blas->buildGraph = nullptr;
     }
     blas->vertices.release(), blas->indices.release();
     blas->geomFirstTri.release(), blas->geomIndexBase.release();

@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <cstring>
 
 namespace vkrt
 {
@@ -770,6 +771,7 @@ __global__ void k_ploc_finish(PlocClusters c, Bvh2 bvh, const uint32_t* state, i
 // loops over levels with __syncthreads(); wide levels take one multi-block launch each, whose last block publishes
 // the next range.  Each kernel is a no-op when the current level belongs to the other kind, so the host just
 // alternates them (see buildBlasOnDevice).
+constexpr int kGraphWidePairs = 12;     // (wide, narrow) launch pairs in a graph-replayed build (no read-back in between)
 constexpr uint32_t kNarrowLevel = 1024; // threads of the one-block sweep
 constexpr uint32_t kNarrowMax = 256;    // largest level the one-block sweep takes: above, a launch over all SMs is faster than one SM
                                         // (Sponza 1.78 -> 1.54 ms default, 0.70 -> 0.61 ms fast build; profiles/r02_y_narrow_max.txt)
@@ -1444,6 +1446,30 @@ __global__ void __launch_bounds__(kThreads) k_min_scale_exponent(const Node8* __
     }
 }
 
+// the same with the node count read on the device (graph-replayed builds never learn it on the host in between)
+__global__ void __launch_bounds__(kThreads) k_min_scale_exponent_dev(const Node8* __restrict__ nodes, const uint32_t* __restrict__ countPtr,
+                                                                      uint32_t* out)
+{
+    const uint32_t count = *countPtr;
+    uint32_t e = 255u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const Node8& n = nodes[i];
+        if (n.imask != 0 || (n.leafBits & 0xFFFFFFu) != 0u)
+        {
+            e = min(e, min(min((uint32_t)n.sx >> 7, (uint32_t)n.sy >> 7), (uint32_t)n.sz >> 7));
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        e = min(e, __shfl_xor_sync(0xFFFFFFFFu, e, o));
+    }
+    if ((threadIdx.x & 31) == 0 && e < 255u)
+    {
+        atomicMin(out, e);
+    }
+}
+
 struct HierarchyResult
 {
     uint32_t nodeCount = 0;
@@ -1481,7 +1507,7 @@ int reserveBuildScratch(Context* ctx, uint32_t n, uint32_t nodeCapacity, bool pa
 // (k_tri_bounds / k_instance_bounds, stream-ordered).  On return buildScratch.primSource[0..n) is the primitive order
 // the leaves refer to, and everything is complete on the host side (the function synchronises).
 int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, bool fastTrace, Node8* nodes, uint32_t nodeCapacity,
-                   HierarchyResult& out)
+                   HierarchyResult& out, bool noSync = false)
 {
     cudaStream_t s = ctx->stream;
     const int sm = ctx->smCount;
@@ -1666,6 +1692,22 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, bool f
     {
         widePairs = std::min(std::max(atoi(e), 1), 32);
     }
+    if (noSync)
+    {
+        // for a CUDA graph: enough (wide, narrow) pairs for any hierarchy of this size class, no read-back in between; the
+        // caller reads the counters once at the end and takes the normal path if the collapse had not finished
+        k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range, narrowMax);
+        const int pairs = getenv("VKRT_BUILD_WIDE_PAIRS") ? widePairs : kGraphWidePairs;
+        for (int k = 0; k < pairs; ++k)
+        {
+            k_collapse_wide<<<(uint32_t)sm * 8u, 128, 0, s>>>(ca, range, narrowMax);
+            k_collapse_narrow<<<1, kNarrowLevel, 0, s>>>(ca, range, narrowMax);
+        }
+        k_min_scale_exponent_dev<<<gridFor(nodeCapacity, kThreads, sm), kThreads, 0, s>>>(nodes, counters + 0, counters + 3);
+        ctx->launches += 2 + 2 * pairs;
+        VKRT_CUDA_TRY(ctx, cudaGetLastError());
+        return VKRT_SUCCESS;
+    }
     for (int batch = 0;; ++batch)
     {
         // one narrow sweep, then (wide, narrow) pairs: enough for 8 wide levels per batch
@@ -1728,6 +1770,103 @@ int buildHierarchy(Context* ctx, uint32_t n, uint32_t maxLeaf, bool fast, bool f
 }
 } // namespace
 
+// Small fast builds as ONE CUDA graph.  A Sponza-sized LBVH build is ~40 launches of 2-50 us each and three host round trips:
+// launch gaps and synchronisation are a third of its 0.6 ms.  The chain is captured without any read-back in between (fixed
+// number of collapse launches, node count read on the device) and replayed by later rebuilds of the same BLAS; the counters
+// come back in one copy at the end.  `done` stays false if the collapse had not finished within the captured launches (the
+// caller then builds the normal way).
+constexpr uint32_t kGraphMaxPrims = 4u << 20;
+
+static int graphBuild(Context* ctx, Blas* blas, const GeometryTable& geo, uint32_t n, uint32_t nodeCapacity, HierarchyResult& h, bool& done)
+{
+    done = false;
+    cudaStream_t s = ctx->stream;
+    const int sm = ctx->smCount;
+    BuildScratch& sc = ctx->buildScratch;
+    if (!ctx->buildReadback)
+    {
+        VKRT_CUDA_TRY(ctx, cudaMallocHost(&ctx->buildReadback, 256));
+    }
+    VKRT_CUDA_TRY(ctx, sc.sortedBox.reserve(std::max<size_t>(n, 1) * 2 * sizeof(float4))); // before the key: capture must not allocate
+    uint32_t* sceneBounds = sc.small.as<uint32_t>();
+    uint32_t* counters = sc.small.as<uint32_t>() + 16;
+    float* sahAccum = reinterpret_cast<float*>(sc.small.as<uint32_t>() + 32);
+    int* root = reinterpret_cast<int*>(sc.small.as<uint32_t>() + 40);
+    auto addr = [](const DeviceBuffer& b) { return (uint64_t)(uintptr_t)b.ptr; };
+    const uint64_t key[24] = {n, blas->flags, nodeCapacity, blas->vertexStride, blas->geometryCount, addr(blas->vertices), addr(blas->indices),
+                              addr(blas->geomFirstTri), addr(blas->geomIndexBase), addr(blas->nodes), addr(blas->tris), addr(sc.triBox),
+                              addr(sc.packedBuild), addr(sc.keysA), addr(sc.keysB), addr(sc.valsA), addr(sc.valsB), addr(sc.tileHist),
+                              addr(sc.binNodes), addr(sc.flags), addr(sc.taskRef), addr(sc.primSource), addr(sc.small), addr(sc.sortedBox)};
+    if (!blas->buildGraph || memcmp(key, blas->buildGraphKey, sizeof(key)) != 0)
+    {
+        if (blas->buildGraph)
+        {
+            cudaGraphExecDestroy(blas->buildGraph);
+            blas->buildGraph = nullptr;
+        }
+        const uint64_t launchesBefore = ctx->launches;
+        VKRT_CUDA_TRY(ctx, cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+        k_init_build<<<1, 32, 0, s>>>(sceneBounds, counters, sahAccum, root);
+        k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, blas->vertices.as<uint8_t>(), blas->vertexStride,
+                                                                      blas->indices.as<uint32_t>(), n, sc.triBox.as<float4>(),
+                                                                      sc.packedBuild.as<float4>(), sceneBounds);
+        ctx->launches += 2;
+        HierarchyResult unused;
+        int r = buildHierarchy(ctx, n, kMaxLeafTris, true, false, blas->nodes.as<Node8>(), nodeCapacity, unused, true);
+        k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
+                                                                     blas->tris.as<PackedTri>());
+        ctx->launches += 1;
+        cudaMemcpyAsync(ctx->buildReadback, sc.small.ptr, 192, cudaMemcpyDeviceToHost, s);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(s, &graph);
+        blas->buildGraphLaunches = (uint32_t)(ctx->launches - launchesBefore);
+        ctx->launches = launchesBefore;
+        if (r != VKRT_SUCCESS || e != cudaSuccess || !graph)
+        {
+            if (graph)
+            {
+                cudaGraphDestroy(graph);
+            }
+            cudaGetLastError();
+            return VKRT_SUCCESS; // not an error: the normal path builds
+        }
+        const cudaError_t ei = cudaGraphInstantiate(&blas->buildGraph, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess)
+        {
+            blas->buildGraph = nullptr;
+            cudaGetLastError();
+            return VKRT_SUCCESS;
+        }
+        memcpy(blas->buildGraphKey, key, sizeof(key));
+    }
+    VKRT_CUDA_TRY(ctx, cudaGraphLaunch(blas->buildGraph, s));
+    ctx->launches += blas->buildGraphLaunches;
+    VKRT_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    const uint32_t* w = static_cast<const uint32_t*>(ctx->buildReadback);
+    const uint32_t* c = w + 16;
+    if (c[2] != 0u || c[4] != c[5] || c[1] != n)
+    {
+        return VKRT_SUCCESS; // capacity exceeded or more wide levels than the captured launches cover: the normal path decides
+    }
+    h = HierarchyResult{};
+    h.nodeCount = c[0];
+    h.levels = c[7];
+    h.minExponent = c[3] == 255u ? 127u : c[3];
+    for (int k = 0; k < 3; ++k)
+    {
+        h.boundsMin[k] = floatFromOrdered(w[k]);
+        h.boundsMax[k] = floatFromOrdered(w[3 + k]);
+    }
+    const float dx = h.boundsMax[0] - h.boundsMin[0], dy = h.boundsMax[1] - h.boundsMin[1], dz = h.boundsMax[2] - h.boundsMin[2];
+    const float rootArea = dx * dy + dy * dz + dz * dx;
+    float sah[2];
+    memcpy(sah, w + 32, sizeof(sah));
+    h.sahCost = rootArea > 0.0f ? (sah[0] + sah[1]) / rootArea : 0.0f;
+    done = true;
+    return VKRT_SUCCESS;
+}
+
 // Runs the whole builder over the BLAS's device geometry copy.
 int buildBlasOnDevice(Context* ctx, Blas* blas)
 {
@@ -1779,7 +1918,22 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         HierarchyResult h;
         const bool fast = (blas->flags & VKRT_BUILD_PREFER_FAST_BUILD) != 0;
         bool fastTrace = !fast && ((blas->flags & VKRT_BUILD_PREFER_FAST_TRACE) != 0 || getenv("VKRT_BUILD_FAST_TRACE") != nullptr);
-        for (;;)
+        bool graphDone = false;
+        // (rebuilds only: capturing and instantiating costs about as much as one small build)
+        if (fast && blas->generation > 0 && n >= 2 && n <= kGraphMaxPrims && !getenv("VKRT_BUILD_NO_GRAPH") && !getenv("VKRT_BUILD_DP_PRIM_COST") &&
+            !getenv("VKRT_BUILD_NO_COMPACT"))
+        {
+            if (int r = graphBuild(ctx, blas, geo, n, nodeCapacity, h, graphDone))
+            {
+                return r;
+            }
+            if (!graphDone)
+            {
+                k_init_build<<<1, 32, 0, s>>>(sceneBounds, counters, sahAccum, root);
+                ctx->launches += 1;
+            }
+        }
+        for (; !graphDone;)
         {
             k_tri_bounds<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(geo, blas->vertices.as<uint8_t>(), blas->vertexStride,
                                                                           blas->indices.as<uint32_t>(), n, sc.triBox.as<float4>(),
@@ -1810,9 +1964,12 @@ int buildBlasOnDevice(Context* ctx, Blas* blas)
         blas->nodeCount = h.nodeCount;
         blas->levels = h.levels;
         blas->boxScale = boxScaleFromExponent(h.minExponent);
-        k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
-                                                                     blas->tris.as<PackedTri>());
-        ctx->launches += 1;
+        if (!graphDone) // (part of the graph otherwise)
+        {
+            k_pack_tris<<<gridFor(n, kThreads, sm), kThreads, 0, s>>>(sc.packedBuild.as<float4>(), sc.primSource.as<uint32_t>(), n,
+                                                                         blas->tris.as<PackedTri>());
+            ctx->launches += 1;
+        }
         for (int k = 0; k < 3; ++k)
         {
             blas->boundsMin[k] = h.boundsMin[k];

@@ -98,6 +98,7 @@ struct Context : VkrtContext
     cudaStream_t copyStream = nullptr; // vkrt_frame_present copies (created on first use)
     cudaStream_t commStream = nullptr; // vkrt_tiles_gather: NCCL exchange + untile, overlapping the next frame's traversal
     cudaEvent_t commReady = nullptr;   // recorded on `stream` when a gather is queued
+    void* buildReadback = nullptr;     // 256 page-locked bytes: the one read-back of a graph-replayed build
     std::string lastError;
     uint64_t launches = 0;
 
@@ -165,6 +166,10 @@ struct Blas : VkrtBlas
     float boxScale = 1.0f;      // power of two that normalises box-test distances in this hierarchy (traverse.cuh::setBoxRay)
     uint64_t generation = 0;    // bumped by every (re)build: a TLAS remembers the generation it saw
     bool shadingLayout = false; // vertices are the 64-byte Model::Vertex (stride % 16 == 0, >= 64): vkrt_trace / vkrt_rasterize can shade it
+    // Small fast builds (LBVH flavour) replay their whole kernel chain as one CUDA graph on vkrt_blas_rebuild (bvh_build.cu).
+    cudaGraphExec_t buildGraph = nullptr;
+    uint64_t buildGraphKey[24] = {}; // every pointer and size the captured chain depends on
+    uint32_t buildGraphLaunches = 0;
 };
 
 struct Tlas : VkrtTlas
